@@ -1,0 +1,397 @@
+#!/usr/bin/env python
+"""bench.py — the drift-check hot path on N B200s, one JSON line on stdout.
+
+Metric (BASELINE.json): objects diffed per second — decisions (row x shard) per second — with
+the bytes/s of the dominant kernel against the measured HBM roofline beside it.
+
+Workload at N=1: BASELINE.json configs[3], the one the north_star quotes its target on and which
+fits one GPU: 1M mixed objects (templates, Secrets, ConfigMaps, canonical length uniform in
+1..16 KiB) x 8 shards, 0.1 % same-length byte drift + 0.01 % missing, ~78 GB resident in HBM.
+At N>1 the same 1M objects are partitioned by ncd_keyhash(template key) % N (strong scaling,
+as the north_star states it) and the per-GPU diff lists are exchanged with ONE NCCL all-gather.
+
+A step = one full scan (join + compare + classify + compaction [+ all-gather]) over inputs
+already resident in HBM.  Inputs (>= 9.8 GB per GPU) are far larger than the 126 MB L2, so no
+flush is needed between steps.  `e2e` is the same metric through the C ABI with HOST (pinned)
+arenas: every step uploads the arenas, builds their index, scans, and reads the diff list back.
+
+--impl reference times the CPU oracle (a port of the reference's lookup + DeepEqual walk; the Go
+reference cannot be built in this image) on the box's host cores, on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "objects_diffed_per_s"
+UNIT = "decisions/s"
+
+WORKLOADS = {
+    # name: (groups, n_secrets, n_configmaps, tmpl_lo, tmpl_hi, dep_lo, dep_hi, shards, flip_ppm, missing_ppm)
+    "cfg2_10k_templates_4KB_x8_nodrift": (10_000, 1, 1, 512, 512, 4096, 4096, 8, 0, 0),
+    "cfg3_100k_configmaps_64KB_x16_1pct": (100_000, 0, 1, 512, 512, 65536, 65536, 16, 10_000, 0),
+    "cfg4_1M_mixed_1-16KB_x8": (333_334, 1, 1, 1024, 16384, 1024, 16384, 8, 1000, 100),
+    "cfg5_10k_secrets_1MB_x4": (10_000, 1, 0, 512, 512, 1 << 20, 1 << 20, 4, 0, 0),
+}
+DEFAULT_WORKLOAD = "cfg4_1M_mixed_1-16KB_x8"
+
+
+def make_cfg(name: str, groups: int | None = None, part_mod: int = 0, part_rem: int = 0):
+    from nexus_configuration_controller_b200._ffi import SynthCfg
+
+    g, ns, nc, tl, th, dl, dh, shards, flip, missing = WORKLOADS[name]
+    c = SynthCfg()
+    c.groups = groups if groups is not None else g
+    c.n_secrets, c.n_configmaps = ns, nc
+    c.tmpl_len_lo, c.tmpl_len_hi, c.dep_len_lo, c.dep_len_hi = tl, th, dl, dh
+    cfg_id = list(WORKLOADS).index(name) + 2
+    c.seed, c.drift_seed = 0xC0FFEE ^ cfg_id, 0xD21F7 ^ cfg_id
+    c.p_flip_ppm, c.p_missing_ppm, c.p_len_ppm, c.p_owner_ppm, c.p_rogue_ppm = flip, missing, 0, 0, 0
+    c.part_mod, c.part_rem, c.shuffle = part_mod, part_rem, 1
+    return c, shards
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.samples, self.stop_flag, self.th = gpu_index, [], threading.Event(), None
+
+    def _run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
+                    capture_output=True, text=True, timeout=5,
+                ).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
+    def start(self):
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+
+    def stop(self) -> dict:
+        self.stop_flag.set()
+        if self.th:
+            self.th.join(timeout=6)
+        sm, mx, reasons = [], 0, set()
+        for s in self.samples:
+            try:
+                sm.append(float(s[0]))
+                mx = max(mx, float(s[1]))
+                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], s[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ----------------------------------------------------------------------------- CPU arm
+class CpuArm:
+    """The oracle (a port of the reference's lookup + DeepEqual walk) on a bounded sample of
+    `workload`.  The sample is produced by the same generator as the GPU arm's input (on the GPU,
+    then copied to host memory); only the CPU walk is timed."""
+
+    def __init__(self, workload: str, sample_groups: int, threads: int):
+        import numpy as np
+
+        import oracle
+        from nexus_configuration_controller_b200.drift import Context
+
+        self.oracle, self.np = oracle, np
+        self.workload, self.groups, self.threads = workload, sample_groups, threads
+        cfg, S = make_cfg(workload, groups=sample_groups)
+        self.S = S
+        with Context(int(os.environ.get("LOCAL_RANK", "0"))) as ctx:
+            ca = ctx.synth_arena(cfg, -1)
+            sas = [ctx.synth_arena(cfg, s) for s in range(S)]
+            d = ctx.scan(ca, sas, 0)
+            self.gpu_codes = d.codes().copy()
+            d.close()
+            self.ch, self.shs = ca.download(), [s.download() for s in sas]
+            for a in sas + [ca]:
+                a.close()
+        self.algo = int(self.ch.rec_len[: self.ch.nobj].astype("uint64").sum()) + sum(
+            int(s.rec_len[: s.nobj].astype("uint64").sum()) for s in self.shs
+        )
+        sec, codes, _ = oracle.scan_timed(self.ch, self.shs, threads, 1)  # warm-up + parity
+        self.identical = bool(np.array_equal(codes, self.gpu_codes))
+        self.pairs = codes.size
+        self.sweep_s = sec
+
+    def time(self, budget_s: float):
+        reps = max(1, min(200, int(budget_s / max(self.sweep_s, 1e-4))))
+        sec, _, _ = self.oracle.scan_timed(self.ch, self.shs, self.threads, reps)
+        return sec, reps
+
+    def report(self, sec: float, reps: int) -> dict:
+        return {
+            "value": self.pairs / sec,
+            "unit": UNIT,
+            "cores": self.threads,
+            "kind": "port",
+            "sample": f"{self.workload}: first {self.groups} groups = {self.ch.nobj} objects x {self.S} shards, "
+                      f"{self.algo / 1e9:.2f} GB, {reps} sweep(s) of {sec * 1e3:.1f} ms; hash-map lookup + memcmp of "
+                      f"canonical records (an upper bound on a reflect.DeepEqual walk)",
+            "gb_per_s": self.algo / sec / 1e9,
+            "identical_to_gpu": self.identical,
+        }
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    t0 = time.time()
+    arm = CpuArm(args.workload, args.cpu_sample_groups, threads)
+    per_step = []
+    for i in range(args.warmup + args.steps):
+        sec, reps = arm.time(budget_s=1.0)
+        if i >= args.warmup:
+            per_step.append(sec)
+    sec = sum(per_step) / len(per_step)
+    base = arm.report(sec, reps)
+    value = base["value"]
+    _, S = make_cfg(args.workload)
+    line = {
+        "impl": "reference",
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": args.workload, "shards": S,
+                   "note": "CPU port of the reference walk on all host threads (the Go reference cannot be built here: "
+                           "no Go toolchain, dependencies un-vendored); a step = one sweep over the bounded sample"},
+        "cpu_baseline": base,
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "wall_s": time.time() - t0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def run_ours(args):
+    import numpy as np
+    import torch
+
+    from nexus_configuration_controller_b200 import arena as A
+    from nexus_configuration_controller_b200.drift import Context
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            sys.exit("bench.py --gpus N>1 must be launched with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    mode = {"direct": A.MODE_DIRECT, "hash64": A.MODE_HASH64, "sha256": A.MODE_SHA256}[args.mode]
+
+    ctx = Context(local)
+    cfg, S = make_cfg(args.workload, groups=args.groups, part_mod=world if world > 1 else 0, part_rem=rank)
+    t_setup = time.time()
+    ca = ctx.synth_arena(cfg, -1)
+    sas = [ctx.synth_arena(cfg, s) for s in range(S)]
+    ctx.sync()
+    setup_s = time.time() - t_setup
+
+    ext = torch.cuda.ExternalStream(ctx.stream, device=local)
+    cap_entries = args.gather_cap
+    sendbuf = torch.zeros(cap_entries * 4 + 4, dtype=torch.int32, device=f"cuda:{local}")
+    recvbuf = torch.zeros(world * sendbuf.numel(), dtype=torch.int32, device=f"cuda:{local}") if world > 1 else None
+
+    def step():
+        """One scan; at N>1 followed by the single all-gather of the per-GPU diff lists."""
+        ctx.scan_launch(ca, sas, mode)
+        d = ctx.scan_finish()
+        if world > 1:
+            d.pack_into(sendbuf.data_ptr(), cap_entries)  # header + entries, enqueued on the scan's stream
+            cur = torch.cuda.current_stream()
+            cur.wait_stream(ext)
+            dist.all_gather_into_tensor(recvbuf, sendbuf)
+            ext.wait_stream(cur)
+        st = ctx.last_stats()
+        d.close()
+        return st
+
+    # warm-up
+    for _ in range(max(args.warmup, 3) if not args.allow_short_warmup else args.warmup):
+        st = step()
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(ext)
+    cmp_ms, tot_ms, launches = [], [], 0
+    for _ in range(args.steps):
+        st = step()
+        cmp_ms.append(st.compare_ms if mode == A.MODE_DIRECT else st.hash_ms)
+        tot_ms.append(st.total_ms)
+        launches += st.launches
+    e1.record(ext)
+    torch.cuda.synchronize()
+    elapsed_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    if dist:
+        t = torch.tensor([elapsed_ms], device=f"cuda:{local}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+        tot = torch.tensor([float(st.pairs), float(st.algo_bytes), float(st.ndiff), float(launches)], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(tot)
+        pairs_all, algo_all, ndiff_all, launches_all = [float(x) for x in tot.tolist()]
+        dist.barrier()
+    else:
+        pairs_all, algo_all, ndiff_all, launches_all = float(st.pairs), float(st.algo_bytes), float(st.ndiff), float(launches)
+
+    result = None
+    if rank == 0:
+        ms_per_step = elapsed_ms / args.steps
+        value = pairs_all / (ms_per_step / 1e3)
+        peak, peak_src = hbm_peak()
+        kern_ms = sum(cmp_ms) / len(cmp_ms)
+        achieved = st.algo_bytes / (kern_ms / 1e3) / 1e9  # this rank's kernel over this rank's bytes
+        result = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {
+                "workload": args.workload, "mode": args.mode, "objects": int(cfg.groups) * (1 + cfg.n_secrets + cfg.n_configmaps),
+                "shards": S, "partition": f"ncd_keyhash(template key) % {world}" if world > 1 else "none",
+                "algorithmic_bytes": algo_all, "l2": "inputs >> 126 MB L2, no flush needed", "setup_s": round(setup_s, 2),
+                "diff_entries": ndiff_all,
+            },
+            "gb_per_s": algo_all / (ms_per_step / 1e3) / 1e9,
+            "roofline": {
+                "bound": "hbm", "kernel": "k_compare" if mode == A.MODE_DIRECT else "hash kernels",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+                "traffic": None, "kernel_ms": kern_ms, "scan_ms": sum(tot_ms) / len(tot_ms),
+            },
+            "gpu_launches": int(launches_all),
+            "clocks": clocks,
+        }
+    # end-to-end and CPU baseline: rank 0, N=1 only (bounded samples)
+    for a in sas + [ca]:
+        a.close()
+    if rank == 0 and world == 1 and not args.skip_e2e:
+        result["e2e"] = run_e2e(ctx, args, mode)
+    ctx.close()
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        arm = CpuArm(args.workload, args.cpu_sample_groups, os.cpu_count() or 1)
+        result["cpu_baseline"] = arm.report(*arm.time(args.cpu_budget_s))
+    if rank == 0:
+        print(json.dumps(result), flush=True)
+    if dist:
+        dist.destroy_process_group()
+    return 0
+
+
+def run_e2e(ctx, args, mode):
+    """Same metric with HOST arenas: every step = upload (H2D) + index build + scan + diff list D2H."""
+    import torch
+
+    cfg, S = make_cfg(args.workload, groups=args.e2e_groups)
+    dev = [ctx.synth_arena(cfg, r) for r in range(-1, S)]
+    hosts = []
+    for a in dev:
+        c = a.counts()
+        from nexus_configuration_controller_b200.drift import Arena
+
+        h = Arena(ctx, c.payload_bytes, c.nobj, c.aux_bytes, c.nowner, c.ndep, device_only=False)
+        v = h.host_view()
+        from nexus_configuration_controller_b200._ffi import check
+
+        check(ctx.lib.ncd_arena_download(a.handle, C.byref(v)))  # fills the pinned host arrays
+        hosts.append((h, c))
+        a.close()
+    h2d = sum(c.payload_bytes + c.aux_bytes + c.nobj * 29 + 8 + c.nowner * 9 + c.ndep * 9 for _, c in hosts)
+
+    def step():
+        for h, c in hosts:
+            h.commit(c.nobj, c.payload_bytes, c.aux_bytes, c.nowner, c.ndep)
+        d = ctx.scan(hosts[0][0], [h for h, _ in hosts[1:]], mode)
+        ents = d.entries()
+        st = ctx.last_stats()
+        d.close()
+        return st, ents
+
+    for _ in range(2):
+        st, ents = step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    reps = max(1, args.e2e_steps)
+    for _ in range(reps):
+        st, ents = step()
+    torch.cuda.synchronize()
+    sec = (time.perf_counter() - t0) / reps
+    for h, _ in hosts:
+        h.close()
+    return {
+        "value": st.pairs / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(ents.nbytes + 64),
+        "ms_per_step": sec * 1e3, "gb_per_s": st.algo_bytes / sec / 1e9,
+        "sample": f"{args.workload}: first {args.e2e_groups} groups = {hosts[0][1].nobj} objects x {S} shards from pinned host arenas; "
+                  f"step = H2D of every arena + index build + scan + diff list D2H",
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--mode", default="direct", choices=["direct", "hash64", "sha256"])
+    ap.add_argument("--groups", type=int, default=None, help="override the number of template groups (smaller runs)")
+    ap.add_argument("--gather-cap", type=int, default=1 << 16, help="entries per rank in the all-gather buffer")
+    ap.add_argument("--cpu-sample-groups", type=int, default=6000)
+    ap.add_argument("--cpu-budget-s", type=float, default=12.0)
+    ap.add_argument("--e2e-groups", type=int, default=40000)
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--allow-short-warmup", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

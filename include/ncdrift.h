@@ -1,0 +1,261 @@
+/*
+ * ncdrift.h — C ABI of libncdrift.so, the B200 (sm_100a) drift checker.
+ *
+ * One hot path of SneaksAndData/nexus-configuration-controller lives behind this
+ * header: the reconcile drift check.  In the reference it is not factored out; it
+ * is six inlined lister.Get calls and four inlined reflect.DeepEqual calls inside
+ * the sync handlers.  Each entry point below names the reference lines it stands
+ * in for (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every handle is opaque and owned by the library
+ *   - every call returns NCD_OK (0) or a negative ncd_status; the text of the last
+ *     failure on the calling thread is in ncd_last_error()
+ *   - there is no CPU fallback: with no usable CUDA device ncd_init fails
+ *   - one ncd_ctx per GPU per process; calls on one ctx must be serialised by the
+ *     caller (the Go side holds a mutex)
+ *
+ * The reference binding for every function here (cgo) is shown in INTEGRATION.md.
+ */
+#ifndef NCDRIFT_H
+#define NCDRIFT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ status */
+typedef enum ncd_status {
+  NCD_OK = 0,
+  NCD_E_INVALID = -1,   /* bad argument / inconsistent arena contents            */
+  NCD_E_CUDA = -2,      /* a CUDA runtime call failed (message has the detail)   */
+  NCD_E_NOMEM = -3,     /* host or device allocation failed                      */
+  NCD_E_CAPACITY = -4,  /* contents exceed the capacity the arena was made with  */
+  NCD_E_STATE = -5      /* call made in the wrong state (e.g. scan before commit)*/
+} ncd_status;
+
+/* Object kinds held in an arena (the four resource types the sync handlers walk,
+ * controller.go:697-845). */
+enum {
+  NCD_KIND_TEMPLATE = 0,  /* NexusAlgorithmTemplate : compared value = .Spec  (controller.go:795) */
+  NCD_KIND_WORKGROUP = 1, /* NexusAlgorithmWorkgroup: compared value = .Spec  (controller.go:725) */
+  NCD_KIND_SECRET = 2,    /* corev1.Secret          : compared value = .Data  (controller.go:539) */
+  NCD_KIND_CONFIGMAP = 3  /* corev1.ConfigMap       : compared value = .Data  (controller.go:600) */
+};
+
+/* Decision codes, one per (row, shard).  They are the branches of the reference's
+ * sync handlers; the diff list is the codes != NCD_SKIP in (row, shard) order. */
+enum {
+  NCD_SKIP = 0,            /* present, DeepEqual, ownership fine: fall-through of :539/:600/:725/:795 */
+  NCD_CREATE = 1,          /* NotFound in the shard cache: :518-520 :580-582 :735-738 :805-808        */
+  NCD_UPDATE_DATA = 2,     /* present, not DeepEqual: :539-541 :600-602 :725-727 :795-797             */
+  NCD_UPDATE_OWNER = 4,    /* dependent has ownerRefs, none is {NexusAlgorithmTemplate, UID of the
+                              shard template}: :489-501 -> :550-552 :612-614.  May be OR-ed with
+                              NCD_UPDATE_DATA (the reference then writes data first, owner second)   */
+  NCD_ERR_ROGUE = 8,       /* dependent on the shard has zero ownerRefs: :494-499                     */
+  NCD_ERR_MISSING_REF = 16 /* dependent name absent from the CONTROLLER cache: :509-514 :571-576
+                              (and earlier :649-653 :672-676)                                         */
+};
+
+/* Scan modes. */
+enum {
+  NCD_MODE_DIRECT = 0, /* byte compare of the canonical records: exact (default)                  */
+  NCD_MODE_HASH64 = 1, /* striped 64-bit hash of every record, verdict from hash equality          */
+  NCD_MODE_SHA256 = 2, /* FIPS 180-4 SHA-256 of every record, verdict from digest equality         */
+  NCD_MODE_CONFIRM = 0x100 /* OR with a hash mode: hash-equal pairs are re-checked by byte compare */
+};
+
+typedef struct ncd_ctx ncd_ctx;
+typedef struct ncd_arena ncd_arena;
+typedef struct ncd_diff ncd_diff;
+
+/* ------------------------------------------------------------------ arenas
+ * An arena is one cluster's informer cache in canonical form: the controller
+ * cluster's, or one shard's.  It replaces what the listers hold in the reference
+ * (controller.go:268-278 and shards.Shard's four listers) for the purposes of the
+ * drift check only.
+ *
+ * Layout (structure of arrays, all little-endian):
+ *   payload   canonical bytes of the compared value of every object, each record
+ *             starting on a 16-byte boundary, zero padded to the next boundary
+ *   rec_off   byte offset of record i in payload (multiple of 16)
+ *   rec_len   canonical length of record i in bytes (without padding)
+ *   kind      NCD_KIND_*
+ *   key       "namespace/name" (cache.ObjectName.String()) of object i, in aux
+ *   uid       metadata.uid of object i, in aux (used for templates only)
+ *   own_*     ownerReferences of object i are entries own_start[i]..own_start[i+1]:
+ *             own_is_template = (Kind == "NexusAlgorithmTemplate"), own_uid in aux
+ *   dep_*     for templates: the dependents named by GetSecretNames() followed by
+ *             GetConfigMapNames() (controller.go:505,567), entries
+ *             dep_start[i]..dep_start[i+1]; dep key = "namespace/name" in aux
+ *   aux       byte pool for keys and uids
+ */
+typedef struct ncd_arena_view {
+  uint64_t nobj;           /* objects                        */
+  uint64_t payload_bytes;  /* used bytes of payload          */
+  uint64_t aux_bytes;      /* used bytes of aux              */
+  uint64_t nowner;         /* owner reference entries        */
+  uint64_t ndep;           /* dependent reference entries    */
+  uint8_t* payload;
+  uint64_t* rec_off;
+  uint32_t* rec_len;
+  uint8_t* kind;
+  uint32_t* key_off;
+  uint32_t* key_len;
+  uint32_t* uid_off;
+  uint32_t* uid_len;
+  uint32_t* own_start;     /* nobj + 1 entries */
+  uint8_t* own_is_template;
+  uint32_t* own_uid_off;
+  uint32_t* own_uid_len;
+  uint32_t* dep_start;     /* nobj + 1 entries */
+  uint8_t* dep_kind;
+  uint32_t* dep_key_off;
+  uint32_t* dep_key_len;
+  uint8_t* aux;
+} ncd_arena_view;
+
+enum {
+  NCD_ARENA_HOST_PINNED = 0, /* pinned host arrays the caller fills + a device mirror */
+  NCD_ARENA_DEVICE_ONLY = 1  /* device arrays only (filled by ncd_synth_fill)         */
+};
+
+/* One diff-list entry: what the host-side replay needs to issue the shard write. */
+typedef struct ncd_entry {
+  uint32_t obj;   /* controller index of the template / workgroup the row belongs to */
+  uint32_t dep;   /* 0 = the object itself, j+1 = its j-th dependent reference        */
+  uint32_t shard; /* index into the shard list passed to ncd_scan                     */
+  uint32_t code;  /* NCD_* decision code (never NCD_SKIP in the list)                 */
+} ncd_entry;
+
+/* Device-side timings of the last scan (CUDA events on the ctx stream), ms. */
+typedef struct ncd_scan_stats {
+  float join_ms;      /* cache join (hash-table probes)              */
+  float hash_ms;      /* hashing kernels (hash modes only)           */
+  float compare_ms;   /* byte-compare kernel (direct / confirm)      */
+  float classify_ms;  /* decision codes + ordered compaction         */
+  float total_ms;     /* first launch to last kernel end             */
+  uint64_t rows;      /* rows of the controller arena                */
+  uint64_t pairs;     /* rows x shards = decisions made              */
+  uint64_t algo_bytes;/* canonical bytes of every compared copy, each counted once */
+  uint64_t ndiff;     /* entries in the diff list                    */
+  uint64_t hash_collisions; /* CONFIRM only: hash-equal pairs whose bytes differ */
+  uint32_t launches;  /* kernels launched by the scan                */
+} ncd_scan_stats;
+
+/* ------------------------------------------------------------------ context */
+/* Library version string. */
+const char* ncd_version(void);
+/* Text of the last error on this thread ("" if none). */
+const char* ncd_last_error(void);
+
+/* Creates the context for one CUDA device (stream, scratch, events).  Replaces
+ * nothing in the reference — it is the set-up NewController (controller.go:227-243)
+ * would do once the controller is given a DriftChecker. */
+int ncd_init(int device, ncd_ctx** out);
+void ncd_destroy(ncd_ctx* ctx);
+/* The CUDA stream (cudaStream_t) every launch of this ctx goes to, for callers that
+ * time with their own events. */
+void* ncd_ctx_stream(ncd_ctx* ctx);
+int ncd_ctx_device(ncd_ctx* ctx);
+int ncd_ctx_sync(ncd_ctx* ctx);
+
+/* 64-bit hash of ("kind", "namespace/name") used by the join and by the multi-GPU
+ * partition (gpu = ncd_keyhash % n_gpus).  Same function on host and device. */
+uint64_t ncd_keyhash(uint32_t kind, const void* key, uint32_t key_len);
+
+/* ------------------------------------------------------------------ arena API */
+/* Allocates an arena with the given capacities.  Stands in for the informer store
+ * behind a lister (controller.go:268-278; shards.Shard.*Lister). */
+int ncd_arena_create(ncd_ctx* ctx, uint64_t payload_cap, uint64_t nobj_cap, uint64_t aux_cap,
+                     uint64_t nowner_cap, uint64_t ndep_cap, uint32_t flags, ncd_arena** out);
+void ncd_arena_destroy(ncd_arena* a);
+/* Host pointers (pinned) the packer writes into; counts in the view are capacities.
+ * NCD_ARENA_HOST_PINNED arenas only. */
+int ncd_arena_host_view(ncd_arena* a, ncd_arena_view* out);
+/* Uploads the first nobj objects and builds the arena's index on the GPU: key
+ * hashes, the open-addressing table that answers lister.Get (controller.go:507,516,
+ * 569,578,722,792), and for a controller arena the row and tile lists.  The arena
+ * is immutable afterwards until the next commit. */
+int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
+                     uint64_t nowner, uint64_t ndep);
+/* Copies the committed device arrays into caller buffers (sized from
+ * ncd_arena_counts); any pointer in dst may be NULL to skip that array. */
+int ncd_arena_download(ncd_arena* a, ncd_arena_view* dst);
+int ncd_arena_counts(ncd_arena* a, ncd_arena_view* counts_only);
+/* Rows of a committed arena when used as the controller side: one per template,
+ * one per dependent reference of a template, one per workgroup. */
+int ncd_arena_rows(ncd_arena* a, uint64_t* rows);
+
+/* ------------------------------------------------------------------ scan */
+/* The drift check: for every row of the controller arena and every shard, the
+ * decision the reference's handlers would take (controller.go:504-626, 720-745,
+ * 790-831), as a compacted, ordered diff list.  mode = NCD_MODE_*. */
+int ncd_scan(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+             uint32_t mode, ncd_diff** out);
+/* Same, split so that a caller can time the GPU work with its own events:
+ * ncd_scan_launch only enqueues on the ctx stream; ncd_scan_finish synchronises
+ * and publishes the diff list. */
+int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards,
+                    int nshards, uint32_t mode);
+int ncd_scan_finish(ncd_ctx* ctx, ncd_diff** out);
+int ncd_scan_last_stats(ncd_ctx* ctx, ncd_scan_stats* out);
+
+/* Host view of a diff list (copied device -> pinned host on first use). */
+int ncd_diff_view(ncd_diff* d, const ncd_entry** entries, uint64_t* n);
+/* Device pointer + count, for a caller that hands the list to a collective
+ * (the all-gather of per-GPU diff lists) without a host round trip. */
+int ncd_diff_device(ncd_diff* d, const void** dev_entries, uint64_t* n);
+/* Enqueues, on the ctx stream, a copy of the list into a caller-owned DEVICE buffer laid out
+ * as uint32 header[4] = {n, nshards, rows (low 32 bits), 0} followed by n ncd_entry: the
+ * send buffer of the all-gather (e.g. an NCCL-registered tensor).  cap_entries = entries the
+ * buffer can hold after the header. */
+int ncd_diff_pack(ncd_diff* d, void* dev_buf, uint64_t cap_entries);
+/* All codes, rows x nshards, row-major, SKIP included (tests and Lookup()). */
+int ncd_diff_codes(ncd_diff* d, uint8_t* codes_out, uint64_t cap);
+void ncd_diff_destroy(ncd_diff* d);
+
+/* ------------------------------------------------------------------ hashing */
+/* Hashes every record of a committed arena on the GPU and copies the digests out.
+ * mode NCD_MODE_HASH64: out is nobj x 8 bytes; NCD_MODE_SHA256: nobj x 32 bytes.
+ * No counterpart in the reference (it never hashes, controller.go:539,600,725,795
+ * call reflect.DeepEqual); this is the hash path BASELINE.json's north_star asks for. */
+int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* out, uint64_t out_bytes,
+                   float* kernel_ms);
+
+/* ------------------------------------------------------------------ synthetic input
+ * Bench / test utility: fills a DEVICE_ONLY arena on the GPU with the synthetic
+ * workload of SURVEY.md section 8(d).  role -1 = controller copy, s >= 0 = shard s.
+ * The same generator is restated on the CPU in oracle/ so that samples can be
+ * checked.  Not part of the drop-in surface. */
+typedef struct ncd_synth_cfg {
+  uint64_t groups;        /* templates; each owns n_secrets + n_configmaps dependents */
+  uint32_t n_secrets;
+  uint32_t n_configmaps;
+  uint32_t tmpl_len_lo, tmpl_len_hi; /* canonical length range of a template spec (inclusive) */
+  uint32_t dep_len_lo, dep_len_hi;   /* canonical length range of a dependent's data          */
+  uint64_t seed;
+  uint64_t drift_seed;
+  uint32_t p_flip_ppm;    /* per (object, shard): one byte flipped (same length)      */
+  uint32_t p_missing_ppm; /* per (object, shard): absent from the shard               */
+  uint32_t p_owner_ppm;   /* per (dependent, shard): owned by a foreign template only */
+  uint32_t p_rogue_ppm;   /* per (dependent, shard): no ownerRefs at all              */
+  uint32_t p_len_ppm;     /* per (object, shard): shard copy one byte longer          */
+  uint32_t part_mod;      /* keep only groups with keyhash(template) % part_mod == part_rem */
+  uint32_t part_rem;      /* (part_mod = 0 or 1 keeps everything)                     */
+  uint32_t shuffle;       /* 1 = shard copies stored in a permuted object order        */
+} ncd_synth_cfg;
+
+/* Capacities an arena needs for cfg (so the caller can size ncd_arena_create). */
+int ncd_synth_sizes(ncd_ctx* ctx, const ncd_synth_cfg* cfg, int role, uint64_t* payload_bytes,
+                    uint64_t* nobj, uint64_t* aux_bytes, uint64_t* nowner, uint64_t* ndep);
+/* Generates and commits. */
+int ncd_synth_fill(ncd_ctx* ctx, ncd_arena* a, const ncd_synth_cfg* cfg, int role);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NCDRIFT_H */

@@ -1,0 +1,323 @@
+// ncd_api.cu — context and arena entry points of the C ABI (include/ncdrift.h).
+#include <stdarg.h>
+#include <stdlib.h>
+
+#include "ncd_common.cuh"
+
+// ------------------------------------------------------------------ errors
+static thread_local char g_err[512] = "";
+
+void ncd_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* ncd_last_error(void) { return g_err; }
+extern "C" const char* ncd_version(void) { return "ncdrift 0.1 (sm_100a)"; }
+
+extern "C" uint64_t ncd_keyhash(uint32_t kind, const void* key, uint32_t key_len) {
+  return ncd_keyhash_impl(kind, (const uint8_t*)key, key_len);
+}
+
+// ------------------------------------------------------------------ context
+extern "C" int ncd_init(int device, ncd_ctx** out) {
+  if (!out) {
+    ncd_set_error("ncd_init: null out");
+    return NCD_E_INVALID;
+  }
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    ncd_set_error("ncd_init: no CUDA device (%s); this library has no CPU path",
+                  e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    return NCD_E_CUDA;
+  }
+  if (device < 0 || device >= ndev) {
+    ncd_set_error("ncd_init: device %d out of range (0..%d)", device, ndev - 1);
+    return NCD_E_INVALID;
+  }
+  NCD_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  NCD_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    ncd_set_error("ncd_init: device %d is sm_%d%d; the kernels are built for sm_100a only", device,
+                  prop.major, prop.minor);
+    return NCD_E_CUDA;
+  }
+  ncd_ctx* ctx = (ncd_ctx*)calloc(1, sizeof(ncd_ctx));
+  if (!ctx) return NCD_E_NOMEM;
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  NCD_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  for (int i = 0; i < 8; ++i) NCD_CUDA(cudaEventCreate(&ctx->ev[i]));
+  NCD_CUDA(cudaMalloc((void**)&ctx->d_counters, 8 * sizeof(uint64_t)));
+  NCD_CUDA(cudaMallocHost((void**)&ctx->h_counters, 8 * sizeof(uint64_t)));
+  // keep stream-ordered allocations cached: the per-scan diff buffers come from this pool
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    uint64_t thr = UINT64_MAX;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+  }
+  *out = ctx;
+  return NCD_OK;
+}
+
+extern "C" void ncd_destroy(ncd_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  if (ctx->pending) ncd_diff_destroy(ctx->pending);
+  if (ctx->scratch) cudaFree(ctx->scratch);
+  if (ctx->d_shards) cudaFree(ctx->d_shards);
+  if (ctx->d_counters) cudaFree(ctx->d_counters);
+  if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
+  for (int i = 0; i < 8; ++i) cudaEventDestroy(ctx->ev[i]);
+  cudaStreamDestroy(ctx->stream);
+  free(ctx);
+}
+
+extern "C" void* ncd_ctx_stream(ncd_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+extern "C" int ncd_ctx_device(ncd_ctx* ctx) { return ctx ? ctx->device : -1; }
+extern "C" int ncd_ctx_sync(ncd_ctx* ctx) {
+  if (!ctx) {
+    ncd_set_error("ncd_ctx_sync: null ctx");
+    return NCD_E_INVALID;
+  }
+  NCD_CUDA(cudaStreamSynchronize(ctx->stream));
+  return NCD_OK;
+}
+
+int ncd_ctx_scratch(ncd_ctx* ctx, size_t bytes, void** out) {
+  if (bytes > ctx->scratch_bytes) {
+    NCD_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (ctx->scratch) cudaFree(ctx->scratch);
+    ctx->scratch = nullptr;
+    ctx->scratch_bytes = 0;
+    size_t want = bytes + bytes / 8;
+    cudaError_t e = cudaMalloc(&ctx->scratch, want);
+    if (e != cudaSuccess) {
+      ncd_set_error("scan scratch of %zu bytes: %s", want, cudaGetErrorString(e));
+      return NCD_E_NOMEM;
+    }
+    ctx->scratch_bytes = want;
+  }
+  *out = ctx->scratch;
+  return NCD_OK;
+}
+
+// ------------------------------------------------------------------ arenas
+namespace {
+struct Field {
+  size_t offset;      // offset of the pointer inside ncd_arena_view
+  size_t elem;        // element size
+  int cap_kind;       // 0 payload, 1 nobj, 2 nobj+1, 3 nowner, 4 ndep, 5 aux
+};
+#define F(member, cap) {offsetof(ncd_arena_view, member), sizeof(*((ncd_arena_view*)0)->member), cap}
+const Field kFields[] = {
+    F(payload, 0),     F(rec_off, 1),     F(rec_len, 1),     F(kind, 1),        F(key_off, 1),
+    F(key_len, 1),     F(uid_off, 1),     F(uid_len, 1),     F(own_start, 2),   F(own_is_template, 3),
+    F(own_uid_off, 3), F(own_uid_len, 3), F(dep_start, 2),   F(dep_kind, 4),    F(dep_key_off, 4),
+    F(dep_key_len, 4), F(aux, 5)};
+#undef F
+constexpr int kNumFields = sizeof(kFields) / sizeof(kFields[0]);
+
+inline void** field_ptr(ncd_arena_view* v, const Field& f) { return (void**)((char*)v + f.offset); }
+inline uint64_t field_count(const Field& f, uint64_t payload, uint64_t nobj, uint64_t aux,
+                            uint64_t nowner, uint64_t ndep) {
+  switch (f.cap_kind) {
+    case 0: return ncd_align_up(payload, 16);
+    case 1: return nobj;
+    case 2: return nobj + 1;
+    case 3: return nowner;
+    case 4: return ndep;
+    default: return aux;
+  }
+}
+}  // namespace
+
+extern "C" int ncd_arena_create(ncd_ctx* ctx, uint64_t payload_cap, uint64_t nobj_cap, uint64_t aux_cap,
+                                uint64_t nowner_cap, uint64_t ndep_cap, uint32_t flags, ncd_arena** out) {
+  if (!ctx || !out) {
+    ncd_set_error("ncd_arena_create: null argument");
+    return NCD_E_INVALID;
+  }
+  *out = nullptr;
+  if (nobj_cap >= 0xFFFFFFFFull || aux_cap >= 0xFFFFFFFFull || nowner_cap >= 0xFFFFFFFFull ||
+      ndep_cap >= 0xFFFFFFFFull) {
+    ncd_set_error("ncd_arena_create: object / aux / owner / dependent capacities are 32-bit");
+    return NCD_E_CAPACITY;
+  }
+  if (flags > NCD_ARENA_DEVICE_ONLY) {
+    ncd_set_error("ncd_arena_create: unknown flags %u", flags);
+    return NCD_E_INVALID;
+  }
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  ncd_arena* a = (ncd_arena*)calloc(1, sizeof(ncd_arena));
+  if (!a) return NCD_E_NOMEM;
+  a->ctx = ctx;
+  a->flags = flags;
+  a->payload_cap = ncd_align_up(payload_cap, 16);
+  a->nobj_cap = nobj_cap;
+  a->aux_cap = aux_cap;
+  a->nowner_cap = nowner_cap;
+  a->ndep_cap = ndep_cap;
+  for (int i = 0; i < kNumFields; ++i) {
+    const Field& f = kFields[i];
+    uint64_t bytes = field_count(f, payload_cap, nobj_cap, aux_cap, nowner_cap, ndep_cap) * f.elem;
+    if (bytes == 0) bytes = 16;
+    cudaError_t e = cudaMalloc(field_ptr(&a->d, f), bytes);
+    if (e == cudaSuccess && flags == NCD_ARENA_HOST_PINNED) e = cudaMallocHost(field_ptr(&a->h, f), bytes);
+    if (e != cudaSuccess) {
+      ncd_set_error("ncd_arena_create: allocating %llu bytes: %s", (unsigned long long)bytes,
+                    cudaGetErrorString(e));
+      ncd_arena_destroy(a);
+      return NCD_E_NOMEM;
+    }
+  }
+  *out = a;
+  return NCD_OK;
+}
+
+extern "C" void ncd_arena_destroy(ncd_arena* a) {
+  if (!a) return;
+  cudaSetDevice(a->ctx->device);
+  cudaStreamSynchronize(a->ctx->stream);
+  for (int i = 0; i < kNumFields; ++i) {
+    void* d = *field_ptr(&a->d, kFields[i]);
+    void* h = *field_ptr(&a->h, kFields[i]);
+    if (d) cudaFree(d);
+    if (h) cudaFreeHost(h);
+  }
+  void* idx[] = {a->keyhash, a->table,     a->row_start,  a->row_obj, a->row_dep, a->row_cidx,
+                 a->tile_obj, a->tile_chunk, a->tile_start, a->h64,     a->sha,     a->h64_parts};
+  for (void* p : idx)
+    if (p) cudaFree(p);
+  free(a);
+}
+
+extern "C" int ncd_arena_host_view(ncd_arena* a, ncd_arena_view* out) {
+  if (!a || !out) {
+    ncd_set_error("ncd_arena_host_view: null argument");
+    return NCD_E_INVALID;
+  }
+  if (a->flags != NCD_ARENA_HOST_PINNED) {
+    ncd_set_error("ncd_arena_host_view: arena is device-only");
+    return NCD_E_STATE;
+  }
+  *out = a->h;
+  out->nobj = a->nobj_cap;
+  out->payload_bytes = a->payload_cap;
+  out->aux_bytes = a->aux_cap;
+  out->nowner = a->nowner_cap;
+  out->ndep = a->ndep_cap;
+  return NCD_OK;
+}
+
+static int check_counts(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
+                        uint64_t nowner, uint64_t ndep) {
+  if (nobj > a->nobj_cap || payload_bytes > a->payload_cap || aux_bytes > a->aux_cap ||
+      nowner > a->nowner_cap || ndep > a->ndep_cap) {
+    ncd_set_error("ncd_arena_commit: contents (%llu objects, %llu payload bytes, %llu aux bytes, "
+                  "%llu owners, %llu dependents) exceed the arena's capacity",
+                  (unsigned long long)nobj, (unsigned long long)payload_bytes,
+                  (unsigned long long)aux_bytes, (unsigned long long)nowner, (unsigned long long)ndep);
+    return NCD_E_CAPACITY;
+  }
+  return NCD_OK;
+}
+
+// Shared by ncd_arena_commit and the synthetic generator (which fills the device arrays itself).
+int ncd_arena_commit_device(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
+                            uint64_t nowner, uint64_t ndep) {
+  NCD_TRY(check_counts(a, nobj, payload_bytes, aux_bytes, nowner, ndep));
+  a->committed = false;
+  a->nobj = nobj;
+  a->payload_bytes = payload_bytes;
+  a->aux_bytes = aux_bytes;
+  a->nowner = nowner;
+  a->ndep = ndep;
+  NCD_TRY(ncd_build_index(a));
+  a->committed = true;
+  return NCD_OK;
+}
+
+extern "C" int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
+                                uint64_t nowner, uint64_t ndep) {
+  if (!a) {
+    ncd_set_error("ncd_arena_commit: null arena");
+    return NCD_E_INVALID;
+  }
+  if (a->flags != NCD_ARENA_HOST_PINNED) {
+    ncd_set_error("ncd_arena_commit: device-only arenas are committed by ncd_synth_fill");
+    return NCD_E_STATE;
+  }
+  NCD_TRY(check_counts(a, nobj, payload_bytes, aux_bytes, nowner, ndep));
+  NCD_CUDA(cudaSetDevice(a->ctx->device));
+  cudaStream_t st = a->ctx->stream;
+  for (int i = 0; i < kNumFields; ++i) {
+    const Field& f = kFields[i];
+    uint64_t bytes = field_count(f, payload_bytes, nobj, aux_bytes, nowner, ndep) * f.elem;
+    if (f.cap_kind == 0) bytes = payload_bytes;  // the padding of the last record is part of it
+    if (bytes)
+      NCD_CUDA(cudaMemcpyAsync(*field_ptr(&a->d, f), *field_ptr(&a->h, f), bytes, cudaMemcpyHostToDevice, st));
+  }
+  return ncd_arena_commit_device(a, nobj, payload_bytes, aux_bytes, nowner, ndep);
+}
+
+extern "C" int ncd_arena_counts(ncd_arena* a, ncd_arena_view* c) {
+  if (!a || !c) {
+    ncd_set_error("ncd_arena_counts: null argument");
+    return NCD_E_INVALID;
+  }
+  memset(c, 0, sizeof(*c));
+  c->nobj = a->nobj;
+  c->payload_bytes = a->payload_bytes;
+  c->aux_bytes = a->aux_bytes;
+  c->nowner = a->nowner;
+  c->ndep = a->ndep;
+  return NCD_OK;
+}
+
+extern "C" int ncd_arena_download(ncd_arena* a, ncd_arena_view* dst) {
+  if (!a || !dst) {
+    ncd_set_error("ncd_arena_download: null argument");
+    return NCD_E_INVALID;
+  }
+  if (!a->committed) {
+    ncd_set_error("ncd_arena_download: arena not committed");
+    return NCD_E_STATE;
+  }
+  NCD_CUDA(cudaSetDevice(a->ctx->device));
+  cudaStream_t st = a->ctx->stream;
+  for (int i = 0; i < kNumFields; ++i) {
+    const Field& f = kFields[i];
+    void* to = *field_ptr(dst, f);
+    if (!to) continue;
+    uint64_t bytes = field_count(f, a->payload_bytes, a->nobj, a->aux_bytes, a->nowner, a->ndep) * f.elem;
+    if (f.cap_kind == 0) bytes = a->payload_bytes;
+    if (bytes) NCD_CUDA(cudaMemcpyAsync(to, *field_ptr(&a->d, f), bytes, cudaMemcpyDeviceToHost, st));
+  }
+  NCD_CUDA(cudaStreamSynchronize(st));
+  dst->nobj = a->nobj;
+  dst->payload_bytes = a->payload_bytes;
+  dst->aux_bytes = a->aux_bytes;
+  dst->nowner = a->nowner;
+  dst->ndep = a->ndep;
+  return NCD_OK;
+}
+
+extern "C" int ncd_arena_rows(ncd_arena* a, uint64_t* rows) {
+  if (!a || !rows) {
+    ncd_set_error("ncd_arena_rows: null argument");
+    return NCD_E_INVALID;
+  }
+  if (!a->committed) {
+    ncd_set_error("ncd_arena_rows: arena not committed");
+    return NCD_E_STATE;
+  }
+  *rows = a->nrows;
+  return NCD_OK;
+}

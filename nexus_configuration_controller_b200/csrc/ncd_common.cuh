@@ -1,0 +1,200 @@
+// ncd_common.cuh — internal types shared by the translation units of libncdrift.so.
+// Nothing here is part of the C ABI (include/ncdrift.h is).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/ncdrift.h"
+
+#define NCD_NOTFOUND 0xFFFFFFFFu
+#define NCD_NO_OFF 0xFFFFFFFFFFFFFFFFull
+
+// Data verdict of one (controller object, shard) pair, the input of the decision codes.
+enum : uint8_t { DV_EQUAL = 0, DV_DIFF = 1, DV_NOTFOUND = 2 };
+
+// Tile of the compare / hash kernels: a controller record is cut into tiles of this many
+// bytes; one warp owns one tile (32 lanes x 16 B x 8 vectors).
+constexpr uint32_t NCD_TILE_BYTES = 4096;
+constexpr uint32_t NCD_TILE_VECS = NCD_TILE_BYTES / 16;
+
+// Device-visible description of a committed arena (all pointers are device pointers).
+struct DevArena {
+  const uint8_t* payload;
+  const uint64_t* rec_off;
+  const uint32_t* rec_len;
+  const uint8_t* kind;
+  const uint32_t* key_off;
+  const uint32_t* key_len;
+  const uint32_t* uid_off;
+  const uint32_t* uid_len;
+  const uint32_t* own_start;
+  const uint8_t* own_is_template;
+  const uint32_t* own_uid_off;
+  const uint32_t* own_uid_len;
+  const uint32_t* dep_start;
+  const uint8_t* dep_kind;
+  const uint32_t* dep_key_off;
+  const uint32_t* dep_key_len;
+  const uint8_t* aux;
+  // index built by commit
+  const uint64_t* keyhash;  // [nobj]
+  const uint32_t* table;    // open addressing, NCD_NOTFOUND = empty
+  uint32_t table_mask;
+  uint32_t nobj;
+  // digests, filled by the hash kernels
+  const uint64_t* h64;      // [nobj]
+  const uint32_t* sha;      // [nobj][8]
+};
+
+struct ncd_ctx {
+  int device;
+  int sm_count;
+  cudaStream_t stream;
+  cudaEvent_t ev[8];
+  // scratch of the scan, grown on demand and kept
+  void* scratch;
+  size_t scratch_bytes;
+  DevArena* d_shards;  // device array of shard descriptors
+  int d_shards_cap;
+  uint64_t* d_counters;  // [8] device counters (diff count, collisions, ...)
+  uint64_t* h_counters;  // pinned mirror
+  // pending scan
+  bool scan_pending;
+  struct ncd_diff* pending;
+  ncd_scan_stats stats;
+  uint32_t pending_mode;
+};
+
+struct ncd_arena {
+  ncd_ctx* ctx;
+  uint32_t flags;
+  // capacities
+  uint64_t payload_cap, nobj_cap, aux_cap, nowner_cap, ndep_cap;
+  // committed counts
+  uint64_t nobj, payload_bytes, aux_bytes, nowner, ndep;
+  uint64_t len_sum;  // sum of rec_len: the arena's share of the algorithmic bytes
+  bool committed;
+  ncd_arena_view h;  // pinned host arrays (HOST_PINNED only)
+  ncd_arena_view d;  // device arrays
+  // index (device)
+  uint64_t* keyhash;
+  uint32_t* table;
+  uint32_t table_size;
+  uint32_t dup_keys;
+  // controller-side lists (device), built by commit
+  uint64_t nrows;
+  uint32_t* row_start;  // [nobj+1] first row of object i
+  uint32_t* row_obj;    // [nrows] owning template / workgroup
+  uint32_t* row_dep;    // [nrows] NCD_NOTFOUND = the object itself, else dep entry index
+  uint32_t* row_cidx;   // [nrows] controller index of the compared object (NCD_NOTFOUND = missing ref)
+  uint64_t ntiles;
+  uint32_t* tile_obj;   // [ntiles]
+  uint32_t* tile_chunk; // [ntiles]
+  uint32_t* tile_start; // [nobj+1]
+  // digests (device), lazily allocated
+  uint64_t* h64;
+  uint32_t* sha;
+  bool h64_valid, sha_valid;
+  uint64_t* h64_parts;  // per tile partial digests
+};
+
+struct ncd_diff {
+  ncd_ctx* ctx;
+  uint64_t rows, nshards, n;
+  ncd_entry* d_entries;  // device, capacity rows*nshards lazily bounded by n
+  ncd_entry* h_entries;  // pinned, filled on first view
+  uint8_t* d_codes;      // device [rows*nshards]
+  bool h_valid;
+  uint32_t hdr[4];       // staging for ncd_diff_pack
+};
+
+// ------------------------------------------------------------------ errors
+void ncd_set_error(const char* fmt, ...);
+#define NCD_CUDA(call)                                                              \
+  do {                                                                              \
+    cudaError_t _e = (call);                                                        \
+    if (_e != cudaSuccess) {                                                        \
+      ncd_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, \
+                    __LINE__);                                                      \
+      return NCD_E_CUDA;                                                            \
+    }                                                                               \
+  } while (0)
+#define NCD_TRY(call)          \
+  do {                         \
+    int _s = (call);           \
+    if (_s != NCD_OK) return _s; \
+  } while (0)
+
+// ------------------------------------------------------------------ shared host/device helpers
+__host__ __device__ __forceinline__ uint64_t ncd_fmix64(uint64_t x) {
+  x ^= x >> 33;
+  x *= 0xff51afd7ed558ccdull;
+  x ^= x >> 33;
+  x *= 0xc4ceb9fe1a85ec53ull;
+  x ^= x >> 33;
+  return x;
+}
+__host__ __device__ __forceinline__ uint64_t ncd_splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+// FNV-1a over the kind byte and the key, then a finaliser.
+__host__ __device__ __forceinline__ uint64_t ncd_keyhash_impl(uint32_t kind, const uint8_t* key,
+                                                             uint32_t len) {
+  uint64_t h = 0xcbf29ce484222325ull;
+  h = (h ^ (uint64_t)(kind & 0xff)) * 0x100000001b3ull;
+  for (uint32_t i = 0; i < len; ++i) h = (h ^ key[i]) * 0x100000001b3ull;
+  return ncd_fmix64(h);
+}
+
+static inline uint64_t ncd_align_up(uint64_t x, uint64_t a) { return (x + a - 1) / a * a; }
+
+// ------------------------------------------------------------------ internal entry points
+// ncd_index.cu
+int ncd_build_index(ncd_arena* a);
+int ncd_exclusive_scan_u32(ncd_ctx* ctx, const uint32_t* in, uint32_t* out, uint64_t n,
+                           uint32_t* total_out_dev);
+int ncd_exclusive_scan_u64(ncd_ctx* ctx, const uint32_t* in, uint64_t* out, uint64_t n,
+                           uint64_t* total_out_dev);
+void ncd_fill_dev_arena(const ncd_arena* a, DevArena* out);
+int ncd_ctx_scratch(ncd_ctx* ctx, size_t bytes, void** out);
+// ncd_hash.cu
+int ncd_hash_launch(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, uint32_t* launches);
+
+// ------------------------------------------------------------------ device helpers
+#ifdef __CUDACC__
+__device__ __forceinline__ bool ncd_bytes_equal(const uint8_t* a, const uint8_t* b, uint32_t n) {
+  for (uint32_t i = 0; i < n; ++i)
+    if (a[i] != b[i]) return false;
+  return true;
+}
+
+// lister.Get on the GPU: exact ("kind", "namespace/name") lookup in an arena's table.
+// Linear probing; a slot matches when key hash, kind, key length and key bytes all match.
+__device__ __forceinline__ uint32_t ncd_probe(const DevArena& t, uint32_t kind, const uint8_t* key,
+                                              uint32_t key_len, uint64_t hash) {
+  if (t.nobj == 0) return NCD_NOTFOUND;
+  uint32_t slot = (uint32_t)hash & t.table_mask;
+  for (;;) {
+    uint32_t idx = t.table[slot];
+    if (idx == NCD_NOTFOUND) return NCD_NOTFOUND;
+    if (t.keyhash[idx] == hash && t.kind[idx] == kind && t.key_len[idx] == key_len &&
+        ncd_bytes_equal(t.aux + t.key_off[idx], key, key_len))
+      return idx;
+    slot = (slot + 1) & t.table_mask;
+  }
+}
+
+__device__ __forceinline__ uint4 ncd_ldg_stream(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+#endif

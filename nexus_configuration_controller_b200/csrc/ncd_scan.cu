@@ -1,0 +1,501 @@
+// ncd_scan.cu — the drift check itself.
+//
+//   k_join      cache join: for every controller object and every shard, the index of the
+//               object with the same ("kind", "namespace/name") in that shard's arena
+//               (reference: shard.*Lister.Get, controller.go:516,578,722,792), NotFound
+//               when absent; lengths (or digests, in the hash modes) are compared here.
+//   k_compare   byte equality of the canonical records, one warp per 4 KB tile of the
+//               controller record against the same tile of every shard copy
+//               (reference: reflect.DeepEqual at controller.go:539,600,725,795 — equality of
+//               the injective canonical encodings is DeepEqual of the values).
+//   k_classify  decision code per (row, shard) from the verdicts + ownerReferences
+//               (reference: controller.go:484-502, 529-560, 591-622, 725-738, 795-808).
+//   k_emit      ordered stream compaction of the codes != SKIP into the diff list.
+#include "ncd_common.cuh"
+
+// ------------------------------------------------------------------ k_join
+__global__ void __launch_bounds__(256)
+k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t mode,
+       uint32_t* __restrict__ sh_idx, uint64_t* __restrict__ sh_off, uint8_t* __restrict__ dv) {
+  const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= (uint64_t)ctrl.nobj * S) return;
+  const uint32_t c = (uint32_t)(p / S), s = (uint32_t)(p % S);
+  const DevArena& sh = shards[s];
+  const uint32_t idx =
+      ncd_probe(sh, ctrl.kind[c], ctrl.aux + ctrl.key_off[c], ctrl.key_len[c], ctrl.keyhash[c]);
+  uint8_t v;
+  uint64_t off = NCD_NO_OFF;
+  if (idx == NCD_NOTFOUND) {
+    v = DV_NOTFOUND;
+  } else if (sh.rec_len[idx] != ctrl.rec_len[c]) {
+    v = DV_DIFF;  // the encoding is injective: different lengths cannot be DeepEqual
+  } else {
+    const uint32_t hm = mode & 0xff;
+    bool maybe_equal = true;
+    if (hm == NCD_MODE_HASH64) {
+      maybe_equal = sh.h64[idx] == ctrl.h64[c];
+    } else if (hm == NCD_MODE_SHA256) {
+      const uint4* x = reinterpret_cast<const uint4*>(sh.sha + (size_t)idx * 8);
+      const uint4* y = reinterpret_cast<const uint4*>(ctrl.sha + (size_t)c * 8);
+      uint4 x0 = x[0], x1 = x[1], y0 = y[0], y1 = y[1];
+      maybe_equal = ((x0.x ^ y0.x) | (x0.y ^ y0.y) | (x0.z ^ y0.z) | (x0.w ^ y0.w) | (x1.x ^ y1.x) |
+                     (x1.y ^ y1.y) | (x1.z ^ y1.z) | (x1.w ^ y1.w)) == 0;
+    }
+    v = maybe_equal ? DV_EQUAL : DV_DIFF;
+    if (maybe_equal && (hm == NCD_MODE_DIRECT || (mode & NCD_MODE_CONFIRM))) off = sh.rec_off[idx];
+  }
+  sh_idx[p] = idx;
+  sh_off[p] = off;
+  dv[p] = v;
+}
+
+// ------------------------------------------------------------------ k_compare
+// One warp per tile.  The controller tile is loaded once into registers (8 x 16 B per lane)
+// and compared with the same tile of each shard copy that is present with an equal length,
+// so every canonical byte of every copy crosses HBM once.
+__device__ __forceinline__ uint4 mask_tail(uint4 v, uint32_t valid /*1..15*/) {
+  uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    int nb = (int)valid - 4 * i;  // valid bytes in word i
+    if (nb <= 0) w[i] = 0;
+    else if (nb < 4) w[i] &= (1u << (8 * nb)) - 1u;
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+constexpr int CMP_U = NCD_TILE_VECS / 32;  // vectors per lane per tile
+
+__global__ void __launch_bounds__(256)
+k_compare(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
+          const uint32_t* __restrict__ tile_obj, const uint32_t* __restrict__ tile_chunk,
+          uint64_t ntiles, const uint64_t* __restrict__ sh_off, uint8_t* __restrict__ dv,
+          uint32_t* __restrict__ counters, uint32_t count_collisions) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t t = warp0; t < ntiles; t += nwarps) {
+    const uint32_t c = tile_obj[t], chunk = tile_chunk[t];
+    const uint32_t len = ctrl.rec_len[c];
+    const uint64_t toff = (uint64_t)chunk * NCD_TILE_BYTES;
+    const uint32_t nbytes = min(NCD_TILE_BYTES, len - (uint32_t)toff);
+    const uint32_t nvec = (nbytes + 15) >> 4;
+    const uint32_t tail = nbytes & 15;
+    const uint4* cp = reinterpret_cast<const uint4*>(ctrl.payload + ctrl.rec_off[c] + toff);
+    uint4 a[CMP_U];
+#pragma unroll
+    for (int u = 0; u < CMP_U; ++u) {
+      const uint32_t v = lane + 32 * u;
+      a[u] = v < nvec ? ncd_ldg_stream(cp + v) : make_uint4(0, 0, 0, 0);
+      if (tail && v == nvec - 1) a[u] = mask_tail(a[u], tail);
+    }
+    for (uint32_t s0 = 0; s0 < S; s0 += 32) {
+      const uint64_t my_off = (s0 + lane < S) ? sh_off[(uint64_t)c * S + s0 + lane] : NCD_NO_OFF;
+      uint32_t active = __ballot_sync(0xffffffffu, my_off != NCD_NO_OFF);
+      while (active) {
+        const int j = __ffs(active) - 1;
+        active &= active - 1;
+        const uint64_t so = __shfl_sync(0xffffffffu, my_off, j);
+        const uint32_t s = s0 + j;
+        const uint4* sp = reinterpret_cast<const uint4*>(shards[s].payload + so + toff);
+        uint4 b[CMP_U];
+#pragma unroll
+        for (int u = 0; u < CMP_U; ++u) {
+          const uint32_t v = lane + 32 * u;
+          b[u] = v < nvec ? ncd_ldg_stream(sp + v) : make_uint4(0, 0, 0, 0);
+        }
+        uint32_t x = 0;
+#pragma unroll
+        for (int u = 0; u < CMP_U; ++u) {
+          const uint32_t v = lane + 32 * u;
+          uint4 bb = b[u];
+          if (tail && v == nvec - 1) bb = mask_tail(bb, tail);
+          x |= (a[u].x ^ bb.x) | (a[u].y ^ bb.y) | (a[u].z ^ bb.z) | (a[u].w ^ bb.w);
+        }
+        if (__any_sync(0xffffffffu, x != 0) && lane == 0) {
+          // DV_EQUAL (0) -> DV_DIFF (1) on the byte of this pair; the first tile to find a
+          // difference sees the old value and, in CONFIRM mode, counts a hash collision
+          const uint64_t p = (uint64_t)c * S + s;
+          uint32_t* word = reinterpret_cast<uint32_t*>(dv) + (p >> 2);
+          const uint32_t sh8 = 8u * (uint32_t)(p & 3);
+          const uint32_t old = atomicOr(word, (uint32_t)DV_DIFF << sh8);
+          if (count_collisions && ((old >> sh8) & 0xffu) == DV_EQUAL) atomicAdd(&counters[1], 1u);
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ k_classify
+__global__ void __launch_bounds__(256)
+k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint64_t nrows,
+           const uint32_t* __restrict__ row_obj, const uint32_t* __restrict__ row_dep,
+           const uint32_t* __restrict__ row_cidx, const uint32_t* __restrict__ sh_idx,
+           const uint8_t* __restrict__ dv, uint8_t* __restrict__ codes,
+           uint32_t* __restrict__ blk_cnt) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t code = NCD_SKIP;
+  if (q < nrows * S) {
+    const uint32_t r = (uint32_t)(q / S), s = (uint32_t)(q % S);
+    const uint32_t cidx = row_cidx[r], dep = row_dep[r];
+    if (dep == NCD_NOTFOUND) {
+      // template (:792-808) or workgroup (:722-738) row
+      const uint8_t v = dv[(uint64_t)cidx * S + s];
+      code = v == DV_NOTFOUND ? NCD_CREATE : (v == DV_DIFF ? NCD_UPDATE_DATA : NCD_SKIP);
+    } else if (cidx == NCD_NOTFOUND) {
+      code = NCD_ERR_MISSING_REF;  // :509-514, :571-576
+    } else {
+      const uint64_t p = (uint64_t)cidx * S + s;
+      const uint8_t v = dv[p];
+      if (v == DV_NOTFOUND) {
+        code = NCD_CREATE;  // :518-520, :580-582
+      } else {
+        const DevArena& sh = shards[s];
+        const uint32_t j = sh_idx[p];
+        const uint32_t o0 = sh.own_start[j], o1 = sh.own_start[j + 1];
+        if (o0 == o1) {
+          code = NCD_ERR_ROGUE;  // :494-499, checked before the data compare (:529 before :539)
+        } else {
+          // isMissingOwnership(:484-502) against the shard's copy of the owning template.  A
+          // template that is about to be created on this shard has a UID no existing
+          // ownerReference can carry, so the reference is missing by definition.
+          const uint32_t obj = row_obj[r];
+          const uint64_t tp = (uint64_t)obj * S + s;
+          bool missing = true;
+          if (dv[tp] != DV_NOTFOUND) {
+            const uint32_t tj = sh_idx[tp];
+            const uint8_t* uid = sh.aux + sh.uid_off[tj];
+            const uint32_t ulen = sh.uid_len[tj];
+            for (uint32_t o = o0; o < o1 && missing; ++o)
+              if (sh.own_is_template[o] && sh.own_uid_len[o] == ulen &&
+                  ncd_bytes_equal(sh.aux + sh.own_uid_off[o], uid, ulen))
+                missing = false;
+          }
+          code = (v == DV_DIFF ? NCD_UPDATE_DATA : 0u) | (missing ? NCD_UPDATE_OWNER : 0u);
+        }
+      }
+    }
+    codes[q] = (uint8_t)code;
+  }
+  const int cnt = __syncthreads_count(code != NCD_SKIP);
+  if (threadIdx.x == 0) blk_cnt[blockIdx.x] = (uint32_t)cnt;
+}
+
+// ------------------------------------------------------------------ k_emit
+// Same block shape as k_classify; blk_off is the exclusive scan of blk_cnt, so the list comes
+// out in (row, shard) order — the order the reference walks (template, then its dependents).
+__global__ void __launch_bounds__(256)
+k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ row_obj,
+       const uint32_t* __restrict__ row_dep, const uint8_t* __restrict__ codes,
+       const uint32_t* __restrict__ blk_off, ncd_entry* __restrict__ out) {
+  __shared__ uint32_t warp_cnt[8];
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t code = q < nrows * S ? codes[q] : 0u;
+  const uint32_t bal = __ballot_sync(0xffffffffu, code != 0);
+  if (lane == 0) warp_cnt[warp] = __popc(bal);
+  __syncthreads();
+  if (code != 0) {
+    uint32_t pos = blk_off[blockIdx.x] + __popc(bal & ((1u << lane) - 1u));
+    for (uint32_t w = 0; w < warp; ++w) pos += warp_cnt[w];
+    const uint32_t r = (uint32_t)(q / S), s = (uint32_t)(q % S);
+    const uint32_t obj = row_obj[r], dep = row_dep[r];
+    ncd_entry e;
+    e.obj = obj;
+    e.dep = dep == NCD_NOTFOUND ? 0u : dep - ctrl.dep_start[obj] + 1u;
+    e.shard = s;
+    e.code = code;
+    out[pos] = e;
+  }
+}
+
+// ------------------------------------------------------------------ host side
+static int check_scan_args(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards,
+                           int nshards, uint32_t mode) {
+  if (!ctx || !ctrl || (!shards && nshards > 0) || nshards < 0) {
+    ncd_set_error("ncd_scan: null argument");
+    return NCD_E_INVALID;
+  }
+  const uint32_t hm = mode & 0xff;
+  if (hm > NCD_MODE_SHA256 || (mode & ~(0xffu | NCD_MODE_CONFIRM))) {
+    ncd_set_error("ncd_scan: unknown mode 0x%x", mode);
+    return NCD_E_INVALID;
+  }
+  if (!ctrl->committed || ctrl->ctx != ctx) {
+    ncd_set_error("ncd_scan: controller arena not committed on this context");
+    return NCD_E_STATE;
+  }
+  for (int s = 0; s < nshards; ++s)
+    if (!shards[s] || !shards[s]->committed || shards[s]->ctx != ctx) {
+      ncd_set_error("ncd_scan: shard arena %d not committed on this context", s);
+      return NCD_E_STATE;
+    }
+  if (ctx->scan_pending) {
+    ncd_set_error("ncd_scan_launch: a scan is already pending, call ncd_scan_finish first");
+    return NCD_E_STATE;
+  }
+  if (ctrl->nrows * (uint64_t)(nshards ? nshards : 1) >= 0xFFFFFFFFull ||
+      ctrl->nobj * (uint64_t)(nshards ? nshards : 1) >= 0xFFFFFFFFull) {
+    ncd_set_error("ncd_scan: rows x shards exceeds 2^32");
+    return NCD_E_CAPACITY;
+  }
+  return NCD_OK;
+}
+
+int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+                    uint32_t mode) {
+  NCD_TRY(check_scan_args(ctx, ctrl, shards, nshards, mode));
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const uint32_t S = (uint32_t)nshards;
+  const uint64_t nc = ctrl->nobj, nrows = ctrl->nrows;
+  const uint64_t npairs = nc * S, nq = nrows * S;
+  const uint32_t hm = mode & 0xff;
+  uint32_t launches = 0;
+
+  // digests first (hash modes): every copy is hashed once, digests are kept with the arena
+  NCD_CUDA(cudaEventRecord(ctx->ev[0], st));
+  if (hm != NCD_MODE_DIRECT) {
+    NCD_TRY(ncd_hash_launch(ctx, const_cast<ncd_arena*>(ctrl), hm, &launches));
+    for (uint32_t s = 0; s < S; ++s)
+      NCD_TRY(ncd_hash_launch(ctx, const_cast<ncd_arena*>(shards[s]), hm, &launches));
+  }
+  NCD_CUDA(cudaEventRecord(ctx->ev[1], st));
+
+  // shard descriptors
+  if ((int)S > ctx->d_shards_cap) {
+    if (ctx->d_shards) cudaFree(ctx->d_shards);
+    ctx->d_shards = nullptr;
+    int cap = S < 16 ? 16 : (int)S;
+    NCD_CUDA(cudaMalloc((void**)&ctx->d_shards, sizeof(DevArena) * cap));
+    ctx->d_shards_cap = cap;
+  }
+  DevArena dctrl;
+  ncd_fill_dev_arena(ctrl, &dctrl);
+  uint64_t algo = 0;
+  {
+    DevArena* tmp = (DevArena*)malloc(sizeof(DevArena) * (S ? S : 1));
+    if (!tmp) return NCD_E_NOMEM;
+    for (uint32_t s = 0; s < S; ++s) {
+      ncd_fill_dev_arena(shards[s], &tmp[s]);
+      algo += shards[s]->len_sum;
+    }
+    // pageable source: the runtime stages it before returning, tmp can be freed right away
+    cudaError_t e = cudaMemcpyAsync(ctx->d_shards, tmp, sizeof(DevArena) * S, cudaMemcpyHostToDevice, st);
+    free(tmp);
+    NCD_CUDA(e);
+  }
+  algo += ctrl->len_sum;
+
+  // scratch: sh_off u64[npairs] | sh_idx u32[npairs] | blk_cnt u32[nblk+1] | blk_off u32[nblk+1] | dv u8[npairs]
+  const uint64_t nblk = (nq + 255) / 256;
+  size_t o_off = 0;
+  size_t o_idx = o_off + ncd_align_up(npairs * 8, 256);
+  size_t o_cnt = o_idx + ncd_align_up(npairs * 4, 256);
+  size_t o_bo = o_cnt + ncd_align_up((nblk + 1) * 4, 256);
+  size_t o_dv = o_bo + ncd_align_up((nblk + 2) * 4, 256);
+  size_t total = o_dv + ncd_align_up(npairs, 256);
+  void* base = nullptr;
+  NCD_TRY(ncd_ctx_scratch(ctx, total, &base));
+  uint64_t* sh_off = (uint64_t*)((char*)base + o_off);
+  uint32_t* sh_idx = (uint32_t*)((char*)base + o_idx);
+  uint32_t* blk_cnt = (uint32_t*)((char*)base + o_cnt);
+  uint32_t* blk_off = (uint32_t*)((char*)base + o_bo);
+  uint8_t* dv = (uint8_t*)((char*)base + o_dv);
+
+  ncd_diff* d = (ncd_diff*)calloc(1, sizeof(ncd_diff));
+  if (!d) return NCD_E_NOMEM;
+  d->ctx = ctx;
+  d->rows = nrows;
+  d->nshards = S;
+  cudaError_t e1 = cudaMallocAsync((void**)&d->d_codes, nq ? nq : 1, st);
+  cudaError_t e2 = cudaMallocAsync((void**)&d->d_entries, (nq ? nq : 1) * sizeof(ncd_entry), st);
+  if (e1 != cudaSuccess || e2 != cudaSuccess) {
+    ncd_set_error("ncd_scan: diff buffers (%llu decisions): %s", (unsigned long long)nq,
+                  cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+    if (e1 == cudaSuccess) cudaFreeAsync(d->d_codes, st);
+    if (e2 == cudaSuccess) cudaFreeAsync(d->d_entries, st);
+    free(d);
+    return NCD_E_NOMEM;
+  }
+  uint32_t* counters = (uint32_t*)ctx->d_counters;
+  NCD_CUDA(cudaMemsetAsync(counters, 0, 8 * sizeof(uint64_t), st));
+
+  if (npairs) {
+    k_join<<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(dctrl, ctx->d_shards, S, mode, sh_idx,
+                                                             sh_off, dv);
+    ++launches;
+  }
+  NCD_CUDA(cudaEventRecord(ctx->ev[2], st));
+  const bool do_compare = (hm == NCD_MODE_DIRECT) || (mode & NCD_MODE_CONFIRM);
+  if (do_compare && npairs && ctrl->ntiles) {
+    // persistent-style grid: a multiple of the SM count, 8 warps per CTA, grid-stride over tiles
+    uint64_t want = (ctrl->ntiles + 7) / 8;
+    uint64_t cap = (uint64_t)ctx->sm_count * 8;
+    unsigned grid = (unsigned)(want < cap ? want : cap);
+    k_compare<<<grid, 256, 0, st>>>(dctrl, ctx->d_shards, S, ctrl->tile_obj, ctrl->tile_chunk,
+                                    ctrl->ntiles, sh_off, dv, counters,
+                                    hm != NCD_MODE_DIRECT ? 1u : 0u);
+    ++launches;
+  }
+  NCD_CUDA(cudaEventRecord(ctx->ev[3], st));
+  if (nq) {
+    k_classify<<<(unsigned)nblk, 256, 0, st>>>(dctrl, ctx->d_shards, S, nrows, ctrl->row_obj,
+                                               ctrl->row_dep, ctrl->row_cidx, sh_idx, dv, d->d_codes,
+                                               blk_cnt);
+    ++launches;
+  }
+  NCD_TRY(ncd_exclusive_scan_u32(ctx, blk_cnt, blk_off, nblk, counters));
+  launches += nblk ? 3 : 0;
+  if (nq) {
+    k_emit<<<(unsigned)nblk, 256, 0, st>>>(dctrl, S, nrows, ctrl->row_obj, ctrl->row_dep, d->d_codes,
+                                           blk_off, d->d_entries);
+    ++launches;
+  }
+  NCD_CUDA(cudaEventRecord(ctx->ev[4], st));
+  NCD_CUDA(cudaMemcpyAsync(ctx->h_counters, counters, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  NCD_CUDA(cudaGetLastError());
+
+  memset(&ctx->stats, 0, sizeof(ctx->stats));
+  ctx->stats.rows = nrows;
+  ctx->stats.pairs = nq;
+  ctx->stats.algo_bytes = algo;
+  ctx->stats.launches = launches;
+  ctx->pending = d;
+  ctx->pending_mode = mode;
+  ctx->scan_pending = true;
+  return NCD_OK;
+}
+
+int ncd_scan_finish(ncd_ctx* ctx, ncd_diff** out) {
+  if (!ctx || !out) {
+    ncd_set_error("ncd_scan_finish: null argument");
+    return NCD_E_INVALID;
+  }
+  if (!ctx->scan_pending) {
+    ncd_set_error("ncd_scan_finish: no scan pending");
+    return NCD_E_STATE;
+  }
+  ncd_diff* d = ctx->pending;
+  ctx->pending = nullptr;
+  ctx->scan_pending = false;
+  cudaError_t e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) {
+    ncd_set_error("scan failed on the GPU: %s", cudaGetErrorString(e));
+    free(d);  // device buffers are lost with the context after a sticky error
+    return NCD_E_CUDA;
+  }
+  const uint32_t* hc = (const uint32_t*)ctx->h_counters;
+  d->n = hc[0];
+  ncd_scan_stats& st = ctx->stats;
+  st.ndiff = d->n;
+  st.hash_collisions = hc[1];
+  cudaEventElapsedTime(&st.hash_ms, ctx->ev[0], ctx->ev[1]);
+  cudaEventElapsedTime(&st.join_ms, ctx->ev[1], ctx->ev[2]);
+  cudaEventElapsedTime(&st.compare_ms, ctx->ev[2], ctx->ev[3]);
+  cudaEventElapsedTime(&st.classify_ms, ctx->ev[3], ctx->ev[4]);
+  cudaEventElapsedTime(&st.total_ms, ctx->ev[0], ctx->ev[4]);
+  *out = d;
+  return NCD_OK;
+}
+
+int ncd_scan(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+             uint32_t mode, ncd_diff** out) {
+  if (!out) {
+    ncd_set_error("ncd_scan: null out");
+    return NCD_E_INVALID;
+  }
+  NCD_TRY(ncd_scan_launch(ctx, ctrl, shards, nshards, mode));
+  return ncd_scan_finish(ctx, out);
+}
+
+int ncd_scan_last_stats(ncd_ctx* ctx, ncd_scan_stats* out) {
+  if (!ctx || !out) {
+    ncd_set_error("ncd_scan_last_stats: null argument");
+    return NCD_E_INVALID;
+  }
+  *out = ctx->stats;
+  return NCD_OK;
+}
+
+// ------------------------------------------------------------------ diff lists
+int ncd_diff_view(ncd_diff* d, const ncd_entry** entries, uint64_t* n) {
+  if (!d || !entries || !n) {
+    ncd_set_error("ncd_diff_view: null argument");
+    return NCD_E_INVALID;
+  }
+  if (!d->h_valid) {
+    NCD_CUDA(cudaSetDevice(d->ctx->device));
+    NCD_CUDA(cudaMallocHost((void**)&d->h_entries, (d->n ? d->n : 1) * sizeof(ncd_entry)));
+    if (d->n) {
+      NCD_CUDA(cudaMemcpyAsync(d->h_entries, d->d_entries, d->n * sizeof(ncd_entry),
+                               cudaMemcpyDeviceToHost, d->ctx->stream));
+      NCD_CUDA(cudaStreamSynchronize(d->ctx->stream));
+    }
+    d->h_valid = true;
+  }
+  *entries = d->h_entries;
+  *n = d->n;
+  return NCD_OK;
+}
+
+int ncd_diff_device(ncd_diff* d, const void** dev_entries, uint64_t* n) {
+  if (!d || !dev_entries || !n) {
+    ncd_set_error("ncd_diff_device: null argument");
+    return NCD_E_INVALID;
+  }
+  *dev_entries = d->d_entries;
+  *n = d->n;
+  return NCD_OK;
+}
+
+int ncd_diff_pack(ncd_diff* d, void* dev_buf, uint64_t cap_entries) {
+  if (!d || !dev_buf) {
+    ncd_set_error("ncd_diff_pack: null argument");
+    return NCD_E_INVALID;
+  }
+  if (d->n > cap_entries) {
+    ncd_set_error("ncd_diff_pack: %llu entries, buffer holds %llu", (unsigned long long)d->n,
+                  (unsigned long long)cap_entries);
+    return NCD_E_CAPACITY;
+  }
+  NCD_CUDA(cudaSetDevice(d->ctx->device));
+  d->hdr[0] = (uint32_t)d->n;
+  d->hdr[1] = (uint32_t)d->nshards;
+  d->hdr[2] = (uint32_t)d->rows;
+  d->hdr[3] = 0;
+  // pageable source: staged by the runtime before the call returns
+  NCD_CUDA(cudaMemcpyAsync(dev_buf, d->hdr, sizeof(d->hdr), cudaMemcpyHostToDevice, d->ctx->stream));
+  if (d->n)
+    NCD_CUDA(cudaMemcpyAsync((char*)dev_buf + sizeof(d->hdr), d->d_entries, d->n * sizeof(ncd_entry),
+                             cudaMemcpyDeviceToDevice, d->ctx->stream));
+  return NCD_OK;
+}
+
+int ncd_diff_codes(ncd_diff* d, uint8_t* codes_out, uint64_t cap) {
+  if (!d || (!codes_out && cap)) {
+    ncd_set_error("ncd_diff_codes: null argument");
+    return NCD_E_INVALID;
+  }
+  const uint64_t nq = d->rows * d->nshards;
+  if (cap < nq) {
+    ncd_set_error("ncd_diff_codes: buffer holds %llu codes, %llu needed", (unsigned long long)cap,
+                  (unsigned long long)nq);
+    return NCD_E_CAPACITY;
+  }
+  if (nq) {
+    NCD_CUDA(cudaSetDevice(d->ctx->device));
+    NCD_CUDA(cudaMemcpyAsync(codes_out, d->d_codes, nq, cudaMemcpyDeviceToHost, d->ctx->stream));
+    NCD_CUDA(cudaStreamSynchronize(d->ctx->stream));
+  }
+  return NCD_OK;
+}
+
+void ncd_diff_destroy(ncd_diff* d) {
+  if (!d) return;
+  cudaSetDevice(d->ctx->device);
+  if (d->d_entries) cudaFreeAsync(d->d_entries, d->ctx->stream);
+  if (d->d_codes) cudaFreeAsync(d->d_codes, d->ctx->stream);
+  if (d->h_entries) cudaFreeHost(d->h_entries);
+  free(d);
+}

@@ -1,0 +1,207 @@
+// oracle/ncd_oracle.cpp — CPU restatement of the drift-check hot path.  TEST INFRASTRUCTURE:
+// only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+// may load this; nothing under nexus_configuration_controller_b200/ links, imports or calls it.
+//
+// Parity status.  The reference (Go) cannot be built here (no Go toolchain, dependencies
+// un-vendored), and it holds no golden vectors for this path.  What pins this oracle:
+//   - DECISIONS are pinned by the nine handler tests of controller_test.go (:800-1285),
+//     transcribed in tests/golden/reference_cases.json and checked in tests/test_oracle_golden.py.
+//   - reflect.DeepEqual lives in the Go standard library (go 1.24.4, go.mod:3), absent from
+//     /root/reference; its documented rules are restated in oracle/go_values.cpp.
+//   - HASH VALUES: parity unpinned against the reference (it never hashes).  SHA-256 and
+//     XXH64 are pinned by the standards' own known answers; NCD-H64 is this project's
+//     definition and the oracle is its normative statement.
+//
+// This file: the arena-level oracle.  It takes the same structure-of-arrays arenas the GPU
+// library takes (include/ncdrift.h, ncd_arena_view) and walks them the way the reference's
+// handlers walk the listers.
+#include <stdint.h>
+#include <string.h>
+
+#include <atomic>
+#include <string>
+#include <string_view>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../include/ncdrift.h"
+
+namespace {
+
+struct KeyRef {
+  uint8_t kind;
+  std::string_view key;
+  bool operator==(const KeyRef& o) const { return kind == o.kind && key == o.key; }
+};
+struct KeyHash {
+  size_t operator()(const KeyRef& k) const {
+    return std::hash<std::string_view>()(k.key) * 31u + k.kind;
+  }
+};
+using Store = std::unordered_map<KeyRef, uint32_t, KeyHash>;
+
+inline std::string_view sv(const ncd_arena_view* a, uint32_t off, uint32_t len) {
+  return std::string_view(reinterpret_cast<const char*>(a->aux) + off, len);
+}
+
+// The informer store of one cluster: "namespace/name" -> object, per kind.  When a key occurs
+// twice the first object wins (a real store could not hold both).
+Store build_store(const ncd_arena_view* a) {
+  Store s;
+  s.reserve(a->nobj * 2);
+  for (uint32_t i = 0; i < a->nobj; ++i) s.emplace(KeyRef{a->kind[i], sv(a, a->key_off[i], a->key_len[i])}, i);
+  return s;
+}
+
+// lister.Get: controller.go:507,516,569,578,722,792
+inline uint32_t store_get(const Store& s, uint8_t kind, std::string_view key) {
+  auto it = s.find(KeyRef{kind, key});
+  return it == s.end() ? 0xFFFFFFFFu : it->second;
+}
+
+// reflect.DeepEqual(a, b) on two canonical records (controller.go:539,600,725,795): the
+// encoding is injective, so the values are DeepEqual iff the records are byte-identical.
+inline bool records_equal(const ncd_arena_view* a, uint32_t i, const ncd_arena_view* b, uint32_t j) {
+  return a->rec_len[i] == b->rec_len[j] &&
+         memcmp(a->payload + a->rec_off[i], b->payload + b->rec_off[j], a->rec_len[i]) == 0;
+}
+
+// isMissingOwnership, controller.go:484-502.  Returns NCD_ERR_ROGUE, NCD_UPDATE_OWNER or 0.
+// shard_tmpl = index of the shard's copy of the owning template, or 0xFFFFFFFF when the
+// template is being created on this shard (fresh UID: nothing can reference it yet).
+uint32_t ownership(const ncd_arena_view* sh, uint32_t dep_idx, uint32_t shard_tmpl) {
+  const uint32_t o0 = sh->own_start[dep_idx], o1 = sh->own_start[dep_idx + 1];
+  if (o0 == o1) return NCD_ERR_ROGUE;  // :494-499
+  if (shard_tmpl != 0xFFFFFFFFu) {
+    std::string_view uid = sv(sh, sh->uid_off[shard_tmpl], sh->uid_len[shard_tmpl]);
+    for (uint32_t o = o0; o < o1; ++o)  // :489-492
+      if (sh->own_is_template[o] && sv(sh, sh->own_uid_off[o], sh->own_uid_len[o]) == uid) return 0;
+  }
+  return NCD_UPDATE_OWNER;  // :501
+}
+
+struct Row {
+  uint32_t obj, dep;  // dep = 0 self, j + 1 = j-th dependent
+};
+
+std::vector<Row> rows_of(const ncd_arena_view* c) {
+  std::vector<Row> rows;
+  for (uint32_t i = 0; i < c->nobj; ++i) {
+    if (c->kind[i] == NCD_KIND_TEMPLATE) {
+      rows.push_back({i, 0});
+      for (uint32_t d = c->dep_start[i]; d < c->dep_start[i + 1]; ++d) rows.push_back({i, d - c->dep_start[i] + 1});
+    } else if (c->kind[i] == NCD_KIND_WORKGROUP) {
+      rows.push_back({i, 0});
+    }
+  }
+  return rows;
+}
+
+// The decision for one row on one shard: the body of the per-shard loops of
+// templateSyncHandler (:790-831), syncSecretsToShard (:504-564), syncConfigMapsToShard
+// (:566-626) and workgroupSyncHandler (:720-745), minus the writes.
+uint32_t decide(const ncd_arena_view* c, const Store& cstore, const ncd_arena_view* sh, const Store& sstore,
+                Row r, uint64_t* bytes_compared) {
+  const uint32_t t = r.obj;
+  std::string_view tkey = sv(c, c->key_off[t], c->key_len[t]);
+  const uint32_t st = store_get(sstore, c->kind[t], tkey);  // :792 / :722
+  if (r.dep == 0) {
+    if (st == 0xFFFFFFFFu) return NCD_CREATE;  // :805-808 / :735-738
+    *bytes_compared += c->rec_len[t];
+    return records_equal(c, t, sh, st) ? NCD_SKIP : NCD_UPDATE_DATA;  // :795-797 / :725-727
+  }
+  const uint32_t d = c->dep_start[t] + r.dep - 1;
+  const uint8_t dk = c->dep_kind[d];
+  std::string_view dkey = sv(c, c->dep_key_off[d], c->dep_key_len[d]);
+  const uint32_t cd = store_get(cstore, dk, dkey);  // :507 / :569
+  if (cd == 0xFFFFFFFFu) return NCD_ERR_MISSING_REF;  // :509-514 / :571-576
+  const uint32_t sd = store_get(sstore, dk, dkey);  // :516 / :578
+  if (sd == 0xFFFFFFFFu) return NCD_CREATE;  // :518-520 / :580-582
+  const uint32_t own = ownership(sh, sd, st);  // :529 / :591
+  if (own == NCD_ERR_ROGUE) return NCD_ERR_ROGUE;
+  *bytes_compared += c->rec_len[cd];
+  const uint32_t data = records_equal(c, cd, sh, sd) ? 0u : (uint32_t)NCD_UPDATE_DATA;  // :539 / :600
+  return data | own;  // :541 then :552 / :602 then :614
+}
+
+}  // namespace
+
+extern "C" {
+
+// Number of rows the controller arena produces.
+uint64_t oracle_rows(const ncd_arena_view* ctrl) { return rows_of(ctrl).size(); }
+
+// codes_out: rows x nshards (row-major).  entries_out (optional, capacity rows x nshards):
+// the codes != SKIP in (row, shard) order.  Returns the number of entries.  nthreads <= 1
+// runs on the calling thread.  bytes_out (optional): controller-side bytes DeepEqual looked at.
+uint64_t oracle_scan(const ncd_arena_view* ctrl, const ncd_arena_view* const* shards, int nshards,
+                     uint8_t* codes_out, ncd_entry* entries_out, int nthreads, uint64_t* bytes_out) {
+  const std::vector<Row> rows = rows_of(ctrl);
+  const Store cstore = build_store(ctrl);
+  std::vector<Store> sstores;
+  sstores.reserve(nshards);
+  for (int s = 0; s < nshards; ++s) sstores.push_back(build_store(shards[s]));
+  const uint64_t R = rows.size();
+  std::atomic<uint64_t> total_bytes{0};
+  auto work = [&](uint64_t r0, uint64_t r1) {
+    uint64_t bytes = 0;
+    for (uint64_t r = r0; r < r1; ++r)
+      for (int s = 0; s < nshards; ++s)
+        codes_out[r * nshards + s] = (uint8_t)decide(ctrl, cstore, shards[s], sstores[s], rows[r], &bytes);
+    total_bytes += bytes;
+  };
+  if (nthreads <= 1 || R < 64) {
+    work(0, R);
+  } else {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t) th.emplace_back(work, R * t / nthreads, R * (t + 1) / nthreads);
+    for (auto& x : th) x.join();
+  }
+  if (bytes_out) *bytes_out = total_bytes.load();
+  uint64_t n = 0;
+  for (uint64_t r = 0; r < R; ++r)
+    for (int s = 0; s < nshards; ++s) {
+      const uint8_t code = codes_out[r * nshards + s];
+      if (code == NCD_SKIP) continue;
+      if (entries_out) entries_out[n] = ncd_entry{rows[r].obj, rows[r].dep, (uint32_t)s, code};
+      ++n;
+    }
+  return n;
+}
+
+// Timed variant for the CPU baseline: stores are built once (the reference's informer caches
+// exist before the handlers run), then `reps` full sweeps are made with nthreads threads.
+// Returns seconds per sweep; codes_out as above.
+double oracle_scan_timed(const ncd_arena_view* ctrl, const ncd_arena_view* const* shards, int nshards,
+                         uint8_t* codes_out, int nthreads, int reps, uint64_t* bytes_out);
+
+}  // extern "C"
+
+#include <chrono>
+extern "C" double oracle_scan_timed(const ncd_arena_view* ctrl, const ncd_arena_view* const* shards, int nshards,
+                                    uint8_t* codes_out, int nthreads, int reps, uint64_t* bytes_out) {
+  const std::vector<Row> rows = rows_of(ctrl);
+  const Store cstore = build_store(ctrl);
+  std::vector<Store> sstores;
+  for (int s = 0; s < nshards; ++s) sstores.push_back(build_store(shards[s]));
+  const uint64_t R = rows.size();
+  if (nthreads < 1) nthreads = 1;
+  std::atomic<uint64_t> total_bytes{0};
+  auto work = [&](uint64_t r0, uint64_t r1) {
+    uint64_t bytes = 0;
+    for (uint64_t r = r0; r < r1; ++r)
+      for (int s = 0; s < nshards; ++s)
+        codes_out[r * nshards + s] = (uint8_t)decide(ctrl, cstore, shards[s], sstores[s], rows[r], &bytes);
+    total_bytes += bytes;
+  };
+  auto t0 = std::chrono::steady_clock::now();
+  for (int rep = 0; rep < reps; ++rep) {
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t) th.emplace_back(work, R * t / nthreads, R * (t + 1) / nthreads);
+    for (auto& x : th) x.join();
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  if (bytes_out) *bytes_out = total_bytes.load() / (reps > 0 ? reps : 1);
+  return std::chrono::duration<double>(t1 - t0).count() / (reps > 0 ? reps : 1);
+}

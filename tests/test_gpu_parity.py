@@ -1,0 +1,196 @@
+"""GPU parity: libncdrift.so through its C ABI against the CPU oracle, bit for bit.
+
+Bar: integer / byte work, so every decision code and every diff-list entry must be identical.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle
+from nexus_configuration_controller_b200 import arena as A
+from nexus_configuration_controller_b200._ffi import SynthCfg
+from tests.helpers import random_clusters, rand_bytes
+from tests import synth_spec
+
+pytestmark = pytest.mark.gpu
+
+MODES = [
+    A.MODE_DIRECT,
+    A.MODE_HASH64,
+    A.MODE_HASH64 | A.MODE_CONFIRM,
+    A.MODE_SHA256,
+    A.MODE_SHA256 | A.MODE_CONFIRM,
+]
+
+
+def gpu_scan(ctx, ctrl_host, shard_hosts, mode):
+    ca = ctx.arena_from_host(ctrl_host)
+    sas = [ctx.arena_from_host(h) for h in shard_hosts]
+    d = ctx.scan(ca, sas, mode)
+    codes, ents = d.codes().copy(), d.entries()
+    st = ctx.last_stats()
+    d.close()
+    for a in sas + [ca]:
+        a.close()
+    return codes, ents, st
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5])
+@pytest.mark.parametrize("mode", MODES)
+def test_random_clusters_match_oracle(ctx, seed, mode):
+    ctrl, shards = random_clusters(seed, n_templates=10 + 3 * seed, n_shards=1 + seed % 4)
+    want_codes, want_ents = oracle.scan(ctrl, shards)
+    codes, ents, st = gpu_scan(ctx, ctrl, shards, mode)
+    assert codes.shape == want_codes.shape
+    np.testing.assert_array_equal(codes, want_codes)
+    np.testing.assert_array_equal(ents, want_ents)
+    assert st.ndiff == len(want_ents) and st.pairs == want_codes.size
+    # every code must occur somewhere in the seeds, or the test is not exercising the path
+    assert set(np.unique(want_codes)) <= {0, 1, 2, 4, 6, 8, 16}
+
+
+def test_all_codes_are_exercised():
+    seen = set()
+    for seed in [1, 2, 3, 4, 5]:
+        ctrl, shards = random_clusters(seed, n_templates=10 + 3 * seed, n_shards=1 + seed % 4)
+        seen |= set(np.unique(oracle.scan(ctrl, shards)[0]).tolist())
+    assert seen == {0, 1, 2, 4, 6, 8, 16}
+
+
+def test_many_shards_more_than_a_warp(ctx):
+    ctrl, shards = random_clusters(11, n_templates=6, n_shards=37, max_len=600)
+    want_codes, want_ents = oracle.scan(ctrl, shards)
+    for mode in (A.MODE_DIRECT, A.MODE_HASH64):
+        codes, ents, _ = gpu_scan(ctx, ctrl, shards, mode)
+        np.testing.assert_array_equal(codes, want_codes)
+        np.testing.assert_array_equal(ents, want_ents)
+
+
+def test_empty_inputs(ctx):
+    empty = A.pack([])
+    one = A.pack([A.CachedObject(A.KIND_WORKGROUP, "default/wg", b"\x01\x02\x03", uid="u")])
+    # no controller objects: nothing to decide
+    codes, ents, st = gpu_scan(ctx, empty, [one], A.MODE_DIRECT)
+    assert codes.size == 0 and len(ents) == 0 and st.ndiff == 0
+    # no shards
+    codes, ents, _ = gpu_scan(ctx, one, [], A.MODE_DIRECT)
+    assert codes.size == 0 and len(ents) == 0
+    # empty shard cache: everything is created (controller.go:735-738)
+    codes, ents, _ = gpu_scan(ctx, one, [empty, one], A.MODE_DIRECT)
+    np.testing.assert_array_equal(codes, [[A.CREATE, A.SKIP]])
+    np.testing.assert_array_equal(ents, [[0, 0, 0, A.CREATE]])
+
+
+def test_tail_bytes_beyond_length_are_ignored(ctx):
+    """Padding after a record is not part of the value: garbage there must not read as drift."""
+    data = bytes(range(1, 38))  # 37 bytes: 5 bytes into the third vector
+    ctrl = A.pack([A.CachedObject(A.KIND_WORKGROUP, "default/wg", data)])
+    shard = A.pack([A.CachedObject(A.KIND_WORKGROUP, "default/wg", data)])
+    shard.payload[37:48] = 0xEE
+    for mode in MODES:
+        codes, _, _ = gpu_scan(ctx, ctrl, [shard], mode)
+        assert codes[0, 0] == A.SKIP, mode
+    shard.payload[36] ^= 0x80  # last real byte
+    for mode in MODES:
+        codes, _, _ = gpu_scan(ctx, ctrl, [shard], mode)
+        assert codes[0, 0] == A.UPDATE_DATA, mode
+
+
+@pytest.mark.parametrize("n", [1, 15, 16, 17, 63, 64, 65, 4095, 4096, 4097, 8192, 100003, 1 << 20])
+def test_every_single_byte_position_class_is_seen(ctx, n):
+    """Same length, one byte differs: first, last, tile edges (the hard case of cfg 3)."""
+    import random
+
+    rng = random.Random(n)
+    base = rand_bytes(rng, n)
+    positions = sorted({0, n - 1, n // 2, min(n - 1, 4095), min(n - 1, 4096), max(0, n - 17)})
+    ctrl = A.pack([A.CachedObject(A.KIND_WORKGROUP, "default/wg", base)])
+    shards = []
+    for p in positions:
+        b = bytearray(base)
+        b[p] ^= 0x01
+        shards.append(A.pack([A.CachedObject(A.KIND_WORKGROUP, "default/wg", bytes(b))]))
+    shards.append(A.pack([A.CachedObject(A.KIND_WORKGROUP, "default/wg", base)]))
+    for mode in (A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256):
+        codes, _, _ = gpu_scan(ctx, ctrl, shards, mode)
+        assert codes[0].tolist() == [A.UPDATE_DATA] * len(positions) + [A.SKIP], (mode, n)
+
+
+def test_digests_match_oracle(ctx):
+    import random
+
+    rng = random.Random(99)
+    lens = [0, 1, 15, 16, 17, 55, 56, 57, 63, 64, 65, 119, 120, 127, 128, 4095, 4096, 4097, 8192, 12289, 70000]
+    objs = [A.CachedObject(A.KIND_SECRET, f"default/s{i}", rand_bytes(rng, n)) for i, n in enumerate(lens)]
+    host = A.pack(objs)
+    a = ctx.arena_from_host(host)
+    h64, _ = ctx.hash_arena(a, A.MODE_HASH64)
+    sha, _ = ctx.hash_arena(a, A.MODE_SHA256)
+    a.close()
+    np.testing.assert_array_equal(h64, oracle.h64_arena(host))
+    np.testing.assert_array_equal(sha, oracle.sha256_arena(host))
+    import hashlib
+
+    for i, o in enumerate(objs):
+        assert bytes(sha[i]) == hashlib.sha256(o.canon).digest()
+
+
+def small_synth(**kw) -> SynthCfg:
+    c = SynthCfg()
+    c.groups, c.n_secrets, c.n_configmaps = 300, 2, 1
+    c.tmpl_len_lo, c.tmpl_len_hi = 100, 700
+    c.dep_len_lo, c.dep_len_hi = 1, 9000
+    c.seed, c.drift_seed = 0xC0FFEE, 0xD21F7
+    c.p_flip_ppm, c.p_missing_ppm, c.p_len_ppm = 60000, 40000, 30000
+    c.p_owner_ppm, c.p_rogue_ppm = 50000, 30000
+    c.part_mod, c.part_rem, c.shuffle = 0, 0, 1
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("shuffle", [0, 1])
+def test_synthetic_arenas_match_oracle_and_spec(ctx, mode, shuffle):
+    cfg = small_synth(shuffle=shuffle)
+    S = 5
+    ca = ctx.synth_arena(cfg, -1)
+    sas = [ctx.synth_arena(cfg, s) for s in range(S)]
+    d = ctx.scan(ca, sas, mode)
+    codes, ents = d.codes().copy(), d.entries()
+    d.close()
+    ch, shs = ca.download(), [s.download() for s in sas]
+    for a in sas + [ca]:
+        a.close()
+    want_codes, want_ents = oracle.scan(ch, shs)
+    np.testing.assert_array_equal(codes, want_codes)
+    np.testing.assert_array_equal(ents, want_ents)
+    # and the codes are the ones the generator's drift function was asked to inject
+    spec = synth_spec.expected_codes(cfg, S)
+    np.testing.assert_array_equal(codes, spec)
+    assert set(np.unique(codes).tolist()) == {0, 1, 2, 4, 6, 8}
+
+
+def test_partition_by_key_hash_covers_everything_once(ctx):
+    """The multi-GPU layout: each key-hash partition scanned alone gives exactly its share."""
+    cfg = small_synth(groups=500)
+    S = 3
+    whole = synth_spec.expected_codes(cfg, S)
+    per = 1 + cfg.n_secrets + cfg.n_configmaps
+    kept_total = 0
+    G = 4
+    for rank in range(G):
+        pc = small_synth(groups=500, part_mod=G, part_rem=rank)
+        ca = ctx.synth_arena(pc, -1)
+        sas = [ctx.synth_arena(pc, s) for s in range(S)]
+        d = ctx.scan(ca, sas, A.MODE_DIRECT)
+        codes = d.codes().copy()
+        d.close()
+        for a in sas + [ca]:
+            a.close()
+        groups = synth_spec.kept_groups(pc)
+        kept_total += len(groups)
+        want = np.concatenate([whole[g * per : (g + 1) * per] for g in groups]) if len(groups) else whole[:0]
+        np.testing.assert_array_equal(codes, want)
+    assert kept_total == 500
