@@ -1,0 +1,55 @@
+"""The C-ABI library loads without a GPU and exports every symbol include/ncdrift.h declares (CPU)."""
+import ctypes as C
+import os
+import re
+
+from nexus_configuration_controller_b200 import _ffi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_functions():
+    src = open(os.path.join(ROOT, "include", "ncdrift.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(ncd_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_header_and_library_agree():
+    names = declared_functions()
+    assert len(names) >= 25
+    lib = C.CDLL(_ffi.LIB_PATH)
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, f"declared in ncdrift.h but not exported: {missing}"
+    # and the Python binding covers the same set
+    assert sorted(_ffi.PROTOTYPES) == names
+
+
+def test_struct_layouts_match_the_header():
+    # sizes a C compiler gives the same declarations (all members naturally aligned)
+    assert C.sizeof(_ffi.ArenaView) == 5 * 8 + 17 * 8
+    assert C.sizeof(_ffi.Entry) == 16
+    assert C.sizeof(_ffi.ScanStats) == 5 * 4 + 4 + 5 * 8 + 4 + 4
+    assert C.sizeof(_ffi.SynthCfg) == 8 + 6 * 4 + 2 * 8 + 8 * 4
+
+
+def test_no_gpu_means_a_loud_error_not_a_fallback():
+    import torch
+
+    if torch.cuda.is_available():
+        return  # on the GPU box the context tests cover init
+    lib = _ffi.load()
+    h = C.c_void_p()
+    rc = lib.ncd_init(0, C.byref(h))
+    assert rc == -2 and not h.value
+    assert b"no CUDA device" in lib.ncd_last_error()
+    # host-only helper still works: the key hash is what the multi-GPU partition uses
+    assert lib.ncd_keyhash(0, b"nexus/t-0000000001", 18) == lib.ncd_keyhash(0, b"nexus/t-0000000001", 18)
+    assert lib.ncd_keyhash(0, b"nexus/t-0000000001", 18) != lib.ncd_keyhash(2, b"nexus/t-0000000001", 18)
+
+
+def test_keyhash_matches_the_spec_used_for_partitioning():
+    from tests import synth_spec
+
+    lib = _ffi.load()
+    for kind, key in [(0, b"nexus/t-0000000042"), (2, b"default/secret"), (3, b""), (1, b"a" * 300)]:
+        assert lib.ncd_keyhash(kind, key, len(key)) == synth_spec.keyhash(kind, key)
