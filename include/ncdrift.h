@@ -226,6 +226,34 @@ void ncd_diff_destroy(ncd_diff* d);
 int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* out, uint64_t out_bytes,
                    float* kernel_ms);
 
+/* ------------------------------------------------------------------ hashing without allocation
+ * No counterpart in the reference, and the one entry point here that needs no ncd_ctx.
+ *
+ * For callers that may not allocate GPU or pinned memory once they are running: a controller
+ * sharing its GPU under a fixed memory reservation, a process whose device memory all belongs
+ * to its own pool, a handler that cannot afford cudaMalloc's device-wide synchronisation or
+ * an out-of-memory failure mid-reconcile.  The caller owns every buffer it passes (all DEVICE
+ * pointers, on the device that is current when the call is made):
+ *   dev_payload  records, each starting on a 16-byte boundary (arena payload layout)
+ *   dev_rec_off  byte offset of record i (multiple of 16), dev_rec_len its length
+ *   dev_out      nrec x uint64, receives the NCD-H64 digests, identical to
+ *                ncd_hash_arena(NCD_MODE_HASH64) on the same records
+ *   stream       cudaStream_t to enqueue on (NULL = the default stream); the call returns
+ *                once the work is enqueued
+ * The working memory of the kernels is a fixed 768.25 KiB array inside the library image
+ * (every GPU that loads libncdrift.so holds it until the process exits), so the call performs
+ * no cudaMalloc / cudaFree / pinned allocation and calls no routine that does.
+ * Limits and rules:
+ *   - at most NCD_STATIC_MAX_RECORDS records per call; more is refused with NCD_E_CAPACITY
+ *   - the first call on each device looks the array's device address up
+ *     (cudaGetSymbolAddress); make that first call before any stream capture begins
+ *   - all calls on a device share the array; a call re-initialises what it reads, but calls
+ *     that overlap on the GPU (two streams, or unordered work) race and corrupt each other's
+ *     digests: serialise them */
+#define NCD_STATIC_MAX_RECORDS 65536u
+int ncd_hash64_static(const void* dev_payload, const uint64_t* dev_rec_off, const uint32_t* dev_rec_len,
+                      uint64_t nrec, uint64_t* dev_out, void* stream);
+
 /* ------------------------------------------------------------------ synthetic input
  * Bench / test utility: fills a DEVICE_ONLY arena on the GPU with the synthetic
  * workload of SURVEY.md section 8(d).  role -1 = controller copy, s >= 0 = shard s.

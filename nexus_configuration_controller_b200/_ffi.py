@@ -122,6 +122,7 @@ PROTOTYPES = {
     "ncd_diff_codes": (C.c_int, [VP, u8p, C.c_uint64]),
     "ncd_diff_destroy": (None, [VP]),
     "ncd_hash_arena": (C.c_int, [VP, VP, C.c_uint32, VP, C.c_uint64, C.POINTER(C.c_float)]),
+    "ncd_hash64_static": (C.c_int, [VP, VP, VP, C.c_uint64, VP, VP]),
     "ncd_synth_sizes": (C.c_int, [VP, C.POINTER(SynthCfg), C.c_int, u64p, u64p, u64p, u64p, u64p]),
     "ncd_synth_fill": (C.c_int, [VP, VP, C.POINTER(SynthCfg), C.c_int]),
 }
