@@ -49,8 +49,32 @@ def load() -> C.CDLL:
         lib.oracle_h64_arena.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         lib.oracle_sha256_arena.restype = None
         lib.oracle_sha256_arena.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        lib.oracle_values_error.restype = C.c_char_p
+        lib.oracle_deep_equal.restype = C.c_int
+        lib.oracle_deep_equal.argtypes = [C.c_char_p, C.c_uint64, C.c_char_p, C.c_uint64]
+        lib.oracle_canon.restype = C.c_int64
+        lib.oracle_canon.argtypes = [C.c_char_p, C.c_uint64, C.c_char_p, C.c_uint64]
         _lib = lib
     return _lib
+
+
+def deep_equal(a_wire: bytes, b_wire: bytes) -> bool:
+    """reflect.DeepEqual of two Go values given in the transport form of tests/govalues.py."""
+    rc = load().oracle_deep_equal(a_wire, len(a_wire), b_wire, len(b_wire))
+    if rc < 0:
+        raise ValueError(load().oracle_values_error().decode())
+    return rc == 1
+
+
+def canon(wire: bytes) -> bytes:
+    """Canonical encoding of a Go value (oracle's own statement of the encoder)."""
+    lib = load()
+    n = lib.oracle_canon(wire, len(wire), None, 0)
+    if n < 0:
+        raise ValueError(lib.oracle_values_error().decode())
+    buf = C.create_string_buffer(max(n, 1))
+    lib.oracle_canon(wire, len(wire), buf, n)
+    return buf.raw[:n]
 
 
 def _views(ctrl, shards):

@@ -1,0 +1,226 @@
+// oracle/go_values.cpp — Go values, reflect.DeepEqual and the canonical encoding, on the CPU.
+// TEST INFRASTRUCTURE (see ncd_oracle.cpp for who may load it).
+//
+// The compare arithmetic of the hot path is reflect.DeepEqual (controller.go:539,600,725,795).
+// It lives in the Go standard library (toolchain go 1.24.4, go.mod:3), which is not under
+// /root/reference, and no Go toolchain exists in this image, so the rules are restated here
+// from the documented behaviour of reflect.DeepEqual:
+//   Map     nil-ness must match; lengths must match; every key of a is present in b with a
+//           deeply equal value
+//   Slice   nil-ness must match (a nil slice is NOT equal to an empty one); lengths match;
+//           elements pairwise deeply equal ([]byte: bytewise)
+//   String  byte equality          Bool, Int  ==          Float  == (NaN != NaN, +0 == -0)
+//   Pointer both nil, or both non-nil with deeply equal pointees
+//   Struct  every field, in order
+//   Interface  both nil, or same dynamic type and deeply equal values
+// Values of different kinds are never equal (DeepEqual requires identical types).
+// What pins these rules to the reference: tests/golden/reference_cases.json (the handler tests
+// of controller_test.go, which exercise empty-vs-empty maps, non-empty-vs-empty maps, *bool
+// dereference and slice length) — checked in tests/test_oracle_golden.py.  Rules no reference
+// test exercises (nil vs empty, key order, same-length byte changes) are marked "extrapolated"
+// there.
+//
+// Values arrive in the tag-length-value transport written by tests/govalues.py.
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <cmath>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace {
+
+enum Tag : uint8_t {
+  T_BOOL = 1, T_INT, T_STRING, T_BYTES, T_NILBYTES, T_SLICE, T_NILSLICE, T_MAP, T_NILMAP, T_PTR, T_NILPTR,
+  T_STRUCT, T_FLOAT, T_IFACE, T_NILIFACE
+};
+
+struct Node {
+  uint8_t tag = 0;
+  uint8_t width = 0;          // T_INT
+  int64_t i = 0;              // T_BOOL, T_INT
+  double f = 0;               // T_FLOAT
+  std::string s;              // T_STRING, T_BYTES, T_IFACE (type name)
+  std::vector<Node> kids;     // T_SLICE, T_STRUCT, T_PTR (1), T_IFACE (1), T_MAP (k0 v0 k1 v1 ...)
+};
+
+struct Reader {
+  const uint8_t* p;
+  const uint8_t* end;
+  uint8_t u8() {
+    if (p >= end) throw std::runtime_error("truncated value");
+    return *p++;
+  }
+  uint32_t u32() {
+    if (end - p < 4) throw std::runtime_error("truncated value");
+    uint32_t v;
+    memcpy(&v, p, 4);
+    p += 4;
+    return v;
+  }
+  std::string bytes(uint32_t n) {
+    if ((uint64_t)(end - p) < n) throw std::runtime_error("truncated value");
+    std::string s(reinterpret_cast<const char*>(p), n);
+    p += n;
+    return s;
+  }
+};
+
+Node parse(Reader& r, int depth = 0) {
+  if (depth > 200) throw std::runtime_error("value nested too deeply");
+  Node n;
+  n.tag = r.u8();
+  switch (n.tag) {
+    case T_BOOL: n.i = r.u8() != 0; break;
+    case T_INT: {
+      n.width = r.u8();
+      std::string b = r.bytes(8);
+      memcpy(&n.i, b.data(), 8);
+      break;
+    }
+    case T_STRING: case T_BYTES: n.s = r.bytes(r.u32()); break;
+    case T_NILBYTES: case T_NILSLICE: case T_NILMAP: case T_NILPTR: case T_NILIFACE: break;
+    case T_SLICE: case T_STRUCT: {
+      uint32_t c = r.u32();
+      for (uint32_t k = 0; k < c; ++k) n.kids.push_back(parse(r, depth + 1));
+      break;
+    }
+    case T_MAP: {
+      uint32_t c = r.u32();
+      for (uint32_t k = 0; k < 2 * c; ++k) n.kids.push_back(parse(r, depth + 1));
+      break;
+    }
+    case T_PTR: n.kids.push_back(parse(r, depth + 1)); break;
+    case T_FLOAT: {
+      std::string b = r.bytes(8);
+      memcpy(&n.f, b.data(), 8);
+      break;
+    }
+    case T_IFACE: n.s = r.bytes(r.u32()); n.kids.push_back(parse(r, depth + 1)); break;
+    default: throw std::runtime_error("unknown value tag");
+  }
+  return n;
+}
+
+bool deep_equal(const Node& a, const Node& b) {
+  if (a.tag != b.tag) return false;  // covers nil vs non-nil of every nilable kind
+  switch (a.tag) {
+    case T_BOOL: return a.i == b.i;
+    case T_INT: return a.width == b.width && a.i == b.i;
+    case T_STRING: case T_BYTES: return a.s == b.s;
+    case T_FLOAT: return a.f == b.f;
+    case T_NILBYTES: case T_NILSLICE: case T_NILMAP: case T_NILPTR: case T_NILIFACE: return true;
+    case T_SLICE: case T_STRUCT:
+      if (a.kids.size() != b.kids.size()) return false;
+      for (size_t k = 0; k < a.kids.size(); ++k)
+        if (!deep_equal(a.kids[k], b.kids[k])) return false;
+      return true;
+    case T_PTR: return deep_equal(a.kids[0], b.kids[0]);
+    case T_IFACE: return a.s == b.s && deep_equal(a.kids[0], b.kids[0]);
+    case T_MAP: {
+      if (a.kids.size() != b.kids.size()) return false;
+      for (size_t k = 0; k < a.kids.size(); k += 2) {
+        bool found = false;
+        for (size_t m = 0; m < b.kids.size(); m += 2)
+          if (deep_equal(a.kids[k], b.kids[m])) {  // map lookup by key ==
+            if (!deep_equal(a.kids[k + 1], b.kids[m + 1])) return false;
+            found = true;
+            break;
+          }
+        if (!found) return false;
+      }
+      return true;
+    }
+  }
+  return false;
+}
+
+void put_u32(std::string& o, uint32_t v) { o.append(reinterpret_cast<const char*>(&v), 4); }
+
+// Canonical encoding: tag, then content; lengths as u32 little endian; map entries sorted by the
+// canonical bytes of their keys.  Prefix-free per node, hence injective on value trees up to map
+// order: canon(a) == canon(b)  <=>  DeepEqual(a, b)  (floats: -0 is written as +0, NaN is refused
+// because NaN is not DeepEqual to itself — no float is reachable from the compared types).
+void canon(const Node& n, std::string& o) {
+  o.push_back((char)n.tag);
+  switch (n.tag) {
+    case T_BOOL: o.push_back((char)n.i); break;
+    case T_INT: o.push_back((char)n.width); o.append(reinterpret_cast<const char*>(&n.i), 8); break;
+    case T_STRING: case T_BYTES: put_u32(o, (uint32_t)n.s.size()); o += n.s; break;
+    case T_NILBYTES: case T_NILSLICE: case T_NILMAP: case T_NILPTR: case T_NILIFACE: break;
+    case T_SLICE: case T_STRUCT:
+      put_u32(o, (uint32_t)n.kids.size());
+      for (const Node& k : n.kids) canon(k, o);
+      break;
+    case T_PTR: canon(n.kids[0], o); break;
+    case T_IFACE: put_u32(o, (uint32_t)n.s.size()); o += n.s; canon(n.kids[0], o); break;
+    case T_FLOAT: {
+      if (std::isnan(n.f)) throw std::runtime_error("NaN has no canonical encoding (NaN != NaN)");
+      double f = n.f == 0 ? 0.0 : n.f;
+      o.append(reinterpret_cast<const char*>(&f), 8);
+      break;
+    }
+    case T_MAP: {
+      std::vector<std::pair<std::string, std::string>> ents;
+      for (size_t k = 0; k < n.kids.size(); k += 2) {
+        std::string ck, cv;
+        canon(n.kids[k], ck);
+        canon(n.kids[k + 1], cv);
+        ents.emplace_back(std::move(ck), std::move(cv));
+      }
+      std::sort(ents.begin(), ents.end());
+      for (size_t k = 1; k < ents.size(); ++k)
+        if (ents[k].first == ents[k - 1].first) throw std::runtime_error("duplicate map key");
+      put_u32(o, (uint32_t)ents.size());
+      for (auto& e : ents) {
+        o += e.first;
+        o += e.second;
+      }
+      break;
+    }
+  }
+}
+
+thread_local std::string g_err;
+
+Node parse_all(const uint8_t* p, uint64_t n) {
+  Reader r{p, p + n};
+  Node v = parse(r);
+  if (r.p != r.end) throw std::runtime_error("trailing bytes after value");
+  return v;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* oracle_values_error(void) { return g_err.c_str(); }
+
+// 1 equal, 0 different, -1 malformed input.
+int oracle_deep_equal(const uint8_t* a, uint64_t alen, const uint8_t* b, uint64_t blen) {
+  try {
+    return deep_equal(parse_all(a, alen), parse_all(b, blen)) ? 1 : 0;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return -1;
+  }
+}
+
+// Writes the canonical encoding to out (capacity cap); returns its length, or -1 on error, or
+// the needed length when cap is too small (nothing written).
+int64_t oracle_canon(const uint8_t* v, uint64_t vlen, uint8_t* out, uint64_t cap) {
+  try {
+    std::string o;
+    canon(parse_all(v, vlen), o);
+    if (o.size() <= cap && out) memcpy(out, o.data(), o.size());
+    return (int64_t)o.size();
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return -1;
+  }
+}
+
+}  // extern "C"
