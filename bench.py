@@ -228,9 +228,11 @@ def run_ours(args):
     ctx.sync()
     setup_s = time.time() - t_setup
 
+    from nexus_configuration_controller_b200 import multigpu as M
+
     ext = torch.cuda.ExternalStream(ctx.stream, device=local)
     cap_entries = args.gather_cap
-    sendbuf = torch.zeros(cap_entries * 4 + 4, dtype=torch.int32, device=f"cuda:{local}")
+    sendbuf = torch.zeros(M.buffer_words(cap_entries), dtype=torch.int32, device=f"cuda:{local}")
     recvbuf = torch.zeros(world * sendbuf.numel(), dtype=torch.int32, device=f"cuda:{local}") if world > 1 else None
 
     def step():
@@ -238,11 +240,7 @@ def run_ours(args):
         ctx.scan_launch(ca, sas, mode)
         d = ctx.scan_finish()
         if world > 1:
-            d.pack_into(sendbuf.data_ptr(), cap_entries)  # header + entries, enqueued on the scan's stream
-            cur = torch.cuda.current_stream()
-            cur.wait_stream(ext)
-            dist.all_gather_into_tensor(recvbuf, sendbuf)
-            ext.wait_stream(cur)
+            M.gather_diffs(d, sendbuf, recvbuf, ext, cap_entries)
         st = ctx.last_stats()
         d.close()
         return st
@@ -269,7 +267,10 @@ def run_ours(args):
     torch.cuda.synchronize()
     elapsed_ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
+    gathered_total = None
     if dist:
+        parts = M.unpack_gathered(recvbuf.cpu().numpy().view(np.uint32), world, cap_entries)
+        gathered_total = sum(len(e) for _, _, e in parts)
         t = torch.tensor([elapsed_ms], device=f"cuda:{local}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed_ms = float(t.item())
@@ -295,7 +296,7 @@ def run_ours(args):
                 "workload": args.workload, "mode": args.mode, "objects": int(cfg.groups) * (1 + cfg.n_secrets + cfg.n_configmaps),
                 "shards": S, "partition": f"ncd_keyhash(template key) % {world}" if world > 1 else "none",
                 "algorithmic_bytes": algo_all, "l2": "inputs >> 126 MB L2, no flush needed", "setup_s": round(setup_s, 2),
-                "diff_entries": ndiff_all,
+                "diff_entries": ndiff_all, "diff_entries_after_allgather": gathered_total,
             },
             "gb_per_s": algo_all / (ms_per_step / 1e3) / 1e9,
             "roofline": {

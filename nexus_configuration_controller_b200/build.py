@@ -16,6 +16,27 @@ NVCC_FLAGS = [
 ]
 
 
+HOST_OUT = os.path.join(HERE, "lib", "libncdhost.so")
+
+
+def host_sources():
+    return sorted(glob.glob(os.path.join(CSRC, "host", "*.cpp")))
+
+
+def build_host(force: bool = False) -> str:
+    """libncdhost.so: the C++ host layer (canonicaliser, packer, DriftChecker, replay) over libncdrift.so."""
+    deps = host_sources() + glob.glob(os.path.join(HERE, "..", "include", "*.h")) + [OUT]
+    if not force and os.path.exists(HOST_OUT) and all(os.path.getmtime(p) <= os.path.getmtime(HOST_OUT) for p in deps):
+        return HOST_OUT
+    cxx = shutil.which("g++") or "g++"
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-Wextra"] + host_sources() + [
+        "-L" + os.path.dirname(OUT), "-lncdrift", "-Wl,-rpath,$ORIGIN", "-o", HOST_OUT]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + res.stdout + res.stderr)
+    return HOST_OUT
+
+
 def sources():
     return sorted(glob.glob(os.path.join(CSRC, "*.cu")))
 
@@ -29,6 +50,7 @@ def stale() -> bool:
 
 def build_native(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
+        build_host(False)
         return OUT
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
@@ -38,6 +60,7 @@ def build_native(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
+    build_host(True)
     return OUT
 
 

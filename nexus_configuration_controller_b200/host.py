@@ -1,0 +1,143 @@
+"""ctypes binding of libncdhost.so (include/ncdhost.h): the host layer the Go controller would own.
+
+``DriftChecker`` mirrors the Go interface of INTEGRATION.md section 2: fill the cluster images the
+way the reference's fixture fills the informer indexers (controller_test.go:546-576), ``scan()``,
+then ``lookup()`` / ``plan_template()`` / ``plan_workgroup()``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import List, Optional, Sequence, Tuple
+
+from . import _ffi
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "lib", "libncdhost.so")
+VP = C.c_void_p
+CPP = C.POINTER(C.c_char_p)
+PROTOTYPES = {
+    "ncdh_last_error": (C.c_char_p, []),
+    "ncdh_canon": (C.c_int64, [C.c_char_p, C.c_uint64, C.c_char_p, C.c_uint64]),
+    "ncdh_checker_create": (C.c_int, [C.c_int, C.c_uint32, C.c_int, C.POINTER(VP)]),
+    "ncdh_checker_destroy": (None, [VP]),
+    "ncdh_cluster_add": (C.c_int, [VP, C.c_int, C.c_uint32, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64,
+                                   CPP, CPP, C.c_int, CPP, C.c_int, CPP, C.c_int]),
+    "ncdh_cluster_remove": (C.c_int, [VP, C.c_int, C.c_uint32, C.c_char_p, C.c_char_p]),
+    "ncdh_scan": (C.c_int, [VP]),
+    "ncdh_lookup": (C.c_int, [VP, C.c_uint32, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint32)]),
+    "ncdh_plan_template": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
+    "ncdh_plan_workgroup": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
+    "ncdh_last_counts": (C.c_int, [VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+}
+_lib = None
+
+
+def load() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: run __graft_entry__.build()")
+        _ffi.load()  # libncdrift.so first (same directory, also found through the rpath)
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+class HostError(RuntimeError):
+    pass
+
+
+def _err() -> HostError:
+    return HostError(load().ncdh_last_error().decode("utf-8", "replace"))
+
+
+def canon(value_wire: bytes) -> bytes:
+    """Canonical bytes of one Go value (transport form in): what the packer appends to an arena."""
+    lib = load()
+    n = lib.ncdh_canon(value_wire, len(value_wire), None, 0)
+    if n < 0:
+        raise _err()
+    buf = C.create_string_buffer(max(n, 1))
+    lib.ncdh_canon(value_wire, len(value_wire), buf, n)
+    return buf.raw[:n]
+
+
+def _strs(items: Sequence[str]):
+    return (C.c_char_p * max(len(items), 1))(*[s.encode() for s in items])
+
+
+class DriftChecker:
+    def __init__(self, nshards: int, device: int = 0, mode: int = 0):
+        self.lib = load()
+        h = VP()
+        if self.lib.ncdh_checker_create(device, mode, nshards, C.byref(h)) != 0:
+            raise _err()
+        self.h, self.nshards = h, nshards
+
+    def close(self):
+        if self.h:
+            self.lib.ncdh_checker_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def add(self, cluster: int, kind: int, namespace: str, name: str, uid: str, value_wire: bytes,
+            owner_refs: Sequence[Tuple[str, str]] = (), secret_names: Sequence[str] = (), configmap_names: Sequence[str] = ()):
+        rc = self.lib.ncdh_cluster_add(
+            self.h, cluster, kind, namespace.encode(), name.encode(), uid.encode(), value_wire, len(value_wire),
+            _strs([k for k, _ in owner_refs]), _strs([u for _, u in owner_refs]), len(owner_refs),
+            _strs(list(secret_names)), len(secret_names), _strs(list(configmap_names)), len(configmap_names))
+        if rc != 0:
+            raise _err()
+
+    def remove(self, cluster: int, kind: int, namespace: str, name: str) -> bool:
+        return self.lib.ncdh_cluster_remove(self.h, cluster, kind, namespace.encode(), name.encode()) == 0
+
+    def scan(self):
+        if self.lib.ncdh_scan(self.h) != 0:
+            raise _err()
+
+    def lookup(self, kind: int, namespace: str, name: str, dep: int, shard: int) -> Optional[int]:
+        code = C.c_uint32()
+        rc = self.lib.ncdh_lookup(self.h, kind, namespace.encode(), name.encode(), dep, shard, C.byref(code))
+        if rc < 0:
+            raise _err()
+        return None if rc == 1 else code.value
+
+    def _plan(self, fn, namespace: str, name: str):
+        n = fn(self.h, namespace.encode(), name.encode(), None, 0)
+        if n < 0:
+            raise _err()
+        buf = C.create_string_buffer(max(n, 1))
+        fn(self.h, namespace.encode(), name.encode(), buf, n)
+        nexus = [[] for _ in range(self.nshards)]
+        kube = [[] for _ in range(self.nshards)]
+        error = None
+        for line in buf.raw[:n].decode().splitlines():
+            parts = line.split("\t")
+            if parts[0] == "error":
+                error = parts[1]
+            else:
+                (nexus if parts[1] == "nexus" else kube)[int(parts[0])].append([parts[2], parts[3], parts[4]])
+        return nexus, kube, error
+
+    def plan_template(self, namespace: str, name: str):
+        """(nexus actions per shard, kube actions per shard, error or None): the shard writes
+        templateSyncHandler would issue, in order."""
+        return self._plan(self.lib.ncdh_plan_template, namespace, name)
+
+    def plan_workgroup(self, namespace: str, name: str):
+        return self._plan(self.lib.ncdh_plan_workgroup, namespace, name)
+
+    def counts(self) -> Tuple[int, int]:
+        a, b = C.c_uint64(), C.c_uint64()
+        if self.lib.ncdh_last_counts(self.h, C.byref(a), C.byref(b)) != 0:
+            raise _err()
+        return a.value, b.value

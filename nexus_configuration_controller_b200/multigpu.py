@@ -1,0 +1,70 @@
+"""Multi-GPU layout of the drift check: partition by object-key hash, one all-gather of diff lists.
+
+One process per GPU.  A template (with its dependents) belongs to rank
+``ncd_keyhash(TEMPLATE, "namespace/name") % world``; a workgroup likewise with its own kind.  Every
+rank holds the controller copy and all shard copies of its key range, so join and compare need no
+cross-GPU traffic.  After the scan each rank packs ``[n, nshards, rows, 0 | n x ncd_entry]`` into a
+fixed-size device buffer (``ncd_diff_pack``) and ONE ``all_gather_into_tensor`` hands every rank
+every list.  PyTorch is only the plumbing here (process group, NCCL / gloo, streams).
+"""
+from __future__ import annotations
+
+from typing import List, Tuple
+
+import numpy as np
+
+from . import _ffi
+
+HEADER_WORDS = 4
+ENTRY_WORDS = 4
+
+
+def owner_rank(kind: int, key: str, world: int) -> int:
+    """Rank that owns an object key (host side of the partition; same hash as the device's)."""
+    k = key.encode()
+    return int(_ffi.load().ncd_keyhash(kind, k, len(k)) % world) if world > 1 else 0
+
+
+def buffer_words(cap_entries: int) -> int:
+    return HEADER_WORDS + ENTRY_WORDS * cap_entries
+
+
+def pack_host(entries: np.ndarray, nshards: int, rows: int, cap_entries: int) -> np.ndarray:
+    """Host-side twin of ncd_diff_pack (used by the CPU tests of the exchange)."""
+    n = len(entries)
+    if n > cap_entries:
+        raise ValueError(f"{n} entries exceed the exchange capacity {cap_entries}")
+    buf = np.zeros(buffer_words(cap_entries), dtype=np.uint32)
+    buf[:HEADER_WORDS] = [n, nshards, rows & 0xFFFFFFFF, 0]
+    buf[HEADER_WORDS : HEADER_WORDS + ENTRY_WORDS * n] = np.asarray(entries, dtype=np.uint32).reshape(-1)
+    return buf
+
+
+def unpack_gathered(gathered: np.ndarray, world: int, cap_entries: int) -> List[Tuple[int, int, np.ndarray]]:
+    """Splits the all-gathered buffer into per-rank (nshards, rows, entries[n, 4])."""
+    words = buffer_words(cap_entries)
+    g = np.asarray(gathered, dtype=np.uint32).reshape(world, words)
+    out = []
+    for r in range(world):
+        n = int(g[r, 0])
+        if n > cap_entries:
+            raise ValueError(f"rank {r} reports {n} entries, capacity is {cap_entries}")
+        out.append((int(g[r, 1]), int(g[r, 2]), g[r, HEADER_WORDS : HEADER_WORDS + ENTRY_WORDS * n].reshape(n, ENTRY_WORDS).copy()))
+    return out
+
+
+def gather_diffs(diff, sendbuf, recvbuf, scan_stream, cap_entries: int, group=None):
+    """Enqueues pack + all-gather after the scan that produced `diff`; returns nothing (device work).
+
+    sendbuf / recvbuf: int32 CUDA tensors of buffer_words(cap) and world * buffer_words(cap) words.
+    scan_stream: torch.cuda.ExternalStream wrapping the context's stream.  The collective runs on
+    torch's current stream, ordered after the scan and before the next one.
+    """
+    import torch
+    import torch.distributed as dist
+
+    diff.pack_into(sendbuf.data_ptr(), cap_entries)
+    cur = torch.cuda.current_stream()
+    cur.wait_stream(scan_stream)
+    dist.all_gather_into_tensor(recvbuf, sendbuf, group=group)
+    scan_stream.wait_stream(cur)
