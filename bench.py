@@ -258,11 +258,14 @@ def run_ours(args):
     torch.cuda.synchronize()
     e0.record(ext)
     cmp_ms, tot_ms, launches = [], [], 0
+    phases = {"join_ms": 0.0, "hash_ms": 0.0, "compare_ms": 0.0, "classify_ms": 0.0}
     for _ in range(args.steps):
         st = step()
         cmp_ms.append(st.compare_ms if mode == A.MODE_DIRECT else st.hash_ms)
         tot_ms.append(st.total_ms)
         launches += st.launches
+        for k in phases:
+            phases[k] += getattr(st, k) / args.steps
     e1.record(ext)
     torch.cuda.synchronize()
     elapsed_ms = e0.elapsed_time(e1)
@@ -303,6 +306,7 @@ def run_ours(args):
                 "bound": "hbm", "kernel": "k_compare" if mode == A.MODE_DIRECT else "hash kernels",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "traffic": None, "kernel_ms": kern_ms, "scan_ms": sum(tot_ms) / len(tot_ms),
+                "phases_ms": {k: round(v, 4) for k, v in phases.items()},
             },
             "gpu_launches": int(launches_all),
             "clocks": clocks,

@@ -191,7 +191,7 @@ extern "C" void ncd_arena_destroy(ncd_arena* a) {
     if (d) cudaFree(d);
     if (h) cudaFreeHost(h);
   }
-  void* idx[] = {a->keyhash, a->table,     a->row_start,  a->row_obj, a->row_dep, a->row_cidx,
+  void* idx[] = {a->meta,    a->table,     a->row_start,  a->row_obj, a->row_dep, a->row_cidx,
                  a->tile_obj, a->tile_chunk, a->tile_start, a->h64,     a->sha,     a->h64_parts};
   for (void* p : idx)
     if (p) cudaFree(p);

@@ -20,6 +20,22 @@ enum : uint8_t { DV_EQUAL = 0, DV_DIFF = 1, DV_NOTFOUND = 2 };
 constexpr uint32_t NCD_TILE_BYTES = 4096;
 constexpr uint32_t NCD_TILE_VECS = NCD_TILE_BYTES / 16;
 
+// Everything a probe needs about one object, in one 64-byte line: the join reads the table
+// slot, then this, and nothing else unless the key is longer than NCD_KEY_INLINE bytes.
+constexpr uint32_t NCD_KEY_INLINE = 36;
+struct __align__(16) ObjMeta {
+  uint64_t keyhash;
+  uint64_t rec_off;
+  uint32_t rec_len;
+  uint32_t key_off;   // in aux (whole key)
+  uint16_t key_len;
+  uint8_t kind;
+  uint8_t pad;
+  uint8_t key[NCD_KEY_INLINE];  // first bytes of the key, zero padded
+};
+static_assert(sizeof(ObjMeta) == 64, "ObjMeta must be one 64-byte line");
+#define NCD_TABLE_EMPTY 0xFFFFFFFFFFFFFFFFull
+
 // Device-visible description of a committed arena (all pointers are device pointers).
 struct DevArena {
   const uint8_t* payload;
@@ -40,8 +56,8 @@ struct DevArena {
   const uint32_t* dep_key_len;
   const uint8_t* aux;
   // index built by commit
-  const uint64_t* keyhash;  // [nobj]
-  const uint32_t* table;    // open addressing, NCD_NOTFOUND = empty
+  const ObjMeta* meta;      // [nobj]
+  const uint64_t* table;    // open addressing; slot = (keyhash >> 32) << 32 | index, all ones = empty
   uint32_t table_mask;
   uint32_t nobj;
   // digests, filled by the hash kernels
@@ -80,8 +96,8 @@ struct ncd_arena {
   ncd_arena_view h;  // pinned host arrays (HOST_PINNED only)
   ncd_arena_view d;  // device arrays
   // index (device)
-  uint64_t* keyhash;
-  uint32_t* table;
+  ObjMeta* meta;
+  uint64_t* table;
   uint32_t table_size;
   uint32_t dup_keys;
   // controller-side lists (device), built by commit
@@ -175,17 +191,57 @@ __device__ __forceinline__ bool ncd_bytes_equal(const uint8_t* a, const uint8_t*
 }
 
 // lister.Get on the GPU: exact ("kind", "namespace/name") lookup in an arena's table.
-// Linear probing; a slot matches when key hash, kind, key length and key bytes all match.
+// Linear probing.  A slot carries the upper half of the key hash, so almost every foreign slot
+// is rejected without touching the object's line; a candidate matches when hash, kind, key
+// length and every key byte match (inline part first, the rest from aux).
 __device__ __forceinline__ uint32_t ncd_probe(const DevArena& t, uint32_t kind, const uint8_t* key,
                                               uint32_t key_len, uint64_t hash) {
   if (t.nobj == 0) return NCD_NOTFOUND;
   uint32_t slot = (uint32_t)hash & t.table_mask;
+  const uint32_t hi = (uint32_t)(hash >> 32);
   for (;;) {
-    uint32_t idx = t.table[slot];
-    if (idx == NCD_NOTFOUND) return NCD_NOTFOUND;
-    if (t.keyhash[idx] == hash && t.kind[idx] == kind && t.key_len[idx] == key_len &&
-        ncd_bytes_equal(t.aux + t.key_off[idx], key, key_len))
-      return idx;
+    const uint64_t e = t.table[slot];
+    if (e == NCD_TABLE_EMPTY) return NCD_NOTFOUND;
+    if ((uint32_t)(e >> 32) == hi) {
+      const uint32_t idx = (uint32_t)e;
+      const ObjMeta& m = t.meta[idx];
+      if (m.keyhash == hash && m.kind == kind && m.key_len == key_len) {
+        const uint32_t inl = key_len < NCD_KEY_INLINE ? key_len : NCD_KEY_INLINE;
+        if (ncd_bytes_equal(m.key, key, inl) &&
+            (key_len <= NCD_KEY_INLINE ||
+             ncd_bytes_equal(t.aux + m.key_off + NCD_KEY_INLINE, key + NCD_KEY_INLINE, key_len - NCD_KEY_INLINE)))
+          return idx;
+      }
+    }
+    slot = (slot + 1) & t.table_mask;
+  }
+}
+
+// Same lookup when the key is itself an object's line (the join: controller object -> shard).
+__device__ __forceinline__ uint32_t ncd_probe_meta(const DevArena& t, const ObjMeta& q, const uint8_t* q_aux) {
+  if (t.nobj == 0) return NCD_NOTFOUND;
+  uint32_t slot = (uint32_t)q.keyhash & t.table_mask;
+  const uint32_t hi = (uint32_t)(q.keyhash >> 32);
+  const uint4* qw = reinterpret_cast<const uint4*>(&q);
+  for (;;) {
+    const uint64_t e = t.table[slot];
+    if (e == NCD_TABLE_EMPTY) return NCD_NOTFOUND;
+    if ((uint32_t)(e >> 32) == hi) {
+      const uint32_t idx = (uint32_t)e;
+      const uint4* mw = reinterpret_cast<const uint4*>(&t.meta[idx]);
+      // words 0-1: keyhash; word 6: key_len | kind | pad; words 7-15: inline key (zero padded)
+      const uint4 m0 = mw[0], m1 = mw[1], m2 = mw[2], m3 = mw[3];
+      const uint4 q0 = qw[0], q1 = qw[1], q2 = qw[2], q3 = qw[3];
+      const uint32_t diff = (m0.x ^ q0.x) | (m0.y ^ q0.y) | ((m1.z ^ q1.z) & 0x00FFFFFFu) | (m1.w ^ q1.w) |
+                            (m2.x ^ q2.x) | (m2.y ^ q2.y) | (m2.z ^ q2.z) | (m2.w ^ q2.w) |
+                            (m3.x ^ q3.x) | (m3.y ^ q3.y) | (m3.z ^ q3.z) | (m3.w ^ q3.w);
+      if (diff == 0) {
+        const uint32_t klen = q.key_len;
+        if (klen <= NCD_KEY_INLINE ||
+            ncd_bytes_equal(t.aux + m1.y + NCD_KEY_INLINE, q_aux + q.key_off + NCD_KEY_INLINE, klen - NCD_KEY_INLINE))
+          return idx;
+      }
+    }
     slot = (slot + 1) & t.table_mask;
   }
 }

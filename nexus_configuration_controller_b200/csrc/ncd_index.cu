@@ -1,5 +1,6 @@
 // ncd_index.cu — what ncd_arena_commit builds on the GPU for a freshly uploaded arena:
-//   key hashes + the open-addressing table that answers lister.Get
+//   one 64-byte line per object (key hash, record offset/length, inline key) + the
+//   open-addressing table that answers lister.Get
 //     (reference: client-go indexer behind controller.go:507,516,569,578,702,722,766,792),
 //   the row list (one row per template, per dependent reference, per workgroup;
 //     reference loop structure controller.go:790-831 with :505,:567 for the dependents),
@@ -121,30 +122,48 @@ int ncd_exclusive_scan_u64(ncd_ctx* ctx, const uint32_t* in, uint64_t* out, uint
   return exclusive_scan<uint64_t>(ctx, in, out, n, total_out_dev);
 }
 
-// ------------------------------------------------------------------ key hashes + table
-__global__ void k_keyhash(DevArena a, uint64_t* __restrict__ keyhash) {
+// ------------------------------------------------------------------ object lines + table
+__global__ void k_meta_build(DevArena a, ObjMeta* __restrict__ meta) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.nobj) return;
-  keyhash[i] = ncd_keyhash_impl(a.kind[i], a.aux + a.key_off[i], a.key_len[i]);
+  const uint8_t* key = a.aux + a.key_off[i];
+  const uint32_t klen = a.key_len[i];
+  ObjMeta m;
+  m.keyhash = ncd_keyhash_impl(a.kind[i], key, klen);
+  m.rec_off = a.rec_off[i];
+  m.rec_len = a.rec_len[i];
+  m.key_off = a.key_off[i];
+  m.key_len = (uint16_t)klen;
+  m.kind = a.kind[i];
+  m.pad = 0;
+#pragma unroll
+  for (uint32_t b = 0; b < NCD_KEY_INLINE; ++b) m.key[b] = b < klen ? key[b] : 0;
+  const uint4* src = reinterpret_cast<const uint4*>(&m);
+  uint4* dst = reinterpret_cast<uint4*>(&meta[i]);
+#pragma unroll
+  for (int w = 0; w < 4; ++w) dst[w] = src[w];
 }
 
 // Inserts every object; on a duplicate ("kind", key) the lowest index wins, as a store keyed
 // by namespace/name would have kept one object only.
-__global__ void k_table_build(DevArena a, uint32_t* __restrict__ table, uint32_t* __restrict__ dup_count) {
+__global__ void k_table_build(DevArena a, unsigned long long* __restrict__ table, uint32_t* __restrict__ dup_count) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.nobj) return;
-  const uint64_t h = a.keyhash[i];
-  const uint32_t kind = a.kind[i], klen = a.key_len[i];
-  const uint8_t* key = a.aux + a.key_off[i];
+  const ObjMeta& me = a.meta[i];
+  const uint64_t h = me.keyhash;
+  const unsigned long long mine = ((h >> 32) << 32) | i;
   uint32_t slot = (uint32_t)h & a.table_mask;
   for (;;) {
-    uint32_t prev = atomicCAS(&table[slot], NCD_NOTFOUND, i);
-    if (prev == NCD_NOTFOUND) return;
-    if (a.keyhash[prev] == h && a.kind[prev] == kind && a.key_len[prev] == klen &&
-        ncd_bytes_equal(a.aux + a.key_off[prev], key, klen)) {
-      atomicMin(&table[slot], i);
-      atomicAdd(dup_count, 1u);
-      return;
+    const unsigned long long prev = atomicCAS(&table[slot], NCD_TABLE_EMPTY, mine);
+    if (prev == NCD_TABLE_EMPTY) return;
+    if ((prev >> 32) == (h >> 32)) {
+      const ObjMeta& o = a.meta[(uint32_t)prev];
+      if (o.keyhash == h && o.kind == me.kind && o.key_len == me.key_len &&
+          ncd_bytes_equal(a.aux + o.key_off, a.aux + me.key_off, me.key_len)) {
+        atomicMin(&table[slot], mine);  // same upper half: orders by index
+        atomicAdd(dup_count, 1u);
+        return;
+      }
     }
     slot = (slot + 1) & a.table_mask;
   }
@@ -220,7 +239,7 @@ __global__ void k_validate(DevArena a, uint64_t payload_bytes, uint64_t aux_byte
   if (i >= a.nobj) return;
   bool ok = (a.rec_off[i] & 15) == 0 && a.rec_off[i] + a.rec_len[i] <= payload_bytes;
   ok = ok && a.kind[i] <= NCD_KIND_CONFIGMAP;
-  ok = ok && (uint64_t)a.key_off[i] + a.key_len[i] <= aux_bytes;
+  ok = ok && (uint64_t)a.key_off[i] + a.key_len[i] <= aux_bytes && a.key_len[i] <= 0xFFFFu;
   ok = ok && (uint64_t)a.uid_off[i] + a.uid_len[i] <= aux_bytes;
   ok = ok && a.own_start[i] <= a.own_start[i + 1] && a.own_start[i + 1] <= nowner;
   ok = ok && a.dep_start[i] <= a.dep_start[i + 1] && a.dep_start[i + 1] <= ndep;
@@ -254,7 +273,7 @@ void ncd_fill_dev_arena(const ncd_arena* a, DevArena* o) {
   o->dep_key_off = d.dep_key_off;
   o->dep_key_len = d.dep_key_len;
   o->aux = d.aux;
-  o->keyhash = a->keyhash;
+  o->meta = a->meta;
   o->table = a->table;
   o->table_mask = a->table_size ? a->table_size - 1 : 0;
   o->nobj = (uint32_t)a->nobj;
@@ -285,12 +304,12 @@ int ncd_build_index(ncd_arena* a) {
   const unsigned blocks = (n + 255) / 256;
 
   a->h64_valid = a->sha_valid = false;
-  NCD_TRY(dev_realloc(&a->keyhash, n));
+  NCD_TRY(dev_realloc(&a->meta, n));
   uint32_t tsize = 16;
   while ((uint64_t)tsize < 2ull * n) tsize <<= 1;
   a->table_size = tsize;
   NCD_TRY(dev_realloc(&a->table, tsize));
-  NCD_CUDA(cudaMemsetAsync(a->table, 0xFF, (size_t)tsize * 4, st));
+  NCD_CUDA(cudaMemsetAsync(a->table, 0xFF, (size_t)tsize * 8, st));
 
   // [0] bad records, [1] duplicate keys, [2] rows, [3] tiles, [4..5] u64 sum of rec_len
   uint32_t* d_small = nullptr;
@@ -316,8 +335,8 @@ int ncd_build_index(ncd_arena* a) {
                     "16-byte aligned, or an unknown kind", bad);
       return NCD_E_INVALID;
     }
-    k_keyhash<<<blocks, 256, 0, st>>>(da, a->keyhash);
-    k_table_build<<<blocks, 256, 0, st>>>(da, a->table, d_small + 1);
+    k_meta_build<<<blocks, 256, 0, st>>>(da, a->meta);
+    k_table_build<<<blocks, 256, 0, st>>>(da, (unsigned long long*)a->table, d_small + 1);
     k_row_counts<<<blocks, 256, 0, st>>>(da, counts);
   }
   NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->row_start, n, d_small + 2));

@@ -21,13 +21,13 @@ k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t 
   if (p >= (uint64_t)ctrl.nobj * S) return;
   const uint32_t c = (uint32_t)(p / S), s = (uint32_t)(p % S);
   const DevArena& sh = shards[s];
-  const uint32_t idx =
-      ncd_probe(sh, ctrl.kind[c], ctrl.aux + ctrl.key_off[c], ctrl.key_len[c], ctrl.keyhash[c]);
+  const ObjMeta& q = ctrl.meta[c];
+  const uint32_t idx = ncd_probe_meta(sh, q, ctrl.aux);
   uint8_t v;
   uint64_t off = NCD_NO_OFF;
   if (idx == NCD_NOTFOUND) {
     v = DV_NOTFOUND;
-  } else if (sh.rec_len[idx] != ctrl.rec_len[c]) {
+  } else if (sh.meta[idx].rec_len != q.rec_len) {
     v = DV_DIFF;  // the encoding is injective: different lengths cannot be DeepEqual
   } else {
     const uint32_t hm = mode & 0xff;
@@ -42,7 +42,7 @@ k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t 
                      (x1.y ^ y1.y) | (x1.z ^ y1.z) | (x1.w ^ y1.w)) == 0;
     }
     v = maybe_equal ? DV_EQUAL : DV_DIFF;
-    if (maybe_equal && (hm == NCD_MODE_DIRECT || (mode & NCD_MODE_CONFIRM))) off = sh.rec_off[idx];
+    if (maybe_equal && (hm == NCD_MODE_DIRECT || (mode & NCD_MODE_CONFIRM))) off = sh.meta[idx].rec_off;
   }
   sh_idx[p] = idx;
   sh_off[p] = off;
