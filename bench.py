@@ -58,6 +58,12 @@ def make_cfg(name: str, groups: int | None = None, part_mod: int = 0, part_rem: 
     c.seed, c.drift_seed = 0xC0FFEE ^ cfg_id, 0xD21F7 ^ cfg_id
     c.p_flip_ppm, c.p_missing_ppm, c.p_len_ppm, c.p_owner_ppm, c.p_rogue_ppm = flip, missing, 0, 0, 0
     c.part_mod, c.part_rem, c.shuffle = part_mod, part_rem, 1
+    # experiment knobs (never set by the driver's default invocation)
+    if os.environ.get("NCD_BENCH_SHUFFLE"):
+        c.shuffle = int(os.environ["NCD_BENCH_SHUFFLE"])
+    if os.environ.get("NCD_BENCH_LEN"):
+        lo, hi = [int(x) for x in os.environ["NCD_BENCH_LEN"].split(",")]
+        c.tmpl_len_lo, c.tmpl_len_hi, c.dep_len_lo, c.dep_len_hi = lo, hi, lo, hi
     return c, shards
 
 
@@ -218,7 +224,8 @@ def run_ours(args):
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    mode = {"direct": A.MODE_DIRECT, "hash64": A.MODE_HASH64, "sha256": A.MODE_SHA256}[args.mode]
+    # hash modes re-hash every copy in every step (digests are otherwise cached per committed arena)
+    mode = {"direct": A.MODE_DIRECT, "hash64": A.MODE_HASH64 | A.MODE_REHASH, "sha256": A.MODE_SHA256 | A.MODE_REHASH}[args.mode]
 
     ctx = Context(local)
     cfg, S = make_cfg(args.workload, groups=args.groups, part_mod=world if world > 1 else 0, part_rem=rank)
@@ -303,7 +310,7 @@ def run_ours(args):
             },
             "gb_per_s": algo_all / (ms_per_step / 1e3) / 1e9,
             "roofline": {
-                "bound": "hbm", "kernel": "k_compare" if mode == A.MODE_DIRECT else "hash kernels",
+                "bound": "hbm", "kernel": "k_compare / k_compare_grouped" if mode == A.MODE_DIRECT else ("k_h64_tiles" if args.mode == "hash64" else "k_sha256"),
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "traffic": None, "kernel_ms": kern_ms, "scan_ms": sum(tot_ms) / len(tot_ms),
                 "phases_ms": {k: round(v, 4) for k, v in phases.items()},

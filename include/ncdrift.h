@@ -65,7 +65,9 @@ enum {
   NCD_MODE_DIRECT = 0, /* byte compare of the canonical records: exact (default)                  */
   NCD_MODE_HASH64 = 1, /* striped 64-bit hash of every record, verdict from hash equality          */
   NCD_MODE_SHA256 = 2, /* FIPS 180-4 SHA-256 of every record, verdict from digest equality         */
-  NCD_MODE_CONFIRM = 0x100 /* OR with a hash mode: hash-equal pairs are re-checked by byte compare */
+  NCD_MODE_CONFIRM = 0x100, /* OR with a hash mode: hash-equal pairs are re-checked by byte compare */
+  NCD_MODE_REHASH = 0x200   /* OR with a hash mode: recompute every digest (by default digests are
+                               kept with a committed arena and reused by later scans)              */
 };
 
 typedef struct ncd_ctx ncd_ctx;

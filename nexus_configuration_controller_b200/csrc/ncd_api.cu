@@ -51,6 +51,10 @@ extern "C" int ncd_init(int device, ncd_ctx** out) {
   if (!ctx) return NCD_E_NOMEM;
   ctx->device = device;
   ctx->sm_count = prop.multiProcessorCount;
+  ctx->compare_variant = -1;  // -1: chosen per scan from the mean tile fill
+  ctx->compare_ctas_per_sm = 8;
+  if (const char* v = getenv("NCD_COMPARE_VARIANT")) ctx->compare_variant = atoi(v);
+  if (const char* v = getenv("NCD_COMPARE_CTAS")) ctx->compare_ctas_per_sm = atoi(v) > 0 ? atoi(v) : 8;
   NCD_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   for (int i = 0; i < 8; ++i) NCD_CUDA(cudaEventCreate(&ctx->ev[i]));
   NCD_CUDA(cudaMalloc((void**)&ctx->d_counters, 8 * sizeof(uint64_t)));
@@ -192,7 +196,8 @@ extern "C" void ncd_arena_destroy(ncd_arena* a) {
     if (h) cudaFreeHost(h);
   }
   void* idx[] = {a->meta,    a->table,     a->row_start,  a->row_obj, a->row_dep, a->row_cidx,
-                 a->tile_obj, a->tile_chunk, a->tile_start, a->h64,     a->sha,     a->h64_parts};
+                 a->tile_obj, a->tile_chunk, a->tile_start, a->h64,     a->sha,     a->h64_parts,
+                 a->ctile_obj, a->ctile_chunk, a->ctile_start};
   for (void* p : idx)
     if (p) cudaFree(p);
   free(a);

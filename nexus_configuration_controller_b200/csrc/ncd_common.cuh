@@ -20,6 +20,13 @@ enum : uint8_t { DV_EQUAL = 0, DV_DIFF = 1, DV_NOTFOUND = 2 };
 constexpr uint32_t NCD_TILE_BYTES = 4096;
 constexpr uint32_t NCD_TILE_VECS = NCD_TILE_BYTES / 16;
 
+// Compare tiles: the same 4 KB cut, except that a short remainder (< 2 KB) is merged into the
+// tile before it, so no warp is sent off for a few hundred bytes: a record of 8704 bytes is
+// tiles of 4096 + 4608, not 4096 + 4096 + 512.  Tiles of a multi-tile record are 2049..6144 bytes.
+__host__ __device__ __forceinline__ uint32_t ncd_ctiles_of(uint32_t len) {
+  return len <= 6144u ? (len ? 1u : 0u) : (uint32_t)(((uint64_t)len + 2047u) >> 12);
+}
+
 // Everything a probe needs about one object, in one 64-byte line: the join reads the table
 // slot, then this, and nothing else unless the key is longer than NCD_KEY_INLINE bytes.
 constexpr uint32_t NCD_KEY_INLINE = 36;
@@ -68,6 +75,8 @@ struct DevArena {
 struct ncd_ctx {
   int device;
   int sm_count;
+  int compare_variant;      // -1 = pick per scan, 0 = per-shard loop, 1/2/4 = grouped with CH vectors per lane
+  int compare_ctas_per_sm;  // grid = sm_count * this
   cudaStream_t stream;
   cudaEvent_t ev[8];
   // scratch of the scan, grown on demand and kept
@@ -110,6 +119,10 @@ struct ncd_arena {
   uint32_t* tile_obj;   // [ntiles]
   uint32_t* tile_chunk; // [ntiles]
   uint32_t* tile_start; // [nobj+1]
+  uint64_t nctiles;     // compare tiles (short remainders merged, ncd_ctiles_of)
+  uint32_t* ctile_obj;
+  uint32_t* ctile_chunk;
+  uint32_t* ctile_start;
   // digests (device), lazily allocated
   uint64_t* h64;
   uint32_t* sha;

@@ -219,6 +219,11 @@ __global__ void k_tile_counts(DevArena a, uint32_t* __restrict__ counts,
   if ((threadIdx.x & 31) == 0 && len) atomicAdd(len_sum, len);
 }
 
+__global__ void k_ctile_counts(DevArena a, uint32_t* __restrict__ counts) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < a.nobj) counts[i] = ncd_ctiles_of(a.rec_len[i]);
+}
+
 // One warp per object; lanes write the object's tiles strided.
 __global__ void k_tiles_fill(uint32_t nobj, const uint32_t* __restrict__ tile_start,
                              uint32_t* __restrict__ tile_obj, uint32_t* __restrict__ tile_chunk) {
@@ -311,7 +316,7 @@ int ncd_build_index(ncd_arena* a) {
   NCD_TRY(dev_realloc(&a->table, tsize));
   NCD_CUDA(cudaMemsetAsync(a->table, 0xFF, (size_t)tsize * 8, st));
 
-  // [0] bad records, [1] duplicate keys, [2] rows, [3] tiles, [4..5] u64 sum of rec_len
+  // [0] bad records, [1] duplicate keys, [2] rows, [3] tiles, [4..5] u64 sum of rec_len, [6] compare tiles
   uint32_t* d_small = nullptr;
   NCD_CUDA(cudaMallocAsync((void**)&d_small, 8 * sizeof(uint32_t), st));
   NCD_CUDA(cudaMemsetAsync(d_small, 0, 8 * sizeof(uint32_t), st));
@@ -322,6 +327,7 @@ int ncd_build_index(ncd_arena* a) {
   NCD_CUDA(cudaMallocAsync((void**)&counts, ((size_t)n + 1) * 4, st));
   NCD_TRY(dev_realloc(&a->row_start, (uint64_t)n + 1));
   NCD_TRY(dev_realloc(&a->tile_start, (uint64_t)n + 1));
+  NCD_TRY(dev_realloc(&a->ctile_start, (uint64_t)n + 1));
 
   if (n) {
     k_validate<<<blocks, 256, 0, st>>>(da, a->payload_bytes, a->aux_bytes, a->nowner, a->ndep, d_small);
@@ -342,6 +348,8 @@ int ncd_build_index(ncd_arena* a) {
   NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->row_start, n, d_small + 2));
   if (n) k_tile_counts<<<blocks, 256, 0, st>>>(da, counts, (unsigned long long*)(d_small + 4));
   NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->tile_start, n, d_small + 3));
+  if (n) k_ctile_counts<<<blocks, 256, 0, st>>>(da, counts);
+  NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->ctile_start, n, d_small + 6));
   uint32_t h_small[8];
   NCD_CUDA(cudaMemcpyAsync(h_small, d_small, sizeof(h_small), cudaMemcpyDeviceToHost, st));
   NCD_CUDA(cudaStreamSynchronize(st));
@@ -349,16 +357,20 @@ int ncd_build_index(ncd_arena* a) {
   memcpy(&a->len_sum, &h_small[4], 8);
   a->nrows = h_small[2];
   a->ntiles = h_small[3];
+  a->nctiles = h_small[6];
 
   NCD_TRY(dev_realloc(&a->row_obj, a->nrows));
   NCD_TRY(dev_realloc(&a->row_dep, a->nrows));
   NCD_TRY(dev_realloc(&a->row_cidx, a->nrows));
   NCD_TRY(dev_realloc(&a->tile_obj, a->ntiles));
   NCD_TRY(dev_realloc(&a->tile_chunk, a->ntiles));
+  NCD_TRY(dev_realloc(&a->ctile_obj, a->nctiles));
+  NCD_TRY(dev_realloc(&a->ctile_chunk, a->nctiles));
   if (n) {
     k_rows_fill<<<blocks, 256, 0, st>>>(da, a->row_start, a->row_obj, a->row_dep, a->row_cidx);
     const unsigned wblocks = (unsigned)(((uint64_t)n * 32 + 255) / 256);
     k_tiles_fill<<<wblocks, 256, 0, st>>>(n, a->tile_start, a->tile_obj, a->tile_chunk);
+    k_tiles_fill<<<wblocks, 256, 0, st>>>(n, a->ctile_start, a->ctile_obj, a->ctile_chunk);
   }
   NCD_CUDA(cudaFreeAsync(counts, st));
   NCD_CUDA(cudaFreeAsync(d_small, st));

@@ -126,6 +126,89 @@ k_compare(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
   }
 }
 
+// ------------------------------------------------------------------ k_compare_grouped
+// Same work item (one warp per 4 KB controller tile) but the tile is walked in chunks of CH
+// vectors per lane and, for every chunk, the loads of the controller copy and of up to G shard
+// copies are all issued before any of them is used: (1 + G) * CH independent 16-byte loads in
+// flight per lane and one memory latency per chunk, instead of one latency per (tile, shard).
+// That is what small records need: their tiles are ragged, so a warp has few bytes per
+// latency unless it covers several copies at once.
+constexpr int CMP_G = 8;
+
+template <int CH>
+__global__ void __launch_bounds__(256)
+k_compare_grouped(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
+                  const uint32_t* __restrict__ tile_obj, const uint32_t* __restrict__ tile_chunk,
+                  uint64_t ntiles, const uint64_t* __restrict__ sh_off, uint8_t* __restrict__ dv,
+                  uint32_t* __restrict__ counters, uint32_t count_collisions) {
+  extern __shared__ const uint8_t* s_payload[];  // payload base of every shard
+  for (uint32_t s = threadIdx.x; s < S; s += blockDim.x) s_payload[s] = shards[s].payload;
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t t = warp0; t < ntiles; t += nwarps) {
+    const uint32_t c = tile_obj[t], chunk = tile_chunk[t];
+    const uint32_t len = ctrl.rec_len[c];
+    const uint64_t toff = (uint64_t)chunk * NCD_TILE_BYTES;
+    // the last compare tile of a record runs to its end (2049..6144 bytes, ncd_ctiles_of)
+    const uint32_t nbytes = chunk + 1 == ncd_ctiles_of(len) ? len - (uint32_t)toff : NCD_TILE_BYTES;
+    const uint32_t nvec = (nbytes + 15) >> 4;
+    const uint32_t tail = nbytes & 15;
+    const uint4* cp = reinterpret_cast<const uint4*>(ctrl.payload + ctrl.rec_off[c] + toff);
+    for (uint32_t s0 = 0; s0 < S; s0 += CMP_G) {
+      const uint64_t my_off = (lane < CMP_G && s0 + lane < S) ? sh_off[(uint64_t)c * S + s0 + lane] : NCD_NO_OFF;
+      const uint4* sp[CMP_G];
+      uint32_t x[CMP_G];
+#pragma unroll
+      for (int k = 0; k < CMP_G; ++k) {
+        const uint64_t off = __shfl_sync(0xffffffffu, my_off, k);
+        sp[k] = off == NCD_NO_OFF ? nullptr
+                                  : reinterpret_cast<const uint4*>(s_payload[s0 + k] + off + toff);
+        x[k] = 0;
+      }
+      if (__all_sync(0xffffffffu, my_off == NCD_NO_OFF)) continue;  // nothing to read in this group
+      for (uint32_t v0 = 0; v0 < nvec; v0 += 32 * CH) {
+        uint4 a[CH], b[CMP_G][CH];
+#pragma unroll
+        for (int u = 0; u < CH; ++u) {
+          const uint32_t v = v0 + lane + 32 * u;
+          a[u] = v < nvec ? ncd_ldg_stream(cp + v) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int k = 0; k < CMP_G; ++k)
+#pragma unroll
+          for (int u = 0; u < CH; ++u) {
+            const uint32_t v = v0 + lane + 32 * u;
+            b[k][u] = (sp[k] != nullptr && v < nvec) ? ncd_ldg_stream(sp[k] + v) : a[u];
+          }
+#pragma unroll
+        for (int u = 0; u < CH; ++u) {
+          const uint32_t v = v0 + lane + 32 * u;
+          const bool last = tail && v == nvec - 1;
+          if (last) a[u] = mask_tail(a[u], tail);
+#pragma unroll
+          for (int k = 0; k < CMP_G; ++k) {
+            uint4 bb = b[k][u];
+            if (last) bb = mask_tail(bb, tail);
+            x[k] |= (a[u].x ^ bb.x) | (a[u].y ^ bb.y) | (a[u].z ^ bb.z) | (a[u].w ^ bb.w);
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < CMP_G; ++k) {
+        if (__any_sync(0xffffffffu, x[k] != 0) && lane == 0) {
+          const uint64_t p = (uint64_t)c * S + s0 + k;
+          uint32_t* word = reinterpret_cast<uint32_t*>(dv) + (p >> 2);
+          const uint32_t sh8 = 8u * (uint32_t)(p & 3);
+          const uint32_t old = atomicOr(word, (uint32_t)DV_DIFF << sh8);
+          if (count_collisions && ((old >> sh8) & 0xffu) == DV_EQUAL) atomicAdd(&counters[1], 1u);
+        }
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ k_classify
 __global__ void __launch_bounds__(256)
 k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint64_t nrows,
@@ -217,7 +300,7 @@ static int check_scan_args(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena*
     return NCD_E_INVALID;
   }
   const uint32_t hm = mode & 0xff;
-  if (hm > NCD_MODE_SHA256 || (mode & ~(0xffu | NCD_MODE_CONFIRM))) {
+  if (hm > NCD_MODE_SHA256 || (mode & ~(0xffu | NCD_MODE_CONFIRM | NCD_MODE_REHASH))) {
     ncd_set_error("ncd_scan: unknown mode 0x%x", mode);
     return NCD_E_INVALID;
   }
@@ -256,6 +339,14 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
   // digests first (hash modes): every copy is hashed once, digests are kept with the arena
   NCD_CUDA(cudaEventRecord(ctx->ev[0], st));
   if (hm != NCD_MODE_DIRECT) {
+    if (mode & NCD_MODE_REHASH) {
+      ncd_arena* all[1] = {const_cast<ncd_arena*>(ctrl)};
+      all[0]->h64_valid = all[0]->sha_valid = false;
+      for (uint32_t s = 0; s < S; ++s) {
+        ncd_arena* a = const_cast<ncd_arena*>(shards[s]);
+        a->h64_valid = a->sha_valid = false;
+      }
+    }
     NCD_TRY(ncd_hash_launch(ctx, const_cast<ncd_arena*>(ctrl), hm, &launches));
     for (uint32_t s = 0; s < S; ++s)
       NCD_TRY(ncd_hash_launch(ctx, const_cast<ncd_arena*>(shards[s]), hm, &launches));
@@ -329,13 +420,36 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
   NCD_CUDA(cudaEventRecord(ctx->ev[2], st));
   const bool do_compare = (hm == NCD_MODE_DIRECT) || (mode & NCD_MODE_CONFIRM);
   if (do_compare && npairs && ctrl->ntiles) {
-    // persistent-style grid: a multiple of the SM count, 8 warps per CTA, grid-stride over tiles
-    uint64_t want = (ctrl->ntiles + 7) / 8;
-    uint64_t cap = (uint64_t)ctx->sm_count * 8;
+    // Grid: a multiple of the SM count, 8 warps per CTA, warps stride over the tiles.
+    // Records made of full 4 KB tiles stream best one shard copy at a time (k_compare: 4 KB
+    // contiguous per copy per warp); ragged or small records need several copies in flight per
+    // warp to have enough bytes per memory latency (k_compare_grouped on the merged tile list).
+    int variant = ctx->compare_variant;
+    if (variant < 0) variant = (ctrl->len_sum / ctrl->ntiles >= 3500) ? 0 : 2;
+    const uint64_t ntl = variant == 0 ? ctrl->ntiles : ctrl->nctiles;
+    const uint32_t* t_obj = variant == 0 ? ctrl->tile_obj : ctrl->ctile_obj;
+    const uint32_t* t_chunk = variant == 0 ? ctrl->tile_chunk : ctrl->ctile_chunk;
+    uint64_t want = (ntl + 7) / 8;
+    uint64_t cap = (uint64_t)ctx->sm_count * ctx->compare_ctas_per_sm;
     unsigned grid = (unsigned)(want < cap ? want : cap);
-    k_compare<<<grid, 256, 0, st>>>(dctrl, ctx->d_shards, S, ctrl->tile_obj, ctrl->tile_chunk,
-                                    ctrl->ntiles, sh_off, dv, counters,
-                                    hm != NCD_MODE_DIRECT ? 1u : 0u);
+    const uint32_t cc = hm != NCD_MODE_DIRECT ? 1u : 0u;
+    const size_t smem = (size_t)S * sizeof(void*);
+    switch (variant) {
+      case 1:
+        k_compare_grouped<1><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, t_obj, t_chunk, ntl, sh_off, dv,
+                                                       counters, cc);
+        break;
+      case 2:
+        k_compare_grouped<2><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, t_obj, t_chunk, ntl, sh_off, dv,
+                                                       counters, cc);
+        break;
+      case 4:
+        k_compare_grouped<4><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, t_obj, t_chunk, ntl, sh_off, dv,
+                                                       counters, cc);
+        break;
+      default:
+        k_compare<<<grid, 256, 0, st>>>(dctrl, ctx->d_shards, S, t_obj, t_chunk, ntl, sh_off, dv, counters, cc);
+    }
     ++launches;
   }
   NCD_CUDA(cudaEventRecord(ctx->ev[3], st));

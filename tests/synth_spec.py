@@ -86,3 +86,40 @@ def expected_codes(cfg, nshards: int) -> np.ndarray:
 
 def expected_diff_count(cfg, nshards: int) -> int:
     return int(np.count_nonzero(expected_codes(cfg, nshards)))
+
+
+# ---------------------------------------------------------------- vectorised (full-size configs)
+def _sm64(x: np.ndarray) -> np.ndarray:
+    with np.errstate(over="ignore"):
+        x = x + np.uint64(0x9E3779B97F4A7C15)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return x ^ (x >> np.uint64(31))
+
+
+def expected_codes_np(cfg, nshards: int) -> np.ndarray:
+    """Same as expected_codes for an UNPARTITIONED config, in numpy (millions of rows)."""
+    assert cfg.part_mod <= 1
+    per = 1 + cfg.n_secrets + cfg.n_configmaps
+    n = cfg.groups * per
+    gid = np.arange(n, dtype=np.uint64)
+    j = (gid % np.uint64(per)).astype(np.int64)
+    out = np.zeros((n, nshards), dtype=np.uint8)
+    pm, pf, pl = cfg.p_missing_ppm, cfg.p_flip_ppm, cfg.p_len_ppm
+    for s in range(nshards):
+        with np.errstate(over="ignore"):
+            d = _sm64(np.uint64(cfg.drift_seed) + gid * np.uint64(0x9E3779B97F4A7C15) + np.uint64((s * 0xD1B54A32D192ED03) & M64))
+        u = d % np.uint64(PPM)
+        missing = u < pm
+        diff = (~missing) & (u < pm + pf + pl)
+        u2 = _sm64(d ^ np.uint64(0x5851F42D4C957F2D)) % np.uint64(PPM)
+        dep = j > 0
+        rogue = dep & (u2 < cfg.p_rogue_ppm)
+        foreign = dep & ~rogue & (u2 < cfg.p_rogue_ppm + cfg.p_owner_ppm)
+        t_missing = np.repeat(missing[::per], per)  # the group's template is absent on this shard
+        code = np.where(diff, UPDATE_DATA, 0).astype(np.uint8)
+        code = np.where(dep & (foreign | t_missing), code | UPDATE_OWNER, code)
+        code = np.where(rogue, ERR_ROGUE, code)
+        code = np.where(missing, CREATE, code)
+        out[:, s] = code
+    return out
