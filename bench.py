@@ -318,11 +318,15 @@ def run_ours(args):
             "gpu_launches": int(launches_all),
             "clocks": clocks,
         }
-    # end-to-end and CPU baseline: rank 0, N=1 only (bounded samples)
+    # end-to-end: every rank, bounded sample; CPU baseline: rank 0 at N=1 only
     for a in sas + [ca]:
         a.close()
-    if rank == 0 and world == 1 and not args.skip_e2e:
-        result["e2e"] = run_e2e(ctx, args, mode)
+    if not args.skip_e2e:
+        gather = (lambda d: M.gather_diffs(d, sendbuf, recvbuf, ext, cap_entries)) if world > 1 else (lambda d: None)
+        e2e_cold, e2e_res = run_e2e(ctx, args, mode & 0xFF, world, rank, dist, ext, gather)
+        if rank == 0:
+            result["e2e"] = e2e_cold
+            result["e2e_resident"] = e2e_res
     ctx.close()
     if rank == 0 and world == 1 and not args.skip_cpu:
         arm = CpuArm(args.workload, args.cpu_sample_groups, os.cpu_count() or 1)
@@ -334,52 +338,119 @@ def run_ours(args):
     return 0
 
 
-def run_e2e(ctx, args, mode):
-    """Same metric with HOST arenas: every step = upload (H2D) + index build + scan + diff list D2H."""
+def run_e2e(ctx, args, mode, world, rank, dist, ext, gather):
+    """The same metric through the C ABI with HOST (pinned) arenas, two ways:
+
+    cold      every step uploads every arena of this rank (H2D), rebuilds its index, scans and reads
+              the diff list back: what a controller without resident state would pay per sweep.
+    resident  arenas stay in HBM; every step the host rewrites a small fraction of the records in the
+              pinned arrays (what informer UpdateFunc events amount to between two resyncs), the
+              library pulls just those records over PCIe (ncd_arena_sync_records), scans, and the
+              diff list is read back.
+    Timed with CUDA events on the library's stream around the whole region (host gaps included),
+    barrier on both sides, max over ranks.
+    """
+    import numpy as np
     import torch
 
-    cfg, S = make_cfg(args.workload, groups=args.e2e_groups)
-    dev = [ctx.synth_arena(cfg, r) for r in range(-1, S)]
+    from nexus_configuration_controller_b200._ffi import check
+    from nexus_configuration_controller_b200.drift import Arena
+
+    cfg, S = make_cfg(args.workload, groups=args.e2e_groups, part_mod=world if world > 1 else 0, part_rem=rank)
     hosts = []
-    for a in dev:
+    slack = 1 << 20
+    for r in range(-1, S):
+        a = ctx.synth_arena(cfg, r)
         c = a.counts()
-        from nexus_configuration_controller_b200.drift import Arena
-
-        h = Arena(ctx, c.payload_bytes, c.nobj, c.aux_bytes, c.nowner, c.ndep, device_only=False)
+        h = Arena(ctx, c.payload_bytes + slack, c.nobj, c.aux_bytes, c.nowner, c.ndep, device_only=False)
         v = h.host_view()
-        from nexus_configuration_controller_b200._ffi import check
-
         check(ctx.lib.ncd_arena_download(a.handle, C.byref(v)))  # fills the pinned host arrays
         hosts.append((h, c))
         a.close()
-    h2d = sum(c.payload_bytes + c.aux_bytes + c.nobj * 29 + 8 + c.nowner * 9 + c.ndep * 9 for _, c in hosts)
+    h2d_cold = sum(c.payload_bytes + c.aux_bytes + c.nobj * 29 + 8 + c.nowner * 9 + c.ndep * 9 for _, c in hosts)
+    arenas = [h for h, _ in hosts]
 
-    def step():
+    def timed(step, reps, warm):
+        for _ in range(warm):
+            out = step()
+        torch.cuda.synchronize()
+        if dist:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(ext)
+        for _ in range(reps):
+            out = step()
+        e1.record(ext)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        if dist:
+            t = torch.tensor([ms], device=f"cuda:{ctx.device}")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, out
+
+    def total(x):
+        if not dist:
+            return float(x)
+        t = torch.tensor([float(x)], dtype=torch.float64, device=f"cuda:{ctx.device}")
+        dist.all_reduce(t)
+        return float(t.item())
+
+    def cold_step():
         for h, c in hosts:
             h.commit(c.nobj, c.payload_bytes, c.aux_bytes, c.nowner, c.ndep)
-        d = ctx.scan(hosts[0][0], [h for h, _ in hosts[1:]], mode)
+        d = ctx.scan(arenas[0], arenas[1:], mode)
+        gather(d)
         ents = d.entries()
         st = ctx.last_stats()
         d.close()
         return st, ents
 
-    for _ in range(2):
-        st, ents = step()
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
     reps = max(1, args.e2e_steps)
-    for _ in range(reps):
-        st, ents = step()
-    torch.cuda.synchronize()
-    sec = (time.perf_counter() - t0) / reps
-    for h, _ in hosts:
-        h.close()
-    return {
-        "value": st.pairs / sec, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(ents.nbytes + 64),
-        "ms_per_step": sec * 1e3, "gb_per_s": st.algo_bytes / sec / 1e9,
-        "sample": f"{args.workload}: first {args.e2e_groups} groups = {hosts[0][1].nobj} objects x {S} shards from pinned host arenas; "
+    cold_ms, (st, ents) = timed(cold_step, reps, 2)
+    pairs, algo = total(st.pairs), total(st.algo_bytes)
+    result = {
+        "value": pairs / (cold_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(total(h2d_cold)),
+        "d2h_bytes_per_step": int(total(ents.nbytes + 64)), "ms_per_step": cold_ms, "gb_per_s": algo / (cold_ms / 1e3) / 1e9,
+        "sample": f"{args.workload}: first {args.e2e_groups} groups = {int(total(hosts[0][1].nobj))} objects x {S} shards in pinned "
+                  f"host arenas{' split over ' + str(world) + ' ranks by key hash' if world > 1 else ''}; "
                   f"step = H2D of every arena + index build + scan + diff list D2H",
     }
+
+    # resident: rewrite ~0.1 % of the records of every cluster per step, pull them, scan
+    rng = np.random.default_rng(1234 + rank)
+    views = [h.host_arrays() for h in arenas]
+    pulled = [0]
+
+    def resident_step():
+        pulled[0] = 0
+        for h, (hh, c), arr in zip(arenas, hosts, views):
+            k = max(1, int(c.nobj * args.resident_fraction))
+            idx = rng.choice(c.nobj, size=k, replace=False).astype(np.uint32)
+            off = arr["rec_off"][idx].astype(np.int64)
+            ln = arr["rec_len"][idx].astype(np.int64)
+            pos = off + (rng.integers(0, 1 << 62, size=k) % np.maximum(ln, 1))
+            arr["payload"][pos] ^= 0x5A  # the event: one byte of the value changed, same length
+            h.sync_records(idx, c.payload_bytes)
+            pulled[0] += int(((ln + 15) // 16 * 16).sum()) + 4 * k
+        d = ctx.scan(arenas[0], arenas[1:], mode)
+        gather(d)
+        ents = d.entries()
+        st = ctx.last_stats()
+        d.close()
+        return st, ents
+
+    res_ms, (st, ents) = timed(resident_step, max(3, reps), 2)
+    result_res = {
+        "value": pairs / (res_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(total(pulled[0])),
+        "d2h_bytes_per_step": int(total(ents.nbytes + 64)), "ms_per_step": res_ms, "gb_per_s": algo / (res_ms / 1e3) / 1e9,
+        "diff_entries_last_step": int(total(len(ents))),
+        "sample": f"same sample, arenas resident in HBM; step = host rewrites {args.resident_fraction:.2%} of the records of every "
+                  f"cluster in the pinned arrays + ncd_arena_sync_records (only those records cross PCIe) + scan + diff list D2H",
+    }
+    for h in arenas:
+        h.close()
+    return result, result_res
 
 
 def main():
@@ -396,6 +467,7 @@ def main():
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     ap.add_argument("--e2e-groups", type=int, default=40000)
     ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--resident-fraction", type=float, default=0.001, help="records rewritten per cluster per resident e2e step")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--allow-short-warmup", action="store_true")

@@ -184,6 +184,16 @@ int ncd_arena_host_view(ncd_arena* a, ncd_arena_view* out);
  * is immutable afterwards until the next commit. */
 int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
                      uint64_t nowner, uint64_t ndep);
+/* Incremental update of a committed NCD_ARENA_HOST_PINNED arena: the records of the listed
+ * objects were rewritten in the pinned host arrays (payload bytes at a new or the same rec_off,
+ * rec_len; a record that grew is appended behind the old payload end) and the device copy must
+ * follow.  Only those records cross PCIe (a kernel pulls them from the pinned arrays), then the
+ * tile lists are rebuilt; keys, ownerReferences and dependents are NOT re-read — an object that
+ * is added, deleted or re-owned needs ncd_arena_commit.  This is what an informer UpdateFunc
+ * (controller.go:288-290, 301-303, 321-330, 344-353) turns into, instead of a full re-upload
+ * on every 30 s resync (main.go:70-71).  obj_idx: host array of n distinct object indices;
+ * new_payload_bytes: the used payload size after the rewrite (<= capacity). */
+int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint64_t new_payload_bytes);
 /* Copies the committed device arrays into caller buffers (sized from
  * ncd_arena_counts); any pointer in dst may be NULL to skip that array. */
 int ncd_arena_download(ncd_arena* a, ncd_arena_view* dst);

@@ -123,6 +123,7 @@ struct ncd_arena {
   uint32_t* ctile_obj;
   uint32_t* ctile_chunk;
   uint32_t* ctile_start;
+  uint64_t tile_cap, ctile_cap;  // allocated entries of the tile lists
   // digests (device), lazily allocated
   uint64_t* h64;
   uint32_t* sha;
@@ -186,6 +187,7 @@ static inline uint64_t ncd_align_up(uint64_t x, uint64_t a) { return (x + a - 1)
 // ------------------------------------------------------------------ internal entry points
 // ncd_index.cu
 int ncd_build_index(ncd_arena* a);
+int ncd_rebuild_tiles(ncd_arena* a);
 int ncd_exclusive_scan_u32(ncd_ctx* ctx, const uint32_t* in, uint32_t* out, uint64_t n,
                            uint32_t* total_out_dev);
 int ncd_exclusive_scan_u64(ncd_ctx* ctx, const uint32_t* in, uint64_t* out, uint64_t n,

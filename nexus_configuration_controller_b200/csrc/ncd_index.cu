@@ -302,6 +302,53 @@ static int dev_realloc(T** p, uint64_t n) {
   return NCD_OK;
 }
 
+// Tile lists (hash tiles and compare tiles) and the sum of record lengths: everything that
+// depends on rec_len only.  Run by commit and again after records were replaced in place.
+int ncd_rebuild_tiles(ncd_arena* a) {
+  ncd_ctx* ctx = a->ctx;
+  cudaStream_t st = ctx->stream;
+  const uint32_t n = (uint32_t)a->nobj;
+  const unsigned blocks = (n + 255) / 256;
+  DevArena da;
+  ncd_fill_dev_arena(a, &da);
+  uint32_t* d_small = nullptr;  // [0] tiles, [1] compare tiles, [2..3] u64 sum of rec_len
+  uint32_t* counts = nullptr;
+  NCD_CUDA(cudaMallocAsync((void**)&d_small, 4 * sizeof(uint32_t), st));
+  NCD_CUDA(cudaMemsetAsync(d_small, 0, 4 * sizeof(uint32_t), st));
+  NCD_CUDA(cudaMallocAsync((void**)&counts, ((size_t)n + 1) * 4, st));
+  if (!a->tile_start) NCD_TRY(dev_realloc(&a->tile_start, (uint64_t)n + 1));
+  if (!a->ctile_start) NCD_TRY(dev_realloc(&a->ctile_start, (uint64_t)n + 1));
+  if (n) k_tile_counts<<<blocks, 256, 0, st>>>(da, counts, (unsigned long long*)(d_small + 2));
+  NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->tile_start, n, d_small + 0));
+  if (n) k_ctile_counts<<<blocks, 256, 0, st>>>(da, counts);
+  NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->ctile_start, n, d_small + 1));
+  uint32_t h_small[4];
+  NCD_CUDA(cudaMemcpyAsync(h_small, d_small, sizeof(h_small), cudaMemcpyDeviceToHost, st));
+  NCD_CUDA(cudaStreamSynchronize(st));
+  memcpy(&a->len_sum, &h_small[2], 8);
+  if (h_small[0] > a->tile_cap || !a->tile_obj) {
+    a->tile_cap = h_small[0] + h_small[0] / 16;
+    NCD_TRY(dev_realloc(&a->tile_obj, a->tile_cap));
+    NCD_TRY(dev_realloc(&a->tile_chunk, a->tile_cap));
+  }
+  if (h_small[1] > a->ctile_cap || !a->ctile_obj) {
+    a->ctile_cap = h_small[1] + h_small[1] / 16;
+    NCD_TRY(dev_realloc(&a->ctile_obj, a->ctile_cap));
+    NCD_TRY(dev_realloc(&a->ctile_chunk, a->ctile_cap));
+  }
+  a->ntiles = h_small[0];
+  a->nctiles = h_small[1];
+  if (n) {
+    const unsigned wblocks = (unsigned)(((uint64_t)n * 32 + 255) / 256);
+    k_tiles_fill<<<wblocks, 256, 0, st>>>(n, a->tile_start, a->tile_obj, a->tile_chunk);
+    k_tiles_fill<<<wblocks, 256, 0, st>>>(n, a->ctile_start, a->ctile_obj, a->ctile_chunk);
+  }
+  NCD_CUDA(cudaFreeAsync(counts, st));
+  NCD_CUDA(cudaFreeAsync(d_small, st));
+  NCD_CUDA(cudaGetLastError());
+  return NCD_OK;
+}
+
 int ncd_build_index(ncd_arena* a) {
   ncd_ctx* ctx = a->ctx;
   cudaStream_t st = ctx->stream;
@@ -316,7 +363,7 @@ int ncd_build_index(ncd_arena* a) {
   NCD_TRY(dev_realloc(&a->table, tsize));
   NCD_CUDA(cudaMemsetAsync(a->table, 0xFF, (size_t)tsize * 8, st));
 
-  // [0] bad records, [1] duplicate keys, [2] rows, [3] tiles, [4..5] u64 sum of rec_len, [6] compare tiles
+  // [0] bad records, [1] duplicate keys, [2] rows
   uint32_t* d_small = nullptr;
   NCD_CUDA(cudaMallocAsync((void**)&d_small, 8 * sizeof(uint32_t), st));
   NCD_CUDA(cudaMemsetAsync(d_small, 0, 8 * sizeof(uint32_t), st));
@@ -328,6 +375,7 @@ int ncd_build_index(ncd_arena* a) {
   NCD_TRY(dev_realloc(&a->row_start, (uint64_t)n + 1));
   NCD_TRY(dev_realloc(&a->tile_start, (uint64_t)n + 1));
   NCD_TRY(dev_realloc(&a->ctile_start, (uint64_t)n + 1));
+  a->tile_cap = a->ctile_cap = 0;
 
   if (n) {
     k_validate<<<blocks, 256, 0, st>>>(da, a->payload_bytes, a->aux_bytes, a->nowner, a->ndep, d_small);
@@ -346,32 +394,17 @@ int ncd_build_index(ncd_arena* a) {
     k_row_counts<<<blocks, 256, 0, st>>>(da, counts);
   }
   NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->row_start, n, d_small + 2));
-  if (n) k_tile_counts<<<blocks, 256, 0, st>>>(da, counts, (unsigned long long*)(d_small + 4));
-  NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->tile_start, n, d_small + 3));
-  if (n) k_ctile_counts<<<blocks, 256, 0, st>>>(da, counts);
-  NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->ctile_start, n, d_small + 6));
   uint32_t h_small[8];
   NCD_CUDA(cudaMemcpyAsync(h_small, d_small, sizeof(h_small), cudaMemcpyDeviceToHost, st));
   NCD_CUDA(cudaStreamSynchronize(st));
   a->dup_keys = h_small[1];
-  memcpy(&a->len_sum, &h_small[4], 8);
   a->nrows = h_small[2];
-  a->ntiles = h_small[3];
-  a->nctiles = h_small[6];
 
   NCD_TRY(dev_realloc(&a->row_obj, a->nrows));
   NCD_TRY(dev_realloc(&a->row_dep, a->nrows));
   NCD_TRY(dev_realloc(&a->row_cidx, a->nrows));
-  NCD_TRY(dev_realloc(&a->tile_obj, a->ntiles));
-  NCD_TRY(dev_realloc(&a->tile_chunk, a->ntiles));
-  NCD_TRY(dev_realloc(&a->ctile_obj, a->nctiles));
-  NCD_TRY(dev_realloc(&a->ctile_chunk, a->nctiles));
-  if (n) {
-    k_rows_fill<<<blocks, 256, 0, st>>>(da, a->row_start, a->row_obj, a->row_dep, a->row_cidx);
-    const unsigned wblocks = (unsigned)(((uint64_t)n * 32 + 255) / 256);
-    k_tiles_fill<<<wblocks, 256, 0, st>>>(n, a->tile_start, a->tile_obj, a->tile_chunk);
-    k_tiles_fill<<<wblocks, 256, 0, st>>>(n, a->ctile_start, a->ctile_obj, a->ctile_chunk);
-  }
+  if (n) k_rows_fill<<<blocks, 256, 0, st>>>(da, a->row_start, a->row_obj, a->row_dep, a->row_cidx);
+  NCD_TRY(ncd_rebuild_tiles(a));
   NCD_CUDA(cudaFreeAsync(counts, st));
   NCD_CUDA(cudaFreeAsync(d_small, st));
   NCD_CUDA(cudaGetLastError());

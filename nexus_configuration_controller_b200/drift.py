@@ -130,6 +130,18 @@ class Arena:
         check(self.ctx.lib.ncd_arena_host_view(self.handle, C.byref(v)))
         return v
 
+    def host_arrays(self) -> Dict[str, np.ndarray]:
+        """numpy views over the pinned host arrays (capacity sized): what the packer writes into."""
+        v = self.host_view()
+        caps = {"payload": v.payload_bytes, "aux": v.aux_bytes, "own_start": v.nobj + 1, "dep_start": v.nobj + 1,
+                "own_is_template": v.nowner, "own_uid_off": v.nowner, "own_uid_len": v.nowner,
+                "dep_kind": v.ndep, "dep_key_off": v.ndep, "dep_key_len": v.ndep}
+        out = {}
+        for name, dt in HostArena.FIELDS:
+            n = int(caps.get(name, v.nobj))
+            out[name] = np.ctypeslib.as_array(getattr(v, name), shape=(max(n, 1),)) if n else np.zeros(0, dtype=dt)
+        return out
+
     def fill_from(self, host: HostArena) -> None:
         """memcpy of a numpy arena image into the pinned host arrays (what the Go packer writes)."""
         v = self.host_view()
@@ -153,6 +165,11 @@ class Arena:
 
     def commit(self, nobj, payload_bytes, aux_bytes, nowner, ndep) -> None:
         check(self.ctx.lib.ncd_arena_commit(self.handle, nobj, payload_bytes, aux_bytes, nowner, ndep))
+
+    def sync_records(self, obj_idx: np.ndarray, new_payload_bytes: int) -> None:
+        """Pushes the records of `obj_idx` (rewritten in the pinned host arrays) to the device copy."""
+        idx = np.ascontiguousarray(obj_idx, dtype=np.uint32)
+        check(self.ctx.lib.ncd_arena_sync_records(self.handle, len(idx), idx.ctypes.data_as(_ffi.u32p), new_payload_bytes))
 
     def counts(self) -> ArenaView:
         v = ArenaView()
