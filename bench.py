@@ -111,6 +111,23 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def api_bound_model(templates: int, shards: int, writes: float) -> dict:
+    """The reference's end-to-end sweep is bound by its own admission limiter and by REST round
+    trips, not by the drift check: 50 items/s, burst 300 (controller.go:257-260, .helm/values.yaml
+    :165-169), one HTTPS write per drifted object (assumed 5 ms in-region).  No Go toolchain or API
+    server exists here, so this is a model, not a measurement."""
+    rate, burst, rtt_s = 50.0, 300, 0.005
+    admit_s = max(0.0, (templates - burst) / rate)
+    return {
+        "kind": "model (not measured: no Go toolchain, no API server on this box)",
+        "limiter": "50 items/s, burst 300 (controller.go:257-260)",
+        "sweep_admission_s": round(admit_s, 1),
+        "rest_writes": int(writes), "rest_write_s_at_5ms_sequential": round(writes * rtt_s, 2),
+        "note": f"a sweep of {templates} templates over {shards} shards takes >= {admit_s:.0f} s in the reference whatever the "
+                "compare costs; the GPU path moves the compare, not this bound, unless the sweep is batched (DESIGN.md section 9)",
+    }
+
+
 def hbm_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -316,6 +333,8 @@ def run_ours(args):
                 "phases_ms": {k: round(v, 4) for k, v in phases.items()},
             },
             "gpu_launches": int(launches_all),
+            # reported separately, as the north_star asks: what bounds a real reconcile sweep is not this path
+            "api_bound_model": api_bound_model(int(cfg.groups), S, ndiff_all),
             "clocks": clocks,
         }
     # end-to-end: every rank, bounded sample; CPU baseline: rank 0 at N=1 only

@@ -5,7 +5,7 @@
 //
 //   k_h64_tiles    striped 64-bit hash, one warp per 4 KB tile, HBM bound
 //   k_h64_final    one thread per object folds the tile sums and the length
-//   k_sha256       FIPS 180-4 SHA-256, one thread per object, integer-pipe bound
+//   k_sha256       FIPS 180-4 SHA-256, persistent lanes pulling records, integer-pipe bound
 #include "ncd_common.cuh"
 
 // ------------------------------------------------------------------ NCD-H64
@@ -122,61 +122,78 @@ __device__ __forceinline__ void sha256_block(uint32_t st[8], uint32_t w[16]) {
   st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
 }
 
-// One thread per object.  Records start on 16-byte boundaries and are zero padded to one, so
-// the message is read as 16-byte vectors; bytes past rec_len are masked before use.
+// Persistent lanes: every lane owns one record at a time and takes the next record index from
+// a global counter when it finishes, so lanes of a warp stay busy although record lengths differ
+// by more than 10x (a fixed record-per-thread mapping idles most lanes while the longest record
+// of the warp finishes).  Every loop iteration is one 64-byte block for every lane: a message
+// block, the padded last block, or the extra length-only block (FIPS 180-4 section 5.1.1).
+// Records start on 16-byte boundaries and are zero padded to one, so blocks are read as 16-byte
+// vectors; bytes past rec_len are masked before use.
 __global__ void __launch_bounds__(128)
-k_sha256(DevArena a, uint32_t* __restrict__ out) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.nobj) return;
-  const uint32_t len = a.rec_len[i];
-  const uint4* p = reinterpret_cast<const uint4*>(a.payload + a.rec_off[i]);
-  uint32_t st[8] = {0x6a09e667, 0xbb67ae85, 0x3c6ef372, 0xa54ff53a,
-                    0x510e527f, 0x9b05688c, 0x1f83d9ab, 0x5be0cd19};
+k_sha256(DevArena a, uint32_t* __restrict__ out, unsigned int* __restrict__ next) {
+  uint32_t st[8];
   uint32_t w[16];
-  const uint32_t full = len >> 6;
-  for (uint32_t blk = 0; blk < full; ++blk) {
+  const uint4* p = nullptr;
+  uint32_t rec = 0, len = 0, pos = 0;
+  bool have = false, extra = false, drained = false;
+  for (;;) {
+    if (!have && !drained) {
+      rec = atomicAdd(next, 1u);
+      drained = rec >= a.nobj;
+      if (!drained) {
+        len = a.rec_len[rec];
+        p = reinterpret_cast<const uint4*>(a.payload + a.rec_off[rec]);
+        pos = 0;
+        extra = false;
+        have = true;
+        st[0] = 0x6a09e667; st[1] = 0xbb67ae85; st[2] = 0x3c6ef372; st[3] = 0xa54ff53a;
+        st[4] = 0x510e527f; st[5] = 0x9b05688c; st[6] = 0x1f83d9ab; st[7] = 0x5be0cd19;
+      }
+    }
+    if (!__any_sync(0xffffffffu, have)) break;  // every lane reaches this point in every iteration
+    if (!have) continue;  // this lane ran out of records; the others finish theirs
+    bool last = false;
+    const uint32_t rem = len - pos;  // unused when extra
+    const uint32_t navail = extra ? 0u : min(4u, (rem + 15) >> 4);
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const uint4 v = ncd_ldg_stream(p + blk * 4 + q);
-      w[4 * q + 0] = bswap32(v.x);
-      w[4 * q + 1] = bswap32(v.y);
-      w[4 * q + 2] = bswap32(v.z);
-      w[4 * q + 3] = bswap32(v.w);
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if ((uint32_t)q < navail) v = ncd_ldg_stream(p + (pos >> 4) + q);
+      w[4 * q + 0] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+    }
+    if (extra) {
+      last = true;
+    } else if (rem < 64) {
+      // little-endian word k holds message bytes 4k..4k+3: keep the first rem bytes, then 0x80
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int nb = (int)rem - 4 * k;
+        uint32_t x = w[k];
+        if (nb <= 0) x = 0;
+        else if (nb < 4) x &= (1u << (8 * nb)) - 1u;
+        if (nb >= 0 && nb < 4) x |= 0x80u << (8 * nb);
+        w[k] = x;
+      }
+      if (rem < 56) last = true;
+      else extra = true;
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) w[k] = bswap32(w[k]);
+    if (last) {
+      const uint64_t bits = (uint64_t)len * 8;
+      w[14] = (uint32_t)(bits >> 32);
+      w[15] = (uint32_t)bits;
     }
     sha256_block(st, w);
+    pos += 64;
+    if (last) {
+      // digest bytes in standard order: big-endian words
+      uint4* o = reinterpret_cast<uint4*>(out + (size_t)rec * 8);
+      o[0] = make_uint4(bswap32(st[0]), bswap32(st[1]), bswap32(st[2]), bswap32(st[3]));
+      o[1] = make_uint4(bswap32(st[4]), bswap32(st[5]), bswap32(st[6]), bswap32(st[7]));
+      have = false;
+    }
   }
-  // last (partial) block + padding
-  const uint32_t rem = len & 63;
-  const uint32_t navail = (rem + 15) >> 4;  // vectors that exist in the arena for this block
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    uint4 v = make_uint4(0, 0, 0, 0);
-    if ((uint32_t)q < navail) v = ncd_ldg_stream(p + full * 4 + q);
-    w[4 * q + 0] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
-  }
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    // little-endian word k holds message bytes 4k..4k+3; keep the first rem bytes, add 0x80
-    const int nb = (int)rem - 4 * k;
-    uint32_t x = w[k];
-    if (nb <= 0) x = 0;
-    else if (nb < 4) x &= (1u << (8 * nb)) - 1u;
-    if (nb >= 0 && nb < 4) x |= 0x80u << (8 * nb);
-    w[k] = bswap32(x);
-  }
-  const uint64_t bits = (uint64_t)len * 8;
-  if (rem >= 56) {
-    sha256_block(st, w);
-#pragma unroll
-    for (int k = 0; k < 16; ++k) w[k] = 0;
-  }
-  w[14] = (uint32_t)(bits >> 32);
-  w[15] = (uint32_t)bits;
-  sha256_block(st, w);
-  // digest bytes in standard order: big-endian words
-  uint4* o = reinterpret_cast<uint4*>(out + (size_t)i * 8);
-  o[0] = make_uint4(bswap32(st[0]), bswap32(st[1]), bswap32(st[2]), bswap32(st[3]));
-  o[1] = make_uint4(bswap32(st[4]), bswap32(st[5]), bswap32(st[6]), bswap32(st[7]));
 }
 
 // ------------------------------------------------------------------ host side
@@ -205,7 +222,10 @@ int ncd_hash_launch(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, uint32_t* launche
     if (!a->sha) NCD_CUDA(cudaMalloc((void**)&a->sha, (size_t)(n ? n : 1) * 32));
     ncd_fill_dev_arena(a, &da);
     if (n) {
-      k_sha256<<<(n + 127) / 128, 128, 0, st>>>(da, a->sha);
+      unsigned int* next = reinterpret_cast<unsigned int*>(ctx->d_counters) + 8;  // words 8.. are free
+      NCD_CUDA(cudaMemsetAsync(next, 0, 4, st));
+      const unsigned want = (n + 127) / 128, cap = (unsigned)ctx->sm_count * 16;
+      k_sha256<<<want < cap ? want : cap, 128, 0, st>>>(da, a->sha, next);
       ++*launches;
     }
     a->sha_valid = true;
