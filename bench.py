@@ -327,7 +327,7 @@ def run_ours(args):
             },
             "gb_per_s": algo_all / (ms_per_step / 1e3) / 1e9,
             "roofline": {
-                "bound": "hbm", "kernel": "k_compare / k_compare_grouped" if mode == A.MODE_DIRECT else ("k_h64_tiles" if args.mode == "hash64" else "k_sha256"),
+                "bound": "hbm", "kernel": {0: "k_compare", 1: "k_compare_grouped<1>", 2: "k_compare_grouped<2>", 4: "k_compare_grouped<4>", 8: "k_compare_tma"}.get(st.compare_variant, "k_compare") if mode == A.MODE_DIRECT else ("k_h64_tiles" if args.mode == "hash64" else "k_sha256"),
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
                 "traffic": None, "kernel_ms": kern_ms, "scan_ms": sum(tot_ms) / len(tot_ms),
                 "phases_ms": {k: round(v, 4) for k, v in phases.items()},

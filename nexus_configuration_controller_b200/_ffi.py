@@ -67,6 +67,7 @@ class ScanStats(C.Structure):
         ("ndiff", C.c_uint64),
         ("hash_collisions", C.c_uint64),
         ("launches", C.c_uint32),
+        ("compare_variant", C.c_uint32),
     ]
 
 

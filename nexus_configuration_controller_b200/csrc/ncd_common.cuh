@@ -194,6 +194,10 @@ int ncd_exclusive_scan_u64(ncd_ctx* ctx, const uint32_t* in, uint64_t* out, uint
                            uint64_t* total_out_dev);
 void ncd_fill_dev_arena(const ncd_arena* a, DevArena* out);
 int ncd_ctx_scratch(ncd_ctx* ctx, size_t bytes, void** out);
+// ncd_compare_tma.cu
+int ncd_launch_compare_tma(ncd_ctx* ctx, const DevArena& dctrl, uint32_t S, const uint32_t* tile_obj,
+                           const uint32_t* tile_chunk, uint64_t ntiles, const uint64_t* sh_off, uint8_t* dv,
+                           uint32_t* counters, uint32_t count_collisions);
 // ncd_hash.cu
 int ncd_hash_launch(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, uint32_t* launches);
 

@@ -8,6 +8,8 @@
 //               controller record against the same tile of every shard copy
 //               (reference: reflect.DeepEqual at controller.go:539,600,725,795 — equality of
 //               the injective canonical encodings is DeepEqual of the values).
+//               (three data-movement variants: k_compare, k_compare_grouped here,
+//               k_compare_tma in ncd_compare_tma.cu)
 //   k_classify  decision code per (row, shard) from the verdicts + ownerReferences
 //               (reference: controller.go:484-502, 529-560, 591-622, 725-738, 795-808).
 //   k_emit      ordered stream compaction of the codes != SKIP into the diff list.
@@ -334,7 +336,7 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
   const uint64_t nc = ctrl->nobj, nrows = ctrl->nrows;
   const uint64_t npairs = nc * S, nq = nrows * S;
   const uint32_t hm = mode & 0xff;
-  uint32_t launches = 0;
+  uint32_t launches = 0, variant_used = 0;
 
   // digests first (hash modes): every copy is hashed once, digests are kept with the arena
   NCD_CUDA(cudaEventRecord(ctx->ev[0], st));
@@ -420,21 +422,34 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
   NCD_CUDA(cudaEventRecord(ctx->ev[2], st));
   const bool do_compare = (hm == NCD_MODE_DIRECT) || (mode & NCD_MODE_CONFIRM);
   if (do_compare && npairs && ctrl->ntiles) {
-    // Grid: a multiple of the SM count, 8 warps per CTA, warps stride over the tiles.
-    // Records made of full 4 KB tiles stream best one shard copy at a time (k_compare: 4 KB
-    // contiguous per copy per warp); ragged or small records need several copies in flight per
-    // warp to have enough bytes per memory latency (k_compare_grouped on the merged tile list).
+    // Three data-movement shapes for the same compare, picked from the mean tile fill
+    // (measured on B200, profiles/r01_variants_and_shapes.txt):
+    //   records made of full 4 KB tiles   k_compare: one shard copy at a time, 4 KB contiguous per
+    //                                     copy per warp, registers as the staging buffer
+    //   ragged records of a few tiles     k_compare_tma: TMA bulk copies into a shared-memory ring,
+    //                                     producer / consumer warps, nothing staged in registers
+    //   small records                     k_compare_grouped: controller + 8 shard copies in flight
+    //                                     per warp, merged tail tiles
     int variant = ctx->compare_variant;
-    if (variant < 0) variant = (ctrl->len_sum / ctrl->ntiles >= 3500) ? 0 : 2;
-    const uint64_t ntl = variant == 0 ? ctrl->ntiles : ctrl->nctiles;
-    const uint32_t* t_obj = variant == 0 ? ctrl->tile_obj : ctrl->ctile_obj;
-    const uint32_t* t_chunk = variant == 0 ? ctrl->tile_chunk : ctrl->ctile_chunk;
+    if (variant < 0) {
+      const uint64_t fill = ctrl->len_sum / ctrl->ntiles;
+      variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : 2);
+    }
+    variant_used = (uint32_t)variant;
+    const bool fixed_tiles = variant == 0 || variant == 8;
+    const uint64_t ntl = fixed_tiles ? ctrl->ntiles : ctrl->nctiles;
+    const uint32_t* t_obj = fixed_tiles ? ctrl->tile_obj : ctrl->ctile_obj;
+    const uint32_t* t_chunk = fixed_tiles ? ctrl->tile_chunk : ctrl->ctile_chunk;
     uint64_t want = (ntl + 7) / 8;
     uint64_t cap = (uint64_t)ctx->sm_count * ctx->compare_ctas_per_sm;
     unsigned grid = (unsigned)(want < cap ? want : cap);
     const uint32_t cc = hm != NCD_MODE_DIRECT ? 1u : 0u;
     const size_t smem = (size_t)S * sizeof(void*);
     switch (variant) {
+      case 8:  // TMA bulk-copy pipeline, fixed 4 KB tiles
+        NCD_TRY(ncd_launch_compare_tma(ctx, dctrl, S, ctrl->tile_obj, ctrl->tile_chunk, ctrl->ntiles, sh_off, dv,
+                                       counters, cc));
+        break;
       case 1:
         k_compare_grouped<1><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, t_obj, t_chunk, ntl, sh_off, dv,
                                                        counters, cc);
@@ -475,6 +490,7 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
   ctx->stats.pairs = nq;
   ctx->stats.algo_bytes = algo;
   ctx->stats.launches = launches;
+  ctx->stats.compare_variant = variant_used;
   ctx->pending = d;
   ctx->pending_mode = mode;
   ctx->scan_pending = true;

@@ -28,7 +28,7 @@ def test_struct_layouts_match_the_header():
     # sizes a C compiler gives the same declarations (all members naturally aligned)
     assert C.sizeof(_ffi.ArenaView) == 5 * 8 + 17 * 8
     assert C.sizeof(_ffi.Entry) == 16
-    assert C.sizeof(_ffi.ScanStats) == 5 * 4 + 4 + 5 * 8 + 4 + 4
+    assert C.sizeof(_ffi.ScanStats) == 5 * 4 + 4 + 5 * 8 + 4 + 4  # 5 floats, pad, 5 u64, 2 u32
     assert C.sizeof(_ffi.SynthCfg) == 8 + 6 * 4 + 2 * 8 + 8 * 4
 
 

@@ -194,3 +194,28 @@ def test_partition_by_key_hash_covers_everything_once(ctx):
         want = np.concatenate([whole[g * per : (g + 1) * per] for g in groups]) if len(groups) else whole[:0]
         np.testing.assert_array_equal(codes, want)
     assert kept_total == 500
+
+
+@pytest.mark.parametrize("variant", [0, 1, 2, 8])
+def test_every_compare_variant_matches_oracle(variant, monkeypatch):
+    """The three data-movement shapes of the byte compare (register-staged per shard, grouped,
+    TMA bulk-copy pipeline) are picked per scan from the record shapes; forced here one by one."""
+    from nexus_configuration_controller_b200.drift import Context
+
+    monkeypatch.setenv("NCD_COMPARE_VARIANT", str(variant))
+    with Context(0) as c2:
+        for seed, nshards in ((7, 3), (8, 9), (9, 17)):
+            ctrl, shards = random_clusters(seed, n_templates=12, n_shards=nshards, max_len=20000)
+            want_codes, want_ents = oracle.scan(ctrl, shards)
+            for mode in (A.MODE_DIRECT, A.MODE_HASH64 | A.MODE_CONFIRM):
+                codes, ents, _ = gpu_scan(c2, ctrl, shards, mode)
+                np.testing.assert_array_equal(codes, want_codes)
+                np.testing.assert_array_equal(ents, want_ents)
+        cfg = small_synth(groups=2000, dep_len_lo=1, dep_len_hi=30000)
+        ca = c2.synth_arena(cfg, -1)
+        sas = [c2.synth_arena(cfg, s) for s in range(5)]
+        d = c2.scan(ca, sas, A.MODE_DIRECT)
+        np.testing.assert_array_equal(d.codes(), synth_spec.expected_codes_np(cfg, 5))
+        d.close()
+        for a in sas + [ca]:
+            a.close()
