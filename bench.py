@@ -69,25 +69,42 @@ def make_cfg(name: str, groups: int | None = None, part_mod: int = 0, part_rem: 
 
 # ----------------------------------------------------------------------------- clocks
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
-
-    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    """SM clock and throttle reasons sampled WHILE the timed region runs (NVML every ~2 ms; the
+    timed region is only ~0.1 s, too short for an nvidia-smi process per sample)."""
 
     def __init__(self, gpu_index: int):
-        self.gpu, self.samples, self.stop_flag, self.th = gpu_index, [], threading.Event(), None
+        self.gpu, self.samples, self.reason_bits, self.stop_flag, self.th = gpu_index, [], 0, threading.Event(), None
+        self.max_mhz, self.nv, self.h = None, None, None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            # NVML indexes physical devices; honour CUDA_VISIBLE_DEVICES when it is a plain index list
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = int(vis.split(",")[gpu_index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else gpu_index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
 
     def _run(self):
+        nv = self.nv
         while not self.stop_flag.is_set():
             try:
-                out = subprocess.run(
-                    ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
-                    capture_output=True, text=True, timeout=5,
-                ).stdout.strip()
-                if out:
-                    self.samples.append([x.strip() for x in out.split(",")])
+                if nv is not None:
+                    self.samples.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                    get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+                    self.reason_bits |= int(get(self.h))
+                else:
+                    out = subprocess.run(
+                        ["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
+                        capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+                    self.samples.append(float(out[0]))
+                    self.max_mhz = float(out[1])
             except Exception:
                 pass
-            self.stop_flag.wait(0.1)
+            self.stop_flag.wait(0.002)
 
     def start(self):
         self.th = threading.Thread(target=self._run, daemon=True)
@@ -97,18 +114,22 @@ class ClockSampler:
         self.stop_flag.set()
         if self.th:
             self.th.join(timeout=6)
-        sm, mx, reasons = [], 0, set()
-        for s in self.samples:
-            try:
-                sm.append(float(s[0]))
-                mx = max(mx, float(s[1]))
-                for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], s[3:7]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
-            except Exception:
-                continue
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+        reasons = []
+        if self.nv is not None:
+            names = {
+                "hw_slowdown": "nvmlClocksEventReasonHwSlowdown", "hw_thermal_slowdown": "nvmlClocksEventReasonHwThermalSlowdown",
+                "sw_thermal_slowdown": "nvmlClocksEventReasonSwThermalSlowdown", "sw_power_cap": "nvmlClocksEventReasonSwPowerCap",
+                "hw_power_brake_slowdown": "nvmlClocksEventReasonHwPowerBrakeSlowdown",
+            }
+            for label, const in names.items():
+                bit = getattr(self.nv, const, None)
+                if bit is None:
+                    bit = getattr(self.nv, const.replace("ClocksEventReason", "ClocksThrottleReason"), 0)
+                if bit and self.reason_bits & int(bit):
+                    reasons.append(label)
+        sm = sorted(self.samples)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_min_mhz": sm[0] if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(reasons), "samples": len(sm), "source": "nvml" if self.nv is not None else "nvidia-smi"}
 
 
 def api_bound_model(templates: int, shards: int, writes: float) -> dict:
