@@ -281,18 +281,15 @@ def run_ours(args):
     recvbuf = torch.zeros(world * sendbuf.numel(), dtype=torch.int32, device=f"cuda:{local}") if world > 1 else None
 
     def step():
-        """One scan; at N>1 followed by the single all-gather of the per-GPU diff lists."""
-        ctx.scan_launch(ca, sas, mode)
-        d = ctx.scan_finish()
-        if world > 1:
-            M.gather_diffs(d, sendbuf, recvbuf, ext, cap_entries)
-        st = ctx.last_stats()
-        d.close()
-        return st
+        """One scan, fully asynchronous: the compaction kernel writes the diff list into `sendbuf`
+        (ncd_scan_into) and, at N>1, the single all-gather of the per-GPU lists is queued behind it."""
+        M.scan_and_gather(ctx, ca, sas, mode, sendbuf, recvbuf, ext, cap_entries)
 
+    if args.steps > 60:
+        sys.exit("--steps <= 60 (per-scan phase timings are kept for the last 64 scans)")
     # warm-up
     for _ in range(max(args.warmup, 3) if not args.allow_short_warmup else args.warmup):
-        st = step()
+        step()
     torch.cuda.synchronize()
     if dist:
         dist.barrier()
@@ -302,19 +299,26 @@ def run_ours(args):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     e0.record(ext)
+    for _ in range(args.steps):
+        step()
+    e1.record(ext)
+    torch.cuda.synchronize()
+    elapsed_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    # per-scan phase timings of the timed steps (CUDA events recorded by the library on its stream)
     cmp_ms, tot_ms, launches = [], [], 0
     phases = {"join_ms": 0.0, "hash_ms": 0.0, "compare_ms": 0.0, "classify_ms": 0.0}
-    for _ in range(args.steps):
-        st = step()
+    for back in range(args.steps):
+        st = ctx.stats_back(back)
         cmp_ms.append(st.compare_ms if mode == A.MODE_DIRECT else st.hash_ms)
         tot_ms.append(st.total_ms)
         launches += st.launches
         for k in phases:
             phases[k] += getattr(st, k) / args.steps
-    e1.record(ext)
-    torch.cuda.synchronize()
-    elapsed_ms = e0.elapsed_time(e1)
-    clocks = sampler.stop() if rank == 0 else None
+    hdr = sendbuf[:4].cpu().numpy().view(np.uint32)
+    if hdr[3]:
+        raise RuntimeError(f"diff list of {hdr[0]} entries exceeds --gather-cap {cap_entries}")
+    assert int(hdr[0]) == st.ndiff
     gathered_total = None
     if dist:
         parts = M.unpack_gathered(recvbuf.cpu().numpy().view(np.uint32), world, cap_entries)
@@ -411,18 +415,21 @@ def run_e2e(ctx, args, mode, world, rank, dist, ext, gather):
     arenas = [h for h, _ in hosts]
 
     def timed(step, reps, warm):
+        """Median step time: the box is shared (PCIe and host memory traffic of other tenants shows up
+        as single slow steps), every step is bracketed by its own events on the library's stream."""
         for _ in range(warm):
             out = step()
         torch.cuda.synchronize()
         if dist:
             dist.barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(ext)
-        for _ in range(reps):
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+        evs[0].record(ext)
+        for i in range(reps):
             out = step()
-        e1.record(ext)
+            evs[i + 1].record(ext)
         torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / reps
+        per_step = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(reps))
+        ms = per_step[len(per_step) // 2]
         if dist:
             t = torch.tensor([ms], device=f"cuda:{ctx.device}")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -454,7 +461,7 @@ def run_e2e(ctx, args, mode, world, rank, dist, ext, gather):
         "d2h_bytes_per_step": int(total(ents.nbytes + 64)), "ms_per_step": cold_ms, "gb_per_s": algo / (cold_ms / 1e3) / 1e9,
         "sample": f"{args.workload}: first {args.e2e_groups} groups = {int(total(hosts[0][1].nobj))} objects x {S} shards in pinned "
                   f"host arenas{' split over ' + str(world) + ' ranks by key hash' if world > 1 else ''}; "
-                  f"step = H2D of every arena + index build + scan + diff list D2H",
+                  f"step = H2D of every arena + index build + scan + diff list D2H; median of {reps} steps",
     }
 
     # resident: rewrite ~0.1 % of the records of every cluster per step, pull them, scan
@@ -506,7 +513,7 @@ def main():
     ap.add_argument("--cpu-sample-groups", type=int, default=6000)
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     ap.add_argument("--e2e-groups", type=int, default=40000)
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--resident-fraction", type=float, default=0.001, help="records rewritten per cluster per resident e2e step")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")

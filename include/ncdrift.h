@@ -216,6 +216,17 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
                     int nshards, uint32_t mode);
 int ncd_scan_finish(ncd_ctx* ctx, ncd_diff** out);
 int ncd_scan_last_stats(ncd_ctx* ctx, ncd_scan_stats* out);
+/* Stats of the scan enqueued `back` scans before the latest one (0 = latest; the last 64 are
+ * kept).  The scan must have completed on the GPU (synchronise first). */
+int ncd_scan_stats_back(ncd_ctx* ctx, uint64_t back, ncd_scan_stats* out);
+/* The same drift check, fully asynchronous and without any allocation or host round trip: the
+ * diff list is written by the compaction kernel straight into a caller-owned DEVICE buffer laid
+ * out like ncd_diff_pack's (uint32 header[4] = {entries found, nshards, rows, 1 if the buffer
+ * was too small} + entries).  This is the form the multi-GPU path uses: the buffer is the send
+ * buffer of the all-gather, so scan and collective queue back to back on the GPU.  The call
+ * returns once everything is enqueued on the ctx stream; no ncd_scan_finish is needed. */
+int ncd_scan_into(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+                  uint32_t mode, void* dev_out, uint64_t cap_entries);
 
 /* Host view of a diff list (copied device -> pinned host on first use). */
 int ncd_diff_view(ncd_diff* d, const ncd_entry** entries, uint64_t* n);

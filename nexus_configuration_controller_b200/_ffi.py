@@ -118,6 +118,8 @@ PROTOTYPES = {
     "ncd_scan_launch": (C.c_int, [VP, VP, C.POINTER(VP), C.c_int, C.c_uint32]),
     "ncd_scan_finish": (C.c_int, [VP, C.POINTER(VP)]),
     "ncd_scan_last_stats": (C.c_int, [VP, C.POINTER(ScanStats)]),
+    "ncd_scan_stats_back": (C.c_int, [VP, C.c_uint64, C.POINTER(ScanStats)]),
+    "ncd_scan_into": (C.c_int, [VP, VP, C.POINTER(VP), C.c_int, C.c_uint32, VP, C.c_uint64]),
     "ncd_diff_view": (C.c_int, [VP, C.POINTER(C.POINTER(Entry)), u64p]),
     "ncd_diff_device": (C.c_int, [VP, C.POINTER(VP), u64p]),
     "ncd_diff_pack": (C.c_int, [VP, VP, C.c_uint64]),

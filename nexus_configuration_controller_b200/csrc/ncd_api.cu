@@ -57,8 +57,10 @@ extern "C" int ncd_init(int device, ncd_ctx** out) {
   if (const char* v = getenv("NCD_COMPARE_CTAS")) ctx->compare_ctas_per_sm = atoi(v) > 0 ? atoi(v) : 8;
   NCD_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   for (int i = 0; i < 8; ++i) NCD_CUDA(cudaEventCreate(&ctx->ev[i]));
+  for (int r = 0; r < NCD_EV_RING; ++r)
+    for (int i = 0; i < 5; ++i) NCD_CUDA(cudaEventCreate(&ctx->evr[r][i]));
   NCD_CUDA(cudaMalloc((void**)&ctx->d_counters, 8 * sizeof(uint64_t)));
-  NCD_CUDA(cudaMallocHost((void**)&ctx->h_counters, 8 * sizeof(uint64_t)));
+  NCD_CUDA(cudaMallocHost((void**)&ctx->h_counters, NCD_EV_RING * 8 * sizeof(uint64_t)));
   // keep stream-ordered allocations cached: the per-scan diff buffers come from this pool
   cudaMemPool_t pool;
   if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
@@ -79,6 +81,8 @@ extern "C" void ncd_destroy(ncd_ctx* ctx) {
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   for (int i = 0; i < 8; ++i) cudaEventDestroy(ctx->ev[i]);
+  for (int r = 0; r < NCD_EV_RING; ++r)
+    for (int i = 0; i < 5; ++i) cudaEventDestroy(ctx->evr[r][i]);
   cudaStreamDestroy(ctx->stream);
   free(ctx);
 }

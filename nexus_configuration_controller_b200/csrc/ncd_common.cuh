@@ -72,13 +72,18 @@ struct DevArena {
   const uint32_t* sha;      // [nobj][8]
 };
 
+constexpr int NCD_EV_RING = 64;
+
 struct ncd_ctx {
   int device;
   int sm_count;
   int compare_variant;      // -1 = pick per scan, 0 = per-shard loop, 1/2/4 = grouped with CH vectors per lane
   int compare_ctas_per_sm;  // grid = sm_count * this
   cudaStream_t stream;
-  cudaEvent_t ev[8];
+  cudaEvent_t ev[8];                        // ev[5], ev[6]: ncd_hash_arena
+  cudaEvent_t evr[NCD_EV_RING][5];          // per-scan phase events, ring indexed by scan_seq
+  ncd_scan_stats stats_ring[NCD_EV_RING];   // host-known part of each scan's stats
+  uint64_t scan_seq;                        // scans enqueued so far
   // scratch of the scan, grown on demand and kept
   void* scratch;
   size_t scratch_bytes;

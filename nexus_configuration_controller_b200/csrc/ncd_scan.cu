@@ -272,7 +272,7 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
 __global__ void __launch_bounds__(256)
 k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ row_obj,
        const uint32_t* __restrict__ row_dep, const uint8_t* __restrict__ codes,
-       const uint32_t* __restrict__ blk_off, ncd_entry* __restrict__ out) {
+       const uint32_t* __restrict__ blk_off, ncd_entry* __restrict__ out, uint64_t cap) {
   __shared__ uint32_t warp_cnt[8];
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -290,8 +290,18 @@ k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ r
     e.dep = dep == NCD_NOTFOUND ? 0u : dep - ctrl.dep_start[obj] + 1u;
     e.shard = s;
     e.code = code;
-    out[pos] = e;
+    if (pos < cap) out[pos] = e;  // a caller-sized buffer may be too small: the header says so
   }
+}
+
+// Header of a packed diff list: {entries found, shards, rows (low 32 bits), 1 if the buffer was too small}.
+__global__ void k_header(const uint32_t* __restrict__ counters, uint32_t S, uint32_t rows, uint64_t cap,
+                         uint32_t* __restrict__ hdr) {
+  const uint32_t n = counters[0];
+  hdr[0] = n;
+  hdr[1] = S;
+  hdr[2] = rows;
+  hdr[3] = n > cap ? 1u : 0u;
 }
 
 // ------------------------------------------------------------------ host side
@@ -327,9 +337,11 @@ static int check_scan_args(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena*
   return NCD_OK;
 }
 
-int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
-                    uint32_t mode) {
-  NCD_TRY(check_scan_args(ctx, ctrl, shards, nshards, mode));
+// Enqueues one whole scan on the ctx stream.  Codes go to a buffer of rows x shards bytes: the
+// diff object's, or (d == nullptr) the tail of the ctx scratch; entries go to `entries_out`
+// (capacity `entry_cap`); when `hdr_out` is given a header is written there on the device.
+static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+                        uint32_t mode, ncd_diff* d, ncd_entry* entries_out, uint64_t entry_cap, uint32_t* hdr_out) {
   NCD_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
   const uint32_t S = (uint32_t)nshards;
@@ -337,9 +349,11 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
   const uint64_t npairs = nc * S, nq = nrows * S;
   const uint32_t hm = mode & 0xff;
   uint32_t launches = 0, variant_used = 0;
+  const int slot = (int)(ctx->scan_seq % NCD_EV_RING);
+  cudaEvent_t* evs = ctx->evr[slot];
 
   // digests first (hash modes): every copy is hashed once, digests are kept with the arena
-  NCD_CUDA(cudaEventRecord(ctx->ev[0], st));
+  NCD_CUDA(cudaEventRecord(evs[0], st));
   if (hm != NCD_MODE_DIRECT) {
     if (mode & NCD_MODE_REHASH) {
       ncd_arena* all[1] = {const_cast<ncd_arena*>(ctrl)};
@@ -353,7 +367,7 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
     for (uint32_t s = 0; s < S; ++s)
       NCD_TRY(ncd_hash_launch(ctx, const_cast<ncd_arena*>(shards[s]), hm, &launches));
   }
-  NCD_CUDA(cudaEventRecord(ctx->ev[1], st));
+  NCD_CUDA(cudaEventRecord(evs[1], st));
 
   // shard descriptors
   if ((int)S > ctx->d_shards_cap) {
@@ -387,7 +401,8 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
   size_t o_cnt = o_idx + ncd_align_up(npairs * 4, 256);
   size_t o_bo = o_cnt + ncd_align_up((nblk + 1) * 4, 256);
   size_t o_dv = o_bo + ncd_align_up((nblk + 2) * 4, 256);
-  size_t total = o_dv + ncd_align_up(npairs, 256);
+  size_t o_codes = o_dv + ncd_align_up(npairs, 256);
+  size_t total = o_codes + (d ? 0 : ncd_align_up(nq, 256));
   void* base = nullptr;
   NCD_TRY(ncd_ctx_scratch(ctx, total, &base));
   uint64_t* sh_off = (uint64_t*)((char*)base + o_off);
@@ -396,21 +411,7 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
   uint32_t* blk_off = (uint32_t*)((char*)base + o_bo);
   uint8_t* dv = (uint8_t*)((char*)base + o_dv);
 
-  ncd_diff* d = (ncd_diff*)calloc(1, sizeof(ncd_diff));
-  if (!d) return NCD_E_NOMEM;
-  d->ctx = ctx;
-  d->rows = nrows;
-  d->nshards = S;
-  cudaError_t e1 = cudaMallocAsync((void**)&d->d_codes, nq ? nq : 1, st);
-  cudaError_t e2 = cudaMallocAsync((void**)&d->d_entries, (nq ? nq : 1) * sizeof(ncd_entry), st);
-  if (e1 != cudaSuccess || e2 != cudaSuccess) {
-    ncd_set_error("ncd_scan: diff buffers (%llu decisions): %s", (unsigned long long)nq,
-                  cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
-    if (e1 == cudaSuccess) cudaFreeAsync(d->d_codes, st);
-    if (e2 == cudaSuccess) cudaFreeAsync(d->d_entries, st);
-    free(d);
-    return NCD_E_NOMEM;
-  }
+  uint8_t* codes = d ? d->d_codes : (uint8_t*)base + o_codes;
   uint32_t* counters = (uint32_t*)ctx->d_counters;
   NCD_CUDA(cudaMemsetAsync(counters, 0, 8 * sizeof(uint64_t), st));
 
@@ -419,7 +420,7 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
                                                              sh_off, dv);
     ++launches;
   }
-  NCD_CUDA(cudaEventRecord(ctx->ev[2], st));
+  NCD_CUDA(cudaEventRecord(evs[2], st));
   const bool do_compare = (hm == NCD_MODE_DIRECT) || (mode & NCD_MODE_CONFIRM);
   if (do_compare && npairs && ctrl->ntiles) {
     // Three data-movement shapes for the same compare, picked from the mean tile fill
@@ -467,34 +468,111 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
     }
     ++launches;
   }
-  NCD_CUDA(cudaEventRecord(ctx->ev[3], st));
+  NCD_CUDA(cudaEventRecord(evs[3], st));
   if (nq) {
     k_classify<<<(unsigned)nblk, 256, 0, st>>>(dctrl, ctx->d_shards, S, nrows, ctrl->row_obj,
-                                               ctrl->row_dep, ctrl->row_cidx, sh_idx, dv, d->d_codes,
+                                               ctrl->row_dep, ctrl->row_cidx, sh_idx, dv, codes,
                                                blk_cnt);
     ++launches;
   }
   NCD_TRY(ncd_exclusive_scan_u32(ctx, blk_cnt, blk_off, nblk, counters));
   launches += nblk ? 3 : 0;
   if (nq) {
-    k_emit<<<(unsigned)nblk, 256, 0, st>>>(dctrl, S, nrows, ctrl->row_obj, ctrl->row_dep, d->d_codes,
-                                           blk_off, d->d_entries);
+    k_emit<<<(unsigned)nblk, 256, 0, st>>>(dctrl, S, nrows, ctrl->row_obj, ctrl->row_dep, codes, blk_off,
+                                           entries_out, entry_cap);
     ++launches;
   }
-  NCD_CUDA(cudaEventRecord(ctx->ev[4], st));
-  NCD_CUDA(cudaMemcpyAsync(ctx->h_counters, counters, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  if (hdr_out) {
+    k_header<<<1, 1, 0, st>>>(counters, S, (uint32_t)nrows, entry_cap, hdr_out);
+    ++launches;
+  }
+  NCD_CUDA(cudaEventRecord(evs[4], st));
+  NCD_CUDA(cudaMemcpyAsync(ctx->h_counters + (size_t)slot * 8, counters, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
   NCD_CUDA(cudaGetLastError());
 
-  memset(&ctx->stats, 0, sizeof(ctx->stats));
-  ctx->stats.rows = nrows;
-  ctx->stats.pairs = nq;
-  ctx->stats.algo_bytes = algo;
-  ctx->stats.launches = launches;
-  ctx->stats.compare_variant = variant_used;
+  ncd_scan_stats& stt = ctx->stats_ring[slot];
+  memset(&stt, 0, sizeof(stt));
+  stt.rows = nrows;
+  stt.pairs = nq;
+  stt.algo_bytes = algo;
+  stt.launches = launches;
+  stt.compare_variant = variant_used;
+  ++ctx->scan_seq;
+  return NCD_OK;
+}
+
+// Phase timings + counters of the scan enqueued `back` scans ago (0 = the latest).  The scan must
+// have completed on the GPU.
+static int stats_of(ncd_ctx* ctx, uint64_t back, ncd_scan_stats* out) {
+  if (back >= ctx->scan_seq || back >= NCD_EV_RING) {
+    ncd_set_error("scan stats: only the last %d scans are kept (asked for %llu back of %llu)", NCD_EV_RING,
+                  (unsigned long long)back, (unsigned long long)ctx->scan_seq);
+    return NCD_E_INVALID;
+  }
+  const int slot = (int)((ctx->scan_seq - 1 - back) % NCD_EV_RING);
+  cudaEvent_t* evs = ctx->evr[slot];
+  ncd_scan_stats st = ctx->stats_ring[slot];
+  cudaError_t e = cudaEventElapsedTime(&st.total_ms, evs[0], evs[4]);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    ncd_set_error("scan stats: that scan has not finished on the GPU (%s)", cudaGetErrorString(e));
+    return NCD_E_STATE;
+  }
+  cudaEventElapsedTime(&st.hash_ms, evs[0], evs[1]);
+  cudaEventElapsedTime(&st.join_ms, evs[1], evs[2]);
+  cudaEventElapsedTime(&st.compare_ms, evs[2], evs[3]);
+  cudaEventElapsedTime(&st.classify_ms, evs[3], evs[4]);
+  const uint32_t* hc = (const uint32_t*)(ctx->h_counters + (size_t)slot * 8);
+  st.ndiff = hc[0];
+  st.hash_collisions = hc[1];
+  *out = st;
+  return NCD_OK;
+}
+
+int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+                    uint32_t mode) {
+  NCD_TRY(check_scan_args(ctx, ctrl, shards, nshards, mode));
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const uint64_t nq = ctrl->nrows * (uint64_t)nshards;
+  ncd_diff* d = (ncd_diff*)calloc(1, sizeof(ncd_diff));
+  if (!d) return NCD_E_NOMEM;
+  d->ctx = ctx;
+  d->rows = ctrl->nrows;
+  d->nshards = (uint64_t)nshards;
+  cudaError_t e1 = cudaMallocAsync((void**)&d->d_codes, nq ? nq : 1, st);
+  cudaError_t e2 = cudaMallocAsync((void**)&d->d_entries, (nq ? nq : 1) * sizeof(ncd_entry), st);
+  if (e1 != cudaSuccess || e2 != cudaSuccess) {
+    ncd_set_error("ncd_scan: diff buffers (%llu decisions): %s", (unsigned long long)nq,
+                  cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+    if (e1 == cudaSuccess) cudaFreeAsync(d->d_codes, st);
+    if (e2 == cudaSuccess) cudaFreeAsync(d->d_entries, st);
+    free(d);
+    return NCD_E_NOMEM;
+  }
+  int rc = scan_enqueue(ctx, ctrl, shards, nshards, mode, d, d->d_entries, nq, nullptr);
+  if (rc != NCD_OK) {
+    cudaFreeAsync(d->d_codes, st);
+    cudaFreeAsync(d->d_entries, st);
+    free(d);
+    return rc;
+  }
   ctx->pending = d;
   ctx->pending_mode = mode;
   ctx->scan_pending = true;
   return NCD_OK;
+}
+
+int ncd_scan_into(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards, uint32_t mode,
+                  void* dev_out, uint64_t cap_entries) {
+  if (!dev_out) {
+    ncd_set_error("ncd_scan_into: null output buffer");
+    return NCD_E_INVALID;
+  }
+  NCD_TRY(check_scan_args(ctx, ctrl, shards, nshards, mode));
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  return scan_enqueue(ctx, ctrl, shards, nshards, mode, nullptr, (ncd_entry*)((char*)dev_out + 16), cap_entries,
+                      (uint32_t*)dev_out);
 }
 
 int ncd_scan_finish(ncd_ctx* ctx, ncd_diff** out) {
@@ -515,16 +593,8 @@ int ncd_scan_finish(ncd_ctx* ctx, ncd_diff** out) {
     free(d);  // device buffers are lost with the context after a sticky error
     return NCD_E_CUDA;
   }
-  const uint32_t* hc = (const uint32_t*)ctx->h_counters;
-  d->n = hc[0];
-  ncd_scan_stats& st = ctx->stats;
-  st.ndiff = d->n;
-  st.hash_collisions = hc[1];
-  cudaEventElapsedTime(&st.hash_ms, ctx->ev[0], ctx->ev[1]);
-  cudaEventElapsedTime(&st.join_ms, ctx->ev[1], ctx->ev[2]);
-  cudaEventElapsedTime(&st.compare_ms, ctx->ev[2], ctx->ev[3]);
-  cudaEventElapsedTime(&st.classify_ms, ctx->ev[3], ctx->ev[4]);
-  cudaEventElapsedTime(&st.total_ms, ctx->ev[0], ctx->ev[4]);
+  NCD_TRY(stats_of(ctx, 0, &ctx->stats));
+  d->n = ctx->stats.ndiff;
   *out = d;
   return NCD_OK;
 }
@@ -539,13 +609,14 @@ int ncd_scan(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards
   return ncd_scan_finish(ctx, out);
 }
 
-int ncd_scan_last_stats(ncd_ctx* ctx, ncd_scan_stats* out) {
+int ncd_scan_last_stats(ncd_ctx* ctx, ncd_scan_stats* out) { return ncd_scan_stats_back(ctx, 0, out); }
+
+int ncd_scan_stats_back(ncd_ctx* ctx, uint64_t back, ncd_scan_stats* out) {
   if (!ctx || !out) {
-    ncd_set_error("ncd_scan_last_stats: null argument");
+    ncd_set_error("ncd_scan_stats_back: null argument");
     return NCD_E_INVALID;
   }
-  *out = ctx->stats;
-  return NCD_OK;
+  return stats_of(ctx, back, out);
 }
 
 // ------------------------------------------------------------------ diff lists

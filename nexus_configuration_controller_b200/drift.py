@@ -80,6 +80,16 @@ class Context:
         ctrl, ns = self._pending
         return Diff(self, out, ctrl, ns)
 
+    def scan_into(self, ctrl: "Arena", shards: Sequence["Arena"], mode: int, dev_ptr: int, cap_entries: int) -> None:
+        """Asynchronous scan whose diff list lands in a caller-owned device buffer (header + entries)."""
+        arr = (C.c_void_p * max(len(shards), 1))(*[s.handle for s in shards])
+        check(self.lib.ncd_scan_into(self.handle, ctrl.handle, arr, len(shards), mode, C.c_void_p(dev_ptr), cap_entries))
+
+    def stats_back(self, back: int) -> ScanStats:
+        st = ScanStats()
+        check(self.lib.ncd_scan_stats_back(self.handle, back, C.byref(st)))
+        return st
+
     def last_stats(self) -> ScanStats:
         st = ScanStats()
         check(self.lib.ncd_scan_last_stats(self.handle, C.byref(st)))

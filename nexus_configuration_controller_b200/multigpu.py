@@ -68,3 +68,18 @@ def gather_diffs(diff, sendbuf, recvbuf, scan_stream, cap_entries: int, group=No
     cur.wait_stream(scan_stream)
     dist.all_gather_into_tensor(recvbuf, sendbuf, group=group)
     scan_stream.wait_stream(cur)
+
+
+def scan_and_gather(ctx, ctrl, shards, mode: int, sendbuf, recvbuf, scan_stream, cap_entries: int, group=None):
+    """One multi-GPU step with no host round trip: the scan writes its diff list straight into
+    `sendbuf` (ncd_scan_into), the all-gather is queued right behind it.  Everything is enqueued
+    when this returns; synchronise before reading `recvbuf`."""
+    import torch
+    import torch.distributed as dist
+
+    ctx.scan_into(ctrl, shards, mode, sendbuf.data_ptr(), cap_entries)
+    if recvbuf is not None:
+        cur = torch.cuda.current_stream()
+        cur.wait_stream(scan_stream)
+        dist.all_gather_into_tensor(recvbuf, sendbuf, group=group)
+        scan_stream.wait_stream(cur)

@@ -219,3 +219,39 @@ def test_every_compare_variant_matches_oracle(variant, monkeypatch):
         d.close()
         for a in sas + [ca]:
             a.close()
+
+
+def test_scan_into_a_caller_buffer_matches_the_diff_object(ctx):
+    """ncd_scan_into: same diff list, written on the device into a caller-owned buffer (the
+    all-gather send buffer), no host round trip; too small a buffer is reported, not overrun."""
+    import torch
+
+    from nexus_configuration_controller_b200 import multigpu as M
+
+    ctrl, shards = random_clusters(4, n_templates=20, n_shards=4)
+    want_codes, want_ents = oracle.scan(ctrl, shards)
+    ca = ctx.arena_from_host(ctrl)
+    sas = [ctx.arena_from_host(h) for h in shards]
+    cap = len(want_ents) + 5
+    buf = torch.full((M.buffer_words(cap) + 64,), -1, dtype=torch.int32, device="cuda:0")
+    for mode in (A.MODE_DIRECT, A.MODE_HASH64):
+        ctx.scan_into(ca, sas, mode, buf.data_ptr(), cap)
+        ctx.sync()
+        host = buf.cpu().numpy().view(np.uint32)
+        (ns, rows, got), = M.unpack_gathered(host[: M.buffer_words(cap)], 1, cap)
+        assert (ns, rows) == (len(shards), want_codes.shape[0]) and host[3] == 0
+        np.testing.assert_array_equal(got, want_ents)
+        assert (host[M.buffer_words(cap):] == 0xFFFFFFFF).all()  # nothing written past the buffer
+        st = ctx.stats_back(0)
+        assert st.ndiff == len(want_ents) and st.pairs == want_codes.size and st.total_ms > 0
+    # a buffer that is too small: header says so, entries up to the capacity are the first ones
+    small = 3
+    buf.fill_(-1)
+    ctx.scan_into(ca, sas, A.MODE_DIRECT, buf.data_ptr(), small)
+    ctx.sync()
+    host = buf.cpu().numpy().view(np.uint32)
+    assert host[0] == len(want_ents) and host[3] == 1
+    np.testing.assert_array_equal(host[4 : 4 + 4 * small].reshape(small, 4), want_ents[:small])
+    assert (host[4 + 4 * small :] == 0xFFFFFFFF).all()
+    for a in sas + [ca]:
+        a.close()
