@@ -149,6 +149,18 @@ def api_bound_model(templates: int, shards: int, writes: float) -> dict:
     }
 
 
+def ncu_traffic(workload: str, kernel: str, n_gpus: int, default_size: bool):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture, if one matches."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)[workload][kernel]
+        if default_size and t["n_gpus"] == n_gpus:
+            return t["dram_bytes_per_launch"], t["source"]
+    except Exception:
+        pass
+    return None, None
+
+
 def hbm_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -340,6 +352,9 @@ def run_ours(args):
         peak, peak_src = hbm_peak()
         kern_ms = sum(cmp_ms) / len(cmp_ms)
         achieved = st.algo_bytes / (kern_ms / 1e3) / 1e9  # this rank's kernel over this rank's bytes
+        kernel_name = ({0: "k_compare", 1: "k_compare_grouped<1>", 2: "k_compare_grouped<2>", 4: "k_compare_grouped<4>", 8: "k_compare_tma"}.get(st.compare_variant, "k_compare")
+                       if mode == A.MODE_DIRECT else ("k_h64_tiles" if args.mode == "hash64" else "k_sha256"))
+        traffic, traffic_src = ncu_traffic(args.workload, kernel_name, world, args.groups is None and not os.environ.get("NCD_BENCH_LEN"))
         result = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -352,9 +367,9 @@ def run_ours(args):
             },
             "gb_per_s": algo_all / (ms_per_step / 1e3) / 1e9,
             "roofline": {
-                "bound": "hbm", "kernel": {0: "k_compare", 1: "k_compare_grouped<1>", 2: "k_compare_grouped<2>", 4: "k_compare_grouped<4>", 8: "k_compare_tma"}.get(st.compare_variant, "k_compare") if mode == A.MODE_DIRECT else ("k_h64_tiles" if args.mode == "hash64" else "k_sha256"),
+                "bound": "hbm", "kernel": kernel_name,
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
-                "traffic": None, "kernel_ms": kern_ms, "scan_ms": sum(tot_ms) / len(tot_ms),
+                "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": int(st.algo_bytes), "kernel_ms": kern_ms, "scan_ms": sum(tot_ms) / len(tot_ms),
                 "phases_ms": {k: round(v, 4) for k, v in phases.items()},
             },
             "gpu_launches": int(launches_all),
