@@ -63,6 +63,14 @@ int ncdh_lookup(ncdh_checker* c, uint32_t kind, const char* ns, const char* name
 int64_t ncdh_plan_template(ncdh_checker* c, const char* ns, const char* name, char* out, uint64_t cap);
 int64_t ncdh_plan_workgroup(ncdh_checker* c, const char* ns, const char* name, char* out, uint64_t cap);
 
+/* The batch sweep (row f-3): after one Scan, the work-queue feed — only the templates and
+ * workgroups with something to do, in controller-cache order.  Replaces re-enqueueing every
+ * object on every resync (controller.go:288-290, 301-303; main.go:70-71) and letting the 50/s
+ * limiter (controller.go:257-260) pace objects that did not drift.  Output, one line per item:
+ *   "<template|workgroup>\t<namespace/name>\n"   (Element{objRef, objTypeName}, controller.go:88-91).
+ * Returns the text length (written only if it fits cap) or -1. */
+int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap);
+
 /* Number of diff-list entries and decisions of the last Scan. */
 int ncdh_last_counts(ncdh_checker* c, uint64_t* ndiff, uint64_t* decisions);
 

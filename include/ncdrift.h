@@ -238,9 +238,32 @@ int ncd_diff_device(ncd_diff* d, const void** dev_entries, uint64_t* n);
  * send buffer of the all-gather (e.g. an NCCL-registered tensor).  cap_entries = entries the
  * buffer can hold after the header. */
 int ncd_diff_pack(ncd_diff* d, void* dev_buf, uint64_t cap_entries);
+/* The sweep feed: controller indices, ascending and without
+ * repeats, of the templates / workgroups that have at least one decision != NCD_SKIP — the only
+ * objects a resync sweep still has to hand to templateSyncHandler / workgroupSyncHandler.  In
+ * the reference every template and workgroup is re-enqueued on every 30 s resync
+ * (controller.go:288-290, 301-303 with main.go:70-71) and then waits for the 50 items/s limiter
+ * (controller.go:257-260) even when nothing drifted.  Writes at most cap indices, *n = the count. */
+int ncd_diff_dirty_objects(ncd_diff* d, uint32_t* obj_out, uint64_t cap, uint64_t* n);
 /* All codes, rows x nshards, row-major, SKIP included (tests and Lookup()). */
 int ncd_diff_codes(ncd_diff* d, uint8_t* codes_out, uint64_t cap);
 void ncd_diff_destroy(ncd_diff* d);
+
+/* ------------------------------------------------------------------ orphans (row f-4)
+ * Objects a shard holds that the controller cluster does not: the reverse join.  The reference
+ * has no such sweep — a template deleted while the controller was down stays on the shards
+ * forever, because deletion is only propagated from the delete EVENT (handleObject,
+ * controller.go:196-205) and the sync handlers never look at what a shard has beyond what the
+ * controller asks about.  The caller decides which shard objects it manages (the packer puts
+ * only those carrying the controller-app label into a shard arena, controller_test.go:183-188).
+ * Writes at most cap entries, ordered by (shard, object index in that shard's arena); *n = the
+ * number found. */
+typedef struct ncd_orphan {
+  uint32_t shard; /* index into the shard list            */
+  uint32_t obj;   /* object index in that shard's arena   */
+} ncd_orphan;
+int ncd_find_orphans(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+                     ncd_orphan* out, uint64_t cap, uint64_t* n);
 
 /* ------------------------------------------------------------------ hashing */
 /* Hashes every record of a committed arena on the GPU and copies the digests out.

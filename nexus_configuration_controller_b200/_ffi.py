@@ -123,8 +123,10 @@ PROTOTYPES = {
     "ncd_diff_view": (C.c_int, [VP, C.POINTER(C.POINTER(Entry)), u64p]),
     "ncd_diff_device": (C.c_int, [VP, C.POINTER(VP), u64p]),
     "ncd_diff_pack": (C.c_int, [VP, VP, C.c_uint64]),
+    "ncd_diff_dirty_objects": (C.c_int, [VP, u32p, C.c_uint64, u64p]),
     "ncd_diff_codes": (C.c_int, [VP, u8p, C.c_uint64]),
     "ncd_diff_destroy": (None, [VP]),
+    "ncd_find_orphans": (C.c_int, [VP, VP, C.POINTER(VP), C.c_int, u32p, C.c_uint64, u64p]),
     "ncd_hash_arena": (C.c_int, [VP, VP, C.c_uint32, VP, C.c_uint64, C.POINTER(C.c_float)]),
     "ncd_hash64_static": (C.c_int, [VP, VP, VP, C.c_uint64, VP, VP]),
     "ncd_synth_sizes": (C.c_int, [VP, C.POINTER(SynthCfg), C.c_int, u64p, u64p, u64p, u64p, u64p]),

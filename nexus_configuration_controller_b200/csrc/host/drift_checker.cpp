@@ -151,6 +151,7 @@ struct ncdh_checker {
   std::vector<uint8_t> codes;                          // rows x nshards
   std::unordered_map<std::string, uint64_t> first_row;  // store_key -> first row of a template / workgroup
   std::unordered_map<std::string, CachedObject> snap;   // the controller objects the rows were made from
+  std::vector<std::string> dirty;                       // sweep feed of the last Scan: "<type>\t<ns/name>"
   uint64_t rows = 0, ndiff = 0;
 
   ClusterImage* image(int cluster) {
@@ -263,6 +264,13 @@ int ncdh_scan(ncdh_checker* c) {
     c->ndiff = st.ndiff;
     c->codes.assign(st.rows * ptrs.size(), 0);
     int rc = ncd_diff_codes(d, c->codes.data(), c->codes.size());
+    std::vector<uint32_t> dirty_idx;
+    if (rc == NCD_OK) {
+      uint64_t nd = 0;
+      rc = ncd_diff_dirty_objects(d, nullptr, 0, &nd);
+      dirty_idx.resize(nd);
+      if (rc == NCD_OK && nd) rc = ncd_diff_dirty_objects(d, dirty_idx.data(), nd, &nd);
+    }
     ncd_diff_destroy(d);
     if (rc != NCD_OK) return fail(ncd_err("ncd_diff_codes"));
     // row numbering: arena order, one row per template + one per dependent, one per workgroup
@@ -277,6 +285,11 @@ int ncdh_scan(ncdh_checker* c) {
       }
     }
     if (row != st.rows) return fail("ncdh_scan: row count disagrees with the library");
+    c->dirty.clear();
+    for (uint32_t i : dirty_idx) {
+      if (i >= order.size()) return fail("ncdh_scan: dirty object index out of range");
+      c->dirty.push_back(std::string(order[i]->kind == NCD_KIND_TEMPLATE ? "template" : "workgroup") + "\t" + order[i]->key);
+    }
     c->scanned = true;
   } catch (const std::exception& e) {
     return fail(std::string("ncdh_scan: ") + e.what());
@@ -362,6 +375,14 @@ int64_t ncdh_plan_workgroup(ncdh_checker* c, const char* ns, const char* name, c
     if (code == NCD_CREATE) acts.push_back({(int)s, "nexus", "create", "NexusAlgorithmWorkgroups", it->second.name});      // :735-738
   }
   return render(acts, "", out, cap);
+}
+
+int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap) {
+  if (!c || !c->scanned) return fail("ncdh_sweep_queue: no scan yet");
+  std::string s;
+  for (const std::string& line : c->dirty) s += line + "\n";
+  if (out && s.size() <= cap) memcpy(out, s.data(), s.size());
+  return (int64_t)s.size();
 }
 
 int ncdh_last_counts(ncdh_checker* c, uint64_t* ndiff, uint64_t* decisions) {

@@ -673,6 +673,25 @@ int ncd_diff_pack(ncd_diff* d, void* dev_buf, uint64_t cap_entries) {
   return NCD_OK;
 }
 
+int ncd_diff_dirty_objects(ncd_diff* d, uint32_t* obj_out, uint64_t cap, uint64_t* n) {
+  if (!d || !n || (!obj_out && cap)) {
+    ncd_set_error("ncd_diff_dirty_objects: null argument");
+    return NCD_E_INVALID;
+  }
+  const ncd_entry* e = nullptr;
+  uint64_t ne = 0;
+  NCD_TRY(ncd_diff_view(d, &e, &ne));
+  // the list is in (row, shard) order and rows are grouped by owning object: equal objs are adjacent
+  uint64_t count = 0;
+  for (uint64_t i = 0; i < ne; ++i) {
+    if (i && e[i].obj == e[i - 1].obj) continue;
+    if (count < cap) obj_out[count] = e[i].obj;
+    ++count;
+  }
+  *n = count;
+  return NCD_OK;
+}
+
 int ncd_diff_codes(ncd_diff* d, uint8_t* codes_out, uint64_t cap) {
   if (!d || (!codes_out && cap)) {
     ncd_set_error("ncd_diff_codes: null argument");

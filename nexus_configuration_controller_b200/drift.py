@@ -90,6 +90,16 @@ class Context:
         check(self.lib.ncd_scan_stats_back(self.handle, back, C.byref(st)))
         return st
 
+    def find_orphans(self, ctrl: "Arena", shards: Sequence["Arena"], cap: int = 1 << 20) -> np.ndarray:
+        """uint32[n, 2] of (shard, object index in that shard's arena) the controller does not hold."""
+        arr = (C.c_void_p * max(len(shards), 1))(*[s.handle for s in shards])
+        out = np.zeros((max(cap, 1), 2), dtype=np.uint32)
+        n = C.c_uint64()
+        check(self.lib.ncd_find_orphans(self.handle, ctrl.handle, arr, len(shards), out.ctypes.data_as(_ffi.u32p), cap, C.byref(n)))
+        if n.value > cap:
+            return self.find_orphans(ctrl, shards, cap=n.value)
+        return out[: n.value].copy()
+
     def last_stats(self) -> ScanStats:
         st = ScanStats()
         check(self.lib.ncd_scan_last_stats(self.handle, C.byref(st)))
@@ -231,6 +241,14 @@ class Diff:
     def pack_into(self, dev_ptr: int, cap_entries: int) -> None:
         """Header + entries into a caller-owned device buffer (the all-gather send buffer)."""
         check(self.ctx.lib.ncd_diff_pack(self.handle, C.c_void_p(dev_ptr), cap_entries))
+
+    def dirty_objects(self) -> np.ndarray:
+        """Controller indices of the templates / workgroups a sweep still has to reconcile."""
+        n = C.c_uint64()
+        check(self.ctx.lib.ncd_diff_dirty_objects(self.handle, None, 0, C.byref(n)))
+        out = np.zeros(max(n.value, 1), dtype=np.uint32)
+        check(self.ctx.lib.ncd_diff_dirty_objects(self.handle, out.ctypes.data_as(_ffi.u32p), n.value, C.byref(n)))
+        return out[: n.value]
 
     def codes(self) -> np.ndarray:
         """All decision codes, uint8[rows, nshards]."""

@@ -27,6 +27,7 @@ PROTOTYPES = {
     "ncdh_lookup": (C.c_int, [VP, C.c_uint32, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint32)]),
     "ncdh_plan_template": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
     "ncdh_plan_workgroup": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
+    "ncdh_sweep_queue": (C.c_int64, [VP, C.c_char_p, C.c_uint64]),
     "ncdh_last_counts": (C.c_int, [VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
 }
 _lib = None
@@ -135,6 +136,15 @@ class DriftChecker:
 
     def plan_workgroup(self, namespace: str, name: str):
         return self._plan(self.lib.ncdh_plan_workgroup, namespace, name)
+
+    def sweep_queue(self) -> List[Tuple[str, str]]:
+        """(objTypeName, "namespace/name") of every template / workgroup the last scan found work for."""
+        n = self.lib.ncdh_sweep_queue(self.h, None, 0)
+        if n < 0:
+            raise _err()
+        buf = C.create_string_buffer(max(n, 1))
+        self.lib.ncdh_sweep_queue(self.h, buf, n)
+        return [tuple(line.split("\t")) for line in buf.raw[:n].decode().splitlines()]
 
     def counts(self) -> Tuple[int, int]:
         a, b = C.c_uint64(), C.c_uint64()
