@@ -78,6 +78,7 @@ extern "C" void ncd_destroy(ncd_ctx* ctx) {
   if (ctx->pending) ncd_diff_destroy(ctx->pending);
   if (ctx->scratch) cudaFree(ctx->scratch);
   if (ctx->d_shards) cudaFree(ctx->d_shards);
+  if (ctx->d_jobs) cudaFree(ctx->d_jobs);
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   for (int i = 0; i < 8; ++i) cudaEventDestroy(ctx->ev[i]);

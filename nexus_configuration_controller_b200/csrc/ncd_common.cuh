@@ -88,6 +88,8 @@ struct ncd_ctx {
   void* scratch;
   size_t scratch_bytes;
   DevArena* d_shards;  // device array of shard descriptors
+  void* d_jobs;        // device array of hash jobs (ncd_hash.cu)
+  int d_jobs_cap;
   int d_shards_cap;
   uint64_t* d_counters;  // [8] device counters (diff count, collisions, ...)
   uint64_t* h_counters;  // pinned mirror
@@ -205,6 +207,7 @@ int ncd_launch_compare_tma(ncd_ctx* ctx, const DevArena& dctrl, uint32_t S, cons
                            uint32_t* counters, uint32_t count_collisions);
 // ncd_hash.cu
 int ncd_hash_launch(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, uint32_t* launches);
+int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint32_t mode, uint32_t* launches);
 
 // ------------------------------------------------------------------ device helpers
 #ifdef __CUDACC__

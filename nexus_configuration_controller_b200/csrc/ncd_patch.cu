@@ -16,7 +16,7 @@ __global__ void __launch_bounds__(128)
 k_pull_records(const uint32_t* __restrict__ idx, const uint8_t* h_payload, const uint64_t* h_rec_off,
                const uint32_t* h_rec_len, uint8_t* __restrict__ d_payload, uint64_t* __restrict__ d_rec_off,
                uint32_t* __restrict__ d_rec_len, ObjMeta* __restrict__ meta, uint32_t nobj,
-               uint64_t payload_limit, uint32_t* __restrict__ bad) {
+               uint64_t payload_limit, uint32_t* __restrict__ bad /*[0] refused, [1] lengths changed*/) {
   const uint32_t i = idx[blockIdx.x];
   if (i >= nobj) {
     if (threadIdx.x == 0) atomicAdd(bad, 1u);
@@ -30,6 +30,7 @@ k_pull_records(const uint32_t* __restrict__ idx, const uint8_t* h_payload, const
     return;
   }
   if (threadIdx.x == 0) {
+    if (d_rec_len[i] != len) atomicAdd(bad + 1, 1u);  // tile lists depend on lengths only
     d_rec_off[i] = off;
     d_rec_len[i] = len;
     meta[i].rec_off = off;
@@ -67,20 +68,23 @@ int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, ui
   NCD_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t st = ctx->stream;
   uint32_t* d_idx = nullptr;
-  NCD_CUDA(cudaMallocAsync((void**)&d_idx, (n + 1) * 4, st));
+  NCD_CUDA(cudaMallocAsync((void**)&d_idx, (n + 2) * 4, st));
   NCD_CUDA(cudaMemcpyAsync(d_idx, obj_idx, n * 4, cudaMemcpyHostToDevice, st));
-  NCD_CUDA(cudaMemsetAsync(d_idx + n, 0, 4, st));
+  NCD_CUDA(cudaMemsetAsync(d_idx + n, 0, 8, st));
   k_pull_records<<<(unsigned)n, 128, 0, st>>>(d_idx, a->h.payload, a->h.rec_off, a->h.rec_len, a->d.payload,
                                               a->d.rec_off, a->d.rec_len, a->meta, (uint32_t)a->nobj,
                                               new_payload_bytes, d_idx + n);
-  uint32_t bad = 0;
-  NCD_CUDA(cudaMemcpyAsync(&bad, d_idx + n, 4, cudaMemcpyDeviceToHost, st));
+  uint32_t flags[2] = {0, 0};
+  NCD_CUDA(cudaMemcpyAsync(flags, d_idx + n, 8, cudaMemcpyDeviceToHost, st));
   NCD_CUDA(cudaFreeAsync(d_idx, st));
   NCD_CUDA(cudaStreamSynchronize(st));
   NCD_CUDA(cudaGetLastError());
   a->payload_bytes = new_payload_bytes;
   a->h64_valid = a->sha_valid = false;
-  NCD_TRY(ncd_rebuild_tiles(a));
+  const uint32_t bad = flags[0];
+  // same-length rewrites (the common event: a value changed in place) leave the tile lists and
+  // the byte count as they are
+  if (flags[1] || bad) NCD_TRY(ncd_rebuild_tiles(a));
   if (bad) {
     ncd_set_error("ncd_arena_sync_records: %u of %llu records were refused (index out of range, record "
                   "not 16-byte aligned or outside the payload); commit the arena again", bad,

@@ -13,6 +13,8 @@
 //   k_classify  decision code per (row, shard) from the verdicts + ownerReferences
 //               (reference: controller.go:484-502, 529-560, 591-622, 725-738, 795-808).
 //   k_emit      ordered stream compaction of the codes != SKIP into the diff list.
+#include <vector>
+
 #include "ncd_common.cuh"
 
 // ------------------------------------------------------------------ k_join
@@ -363,9 +365,10 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
         a->h64_valid = a->sha_valid = false;
       }
     }
-    NCD_TRY(ncd_hash_launch(ctx, const_cast<ncd_arena*>(ctrl), hm, &launches));
-    for (uint32_t s = 0; s < S; ++s)
-      NCD_TRY(ncd_hash_launch(ctx, const_cast<ncd_arena*>(shards[s]), hm, &launches));
+    std::vector<ncd_arena*> all;
+    all.push_back(const_cast<ncd_arena*>(ctrl));
+    for (uint32_t s = 0; s < S; ++s) all.push_back(const_cast<ncd_arena*>(shards[s]));
+    NCD_TRY(ncd_hash_launch_many(ctx, all.data(), (int)all.size(), hm, &launches));
   }
   NCD_CUDA(cudaEventRecord(evs[1], st));
 
