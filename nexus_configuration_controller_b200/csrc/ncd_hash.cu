@@ -82,22 +82,30 @@ k_h64_tiles(const HashJob* __restrict__ jobs, int njobs, uint64_t ntiles) {
       const uint32_t v = lane + 32 * u;
       d[u] = v < nvec ? ncd_ldg_stream(p + v) : make_uint4(0, 0, 0, 0);
     }
+    // bytes past rec_len in the record's last vector do not belong to the value: clear them once,
+    // outside the accumulate loop (one lane of one tile of a record ever takes this branch)
+    if (tail && (nvec - 1) % 32 == lane) {
+      const uint32_t ut = (nvec - 1) / 32;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if ((uint32_t)u == ut) {
+          uint32_t w[4] = {d[u].x, d[u].y, d[u].z, d[u].w};
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int nb = (int)tail - 4 * i;
+            if (nb <= 0) w[i] = 0;
+            else if (nb < 4) w[i] &= (1u << (8 * nb)) - 1u;
+          }
+          d[u] = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+    }
     uint64_t A = 0, B = 0;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const uint32_t v = lane + 32 * u;
       if (v < nvec) {
-        uint4 x = d[u];
-        if (tail && v == nvec - 1) {
-          uint32_t w[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            int nb = (int)tail - 4 * i;
-            if (nb <= 0) w[i] = 0;
-            else if (nb < 4) w[i] &= (1u << (8 * nb)) - 1u;
-          }
-          x = make_uint4(w[0], w[1], w[2], w[3]);
-        }
+        const uint4 x = d[u];
         const uint4 k = keys[v];
         const uint64_t d0 = (uint64_t)x.x | ((uint64_t)x.y << 32);
         const uint64_t d1 = (uint64_t)x.z | ((uint64_t)x.w << 32);
