@@ -97,7 +97,6 @@ struct ncd_ctx {
   bool scan_pending;
   struct ncd_diff* pending;
   ncd_scan_stats stats;
-  uint32_t pending_mode;
 };
 
 struct ncd_arena {
@@ -135,7 +134,6 @@ struct ncd_arena {
   uint64_t* h64;
   uint32_t* sha;
   bool h64_valid, sha_valid;
-  uint64_t* h64_parts;  // per tile partial digests
 };
 
 struct ncd_diff {

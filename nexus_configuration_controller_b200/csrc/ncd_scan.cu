@@ -357,17 +357,11 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   // digests first (hash modes): every copy is hashed once, digests are kept with the arena
   NCD_CUDA(cudaEventRecord(evs[0], st));
   if (hm != NCD_MODE_DIRECT) {
-    if (mode & NCD_MODE_REHASH) {
-      ncd_arena* all[1] = {const_cast<ncd_arena*>(ctrl)};
-      all[0]->h64_valid = all[0]->sha_valid = false;
-      for (uint32_t s = 0; s < S; ++s) {
-        ncd_arena* a = const_cast<ncd_arena*>(shards[s]);
-        a->h64_valid = a->sha_valid = false;
-      }
-    }
     std::vector<ncd_arena*> all;
     all.push_back(const_cast<ncd_arena*>(ctrl));
     for (uint32_t s = 0; s < S; ++s) all.push_back(const_cast<ncd_arena*>(shards[s]));
+    if (mode & NCD_MODE_REHASH)
+      for (ncd_arena* a : all) a->h64_valid = a->sha_valid = false;
     NCD_TRY(ncd_hash_launch_many(ctx, all.data(), (int)all.size(), hm, &launches));
   }
   NCD_CUDA(cudaEventRecord(evs[1], st));
@@ -561,7 +555,6 @@ int ncd_scan_launch(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const*
     return rc;
   }
   ctx->pending = d;
-  ctx->pending_mode = mode;
   ctx->scan_pending = true;
   return NCD_OK;
 }
