@@ -195,6 +195,16 @@ int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64
  * on every 30 s resync (main.go:70-71).  obj_idx: host array of n distinct object indices;
  * new_payload_bytes: the used payload size after the rewrite (<= capacity). */
 int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint64_t new_payload_bytes);
+/* Commit after a structural change (objects added, deleted or re-owned: informer AddFunc /
+ * DeleteFunc, controller.go:286-305, 319-355) WITHOUT re-uploading the payload that did not
+ * change.  The packer has rewritten the small per-object arrays in the pinned host arena (any
+ * object order; a surviving object keeps its rec_off, so its bytes stay where they are on the
+ * device; a deleted object's bytes simply become unreferenced) and appended the records of new
+ * objects behind payload_dirty_from.  This call uploads every array except payload, uploads
+ * payload[payload_dirty_from, payload_bytes) only, and rebuilds the index — per-object metadata
+ * is ~40 bytes, so a 1M-object arena re-commits in tens of MB instead of its 8.7 GB. */
+int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
+                       uint64_t nowner, uint64_t ndep, uint64_t payload_dirty_from);
 /* Copies the committed device arrays into caller buffers (sized from
  * ncd_arena_counts); any pointer in dst may be NULL to skip that array. */
 int ncd_arena_download(ncd_arena* a, ncd_arena_view* dst);

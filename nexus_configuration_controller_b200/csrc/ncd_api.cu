@@ -277,6 +277,42 @@ extern "C" int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_by
   return ncd_arena_commit_device(a, nobj, payload_bytes, aux_bytes, nowner, ndep);
 }
 
+extern "C" int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
+                                  uint64_t nowner, uint64_t ndep, uint64_t payload_dirty_from) {
+  if (!a) {
+    ncd_set_error("ncd_arena_recommit: null arena");
+    return NCD_E_INVALID;
+  }
+  if (a->flags != NCD_ARENA_HOST_PINNED) {
+    ncd_set_error("ncd_arena_recommit: the arena has no pinned host arrays");
+    return NCD_E_STATE;
+  }
+  if (!a->committed) {
+    ncd_set_error("ncd_arena_recommit: nothing is resident yet, use ncd_arena_commit");
+    return NCD_E_STATE;
+  }
+  if (payload_dirty_from > payload_bytes || (payload_dirty_from & 15)) {
+    ncd_set_error("ncd_arena_recommit: payload_dirty_from must be a multiple of 16 within the payload");
+    return NCD_E_INVALID;
+  }
+  NCD_TRY(check_counts(a, nobj, payload_bytes, aux_bytes, nowner, ndep));
+  NCD_CUDA(cudaSetDevice(a->ctx->device));
+  cudaStream_t st = a->ctx->stream;
+  for (int i = 0; i < kNumFields; ++i) {
+    const Field& f = kFields[i];
+    uint64_t bytes = field_count(f, payload_bytes, nobj, aux_bytes, nowner, ndep) * f.elem;
+    uint64_t from = 0;
+    if (f.cap_kind == 0) {  // payload: only what was appended
+      from = payload_dirty_from;
+      bytes = payload_bytes - payload_dirty_from;
+    }
+    if (bytes)
+      NCD_CUDA(cudaMemcpyAsync((char*)*field_ptr(&a->d, f) + from, (const char*)*field_ptr(&a->h, f) + from, bytes,
+                               cudaMemcpyHostToDevice, st));
+  }
+  return ncd_arena_commit_device(a, nobj, payload_bytes, aux_bytes, nowner, ndep);
+}
+
 extern "C" int ncd_arena_counts(ncd_arena* a, ncd_arena_view* c) {
   if (!a || !c) {
     ncd_set_error("ncd_arena_counts: null argument");

@@ -186,6 +186,10 @@ class Arena:
     def commit(self, nobj, payload_bytes, aux_bytes, nowner, ndep) -> None:
         check(self.ctx.lib.ncd_arena_commit(self.handle, nobj, payload_bytes, aux_bytes, nowner, ndep))
 
+    def recommit(self, nobj, payload_bytes, aux_bytes, nowner, ndep, payload_dirty_from) -> None:
+        """Structural change: re-upload the per-object arrays and only the appended payload."""
+        check(self.ctx.lib.ncd_arena_recommit(self.handle, nobj, payload_bytes, aux_bytes, nowner, ndep, payload_dirty_from))
+
     def sync_records(self, obj_idx: np.ndarray, new_payload_bytes: int) -> None:
         """Pushes the records of `obj_idx` (rewritten in the pinned host arrays) to the device copy."""
         idx = np.ascontiguousarray(obj_idx, dtype=np.uint32)

@@ -99,3 +99,84 @@ def test_sync_refuses_what_it_cannot_place(ctx):
         dev_only.close()
     finally:
         a.close()
+
+
+def test_structural_change_recommits_without_the_old_payload(ctx):
+    """Objects deleted, added and re-owned: the small arrays are rewritten and re-uploaded, records
+    that survive stay where they are on the device, only appended records cross PCIe."""
+    rng = random.Random(77)
+    ctrl_h, shard_hs = random_clusters(31, n_templates=12, n_shards=2)
+    arenas = [ctx.arena_from_host(ctrl_h)]
+    # shard 0 is resident with room to grow
+    sh = shard_hs[0]
+    a = Arena(ctx, sh.payload_bytes + (1 << 16), sh.nobj + 8, sh.aux_bytes + 4096, sh.nowner + 16, sh.ndep + 16, device_only=False)
+    a.fill_from(sh)
+    a.commit(sh.nobj, sh.payload_bytes, sh.aux_bytes, sh.nowner, sh.ndep)
+    other = ctx.arena_from_host(shard_hs[1])
+    try:
+        # rebuild shard 0's object list on the host: drop two objects, add one the controller has
+        # but the shard lacked, give one dependent another owner
+        objs = []
+        for i in range(sh.nobj):
+            owners = [(bool(sh.own_is_template[o]), sh.aux[int(sh.own_uid_off[o]) : int(sh.own_uid_off[o]) + int(sh.own_uid_len[o])].tobytes().decode())
+                      for o in range(int(sh.own_start[i]), int(sh.own_start[i + 1]))]
+            uid = sh.aux[int(sh.uid_off[i]) : int(sh.uid_off[i]) + int(sh.uid_len[i])].tobytes().decode()
+            objs.append((A.CachedObject(int(sh.kind[i]), sh.key(i), sh.record(i), uid=uid, owners=owners), int(sh.rec_off[i])))
+        del objs[3], objs[0]
+        for k, (o, off) in enumerate(objs):
+            if o.kind in (A.KIND_SECRET, A.KIND_CONFIGMAP) and o.owners:
+                o.owners = [(True, "a-new-owner")]
+                break
+        have = {(o.kind, o.key) for o, _ in objs}
+        added = None
+        for i in range(ctrl_h.nobj):
+            if (int(ctrl_h.kind[i]), ctrl_h.key(i)) not in have and int(ctrl_h.kind[i]) in (A.KIND_SECRET, A.KIND_CONFIGMAP):
+                added = A.CachedObject(int(ctrl_h.kind[i]), ctrl_h.key(i), ctrl_h.record(i), uid="fresh", owners=[(True, "x")])
+                break
+        assert added is not None
+        # write the new image into the pinned arrays: metadata from scratch, surviving records keep
+        # their offsets, the added record is appended behind the old payload end
+        arr = a.host_arrays()
+        dirty_from = sh.payload_bytes
+        used = dirty_from
+        aux = bytearray()
+
+        def put(b):
+            off = len(aux)
+            aux.extend(b)
+            return off, len(b)
+
+        oi = 0
+        final = objs + [(added, None)]
+        for i, (o, off) in enumerate(final):
+            if off is None:
+                off = used
+                pad = (len(o.canon) + 15) // 16 * 16
+                arr["payload"][off : off + len(o.canon)] = np.frombuffer(o.canon, dtype=np.uint8)
+                arr["payload"][off + len(o.canon) : off + pad] = 0
+                used += pad
+            arr["rec_off"][i], arr["rec_len"][i], arr["kind"][i] = off, len(o.canon), o.kind
+            arr["key_off"][i], arr["key_len"][i] = put(o.key.encode())
+            arr["uid_off"][i], arr["uid_len"][i] = put(o.uid.encode())
+            arr["own_start"][i] = oi
+            for is_t, uid in o.owners:
+                arr["own_is_template"][oi] = int(is_t)
+                arr["own_uid_off"][oi], arr["own_uid_len"][oi] = put(uid.encode())
+                oi += 1
+            arr["dep_start"][i] = 0
+        n = len(final)
+        arr["own_start"][n], arr["dep_start"][n] = oi, 0
+        arr["aux"][: len(aux)] = np.frombuffer(bytes(aux), dtype=np.uint8)
+        a.recommit(n, used, len(aux), oi, 0, dirty_from)
+        want_codes, want_ents = oracle.scan(arenas[0].download(), [a.download(), other.download()])
+        ref = A.pack([o for o, _ in final])  # the same contents, freshly packed
+        ref_codes, _ = oracle.scan(ctrl_h, [ref, shard_hs[1]])
+        np.testing.assert_array_equal(want_codes, ref_codes)
+        for mode in (A.MODE_DIRECT, A.MODE_HASH64):
+            d = ctx.scan(arenas[0], [a, other], mode)
+            np.testing.assert_array_equal(d.codes(), ref_codes)
+            np.testing.assert_array_equal(d.entries(), want_ents)
+            d.close()
+    finally:
+        for x in arenas + [a, other]:
+            x.close()
