@@ -45,7 +45,9 @@ int ncdh_cluster_add(ncdh_checker* c, int cluster, uint32_t kind, const char* ns
                      const char* const* configmap_names, int nconfigmaps);
 int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char* ns, const char* name);
 
-/* DriftChecker.Scan: canonicalise + pack every cluster into pinned arenas, commit, ncd_scan.
+/* DriftChecker.Scan: bring every cluster's resident arena up to date with what was added /
+ * removed since the last Scan (only changed records or the small per-object arrays cross PCIe,
+ * a full upload happens on the first Scan or when an arena runs out of room), then ncd_scan.
  * Replaces recomputing the six lister.Get and four reflect.DeepEqual per handler call. */
 int ncdh_scan(ncdh_checker* c);
 
@@ -70,6 +72,11 @@ int64_t ncdh_plan_workgroup(ncdh_checker* c, const char* ns, const char* name, c
  *   "<template|workgroup>\t<namespace/name>\n"   (Element{objRef, objTypeName}, controller.go:88-91).
  * Returns the text length (written only if it fits cap) or -1. */
 int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap);
+
+/* How a cluster's data has reached the GPU so far: scans that needed a full arena upload
+ * (ncd_arena_commit), a structural one (ncd_arena_recommit: per-object arrays + new records) or
+ * only rewritten records (ncd_arena_sync_records).  The arenas stay resident between scans. */
+int ncdh_upload_counts(ncdh_checker* c, int cluster, uint64_t* full, uint64_t* structural, uint64_t* values);
 
 /* Number of diff-list entries and decisions of the last Scan. */
 int ncdh_last_counts(ncdh_checker* c, uint64_t* ndiff, uint64_t* decisions);

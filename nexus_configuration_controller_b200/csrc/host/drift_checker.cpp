@@ -32,6 +32,7 @@ std::string ncd_err(const char* op) { return std::string(op) + ": " + ncd_last_e
 
 struct OwnerRef {
   std::string kind, uid;
+  bool operator==(const OwnerRef& o) const { return kind == o.kind && uid == o.uid; }
 };
 struct CachedObject {
   uint32_t kind = 0;
@@ -41,103 +42,217 @@ struct CachedObject {
   std::vector<OwnerRef> owners;
   std::vector<std::string> secrets, configmaps;  // dependent names (templates)
   bool live = true;
+  // where the record lives in the resident arena's payload (-1: not placed yet)
+  int64_t rec_off = -1;
+  uint64_t rec_cap = 0;     // padded bytes reserved at rec_off
+  bool value_dirty = false; // canon changed since the device copy was written
 };
 
 std::string store_key(uint32_t kind, const std::string& key) { return std::string(1, (char)('0' + kind)) + key; }
+inline uint64_t pad16(uint64_t n) { return (n + 15) & ~15ull; }
 
-// One cluster's informer caches (all four listers), insertion ordered.
+struct ArenaHandle {
+  ncd_arena* a = nullptr;
+  ArenaHandle() = default;
+  ArenaHandle(const ArenaHandle&) = delete;
+  ArenaHandle& operator=(const ArenaHandle&) = delete;
+  ArenaHandle(ArenaHandle&& o) noexcept : a(o.a) { o.a = nullptr; }
+  void reset() {
+    if (a) ncd_arena_destroy(a);
+    a = nullptr;
+  }
+  ~ArenaHandle() { reset(); }
+};
+
+// One cluster's informer caches (all four listers), insertion ordered, plus its resident arena.
+// Informer events map onto three costs (include/ncdrift.h):
+//   value of an existing object changed (UpdateFunc)   -> ncd_arena_sync_records: that record only
+//   object added / deleted / re-owned (Add/DeleteFunc) -> ncd_arena_recommit: small arrays + new records
+//   first scan, or the arena ran out of room           -> ncd_arena_commit of a fresh, larger arena
 struct ClusterImage {
   std::vector<CachedObject> objs;
   std::unordered_map<std::string, size_t> index;
+  ArenaHandle arena;
+  uint64_t payload_used = 0, payload_cap = 0, nobj_cap = 0, aux_cap = 0, nowner_cap = 0, ndep_cap = 0;
+  bool structural = true;  // keys / owners / dependents changed since the last commit
+  uint64_t uploads_full = 0, uploads_structural = 0, uploads_values = 0;  // how each scan got its data across
 
   void put(CachedObject&& o) {
     const std::string k = store_key(o.kind, o.key);
     auto it = index.find(k);
-    if (it != index.end()) objs[it->second] = std::move(o);
-    else {
+    if (it == index.end()) {
       index.emplace(k, objs.size());
       objs.push_back(std::move(o));
+      structural = true;
+      return;
     }
+    CachedObject& old = objs[it->second];
+    if (old.uid != o.uid || !(old.owners == o.owners) || old.secrets != o.secrets || old.configmaps != o.configmaps)
+      structural = true;
+    if (old.canon != o.canon) {
+      old.canon = std::move(o.canon);
+      old.value_dirty = true;
+    }
+    old.name = std::move(o.name);
+    old.uid = std::move(o.uid);
+    old.owners = std::move(o.owners);
+    old.secrets = std::move(o.secrets);
+    old.configmaps = std::move(o.configmaps);
   }
   bool drop(uint32_t kind, const std::string& key) {
     auto it = index.find(store_key(kind, key));
     if (it == index.end()) return false;
     objs[it->second].live = false;
     index.erase(it);
+    structural = true;
     return true;
   }
   const CachedObject* get(uint32_t kind, const std::string& key) const {
     auto it = index.find(store_key(kind, key));
     return it == index.end() ? nullptr : &objs[it->second];
   }
-};
 
-struct ArenaHandle {
-  ncd_arena* a = nullptr;
-  ~ArenaHandle() {
-    if (a) ncd_arena_destroy(a);
-  }
-};
-
-inline uint64_t pad16(uint64_t n) { return (n + 15) & ~15ull; }
-
-// The packer: one cluster image -> one committed arena (layout: ncdrift.h "arenas").
-// `order` receives, for the controller image, the arena index of every live object.
-void pack(ncd_ctx* ctx, const ClusterImage& img, ArenaHandle& out, std::vector<const CachedObject*>* order) {
-  uint64_t payload = 0, aux = 0, nowner = 0, ndep = 0, n = 0;
-  for (const CachedObject& o : img.objs) {
-    if (!o.live) continue;
-    ++n;
-    payload += pad16(o.canon.size());
-    aux += o.key.size() + o.uid.size();
-    for (const OwnerRef& r : o.owners) aux += r.uid.size();
-    nowner += o.owners.size();
-    for (const auto& s : o.secrets) aux += o.key.size() + s.size();  // "namespace/" + name, bounded by key + name
-    for (const auto& s : o.configmaps) aux += o.key.size() + s.size();
-    ndep += o.secrets.size() + o.configmaps.size();
-  }
-  if (ncd_arena_create(ctx, payload, n, aux, nowner, ndep, NCD_ARENA_HOST_PINNED, &out.a) != NCD_OK)
-    throw std::runtime_error(ncd_err("ncd_arena_create"));
-  ncd_arena_view v;
-  if (ncd_arena_host_view(out.a, &v) != NCD_OK) throw std::runtime_error(ncd_err("ncd_arena_host_view"));
-  uint64_t off = 0, ax = 0, oi = 0, di = 0, i = 0;
-  auto put_aux = [&](const std::string& s, uint32_t* o, uint32_t* l) {
-    memcpy(v.aux + ax, s.data(), s.size());
-    *o = (uint32_t)ax;
-    *l = (uint32_t)s.size();
-    ax += s.size();
-  };
-  for (const CachedObject& o : img.objs) {
-    if (!o.live) continue;
-    if (order) order->push_back(&o);
-    v.rec_off[i] = off;
-    v.rec_len[i] = (uint32_t)o.canon.size();
-    memcpy(v.payload + off, o.canon.data(), o.canon.size());
-    memset(v.payload + off + o.canon.size(), 0, pad16(o.canon.size()) - o.canon.size());
-    off += pad16(o.canon.size());
-    v.kind[i] = (uint8_t)o.kind;
-    put_aux(o.key, &v.key_off[i], &v.key_len[i]);
-    put_aux(o.uid, &v.uid_off[i], &v.uid_len[i]);
-    v.own_start[i] = (uint32_t)oi;
-    for (const OwnerRef& r : o.owners) {
-      v.own_is_template[oi] = r.kind == "NexusAlgorithmTemplate";  // the Kind test of controller.go:490
-      put_aux(r.uid, &v.own_uid_off[oi], &v.own_uid_len[oi]);
-      ++oi;
+  // Brings the resident arena up to date with the image.  `order` (controller image only)
+  // receives the live objects in arena order.
+  void sync(ncd_ctx* ctx, std::vector<const CachedObject*>* order) {
+    // forget dead objects (their payload becomes unreferenced until the next full commit)
+    if (structural) {
+      std::vector<CachedObject> keep;
+      for (CachedObject& o : objs)
+        if (o.live) keep.push_back(std::move(o));
+      objs.swap(keep);
+      index.clear();
+      for (size_t i = 0; i < objs.size(); ++i) index.emplace(store_key(objs[i].kind, objs[i].key), i);
     }
-    v.dep_start[i] = (uint32_t)di;
-    const std::string ns = o.key.substr(0, o.key.find('/') + 1);
-    for (int pass = 0; pass < 2; ++pass)  // secrets first, then configmaps (:817 before :825)
-      for (const std::string& name : pass == 0 ? o.secrets : o.configmaps) {
-        v.dep_kind[di] = pass == 0 ? NCD_KIND_SECRET : NCD_KIND_CONFIGMAP;
-        put_aux(ns + name, &v.dep_key_off[di], &v.dep_key_len[di]);
-        ++di;
+    if (order)
+      for (const CachedObject& o : objs) order->push_back(&o);
+
+    if (!arena.a || structural) {
+      uint64_t aux = 0, nowner = 0, ndep = 0, append = 0, compact = 0;
+      for (const CachedObject& o : objs) {
+        aux += o.key.size() + o.uid.size();
+        for (const OwnerRef& r : o.owners) aux += r.uid.size();
+        nowner += o.owners.size();
+        for (const auto& s : o.secrets) aux += o.key.size() + s.size();  // "namespace/" + name <= key + name
+        for (const auto& s : o.configmaps) aux += o.key.size() + s.size();
+        ndep += o.secrets.size() + o.configmaps.size();
+        compact += pad16(o.canon.size());
+        if (o.rec_off < 0 || o.value_dirty) append += pad16(o.canon.size());
       }
-    ++i;
+      const bool fits = arena.a && objs.size() <= nobj_cap && aux <= aux_cap && nowner <= nowner_cap &&
+                        ndep <= ndep_cap && payload_used + append <= payload_cap;
+      if (!fits) {
+        // a fresh arena with room to grow; every record is placed again, compactly
+        arena.reset();
+        payload_cap = compact + compact / 2 + (64 << 10);
+        nobj_cap = objs.size() + objs.size() / 2 + 16;
+        aux_cap = aux + aux / 2 + 1024;
+        nowner_cap = nowner + nowner / 2 + 16;
+        ndep_cap = ndep + ndep / 2 + 16;
+        if (ncd_arena_create(ctx, payload_cap, nobj_cap, aux_cap, nowner_cap, ndep_cap, NCD_ARENA_HOST_PINNED,
+                             &arena.a) != NCD_OK)
+          throw std::runtime_error(ncd_err("ncd_arena_create"));
+        payload_used = 0;
+        for (CachedObject& o : objs) o.rec_off = -1;
+      }
+      ncd_arena_view v;
+      if (ncd_arena_host_view(arena.a, &v) != NCD_OK) throw std::runtime_error(ncd_err("ncd_arena_host_view"));
+      const uint64_t dirty_from = payload_used;
+      write_all(v);
+      const uint64_t n = objs.size();
+      const int rc = fits ? ncd_arena_recommit(arena.a, n, payload_used, aux_used, own_used, dep_used, dirty_from)
+                          : ncd_arena_commit(arena.a, n, payload_used, aux_used, own_used, dep_used);
+      if (rc != NCD_OK) throw std::runtime_error(ncd_err(fits ? "ncd_arena_recommit" : "ncd_arena_commit"));
+      ++(fits ? uploads_structural : uploads_full);
+      structural = false;
+      return;
+    }
+
+    // same objects, some values changed: rewrite those records and push only them
+    std::vector<uint32_t> changed;
+    uint64_t append = 0;
+    for (const CachedObject& o : objs)
+      if (o.value_dirty && pad16(o.canon.size()) > o.rec_cap) append += pad16(o.canon.size());
+    if (payload_used + append > payload_cap) {  // no room to append: start over with a larger arena
+      structural = true;
+      arena.reset();
+      if (order) order->clear();
+      sync(ctx, order);
+      return;
+    }
+    ncd_arena_view v;
+    if (ncd_arena_host_view(arena.a, &v) != NCD_OK) throw std::runtime_error(ncd_err("ncd_arena_host_view"));
+    for (size_t i = 0; i < objs.size(); ++i) {
+      CachedObject& o = objs[i];
+      if (!o.value_dirty) continue;
+      place(v, o, /*force_append=*/false);
+      v.rec_off[i] = (uint64_t)o.rec_off;
+      v.rec_len[i] = (uint32_t)o.canon.size();
+      changed.push_back((uint32_t)i);
+    }
+    if (!changed.empty()) {
+      if (ncd_arena_sync_records(arena.a, changed.size(), changed.data(), payload_used) != NCD_OK)
+        throw std::runtime_error(ncd_err("ncd_arena_sync_records"));
+      ++uploads_values;
+    }
   }
-  v.own_start[n] = (uint32_t)oi;
-  v.dep_start[n] = (uint32_t)di;
-  if (ncd_arena_commit(out.a, n, off, ax, oi, di) != NCD_OK) throw std::runtime_error(ncd_err("ncd_arena_commit"));
-}
+
+ private:
+  uint64_t aux_used = 0, own_used = 0, dep_used = 0;
+
+  // Writes o's record into the pinned payload: where it already is if it fits, else at the end.
+  void place(ncd_arena_view& v, CachedObject& o, bool force_append) {
+    const uint64_t need = pad16(o.canon.size());
+    if (o.rec_off < 0 || need > o.rec_cap || force_append) {
+      o.rec_off = (int64_t)payload_used;
+      o.rec_cap = need;
+      payload_used += need;
+    }
+    memcpy(v.payload + o.rec_off, o.canon.data(), o.canon.size());
+    memset(v.payload + o.rec_off + o.canon.size(), 0, need - o.canon.size());
+    o.value_dirty = false;
+  }
+
+  // Every per-object array from scratch (arena layout: ncdrift.h "arenas"); records that are
+  // already on the device and did not change keep their place, the others are appended.
+  void write_all(ncd_arena_view& v) {
+    uint64_t ax = 0, oi = 0, di = 0, i = 0;
+    auto put_aux = [&](const std::string& s, uint32_t* o, uint32_t* l) {
+      memcpy(v.aux + ax, s.data(), s.size());
+      *o = (uint32_t)ax;
+      *l = (uint32_t)s.size();
+      ax += s.size();
+    };
+    for (CachedObject& o : objs) {
+      if (o.rec_off < 0 || o.value_dirty) place(v, o, /*force_append=*/true);  // only appended payload is re-uploaded
+      v.rec_off[i] = (uint64_t)o.rec_off;
+      v.rec_len[i] = (uint32_t)o.canon.size();
+      v.kind[i] = (uint8_t)o.kind;
+      put_aux(o.key, &v.key_off[i], &v.key_len[i]);
+      put_aux(o.uid, &v.uid_off[i], &v.uid_len[i]);
+      v.own_start[i] = (uint32_t)oi;
+      for (const OwnerRef& r : o.owners) {
+        v.own_is_template[oi] = r.kind == "NexusAlgorithmTemplate";  // the Kind test of controller.go:490
+        put_aux(r.uid, &v.own_uid_off[oi], &v.own_uid_len[oi]);
+        ++oi;
+      }
+      v.dep_start[i] = (uint32_t)di;
+      const std::string ns = o.key.substr(0, o.key.find('/') + 1);
+      for (int pass = 0; pass < 2; ++pass)  // secrets first, then configmaps (:817 before :825)
+        for (const std::string& name : pass == 0 ? o.secrets : o.configmaps) {
+          v.dep_kind[di] = pass == 0 ? NCD_KIND_SECRET : NCD_KIND_CONFIGMAP;
+          put_aux(ns + name, &v.dep_key_off[di], &v.dep_key_len[di]);
+          ++di;
+        }
+      ++i;
+    }
+    v.own_start[i] = (uint32_t)oi;
+    v.dep_start[i] = (uint32_t)di;
+    aux_used = ax;
+    own_used = oi;
+    dep_used = di;
+  }
+};
 
 }  // namespace
 
@@ -208,6 +323,8 @@ int ncdh_checker_create(int device, uint32_t mode, int nshards, ncdh_checker** o
 
 void ncdh_checker_destroy(ncdh_checker* c) {
   if (!c) return;
+  c->controller.arena.reset();  // arenas before the context they live in
+  for (ClusterImage& sh : c->shards) sh.arena.reset();
   if (c->ctx) ncd_destroy(c->ctx);
   delete c;
 }
@@ -246,17 +363,15 @@ int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char*
 int ncdh_scan(ncdh_checker* c) {
   if (!c) return fail("ncdh_scan: null checker");
   try {
-    ArenaHandle ctrl;
-    std::vector<ArenaHandle> sh(c->shards.size());
     std::vector<const CachedObject*> order;
-    pack(c->ctx, c->controller, ctrl, &order);
+    c->controller.sync(c->ctx, &order);
     std::vector<const ncd_arena*> ptrs;
-    for (size_t s = 0; s < sh.size(); ++s) {
-      pack(c->ctx, c->shards[s], sh[s], nullptr);
-      ptrs.push_back(sh[s].a);
+    for (ClusterImage& sh : c->shards) {
+      sh.sync(c->ctx, nullptr);
+      ptrs.push_back(sh.arena.a);
     }
     ncd_diff* d = nullptr;
-    if (ncd_scan(c->ctx, ctrl.a, ptrs.data(), (int)ptrs.size(), c->mode, &d) != NCD_OK)
+    if (ncd_scan(c->ctx, c->controller.arena.a, ptrs.data(), (int)ptrs.size(), c->mode, &d) != NCD_OK)
       return fail(ncd_err("ncd_scan"));
     ncd_scan_stats st;
     ncd_scan_last_stats(c->ctx, &st);
@@ -383,6 +498,15 @@ int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap) {
   for (const std::string& line : c->dirty) s += line + "\n";
   if (out && s.size() <= cap) memcpy(out, s.data(), s.size());
   return (int64_t)s.size();
+}
+
+int ncdh_upload_counts(ncdh_checker* c, int cluster, uint64_t* full, uint64_t* structural, uint64_t* values) {
+  ClusterImage* img = c ? c->image(cluster) : nullptr;
+  if (!img) return fail("ncdh_upload_counts: no such cluster");
+  if (full) *full = img->uploads_full;
+  if (structural) *structural = img->uploads_structural;
+  if (values) *values = img->uploads_values;
+  return 0;
 }
 
 int ncdh_last_counts(ncdh_checker* c, uint64_t* ndiff, uint64_t* decisions) {

@@ -28,6 +28,7 @@ PROTOTYPES = {
     "ncdh_plan_template": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
     "ncdh_plan_workgroup": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
     "ncdh_sweep_queue": (C.c_int64, [VP, C.c_char_p, C.c_uint64]),
+    "ncdh_upload_counts": (C.c_int, [VP, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "ncdh_last_counts": (C.c_int, [VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
 }
 _lib = None
@@ -145,6 +146,13 @@ class DriftChecker:
         buf = C.create_string_buffer(max(n, 1))
         self.lib.ncdh_sweep_queue(self.h, buf, n)
         return [tuple(line.split("\t")) for line in buf.raw[:n].decode().splitlines()]
+
+    def upload_counts(self, cluster: int) -> Tuple[int, int, int]:
+        """(full uploads, structural re-commits, value-only syncs) of one cluster so far."""
+        a, b, d = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        if self.lib.ncdh_upload_counts(self.h, cluster, C.byref(a), C.byref(b), C.byref(d)) != 0:
+            raise _err()
+        return a.value, b.value, d.value
 
     def counts(self) -> Tuple[int, int]:
         a, b = C.c_uint64(), C.c_uint64()
