@@ -67,6 +67,10 @@ struct DevArena {
   const uint64_t* table;    // open addressing; slot = (keyhash >> 32) << 32 | index, all ones = empty
   uint32_t table_mask;
   uint32_t nobj;
+  // join cache (shard side): the controller-object -> shard-object map of the previous scan,
+  // valid while neither arena's keys changed; exactly one of the two is set by ncd_scan
+  const uint32_t* join_cache;  // [controller nobj] read instead of probing
+  uint32_t* join_cache_out;    // [controller nobj] filled by this scan's probes
   // digests, filled by the hash kernels
   const uint64_t* h64;      // [nobj]
   const uint32_t* sha;      // [nobj][8]
@@ -134,6 +138,11 @@ struct ncd_arena {
   uint64_t* h64;
   uint32_t* sha;
   bool h64_valid, sha_valid;
+  // index generation (bumped by every commit / recommit) and the join cache kept for one controller arena
+  uint64_t generation;
+  uint32_t* jc_idx;
+  const ncd_arena* jc_ctrl;
+  uint64_t jc_ctrl_gen, jc_gen, jc_n;
 };
 
 struct ncd_diff {

@@ -282,6 +282,8 @@ void ncd_fill_dev_arena(const ncd_arena* a, DevArena* o) {
   o->table = a->table;
   o->table_mask = a->table_size ? a->table_size - 1 : 0;
   o->nobj = (uint32_t)a->nobj;
+  o->join_cache = nullptr;
+  o->join_cache_out = nullptr;
   o->h64 = a->h64;
   o->sha = a->sha;
 }
@@ -349,8 +351,11 @@ int ncd_rebuild_tiles(ncd_arena* a) {
   return NCD_OK;
 }
 
+static uint64_t g_generation = 0;
+
 int ncd_build_index(ncd_arena* a) {
   ncd_ctx* ctx = a->ctx;
+  a->generation = ++g_generation;  // keys may have changed: join caches built on the old index are stale
   cudaStream_t st = ctx->stream;
   const uint32_t n = (uint32_t)a->nobj;
   const unsigned blocks = (n + 255) / 256;

@@ -26,7 +26,15 @@ k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t 
   const uint32_t c = (uint32_t)(p / S), s = (uint32_t)(p % S);
   const DevArena& sh = shards[s];
   const ObjMeta& q = ctrl.meta[c];
-  const uint32_t idx = ncd_probe_meta(sh, q, ctrl.aux);
+  // lister.Get: probe the shard's table, or reuse the previous scan's answer while neither
+  // arena's keys have changed (value rewrites do not touch keys)
+  uint32_t idx;
+  if (sh.join_cache) {
+    idx = sh.join_cache[c];
+  } else {
+    idx = ncd_probe_meta(sh, q, ctrl.aux);
+    if (sh.join_cache_out) sh.join_cache_out[c] = idx;
+  }
   uint8_t v;
   uint64_t off = NCD_NO_OFF;
   if (idx == NCD_NOTFOUND) {
@@ -377,12 +385,35 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   DevArena dctrl;
   ncd_fill_dev_arena(ctrl, &dctrl);
   uint64_t algo = 0;
+  std::vector<ncd_arena*> jc_filled;  // shard arenas whose join cache this scan fills
   {
     DevArena* tmp = (DevArena*)malloc(sizeof(DevArena) * (S ? S : 1));
     if (!tmp) return NCD_E_NOMEM;
     for (uint32_t s = 0; s < S; ++s) {
       ncd_fill_dev_arena(shards[s], &tmp[s]);
       algo += shards[s]->len_sum;
+      // join cache of this (controller, shard) pair
+      ncd_arena* sa = const_cast<ncd_arena*>(shards[s]);
+      bool listed_before = false;
+      for (uint32_t q = 0; q < s; ++q) listed_before = listed_before || shards[q] == shards[s];
+      const bool valid = sa->jc_idx && sa->jc_ctrl == ctrl && sa->jc_ctrl_gen == ctrl->generation &&
+                         sa->jc_gen == sa->generation && sa->jc_n == nc;
+      if (valid) {
+        tmp[s].join_cache = sa->jc_idx;
+      } else if (!listed_before && nc) {
+        if (sa->jc_n != nc || !sa->jc_idx) {
+          if (sa->jc_idx) cudaFree(sa->jc_idx);
+          sa->jc_idx = nullptr;
+          if (cudaMalloc((void**)&sa->jc_idx, nc * sizeof(uint32_t)) != cudaSuccess) {
+            cudaGetLastError();
+            sa->jc_idx = nullptr;  // no cache: the scan just probes
+          }
+        }
+        sa->jc_ctrl = nullptr;  // becomes valid once the join that fills it is enqueued (below)
+        sa->jc_n = sa->jc_idx ? nc : 0;
+        tmp[s].join_cache_out = sa->jc_idx;
+        if (sa->jc_idx) jc_filled.push_back(sa);
+      }
     }
     // pageable source: the runtime stages it before returning, tmp can be freed right away
     cudaError_t e = cudaMemcpyAsync(ctx->d_shards, tmp, sizeof(DevArena) * S, cudaMemcpyHostToDevice, st);
@@ -416,6 +447,11 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     k_join<<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(dctrl, ctx->d_shards, S, mode, sh_idx,
                                                              sh_off, dv);
     ++launches;
+    for (ncd_arena* sa : jc_filled) {
+      sa->jc_ctrl = ctrl;
+      sa->jc_ctrl_gen = ctrl->generation;
+      sa->jc_gen = sa->generation;
+    }
   }
   NCD_CUDA(cudaEventRecord(evs[2], st));
   const bool do_compare = (hm == NCD_MODE_DIRECT) || (mode & NCD_MODE_CONFIRM);

@@ -114,6 +114,12 @@ def test_structural_change_recommits_without_the_old_payload(ctx):
     a.commit(sh.nobj, sh.payload_bytes, sh.aux_bytes, sh.nowner, sh.ndep)
     other = ctx.arena_from_host(shard_hs[1])
     try:
+        # scan twice before the change: the second scan answers the join from the cache the first
+        # one filled, and the re-commit below must invalidate that cache
+        for _ in range(2):
+            d = ctx.scan(arenas[0], [a, other], A.MODE_DIRECT)
+            np.testing.assert_array_equal(d.codes(), oracle.scan(ctrl_h, shard_hs)[0])
+            d.close()
         # rebuild shard 0's object list on the host: drop two objects, add one the controller has
         # but the shard lacked, give one dependent another owner
         objs = []
