@@ -67,6 +67,9 @@ struct DevArena {
   const uint64_t* table;    // open addressing; slot = (keyhash >> 32) << 32 | index, all ones = empty
   uint32_t table_mask;
   uint32_t nobj;
+  // UID interning built by commit: equal ids <=> byte-equal UID strings within this arena
+  const uint32_t* uid_id;      // [nobj] id of the object's own metadata.uid
+  const uint32_t* own_packed;  // [nowner] (is_template << 31) | id of the owner's UID
   // join cache (shard side): the controller-object -> shard-object map of the previous scan,
   // valid while neither arena's keys changed; exactly one of the two is set by ncd_scan
   const uint32_t* join_cache;  // [controller nobj] read instead of probing
@@ -140,6 +143,8 @@ struct ncd_arena {
   bool h64_valid, sha_valid;
   // index generation (bumped by every commit / recommit) and the join cache kept for one controller arena
   uint64_t generation;
+  uint32_t* uid_id;      // [nobj]
+  uint32_t* own_packed;  // [nowner]
   uint32_t* jc_idx;
   const ncd_arena* jc_ctrl;
   uint64_t jc_ctrl_gen, jc_gen, jc_n;

@@ -169,6 +169,69 @@ __global__ void k_table_build(DevArena a, unsigned long long* __restrict__ table
   }
 }
 
+// ------------------------------------------------------------------ UID interning
+// isMissingOwnership (controller.go:484-502) compares ownerReference UIDs with the UID of the
+// shard's copy of the owning template, for every (dependent, shard) of every scan.  The strings
+// never change between commits, so they are interned once here: string j (j < nobj: object j's
+// uid, else owner entry j - nobj) gets the smallest j' whose bytes are identical.  The scan then
+// compares two integers, exactly: equal ids <=> equal bytes.
+__device__ __forceinline__ void uid_string(const DevArena& a, uint32_t j, const uint8_t** p, uint32_t* len) {
+  if (j < a.nobj) {
+    *p = a.aux + a.uid_off[j];
+    *len = a.uid_len[j];
+  } else {
+    *p = a.aux + a.own_uid_off[j - a.nobj];
+    *len = a.own_uid_len[j - a.nobj];
+  }
+}
+__device__ __forceinline__ uint64_t uid_hash(const uint8_t* p, uint32_t len) {
+  uint64_t h = 0xcbf29ce484222325ull;
+  for (uint32_t i = 0; i < len; ++i) h = (h ^ p[i]) * 0x100000001b3ull;
+  return ncd_fmix64(h ^ len);
+}
+
+__global__ void k_uid_insert(DevArena a, uint32_t nstr, uint32_t* __restrict__ table, uint32_t mask) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nstr) return;
+  const uint8_t* p;
+  uint32_t len;
+  uid_string(a, j, &p, &len);
+  uint32_t slot = (uint32_t)uid_hash(p, len) & mask;
+  for (;;) {
+    const uint32_t prev = atomicCAS(&table[slot], NCD_NOTFOUND, j);
+    if (prev == NCD_NOTFOUND) return;
+    const uint8_t* q;
+    uint32_t qlen;
+    uid_string(a, prev, &q, &qlen);
+    if (qlen == len && ncd_bytes_equal(p, q, len)) {
+      atomicMin(&table[slot], j);  // any member of the group may sit here: they are byte-equal
+      return;
+    }
+    slot = (slot + 1) & mask;
+  }
+}
+
+__global__ void k_uid_resolve(DevArena a, uint32_t nstr, const uint32_t* __restrict__ table, uint32_t mask,
+                              uint32_t* __restrict__ uid_id, uint32_t* __restrict__ own_packed) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nstr) return;
+  const uint8_t* p;
+  uint32_t len;
+  uid_string(a, j, &p, &len);
+  uint32_t slot = (uint32_t)uid_hash(p, len) & mask;
+  uint32_t id;
+  for (;;) {
+    id = table[slot];  // never empty before this string's own group is met
+    const uint8_t* q;
+    uint32_t qlen;
+    uid_string(a, id, &q, &qlen);
+    if (qlen == len && ncd_bytes_equal(p, q, len)) break;
+    slot = (slot + 1) & mask;
+  }
+  if (j < a.nobj) uid_id[j] = id;
+  else own_packed[j - a.nobj] = id | (a.own_is_template[j - a.nobj] ? 0x80000000u : 0u);
+}
+
 // ------------------------------------------------------------------ rows
 __global__ void k_row_counts(DevArena a, uint32_t* __restrict__ counts) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -282,6 +345,8 @@ void ncd_fill_dev_arena(const ncd_arena* a, DevArena* o) {
   o->table = a->table;
   o->table_mask = a->table_size ? a->table_size - 1 : 0;
   o->nobj = (uint32_t)a->nobj;
+  o->uid_id = a->uid_id;
+  o->own_packed = a->own_packed;
   o->join_cache = nullptr;
   o->join_cache_out = nullptr;
   o->h64 = a->h64;
@@ -393,6 +458,24 @@ int ncd_build_index(ncd_arena* a) {
       ncd_set_error("arena commit: %u objects have records/keys outside the arena, a record not "
                     "16-byte aligned, or an unknown kind", bad);
       return NCD_E_INVALID;
+    }
+    {
+      const uint64_t nstr = (uint64_t)n + a->nowner;
+      if (nstr >= 0x7FFFFFFFull) {
+        ncd_set_error("arena commit: objects + ownerReferences exceed 2^31");
+        return NCD_E_CAPACITY;
+      }
+      NCD_TRY(dev_realloc(&a->uid_id, n));
+      NCD_TRY(dev_realloc(&a->own_packed, a->nowner));
+      uint32_t usize = 16;
+      while ((uint64_t)usize < 2 * nstr) usize <<= 1;
+      uint32_t* utable = nullptr;
+      NCD_CUDA(cudaMallocAsync((void**)&utable, (size_t)usize * 4, st));
+      NCD_CUDA(cudaMemsetAsync(utable, 0xFF, (size_t)usize * 4, st));
+      const unsigned ublocks = (unsigned)((nstr + 255) / 256);
+      k_uid_insert<<<ublocks, 256, 0, st>>>(da, (uint32_t)nstr, utable, usize - 1);
+      k_uid_resolve<<<ublocks, 256, 0, st>>>(da, (uint32_t)nstr, utable, usize - 1, a->uid_id, a->own_packed);
+      NCD_CUDA(cudaFreeAsync(utable, st));
     }
     k_meta_build<<<blocks, 256, 0, st>>>(da, a->meta);
     k_table_build<<<blocks, 256, 0, st>>>(da, (unsigned long long*)a->table, d_small + 1);

@@ -258,13 +258,10 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
           const uint64_t tp = (uint64_t)obj * S + s;
           bool missing = true;
           if (dv[tp] != DV_NOTFOUND) {
-            const uint32_t tj = sh_idx[tp];
-            const uint8_t* uid = sh.aux + sh.uid_off[tj];
-            const uint32_t ulen = sh.uid_len[tj];
+            // UIDs were interned at commit: equal ids <=> byte-equal strings (ncd_index.cu)
+            const uint32_t want = sh.uid_id[sh_idx[tp]] | 0x80000000u;  // Kind == NexusAlgorithmTemplate && same UID
             for (uint32_t o = o0; o < o1 && missing; ++o)
-              if (sh.own_is_template[o] && sh.own_uid_len[o] == ulen &&
-                  ncd_bytes_equal(sh.aux + sh.own_uid_off[o], uid, ulen))
-                missing = false;
+              if (sh.own_packed[o] == want) missing = false;
           }
           code = (v == DV_DIFF ? NCD_UPDATE_DATA : 0u) | (missing ? NCD_UPDATE_OWNER : 0u);
         }
