@@ -67,11 +67,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   for (uint32_t spins = 0; !mbar_try_wait(bar, parity); ++spins)
     if (spins > (1u << 28)) __trap();
 }
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                   smem_u32(dst)),
-               "l"(src), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
+// Streaming data: every byte is read once, so the copies carry an evict-first L2 policy and the
+// index arrays (tile lists, object lines, offsets) keep their place in the 126 MB L2.
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar, uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(
+          smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+      : "memory");
 }
 
 __global__ void __launch_bounds__(32 * (NPROD + NCONS), 1)
@@ -106,6 +114,7 @@ k_compare_tma(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
 
   if (warp < NPROD) {
     // ------------------------------------------------------------ producers
+    const uint64_t pol = l2_evict_first_policy();
     // Raw index data of one item per lane.  Loading the next batch is started before the current
     // batch is issued and only consumed an iteration later, so its two dependent load levels
     // (tile -> object -> record / shard offsets) hide behind the copies in flight.
@@ -170,12 +179,12 @@ k_compare_tma(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
             mbar_arrive(&sm->full[stage]);  // nothing to compare: an empty stage keeps the order
           } else {
             mbar_arrive_expect_tx(&sm->full[stage], padded * (1 + __popc(i_vmask)));
-            bulk_g2s(dst, ctrl.payload + i_src, padded, &sm->full[stage]);
+            bulk_g2s(dst, ctrl.payload + i_src, padded, &sm->full[stage], pol);
 #pragma unroll
             for (int k = 0; k < TG; ++k)
               if (i_vmask & (1u << k))
                 bulk_g2s(dst + (size_t)(1 + k) * NCD_TILE_BYTES, s_payload[i_s0 + k] + i_off[k] + i_toff, padded,
-                         &sm->full[stage]);
+                         &sm->full[stage], pol);
           }
         }
         __syncwarp();
