@@ -527,7 +527,7 @@ def main():
     ap.add_argument("--gather-cap", type=int, default=1 << 16, help="entries per rank in the all-gather buffer")
     ap.add_argument("--cpu-sample-groups", type=int, default=6000)
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
-    ap.add_argument("--e2e-groups", type=int, default=40000)
+    ap.add_argument("--e2e-groups", type=int, default=100000)
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--resident-fraction", type=float, default=0.001, help="records rewritten per cluster per resident e2e step")
     ap.add_argument("--skip-e2e", action="store_true")
