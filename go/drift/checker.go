@@ -6,6 +6,7 @@ package drift
 import (
 	"fmt"
 	"reflect"
+	"strings"
 	"sync/atomic"
 
 	v1 "github.com/SneaksAndData/nexus-core/pkg/apis/science/v1"
@@ -156,7 +157,7 @@ func (k *Checker) pack(objs []object) (*Arena, error) {
 			oi++
 		}
 		a.DepStart[i] = di
-		ns := o.key[:len(o.key)-len(o.key[indexByte(o.key, '/')+1:])] // "namespace/"
+		ns := o.key[:strings.IndexByte(o.key, '/')+1] // "namespace/"
 		for pass, names := range [][]string{o.secrets, o.configMap} {
 			for _, n := range names {
 				if pass == 0 {
@@ -175,15 +176,6 @@ func (k *Checker) pack(objs []object) (*Arena, error) {
 		return nil, err
 	}
 	return a, nil
-}
-
-func indexByte(s string, c byte) int {
-	for i := 0; i < len(s); i++ {
-		if s[i] == c {
-			return i
-		}
-	}
-	return -1
 }
 
 // Scan: one drift check over the controller cluster and every shard.  Called once per resync
