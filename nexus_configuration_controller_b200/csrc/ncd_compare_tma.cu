@@ -268,7 +268,10 @@ int ncd_launch_compare_tma(ncd_ctx* ctx, const DevArena& dctrl, uint32_t S, cons
   uint32_t nstage, stage_bytes;
   size_t smem;
   tma_shape(S, &nstage, &stage_bytes, &smem);
-  if (nstage < 2 || smem > 227 * 1024) {
+  // A producer warp owns every NPROD-th item and waits on mbarrier phase PARITY, which cannot tell
+  // two phases apart: with fewer stages than producers its next item would alias the stage of an
+  // item still in flight.  (1 + 8) x 4 KB stages always give at least 5.
+  if (nstage < (uint32_t)NPROD || smem > 227 * 1024) {
     ncd_set_error("compare: %u shards do not fit the shared-memory pipeline", S);
     return NCD_E_CAPACITY;
   }
