@@ -23,8 +23,14 @@ namespace {
 
 constexpr int TG = 8;                    // shard copies per work item
 constexpr int MAX_STAGES = 24;           // stages actually used = what fits ~216 KB of shared memory
-constexpr int NCONS = 8;                 // consumer warps
-constexpr int NPROD = 4;                 // producer warps: a bulk copy is one warp-wide (uniform) instruction, so
+#ifndef NCD_TMA_NCONS
+#define NCD_TMA_NCONS 8
+#endif
+#ifndef NCD_TMA_NPROD
+#define NCD_TMA_NPROD 4
+#endif
+constexpr int NCONS = NCD_TMA_NCONS;     // consumer warps
+constexpr int NPROD = NCD_TMA_NPROD;     // producer warps: a bulk copy is one warp-wide (uniform) instruction, so
                                          // issue bandwidth scales with warps, not lanes
 constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
 
@@ -208,10 +214,10 @@ k_compare_tma(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
       const uint4* base = reinterpret_cast<const uint4*>(data + (size_t)stage * STAGE_BYTES);
       const uint32_t nvec = (d.nbytes + 15) >> 4, tail = d.nbytes & 15;
       uint32_t bits = 0;
-      if (v < nvec) {
-        uint4 a = base[v];
+      for (uint32_t vv = v; vv < nvec; vv += 32 * NCONS) {  // one trip when 8 consumer warps cover the 256 vectors
+        const uint4 a = base[vv];
         uint32_t keep[4] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu};
-        if (tail && v == nvec - 1) {
+        if (tail && vv == nvec - 1) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const int nb = (int)tail - 4 * i;
@@ -221,7 +227,7 @@ k_compare_tma(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
 #pragma unroll
         for (int k = 0; k < TG; ++k) {
           if (d.vmask & (1u << k)) {
-            const uint4 b = base[(size_t)(1 + k) * NCD_TILE_VECS + v];
+            const uint4 b = base[(size_t)(1 + k) * NCD_TILE_VECS + vv];
             const uint32_t x = ((a.x ^ b.x) & keep[0]) | ((a.y ^ b.y) & keep[1]) | ((a.z ^ b.z) & keep[2]) |
                                ((a.w ^ b.w) & keep[3]);
             if (x) bits |= 1u << k;
