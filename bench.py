@@ -288,7 +288,18 @@ def run_ours(args):
     from nexus_configuration_controller_b200 import multigpu as M
 
     ext = torch.cuda.ExternalStream(ctx.stream, device=local)
+    # size of the diff-list buffer (the all-gather's send buffer): twice what a first scan finds,
+    # the same on every rank
     cap_entries = args.gather_cap
+    if cap_entries is None:
+        d0 = ctx.scan(ca, sas, mode)
+        n0 = len(d0.entries())
+        d0.close()
+        if dist:
+            t = torch.tensor([n0], dtype=torch.int64, device=f"cuda:{local}")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            n0 = int(t.item())
+        cap_entries = 1 << max(12, (2 * n0 + 1024 - 1).bit_length())
     sendbuf = torch.zeros(M.buffer_words(cap_entries), dtype=torch.int32, device=f"cuda:{local}")
     recvbuf = torch.zeros(world * sendbuf.numel(), dtype=torch.int32, device=f"cuda:{local}") if world > 1 else None
 
@@ -380,7 +391,14 @@ def run_ours(args):
     for a in sas + [ca]:
         a.close()
     if not args.skip_e2e:
-        gather = (lambda d: M.gather_diffs(d, sendbuf, recvbuf, ext, cap_entries)) if world > 1 else (lambda d: None)
+        # the resident e2e steps accumulate drift, so their exchange buffer is sized generously
+        e2e_cap = 1 << 18
+        if world > 1:
+            e2e_send = torch.zeros(M.buffer_words(e2e_cap), dtype=torch.int32, device=f"cuda:{local}")
+            e2e_recv = torch.zeros(world * e2e_send.numel(), dtype=torch.int32, device=f"cuda:{local}")
+            gather = lambda d: M.gather_diffs(d, e2e_send, e2e_recv, ext, e2e_cap)  # noqa: E731
+        else:
+            gather = lambda d: None  # noqa: E731
         e2e_cold, e2e_res = run_e2e(ctx, args, mode & 0xFF, world, rank, dist, ext, gather)
         if rank == 0:
             result["e2e"] = e2e_cold
@@ -523,7 +541,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
     ap.add_argument("--mode", default="direct", choices=["direct", "hash64", "sha256"])
     ap.add_argument("--groups", type=int, default=None, help="override the number of template groups (smaller runs)")
-    ap.add_argument("--gather-cap", type=int, default=1 << 16, help="entries per rank in the all-gather buffer")
+    ap.add_argument("--gather-cap", type=int, default=None, help="entries per rank in the all-gather buffer (default: sized from a first scan)")
     ap.add_argument("--cpu-sample-groups", type=int, default=6000)
     ap.add_argument("--cpu-budget-s", type=float, default=12.0)
     ap.add_argument("--e2e-groups", type=int, default=100000)
