@@ -227,7 +227,8 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
            const uint32_t* __restrict__ row_obj, const uint32_t* __restrict__ row_dep,
            const uint32_t* __restrict__ row_cidx, const uint32_t* __restrict__ sh_idx,
            const uint8_t* __restrict__ dv, uint8_t* __restrict__ codes,
-           uint32_t* __restrict__ blk_cnt) {
+           uint32_t* __restrict__ blk_cnt, uint32_t* __restrict__ blk_off, uint32_t* __restrict__ counters,
+           uint32_t fuse_scan) {
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t code = NCD_SKIP;
   if (q < nrows * S) {
@@ -270,7 +271,46 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
     codes[q] = (uint8_t)code;
   }
   const int cnt = __syncthreads_count(code != NCD_SKIP);
-  if (threadIdx.x == 0) blk_cnt[blockIdx.x] = (uint32_t)cnt;
+  // Small grids (launch-latency bound scans): the block that finishes last turns the per-block
+  // counts into offsets (exclusive scan) and the total into counters[0], so the ordered compaction
+  // needs no separate scan launches.  Large grids keep the three-launch scan: a fence and a
+  // ticket per block cost more there than the launches do.
+  __shared__ bool is_last;
+  __shared__ uint32_t part[256];
+  if (threadIdx.x == 0) {
+    blk_cnt[blockIdx.x] = (uint32_t)cnt;
+    if (!fuse_scan) return;
+    __threadfence();
+    is_last = atomicAdd(&counters[2], 1u) == gridDim.x - 1;
+  }
+  if (!fuse_scan) return;
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  // counts written by other blocks: read past L1 (__ldcg), independent loads so they pipeline
+  const uint32_t nblk = gridDim.x, per = (nblk + 255) / 256;
+  const uint32_t b0 = threadIdx.x * per, b1 = min(nblk, b0 + per);
+  uint32_t sum = 0;
+#pragma unroll 8
+  for (uint32_t b = b0; b < b1; ++b) sum += __ldcg(blk_cnt + b);
+  part[threadIdx.x] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t run = 0;
+    for (int t = 0; t < 256; ++t) {
+      const uint32_t v = part[t];
+      part[t] = run;
+      run += v;
+    }
+    counters[0] = run;
+  }
+  __syncthreads();
+  uint32_t run = part[threadIdx.x];
+#pragma unroll 8
+  for (uint32_t b = b0; b < b1; ++b) {
+    blk_off[b] = run;
+    run += __ldcg(blk_cnt + b);
+  }
 }
 
 // ------------------------------------------------------------------ k_emit
@@ -279,7 +319,16 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
 __global__ void __launch_bounds__(256)
 k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ row_obj,
        const uint32_t* __restrict__ row_dep, const uint8_t* __restrict__ codes,
-       const uint32_t* __restrict__ blk_off, ncd_entry* __restrict__ out, uint64_t cap) {
+       const uint32_t* __restrict__ blk_off, ncd_entry* __restrict__ out, uint64_t cap,
+       const uint32_t* __restrict__ counters, uint32_t* __restrict__ hdr) {
+  // header of a packed diff list: {entries found, shards, rows (low 32 bits), 1 if the buffer was too small}
+  if (hdr && blockIdx.x == 0 && threadIdx.x == 0) {
+    const uint32_t n = counters[0];
+    hdr[0] = n;
+    hdr[1] = S;
+    hdr[2] = (uint32_t)nrows;
+    hdr[3] = n > cap ? 1u : 0u;
+  }
   __shared__ uint32_t warp_cnt[8];
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -301,15 +350,6 @@ k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ r
   }
 }
 
-// Header of a packed diff list: {entries found, shards, rows (low 32 bits), 1 if the buffer was too small}.
-__global__ void k_header(const uint32_t* __restrict__ counters, uint32_t S, uint32_t rows, uint64_t cap,
-                         uint32_t* __restrict__ hdr) {
-  const uint32_t n = counters[0];
-  hdr[0] = n;
-  hdr[1] = S;
-  hdr[2] = rows;
-  hdr[3] = n > cap ? 1u : 0u;
-}
 
 // ------------------------------------------------------------------ host side
 static int check_scan_args(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards,
@@ -500,21 +540,20 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   }
   NCD_CUDA(cudaEventRecord(evs[3], st));
   if (nq) {
+    const bool fuse = nblk <= 4096;
     k_classify<<<(unsigned)nblk, 256, 0, st>>>(dctrl, ctx->d_shards, S, nrows, ctrl->row_obj,
                                                ctrl->row_dep, ctrl->row_cidx, sh_idx, dv, codes,
-                                               blk_cnt);
-    ++launches;
-  }
-  NCD_TRY(ncd_exclusive_scan_u32(ctx, blk_cnt, blk_off, nblk, counters));
-  launches += nblk ? 3 : 0;
-  if (nq) {
+                                               blk_cnt, blk_off, counters, fuse ? 1u : 0u);
+    if (!fuse) {
+      NCD_TRY(ncd_exclusive_scan_u32(ctx, blk_cnt, blk_off, nblk, counters));
+      launches += 3;
+    }
     k_emit<<<(unsigned)nblk, 256, 0, st>>>(dctrl, S, nrows, ctrl->row_obj, ctrl->row_dep, codes, blk_off,
-                                           entries_out, entry_cap);
-    ++launches;
-  }
-  if (hdr_out) {
-    k_header<<<1, 1, 0, st>>>(counters, S, (uint32_t)nrows, entry_cap, hdr_out);
-    ++launches;
+                                           entries_out, entry_cap, counters, hdr_out);
+    launches += 2;
+  } else if (hdr_out) {
+    const uint32_t empty_hdr[4] = {0, S, (uint32_t)nrows, 0};  // nothing to decide: an empty list
+    NCD_CUDA(cudaMemcpyAsync(hdr_out, empty_hdr, sizeof(empty_hdr), cudaMemcpyHostToDevice, st));  // pageable: staged now
   }
   NCD_CUDA(cudaEventRecord(evs[4], st));
   NCD_CUDA(cudaMemcpyAsync(ctx->h_counters + (size_t)slot * 8, counters, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
