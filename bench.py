@@ -275,7 +275,8 @@ def run_ours(args):
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     # hash modes re-hash every copy in every step (digests are otherwise cached per committed arena)
-    mode = {"direct": A.MODE_DIRECT, "hash64": A.MODE_HASH64 | A.MODE_REHASH, "sha256": A.MODE_SHA256 | A.MODE_REHASH}[args.mode]
+    mode = {"direct": A.MODE_DIRECT, "hash64": A.MODE_HASH64 | A.MODE_REHASH, "sha256": A.MODE_SHA256 | A.MODE_REHASH,
+            "xxh64": A.MODE_XXH64 | A.MODE_REHASH}[args.mode]
 
     ctx = Context(local)
     cfg, S = make_cfg(args.workload, groups=args.groups, part_mod=world if world > 1 else 0, part_rem=rank)
@@ -363,7 +364,7 @@ def run_ours(args):
         kern_ms = sum(cmp_ms) / len(cmp_ms)
         achieved = st.algo_bytes / (kern_ms / 1e3) / 1e9  # this rank's kernel over this rank's bytes
         kernel_name = ({0: "k_compare", 1: "k_compare_grouped<1>", 2: "k_compare_grouped<2>", 4: "k_compare_grouped<4>", 8: "k_compare_tma"}.get(st.compare_variant, "k_compare")
-                       if mode == A.MODE_DIRECT else ("k_h64_tiles" if args.mode == "hash64" else "k_sha256"))
+                       if mode == A.MODE_DIRECT else {"hash64": "k_h64_tiles", "sha256": "k_sha256", "xxh64": "k_xxh64"}[args.mode])
         traffic, traffic_src = ncu_traffic(args.workload, kernel_name, world, args.groups is None and not os.environ.get("NCD_BENCH_LEN"))
         result = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -539,7 +540,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
-    ap.add_argument("--mode", default="direct", choices=["direct", "hash64", "sha256"])
+    ap.add_argument("--mode", default="direct", choices=["direct", "hash64", "sha256", "xxh64"])
     ap.add_argument("--groups", type=int, default=None, help="override the number of template groups (smaller runs)")
     ap.add_argument("--gather-cap", type=int, default=None, help="entries per rank in the all-gather buffer (default: sized from a first scan)")
     ap.add_argument("--cpu-sample-groups", type=int, default=6000)

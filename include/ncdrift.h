@@ -65,6 +65,7 @@ enum {
   NCD_MODE_DIRECT = 0, /* byte compare of the canonical records: exact (default)                  */
   NCD_MODE_HASH64 = 1, /* striped 64-bit hash of every record, verdict from hash equality          */
   NCD_MODE_SHA256 = 2, /* FIPS 180-4 SHA-256 of every record, verdict from digest equality         */
+  NCD_MODE_XXH64 = 3,  /* standard XXH64 (seed 0) of every record, verdict from digest equality    */
   NCD_MODE_CONFIRM = 0x100, /* OR with a hash mode: hash-equal pairs are re-checked by byte compare */
   NCD_MODE_REHASH = 0x200   /* OR with a hash mode: recompute every digest (by default digests are
                                kept with a committed arena and reused by later scans)              */
@@ -277,7 +278,7 @@ int ncd_find_orphans(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const
 
 /* ------------------------------------------------------------------ hashing */
 /* Hashes every record of a committed arena on the GPU and copies the digests out.
- * mode NCD_MODE_HASH64: out is nobj x 8 bytes; NCD_MODE_SHA256: nobj x 32 bytes.
+ * mode NCD_MODE_HASH64 / NCD_MODE_XXH64: out is nobj x 8 bytes; NCD_MODE_SHA256: nobj x 32 bytes.
  * No counterpart in the reference (it never hashes, controller.go:539,600,725,795
  * call reflect.DeepEqual); this is the hash path BASELINE.json's north_star asks for. */
 int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* out, uint64_t out_bytes,

@@ -201,7 +201,7 @@ extern "C" void ncd_arena_destroy(ncd_arena* a) {
     if (h) cudaFreeHost(h);
   }
   void* idx[] = {a->meta,    a->table,     a->row_start,  a->row_obj, a->row_dep, a->row_cidx,
-                 a->tile_obj, a->tile_chunk, a->tile_start, a->h64,     a->sha,     a->jc_idx,  a->uid_id,  a->own_packed,
+                 a->tile_obj, a->tile_chunk, a->tile_start, a->h64,     a->sha,     a->xxh,     a->jc_idx,  a->uid_id,  a->own_packed,
                  a->ctile_obj, a->ctile_chunk, a->ctile_start};
   for (void* p : idx)
     if (p) cudaFree(p);

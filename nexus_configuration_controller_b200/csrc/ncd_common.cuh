@@ -77,6 +77,7 @@ struct DevArena {
   // digests, filled by the hash kernels
   const uint64_t* h64;      // [nobj]
   const uint32_t* sha;      // [nobj][8]
+  const uint64_t* xxh;      // [nobj] XXH64
 };
 
 constexpr int NCD_EV_RING = 64;
@@ -140,7 +141,8 @@ struct ncd_arena {
   // digests (device), lazily allocated
   uint64_t* h64;
   uint32_t* sha;
-  bool h64_valid, sha_valid;
+  bool h64_valid, sha_valid, xxh_valid;
+  uint64_t* xxh;
   // index generation (bumped by every commit / recommit) and the join cache kept for one controller arena
   uint64_t generation;
   uint32_t* uid_id;      // [nobj]

@@ -27,6 +27,7 @@ struct HashJob {
   const uint32_t* tile_chunk;
   unsigned long long* acc;  // NCD-H64: per-record accumulator, becomes the digest
   uint32_t* sha;            // SHA-256 digests
+  uint64_t* xxh;            // XXH64 digests
   uint64_t tile_base;       // global index of this job's first tile
   uint64_t ntiles;
   uint64_t rec_base;        // global index of this job's first record
@@ -253,11 +254,137 @@ k_sha256(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned i
   }
 }
 
+// ------------------------------------------------------------------ XXH64 (xxHash specification, seed 0)
+// The standard function, for callers that want digests other tools can reproduce.  It is serial
+// per record (four accumulators over 32-byte stripes), so the parallelism is across records: the
+// same persistent-lane scheme as k_sha256, one stripe per lane per iteration.
+__device__ __forceinline__ uint64_t xxh_round(uint64_t acc, uint64_t in) {
+  acc += in * 14029467366897019727ull;
+  return rotl64(acc, 31) * 11400714785074694791ull;
+}
+__device__ __forceinline__ uint64_t xxh_merge(uint64_t h, uint64_t v) {
+  return (h ^ xxh_round(0, v)) * 11400714785074694791ull + 9650029242287828579ull;
+}
+
+// Each lane owns one record, but a lane reading its own record 32 bytes at a time turns the pass
+// into random-sector traffic (measured 0.8 TB/s).  So the warp loads together: per round, 8 lanes
+// fetch 128 contiguous bytes of one owner's record (4 owners per LDG.128, 8 instructions for the
+// 32 owners), the window goes through shared memory (rows padded to 144 B: conflict-free LDS.128),
+// and every lane then runs up to four stripes of its own record out of its row.
+constexpr int XXH_WIN = 128;            // bytes of one record staged per round
+constexpr int XXH_ROW = XXH_WIN / 16 + 1;  // uint4 per shared-memory row (one vector of padding)
+
+__global__ void __launch_bounds__(128)
+k_xxh64(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned int* __restrict__ next) {
+  constexpr uint64_t P1 = 11400714785074694791ull, P2 = 14029467366897019727ull, P3 = 1609587929392839161ull,
+                     P4 = 9650029242287828579ull, P5 = 2870177450012600261ull;
+  __shared__ uint4 s_win[4][32][XXH_ROW];
+  extern __shared__ uint64_t s_base[];  // [njobs] first global record of each job
+  for (int j = threadIdx.x; j < njobs; j += blockDim.x) s_base[j] = jobs[j].rec_base;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  uint4(*win)[XXH_ROW] = s_win[threadIdx.x >> 5];
+  const unsigned char* base = nullptr;  // first byte of the record
+  uint64_t* out = nullptr;
+  uint64_t v1 = 0, v2 = 0, v3 = 0, v4 = 0;
+  uint32_t rec = 0, len = 0, pos = 0;
+  bool have = false, drained = false;
+  for (;;) {
+    if (!have && !drained) {
+      const uint32_t g = atomicAdd(next, 1u);
+      drained = g >= nrecs;
+      if (!drained) {
+        const HashJob& a = jobs[find_job(s_base, njobs, g)];
+        rec = (uint32_t)(g - a.rec_base);
+        out = a.xxh;
+        len = a.rec_len[rec];
+        base = a.payload + a.rec_off[rec];
+        pos = 0;
+        have = true;
+        v1 = P1 + P2;
+        v2 = P2;
+        v3 = 0;
+        v4 = 0ull - P1;
+      }
+    }
+    if (!__any_sync(0xffffffffu, have)) break;
+    // stage: what each owner wants this round (16-byte vectors; the arena pads records to 16)
+    const uint64_t cur = have ? (uint64_t)(base + pos) : 0;
+    const uint32_t want = have ? min((uint32_t)XXH_WIN, (len - pos + 15u) & ~15u) : 0u;
+    uint4 st[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int o = 4 * j + (lane >> 3);
+      const uint32_t lo = __shfl_sync(0xffffffffu, (uint32_t)cur, o), hi = __shfl_sync(0xffffffffu, (uint32_t)(cur >> 32), o);
+      const uint32_t w = __shfl_sync(0xffffffffu, want, o);
+      const uint32_t c = (uint32_t)(lane & 7) * 16u;
+      st[j] = make_uint4(0, 0, 0, 0);
+      if (c < w) st[j] = ncd_ldg_stream(reinterpret_cast<const uint4*>((((uint64_t)hi << 32) | lo) + c));
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) win[4 * j + (lane >> 3)][lane & 7] = st[j];
+    __syncwarp();
+    if (have) {
+      const uint4* row = win[lane];
+      uint32_t w = 0;  // bytes of the window consumed
+#pragma unroll
+      for (int k = 0; k < XXH_WIN / 32; ++k) {
+        if (len - pos >= 32) {
+          const uint4 x = row[2 * k], y = row[2 * k + 1];
+          v1 = xxh_round(v1, (uint64_t)x.x | ((uint64_t)x.y << 32));
+          v2 = xxh_round(v2, (uint64_t)x.z | ((uint64_t)x.w << 32));
+          v3 = xxh_round(v3, (uint64_t)y.x | ((uint64_t)y.y << 32));
+          v4 = xxh_round(v4, (uint64_t)y.z | ((uint64_t)y.w << 32));
+          pos += 32;
+          w += 32;
+        }
+      }
+      const uint32_t rem = len - pos;
+      if (rem < 32 && w + rem <= XXH_WIN) {  // the tail is inside this window: finish the record
+        uint64_t h;
+        if (len >= 32) {
+          h = rotl64(v1, 1) + rotl64(v2, 7) + rotl64(v3, 12) + rotl64(v4, 18);
+          h = xxh_merge(h, v1);
+          h = xxh_merge(h, v2);
+          h = xxh_merge(h, v3);
+          h = xxh_merge(h, v4);
+        } else {
+          h = P5;
+        }
+        h += (uint64_t)len;
+        const uint32_t* t = reinterpret_cast<const uint32_t*>(row) + (w >> 2);  // the tail, as words
+        uint32_t o = 0;  // byte offset inside the tail; bytes past rem (padding) are never used
+        for (; o + 8 <= rem; o += 8) {
+          h ^= xxh_round(0, (uint64_t)t[o >> 2] | ((uint64_t)t[(o >> 2) + 1] << 32));
+          h = rotl64(h, 27) * P1 + P4;
+        }
+        if (o + 4 <= rem) {
+          h ^= (uint64_t)t[o >> 2] * P1;
+          h = rotl64(h, 23) * P2 + P3;
+          o += 4;
+        }
+        for (; o < rem; ++o) {
+          h ^= (uint64_t)((t[o >> 2] >> (8 * (o & 3))) & 0xffu) * P5;
+          h = rotl64(h, 11) * P1;
+        }
+        h ^= h >> 33;
+        h *= P2;
+        h ^= h >> 29;
+        h *= P3;
+        h ^= h >> 32;
+        out[rec] = h;
+        have = false;
+      }
+    }
+    __syncwarp();  // rows are rewritten by other lanes in the next round
+  }
+}
+
 // ------------------------------------------------------------------ host side
 // Digests of every arena of the list that does not have valid ones yet, in ONE pass of kernels.
 int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint32_t mode, uint32_t* launches) {
   cudaStream_t st = ctx->stream;
-  if (mode != NCD_MODE_HASH64 && mode != NCD_MODE_SHA256) {
+  if (mode != NCD_MODE_HASH64 && mode != NCD_MODE_SHA256 && mode != NCD_MODE_XXH64) {
     ncd_set_error("hash: unknown mode %u", mode);
     return NCD_E_INVALID;
   }
@@ -268,7 +395,7 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
     ncd_arena* a = arenas[k];
     bool seen = false;
     for (int q = 0; q < k; ++q) seen = seen || arenas[q] == a;  // the same arena may be listed twice
-    if (seen || (mode == NCD_MODE_HASH64 ? a->h64_valid : a->sha_valid)) continue;
+    if (seen || (mode == NCD_MODE_HASH64 ? a->h64_valid : mode == NCD_MODE_SHA256 ? a->sha_valid : a->xxh_valid)) continue;
     if (njobs == MAX_HASH_JOBS) {
       ncd_set_error("hash: more than %d arenas in one scan", MAX_HASH_JOBS);
       return NCD_E_CAPACITY;
@@ -278,9 +405,12 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
       if (!a->h64) NCD_CUDA(cudaMalloc((void**)&a->h64, (size_t)(n ? n : 1) * 8));
       NCD_CUDA(cudaMemsetAsync(a->h64, 0, (size_t)(n ? n : 1) * 8, st));
       a->h64_valid = true;
-    } else {
+    } else if (mode == NCD_MODE_SHA256) {
       if (!a->sha) NCD_CUDA(cudaMalloc((void**)&a->sha, (size_t)(n ? n : 1) * 32));
       a->sha_valid = true;
+    } else {
+      if (!a->xxh) NCD_CUDA(cudaMalloc((void**)&a->xxh, (size_t)(n ? n : 1) * 8));
+      a->xxh_valid = true;
     }
     HashJob& j = jobs[njobs++];
     j.payload = a->d.payload;
@@ -290,6 +420,7 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
     j.tile_chunk = a->tile_chunk;
     j.acc = (unsigned long long*)a->h64;
     j.sha = a->sha;
+    j.xxh = a->xxh;
     j.tile_base = 0;  // NCD-H64 tiles are launched per arena (below), so tile indices are local
     j.ntiles = a->ntiles;
     j.rec_base = recs;
@@ -328,8 +459,11 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
   } else {
     unsigned int* next = reinterpret_cast<unsigned int*>(ctx->d_counters) + 8;  // words 8.. are free
     NCD_CUDA(cudaMemsetAsync(next, 0, 4, st));
-    const uint64_t want = (recs + 127) / 128, cap = (uint64_t)ctx->sm_count * 16;
-    k_sha256<<<(unsigned)(want < cap ? want : cap), 128, smem, st>>>(dj, njobs, (uint32_t)recs, next);
+    const uint64_t want = (recs + 127) / 128, cap = (uint64_t)ctx->sm_count * (mode == NCD_MODE_SHA256 ? 16 : 12);
+    if (mode == NCD_MODE_SHA256)
+      k_sha256<<<(unsigned)(want < cap ? want : cap), 128, smem, st>>>(dj, njobs, (uint32_t)recs, next);
+    else
+      k_xxh64<<<(unsigned)(want < cap ? want : cap), 128, smem, st>>>(dj, njobs, (uint32_t)recs, next);
     ++*launches;
   }
   NCD_CUDA(cudaGetLastError());
@@ -351,11 +485,11 @@ extern "C" int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* o
     return NCD_E_STATE;
   }
   const uint32_t hm = mode & 0xff;
-  if (hm != NCD_MODE_HASH64 && hm != NCD_MODE_SHA256) {
-    ncd_set_error("ncd_hash_arena: mode must be NCD_MODE_HASH64 or NCD_MODE_SHA256");
+  if (hm != NCD_MODE_HASH64 && hm != NCD_MODE_SHA256 && hm != NCD_MODE_XXH64) {
+    ncd_set_error("ncd_hash_arena: mode must be NCD_MODE_HASH64, NCD_MODE_SHA256 or NCD_MODE_XXH64");
     return NCD_E_INVALID;
   }
-  const uint64_t need = a->nobj * (hm == NCD_MODE_HASH64 ? 8 : 32);
+  const uint64_t need = a->nobj * (hm == NCD_MODE_SHA256 ? 32 : 8);
   if (out && out_bytes < need) {
     ncd_set_error("ncd_hash_arena: out holds %llu bytes, %llu needed", (unsigned long long)out_bytes,
                   (unsigned long long)need);
@@ -364,13 +498,14 @@ extern "C" int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* o
   NCD_CUDA(cudaSetDevice(ctx->device));
   // always recompute: this entry point is also the timing harness of the hash kernels
   if (hm == NCD_MODE_HASH64) a->h64_valid = false;
-  else a->sha_valid = false;
+  else if (hm == NCD_MODE_SHA256) a->sha_valid = false;
+  else a->xxh_valid = false;
   uint32_t launches = 0;
   NCD_CUDA(cudaEventRecord(ctx->ev[5], ctx->stream));
   NCD_TRY(ncd_hash_launch(ctx, a, hm, &launches));
   NCD_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
   if (out && need)
-    NCD_CUDA(cudaMemcpyAsync(out, hm == NCD_MODE_HASH64 ? (void*)a->h64 : (void*)a->sha, need,
+    NCD_CUDA(cudaMemcpyAsync(out, hm == NCD_MODE_HASH64 ? (void*)a->h64 : hm == NCD_MODE_SHA256 ? (void*)a->sha : (void*)a->xxh, need,
                              cudaMemcpyDeviceToHost, ctx->stream));
   NCD_CUDA(cudaStreamSynchronize(ctx->stream));
   if (kernel_ms) cudaEventElapsedTime(kernel_ms, ctx->ev[5], ctx->ev[6]);

@@ -351,6 +351,7 @@ void ncd_fill_dev_arena(const ncd_arena* a, DevArena* o) {
   o->join_cache_out = nullptr;
   o->h64 = a->h64;
   o->sha = a->sha;
+  o->xxh = a->xxh;
 }
 
 template <typename T>
@@ -425,7 +426,7 @@ int ncd_build_index(ncd_arena* a) {
   const uint32_t n = (uint32_t)a->nobj;
   const unsigned blocks = (n + 255) / 256;
 
-  a->h64_valid = a->sha_valid = false;
+  a->h64_valid = a->sha_valid = a->xxh_valid = false;
   NCD_TRY(dev_realloc(&a->meta, n));
   uint32_t tsize = 16;
   while ((uint64_t)tsize < 2ull * n) tsize <<= 1;

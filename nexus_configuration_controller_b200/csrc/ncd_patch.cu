@@ -80,7 +80,7 @@ int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, ui
   NCD_CUDA(cudaStreamSynchronize(st));
   NCD_CUDA(cudaGetLastError());
   a->payload_bytes = new_payload_bytes;
-  a->h64_valid = a->sha_valid = false;
+  a->h64_valid = a->sha_valid = a->xxh_valid = false;
   const uint32_t bad = flags[0];
   // same-length rewrites (the common event: a value changed in place) leave the tile lists and
   // the byte count as they are

@@ -46,6 +46,8 @@ k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t 
     bool maybe_equal = true;
     if (hm == NCD_MODE_HASH64) {
       maybe_equal = sh.h64[idx] == ctrl.h64[c];
+    } else if (hm == NCD_MODE_XXH64) {
+      maybe_equal = sh.xxh[idx] == ctrl.xxh[c];
     } else if (hm == NCD_MODE_SHA256) {
       const uint4* x = reinterpret_cast<const uint4*>(sh.sha + (size_t)idx * 8);
       const uint4* y = reinterpret_cast<const uint4*>(ctrl.sha + (size_t)c * 8);
@@ -359,7 +361,7 @@ static int check_scan_args(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena*
     return NCD_E_INVALID;
   }
   const uint32_t hm = mode & 0xff;
-  if (hm > NCD_MODE_SHA256 || (mode & ~(0xffu | NCD_MODE_CONFIRM | NCD_MODE_REHASH))) {
+  if (hm > NCD_MODE_XXH64 || (mode & ~(0xffu | NCD_MODE_CONFIRM | NCD_MODE_REHASH))) {
     ncd_set_error("ncd_scan: unknown mode 0x%x", mode);
     return NCD_E_INVALID;
   }
@@ -406,7 +408,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     all.push_back(const_cast<ncd_arena*>(ctrl));
     for (uint32_t s = 0; s < S; ++s) all.push_back(const_cast<ncd_arena*>(shards[s]));
     if (mode & NCD_MODE_REHASH)
-      for (ncd_arena* a : all) a->h64_valid = a->sha_valid = false;
+      for (ncd_arena* a : all) a->h64_valid = a->sha_valid = a->xxh_valid = false;
     NCD_TRY(ncd_hash_launch_many(ctx, all.data(), (int)all.size(), hm, &launches));
   }
   NCD_CUDA(cudaEventRecord(evs[1], st));

@@ -106,9 +106,9 @@ class Context:
         return st
 
     def hash_arena(self, arena: "Arena", mode: int, fetch: bool = True) -> Tuple[Optional[np.ndarray], float]:
-        """Digests of every record (uint64[n] for HASH64, uint8[n,32] for SHA256) and kernel ms."""
+        """Digests of every record (uint64[n] for HASH64 and XXH64, uint8[n,32] for SHA256) and kernel ms."""
         n = arena.counts().nobj
-        width = 8 if (mode & 0xFF) == 1 else 32
+        width = 32 if (mode & 0xFF) == 2 else 8
         out = np.zeros(max(n, 1) * width, dtype=np.uint8) if fetch else None
         ms = C.c_float()
         check(

@@ -21,6 +21,8 @@ MODES = [
     A.MODE_HASH64 | A.MODE_CONFIRM,
     A.MODE_SHA256,
     A.MODE_SHA256 | A.MODE_CONFIRM,
+    A.MODE_XXH64,
+    A.MODE_XXH64 | A.MODE_CONFIRM,
 ]
 
 
@@ -112,7 +114,7 @@ def test_every_single_byte_position_class_is_seen(ctx, n):
         b[p] ^= 0x01
         shards.append(A.pack([A.CachedObject(A.KIND_WORKGROUP, "default/wg", bytes(b))]))
     shards.append(A.pack([A.CachedObject(A.KIND_WORKGROUP, "default/wg", base)]))
-    for mode in (A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256):
+    for mode in (A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64):
         codes, _, _ = gpu_scan(ctx, ctrl, shards, mode)
         assert codes[0].tolist() == [A.UPDATE_DATA] * len(positions) + [A.SKIP], (mode, n)
 
@@ -134,6 +136,31 @@ def test_digests_match_oracle(ctx):
 
     for i, o in enumerate(objs):
         assert bytes(sha[i]) == hashlib.sha256(o.canon).digest()
+
+
+def test_xxh64_is_the_standard_function(ctx):
+    """NCD_MODE_XXH64 digests are XXH64(seed 0): the published known answers, then every tail length
+    0..71 (all 8/4/1-byte tail combinations, with and without full stripes) and some long records."""
+    import random
+
+    rng = random.Random(64)
+    kats = {
+        b"": 0xEF46DB3751D8E999,
+        b"a": 0xD24EC4F1A98C6E5B,
+        b"abc": 0x44BC2CF5AD770999,
+        b"Nobody inspects the spammish repetition": 0xFBCEA83C8A378BF1,
+    }
+    datas = list(kats) + [rand_bytes(rng, n) for n in list(range(72)) + [95, 96, 97, 4095, 4096, 4097, 12289, 70000]]
+    objs = [A.CachedObject(A.KIND_SECRET, f"default/s{i}", d) for i, d in enumerate(datas)]
+    host = A.pack(objs)
+    a = ctx.arena_from_host(host)
+    got, _ = ctx.hash_arena(a, A.MODE_XXH64)
+    a.close()
+    assert got.dtype == np.uint64 and got.shape == (len(datas),)
+    for i, d in enumerate(datas):
+        assert int(got[i]) == oracle.xxh64(d), (i, len(d))
+    for i, want in enumerate(kats.values()):
+        assert int(got[i]) == want
 
 
 def small_synth(**kw) -> SynthCfg:
