@@ -29,6 +29,7 @@ const (
 	ModeDirect     = uint32(C.NCD_MODE_DIRECT)
 	ModeHash64     = uint32(C.NCD_MODE_HASH64)
 	ModeSHA256     = uint32(C.NCD_MODE_SHA256)
+	ModeXXH64      = uint32(C.NCD_MODE_XXH64)
 	ModeConfirm    = uint32(C.NCD_MODE_CONFIRM)
 	arenaHostPinned = C.uint32_t(C.NCD_ARENA_HOST_PINNED)
 )

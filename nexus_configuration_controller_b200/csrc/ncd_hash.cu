@@ -7,6 +7,7 @@
 //   k_h64_final    one thread per object folds the tile sums and the length
 //   k_sha256       FIPS 180-4 SHA-256, persistent lanes pulling records, integer-pipe bound
 #include "ncd_common.cuh"
+#include "ncd_tma.cuh"
 
 // ------------------------------------------------------------------ NCD-H64
 // Per 16-byte vector v of a tile (words d0, d1, little endian) with keys k0[v], k1[v]:
@@ -267,38 +268,64 @@ __device__ __forceinline__ uint64_t xxh_merge(uint64_t h, uint64_t v) {
 }
 
 // Each lane owns one record, but a lane reading its own record 32 bytes at a time turns the pass
-// into random-sector traffic (measured 0.8 TB/s).  So the warp loads together: per round, 8 lanes
-// fetch 128 contiguous bytes of one owner's record (4 owners per LDG.128, 8 instructions for the
-// 32 owners), the window goes through shared memory (rows padded to 144 B: conflict-free LDS.128),
-// and every lane then runs up to four stripes of its own record out of its row.
-constexpr int XXH_WIN = 128;            // bytes of one record staged per round
-constexpr int XXH_ROW = XXH_WIN / 16 + 1;  // uint4 per shared-memory row (one vector of padding)
+// into random-sector traffic (measured 0.8 TB/s), and 128-byte windows gathered with LDG.128 and
+// shuffles reach 3.0 TB/s.  So every lane moves the next XXH_WIN contiguous bytes of its record
+// into its own shared-memory row with one bulk copy (cp.async.bulk, completion counted in bytes on
+// the warp's mbarrier), and then runs the stripes out of that row.  Rows are padded by one vector
+// so that LDS.128 at a row stride is conflict-free.
+#ifndef NCD_XXH_WIN
+#define NCD_XXH_WIN 512
+#endif
+constexpr int XXH_WIN = NCD_XXH_WIN;       // bytes of one record staged per round (multiple of 32)
+constexpr int XXH_ROW = XXH_WIN / 16 + 1;  // uint4 per shared-memory row
+constexpr int XXH_Q = 64;                  // records a warp takes from the global counter at a time
+constexpr int XXH_WARPS = 4;
+
+struct XxhSmem {
+  uint4 win[XXH_WARPS][32][XXH_ROW];
+  const unsigned char* qbase[XXH_WARPS][XXH_Q];
+  uint64_t* qout[XXH_WARPS][XXH_Q];
+  uint32_t qlen[XXH_WARPS][XXH_Q];
+  uint64_t bar[XXH_WARPS];
+};
 
 __global__ void __launch_bounds__(128)
 k_xxh64(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned int* __restrict__ next) {
   constexpr uint64_t P1 = 11400714785074694791ull, P2 = 14029467366897019727ull, P3 = 1609587929392839161ull,
                      P4 = 9650029242287828579ull, P5 = 2870177450012600261ull;
-  __shared__ uint4 s_win[4][32][XXH_ROW];
-  extern __shared__ uint64_t s_base[];  // [njobs] first global record of each job
+  extern __shared__ __align__(128) uint8_t xxh_raw[];
+  XxhSmem* sm = reinterpret_cast<XxhSmem*>(xxh_raw);
+  uint64_t* s_base = reinterpret_cast<uint64_t*>(sm + 1);  // [njobs] first global record of each job
   for (int j = threadIdx.x; j < njobs; j += blockDim.x) s_base[j] = jobs[j].rec_base;
+  if (threadIdx.x < XXH_WARPS) mbar_init(&sm->bar[threadIdx.x], 1);
+  if (threadIdx.x == 0) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
-  const int lane = threadIdx.x & 31;
-  uint4(*win)[XXH_ROW] = s_win[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  uint4(*win)[XXH_ROW] = sm->win[wid];
+  uint64_t* bar = &sm->bar[wid];
+  const uint64_t pol = l2_evict_first_policy();
+  uint32_t phase = 0;
+  // Records are handed out to the warp XXH_Q at a time (one global atomic and one round of index
+  // loads per XXH_Q records, not per record); inside the warp, lanes that finished take the next
+  // entries in ballot order.  head / qn / drained are warp-uniform.
+  const unsigned char** qb = sm->qbase[wid];
+  uint32_t* ql = sm->qlen[wid];
+  uint64_t** qo = sm->qout[wid];
+  uint32_t head = 0, qn = 0;
   const unsigned char* base = nullptr;  // first byte of the record
   uint64_t* out = nullptr;
   uint64_t v1 = 0, v2 = 0, v3 = 0, v4 = 0;
-  uint32_t rec = 0, len = 0, pos = 0;
+  uint32_t len = 0, pos = 0;
   bool have = false, drained = false;
   for (;;) {
-    if (!have && !drained) {
-      const uint32_t g = atomicAdd(next, 1u);
-      drained = g >= nrecs;
-      if (!drained) {
-        const HashJob& a = jobs[find_job(s_base, njobs, g)];
-        rec = (uint32_t)(g - a.rec_base);
-        out = a.xxh;
-        len = a.rec_len[rec];
-        base = a.payload + a.rec_off[rec];
+    for (int pass = 0; pass < 2; ++pass) {
+      const unsigned m = __ballot_sync(0xffffffffu, !have);
+      if (!m) break;
+      const uint32_t rank = __popc(m & ((1u << lane) - 1u)), avail = qn - head;
+      if (!have && rank < avail) {
+        base = qb[head + rank];
+        len = ql[head + rank];
+        out = qo[head + rank];
         pos = 0;
         have = true;
         v1 = P1 + P2;
@@ -306,24 +333,36 @@ k_xxh64(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned in
         v3 = 0;
         v4 = 0ull - P1;
       }
+      head += min((uint32_t)__popc(m), avail);
+      if ((uint32_t)__popc(m) <= avail || drained || pass) break;
+      // queue empty and lanes still idle: next batch
+      __syncwarp();
+      uint32_t g0 = 0;
+      if (lane == 0) g0 = atomicAdd(next, (unsigned)XXH_Q);
+      g0 = __shfl_sync(0xffffffffu, g0, 0);
+      qn = g0 < nrecs ? min((uint32_t)XXH_Q, nrecs - g0) : 0u;
+      drained = qn < (uint32_t)XXH_Q;
+      head = 0;
+      for (uint32_t i = lane; i < qn; i += 32) {
+        const HashJob& a = jobs[find_job(s_base, njobs, g0 + i)];
+        const uint32_t rec = (uint32_t)(g0 + i - a.rec_base);
+        qb[i] = a.payload + a.rec_off[rec];
+        ql[i] = a.rec_len[rec];
+        qo[i] = a.xxh + rec;
+      }
+      __syncwarp();
     }
     if (!__any_sync(0xffffffffu, have)) break;
-    // stage: what each owner wants this round (16-byte vectors; the arena pads records to 16)
-    const uint64_t cur = have ? (uint64_t)(base + pos) : 0;
+    // stage: the next window of every lane's record (16-byte granular; the arena pads records to 16)
     const uint32_t want = have ? min((uint32_t)XXH_WIN, (len - pos + 15u) & ~15u) : 0u;
-    uint4 st[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int o = 4 * j + (lane >> 3);
-      const uint32_t lo = __shfl_sync(0xffffffffu, (uint32_t)cur, o), hi = __shfl_sync(0xffffffffu, (uint32_t)(cur >> 32), o);
-      const uint32_t w = __shfl_sync(0xffffffffu, want, o);
-      const uint32_t c = (uint32_t)(lane & 7) * 16u;
-      st[j] = make_uint4(0, 0, 0, 0);
-      if (c < w) st[j] = ncd_ldg_stream(reinterpret_cast<const uint4*>((((uint64_t)hi << 32) | lo) + c));
+    const uint32_t total = __reduce_add_sync(0xffffffffu, want);
+    if (total) {
+      if (lane == 0) mbar_arrive_expect_tx(bar, total);
+      __syncwarp();
+      if (want) bulk_g2s(win[lane], base + pos, want, bar, pol);
+      mbar_wait(bar, phase);
+      phase ^= 1u;
     }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) win[4 * j + (lane >> 3)][lane & 7] = st[j];
-    __syncwarp();
     if (have) {
       const uint4* row = win[lane];
       uint32_t w = 0;  // bytes of the window consumed
@@ -372,11 +411,10 @@ k_xxh64(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned in
         h ^= h >> 29;
         h *= P3;
         h ^= h >> 32;
-        out[rec] = h;
+        *out = h;
         have = false;
       }
     }
-    __syncwarp();  // rows are rewritten by other lanes in the next round
   }
 }
 
@@ -459,11 +497,16 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
   } else {
     unsigned int* next = reinterpret_cast<unsigned int*>(ctx->d_counters) + 8;  // words 8.. are free
     NCD_CUDA(cudaMemsetAsync(next, 0, 4, st));
-    const uint64_t want = (recs + 127) / 128, cap = (uint64_t)ctx->sm_count * (mode == NCD_MODE_SHA256 ? 16 : 12);
-    if (mode == NCD_MODE_SHA256)
+    if (mode == NCD_MODE_SHA256) {
+      const uint64_t want = (recs + 127) / 128, cap = (uint64_t)ctx->sm_count * 16;
       k_sha256<<<(unsigned)(want < cap ? want : cap), 128, smem, st>>>(dj, njobs, (uint32_t)recs, next);
-    else
-      k_xxh64<<<(unsigned)(want < cap ? want : cap), 128, smem, st>>>(dj, njobs, (uint32_t)recs, next);
+    } else {
+      const size_t xs = sizeof(XxhSmem) + smem;
+      NCD_CUDA(cudaFuncSetAttribute(k_xxh64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xs));
+      const uint64_t per_sm = (216u * 1024u) / xs ? (216u * 1024u) / xs : 1;
+      const uint64_t want = (recs + 32 * XXH_WARPS - 1) / (32 * XXH_WARPS), cap = (uint64_t)ctx->sm_count * per_sm;
+      k_xxh64<<<(unsigned)(want < cap ? want : cap), 32 * XXH_WARPS, xs, st>>>(dj, njobs, (uint32_t)recs, next);
+    }
     ++*launches;
   }
   NCD_CUDA(cudaGetLastError());
