@@ -304,10 +304,19 @@ def run_ours(args):
     sendbuf = torch.zeros(M.buffer_words(cap_entries), dtype=torch.int32, device=f"cuda:{local}")
     recvbuf = torch.zeros(world * sendbuf.numel(), dtype=torch.int32, device=f"cuda:{local}") if world > 1 else None
 
+    xchg = None
+    if world > 1 and args.exchange == "peer":
+        xchg = M.PeerExchange(ctx, world, rank, cap_entries)
+        xchg.connect_group()
+
     def step():
-        """One scan, fully asynchronous: the compaction kernel writes the diff list into `sendbuf`
-        (ncd_scan_into) and, at N>1, the single all-gather of the per-GPU lists is queued behind it."""
-        M.scan_and_gather(ctx, ca, sas, mode, sendbuf, recvbuf, ext, cap_entries)
+        """One scan, fully asynchronous: the compaction kernel writes the diff list into the exchange
+        slot (ncd_scan_into) and, at N>1, the exchange of the per-GPU lists is queued behind it: one
+        kernel of peer-memory stores (ncd_scan_exchange), or with --exchange nccl one all-gather."""
+        if xchg is not None:
+            xchg.scan(ca, sas, mode)
+        else:
+            M.scan_and_gather(ctx, ca, sas, mode, sendbuf, recvbuf, ext, cap_entries)
 
     # warm-up
     for _ in range(max(args.warmup, 3) if not args.allow_short_warmup else args.warmup):
@@ -337,14 +346,15 @@ def run_ours(args):
         tot_ms.append(st.total_ms)
         for k in phases:
             phases[k] += getattr(st, k) / kept
-    launches = st.launches * args.steps  # every step launches the same kernels
-    hdr = sendbuf[:4].cpu().numpy().view(np.uint32)
+    launches = (st.launches + (1 if xchg is not None else 0)) * args.steps  # every step launches the same kernels
+    gathered = xchg.fetch() if xchg is not None else None
+    hdr = gathered[rank, :4] if xchg is not None else sendbuf[:4].cpu().numpy().view(np.uint32)
     if hdr[3]:
         raise RuntimeError(f"diff list of {hdr[0]} entries exceeds --gather-cap {cap_entries}")
     assert int(hdr[0]) == st.ndiff
     gathered_total = None
     if dist:
-        parts = M.unpack_gathered(recvbuf.cpu().numpy().view(np.uint32), world, cap_entries)
+        parts = M.unpack_gathered(gathered if xchg is not None else recvbuf.cpu().numpy().view(np.uint32), world, cap_entries)
         gathered_total = sum(len(e) for _, _, e in parts)
         t = torch.tensor([elapsed_ms], device=f"cuda:{local}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -375,6 +385,7 @@ def run_ours(args):
                 "shards": S, "partition": f"ncd_keyhash(template key) % {world}" if world > 1 else "none",
                 "algorithmic_bytes": algo_all, "l2": "inputs >> 126 MB L2, no flush needed", "setup_s": round(setup_s, 2),
                 "diff_entries": ndiff_all, "diff_entries_after_allgather": gathered_total,
+                "exchange": None if world == 1 else ("peer-memory stores over NVLink (k_exchange)" if xchg is not None else "nccl all_gather_into_tensor"),
             },
             "gb_per_s": algo_all / (ms_per_step / 1e3) / 1e9,
             "roofline": {
@@ -389,6 +400,9 @@ def run_ours(args):
             "clocks": clocks,
         }
     # end-to-end: every rank, bounded sample; CPU baseline: rank 0 at N=1 only
+    if xchg is not None:
+        dist.barrier()  # nobody unmaps a buffer a peer may still be writing
+        xchg.close()
     for a in sas + [ca]:
         a.close()
     if not args.skip_e2e:
@@ -540,6 +554,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=list(WORKLOADS))
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N>1: how the per-GPU diff lists reach every rank")
     ap.add_argument("--mode", default="direct", choices=["direct", "hash64", "sha256", "xxh64"])
     ap.add_argument("--groups", type=int, default=None, help="override the number of template groups (smaller runs)")
     ap.add_argument("--gather-cap", type=int, default=None, help="entries per rank in the all-gather buffer (default: sized from a first scan)")

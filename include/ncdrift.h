@@ -74,6 +74,7 @@ enum {
 typedef struct ncd_ctx ncd_ctx;
 typedef struct ncd_arena ncd_arena;
 typedef struct ncd_diff ncd_diff;
+typedef struct ncd_xchg ncd_xchg;
 
 /* ------------------------------------------------------------------ arenas
  * An arena is one cluster's informer cache in canonical form: the controller
@@ -238,6 +239,39 @@ int ncd_scan_stats_back(ncd_ctx* ctx, uint64_t back, ncd_scan_stats* out);
  * returns once everything is enqueued on the ctx stream; no ncd_scan_finish is needed. */
 int ncd_scan_into(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
                   uint32_t mode, void* dev_out, uint64_t cap_entries);
+
+/* ---- exchange of diff lists between GPUs through peer memory (ncd_exchange.cu) ----------------
+ * The multi-GPU drift check partitions objects by key hash (ncd_keyhash % world) and ends with
+ * every rank holding every rank's diff list.  An ncd_xchg is one rank's end of that exchange:
+ * a device buffer of [2 generations][world slots][header + cap_entries entries] that peers write
+ * into directly over NVLink.  No reference counterpart: the reference is a single CPU process
+ * (controller.go:790-831 loops over the shards); this replaces a library all-gather.
+ *
+ * Set-up, once:   ncd_xchg_create on every rank
+ *   ranks in separate processes:  ncd_xchg_handle -> ship the 64 bytes to every rank by any
+ *                                 channel -> ncd_xchg_open(all handles, rank order)
+ *   ranks in one process:         ncd_xchg_buffer -> ncd_xchg_connect(all buffers, rank order;
+ *                                 needs peer access between the devices, or the same device)
+ * Per step:       ncd_scan_exchange (asynchronous: scan, compaction into this rank's slot, one
+ *                 kernel that stores the slot into every peer's buffer, flags it and waits for
+ *                 the peers' flags), then ncd_xchg_fetch (host copy) or ncd_xchg_result + ncd_sync
+ *                 (device view): world x (16 + 16 * cap_entries) bytes, slot r = rank r's list in
+ *                 ncd_diff_pack layout.
+ * Rules: every rank calls ncd_scan_exchange the same number of times; use a gathered list (or
+ * enqueue its use on the ctx stream) before the next ncd_scan_exchange on that context; a peer
+ * that does not arrive within the timeout (default 10 s) makes ncd_xchg_fetch fail with
+ * NCD_E_STATE instead of hanging the GPU. */
+int ncd_xchg_create(ncd_ctx* ctx, int world, int rank, uint64_t cap_entries, ncd_xchg** out);
+int ncd_xchg_buffer(ncd_xchg* x, void** dev_ptr, uint64_t* bytes);
+int ncd_xchg_handle(ncd_xchg* x, void* handle64);
+int ncd_xchg_open(ncd_xchg* x, const void* handles /* world x 64 bytes; own entry ignored */);
+int ncd_xchg_connect(ncd_xchg* x, void* const* peer_bufs /* world pointers; own entry ignored */);
+int ncd_scan_exchange(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+                      uint32_t mode, ncd_xchg* x);
+int ncd_xchg_result(ncd_xchg* x, const void** dev_ptr, uint64_t* bytes);
+int ncd_xchg_fetch(ncd_xchg* x, void* host_out, uint64_t bytes);
+int ncd_xchg_set_timeout(ncd_xchg* x, double seconds);
+void ncd_xchg_destroy(ncd_xchg* x);
 
 /* Host view of a diff list (copied device -> pinned host on first use). */
 int ncd_diff_view(ncd_diff* d, const ncd_entry** entries, uint64_t* n);

@@ -121,6 +121,16 @@ PROTOTYPES = {
     "ncd_scan_last_stats": (C.c_int, [VP, C.POINTER(ScanStats)]),
     "ncd_scan_stats_back": (C.c_int, [VP, C.c_uint64, C.POINTER(ScanStats)]),
     "ncd_scan_into": (C.c_int, [VP, VP, C.POINTER(VP), C.c_int, C.c_uint32, VP, C.c_uint64]),
+    "ncd_xchg_create": (C.c_int, [VP, C.c_int, C.c_int, C.c_uint64, C.POINTER(VP)]),
+    "ncd_xchg_buffer": (C.c_int, [VP, C.POINTER(VP), u64p]),
+    "ncd_xchg_handle": (C.c_int, [VP, VP]),
+    "ncd_xchg_open": (C.c_int, [VP, VP]),
+    "ncd_xchg_connect": (C.c_int, [VP, C.POINTER(VP)]),
+    "ncd_scan_exchange": (C.c_int, [VP, VP, C.POINTER(VP), C.c_int, C.c_uint32, VP]),
+    "ncd_xchg_result": (C.c_int, [VP, C.POINTER(VP), u64p]),
+    "ncd_xchg_fetch": (C.c_int, [VP, VP, C.c_uint64]),
+    "ncd_xchg_set_timeout": (C.c_int, [VP, C.c_double]),
+    "ncd_xchg_destroy": (None, [VP]),
     "ncd_diff_view": (C.c_int, [VP, C.POINTER(C.POINTER(Entry)), u64p]),
     "ncd_diff_device": (C.c_int, [VP, C.POINTER(VP), u64p]),
     "ncd_diff_pack": (C.c_int, [VP, VP, C.c_uint64]),

@@ -83,3 +83,90 @@ def scan_and_gather(ctx, ctrl, shards, mode: int, sendbuf, recvbuf, scan_stream,
         cur.wait_stream(scan_stream)
         dist.all_gather_into_tensor(recvbuf, sendbuf, group=group)
         scan_stream.wait_stream(cur)
+
+
+class PeerExchange:
+    """One rank's end of the peer-memory exchange of diff lists (``ncd_xchg_*``, ncd_exchange.cu).
+
+    Replaces ``all_gather_into_tensor`` in the step: the compaction kernel writes this rank's list
+    into its slot, one more kernel stores the slot into every peer's buffer over NVLink, flags it
+    and waits for the peers.  ``torch.distributed`` is used once, to ship the 64-byte memory
+    handles (``connect_group``); ranks living in one process connect by pointer (``connect_local``).
+    """
+
+    def __init__(self, ctx, world: int, rank: int, cap_entries: int):
+        import ctypes as C
+
+        self.ctx, self.world, self.rank, self.cap = ctx, world, rank, cap_entries
+        self.lib = ctx.lib
+        h = C.c_void_p()
+        _ffi.check(self.lib.ncd_xchg_create(ctx.handle, world, rank, cap_entries, C.byref(h)))
+        self.handle = h
+
+    # -- set-up
+    def ipc_handle(self) -> bytes:
+        import ctypes as C
+
+        buf = C.create_string_buffer(64)
+        _ffi.check(self.lib.ncd_xchg_handle(self.handle, buf))
+        return buf.raw
+
+    def open(self, handles: List[bytes]) -> None:
+        assert len(handles) == self.world and all(len(h) == 64 for h in handles)
+        _ffi.check(self.lib.ncd_xchg_open(self.handle, b"".join(handles)))
+
+    def connect_group(self, group=None) -> None:
+        """Ranks in separate processes: exchange the handles through the process group."""
+        import torch.distributed as dist
+
+        if self.world == 1:
+            return
+        handles: List[bytes] = [b""] * self.world
+        dist.all_gather_object(handles, self.ipc_handle(), group=group)
+        self.open(handles)
+        dist.barrier(group=group)  # nobody pushes before every rank has mapped every buffer
+
+    def buffer(self) -> int:
+        import ctypes as C
+
+        p = C.c_void_p()
+        _ffi.check(self.lib.ncd_xchg_buffer(self.handle, C.byref(p), None))
+        return p.value
+
+    @staticmethod
+    def connect_local(ends: "List[PeerExchange]") -> None:
+        """Ranks in one process (one context per rank): connect by device pointer."""
+        import ctypes as C
+
+        ptrs = (C.c_void_p * len(ends))(*[e.buffer() for e in ends])
+        for e in ends:
+            if e.world > 1:
+                _ffi.check(e.lib.ncd_xchg_connect(e.handle, ptrs))
+
+    def set_timeout(self, seconds: float) -> None:
+        _ffi.check(self.lib.ncd_xchg_set_timeout(self.handle, seconds))
+
+    # -- per step
+    def scan(self, ctrl, shards, mode: int) -> None:
+        """Enqueue scan + exchange on the context's stream (asynchronous)."""
+        import ctypes as C
+
+        arr = (C.c_void_p * max(len(shards), 1))(*[s.handle for s in shards])
+        _ffi.check(self.lib.ncd_scan_exchange(self.ctx.handle, ctrl.handle, arr, len(shards), mode, self.handle))
+
+    def fetch(self) -> np.ndarray:
+        """Waits for the latest exchange and returns uint32[world, buffer_words(cap)] (see unpack_gathered)."""
+        out = np.zeros(self.world * buffer_words(self.cap), dtype=np.uint32)
+        _ffi.check(self.lib.ncd_xchg_fetch(self.handle, out.ctypes.data, out.nbytes))
+        return out.reshape(self.world, buffer_words(self.cap))
+
+    def close(self) -> None:
+        if self.handle:
+            self.lib.ncd_xchg_destroy(self.handle)
+            self.handle = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
