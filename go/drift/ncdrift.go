@@ -186,3 +186,86 @@ func (c *Ctx) Scan(ctrl *Arena, shards []*Arena, mode uint32) (*Result, error) {
 func KeyHash(kind uint32, key string) uint64 {
 	return uint64(C.ncd_keyhash(C.uint32_t(kind), unsafe.Pointer(unsafe.StringData(key)), C.uint32_t(len(key))))
 }
+
+// Exchange is one GPU's end of the peer-memory exchange of diff lists (ncd_xchg_*): after a
+// partitioned scan every GPU holds every GPU's list.
+type Exchange struct {
+	c     *Ctx
+	h     *C.ncd_xchg
+	world int
+	cap   uint64
+}
+
+func (c *Ctx) NewExchange(world, rank int, capEntries uint64) (*Exchange, error) {
+	x := &Exchange{c: c, world: world, cap: capEntries}
+	if C.ncd_xchg_create(c.h, C.int(world), C.int(rank), C.uint64_t(capEntries), &x.h) != 0 {
+		return nil, lastErr("ncd_xchg_create")
+	}
+	return x, nil
+}
+
+func (x *Exchange) Close() { C.ncd_xchg_destroy(x.h) }
+
+// Handle returns the 64 bytes every other rank needs to map this rank's buffer.
+func (x *Exchange) Handle() ([64]byte, error) {
+	var h [64]byte
+	if C.ncd_xchg_handle(x.h, unsafe.Pointer(&h[0])) != 0 {
+		return h, lastErr("ncd_xchg_handle")
+	}
+	return h, nil
+}
+
+// Open maps the buffers of all ranks (handles in rank order; the own entry is ignored).
+func (x *Exchange) Open(handles [][64]byte) error {
+	if len(handles) != x.world {
+		return errors.New("ncd_xchg_open: one handle per rank")
+	}
+	flat := make([]byte, 0, 64*len(handles))
+	for i := range handles {
+		flat = append(flat, handles[i][:]...)
+	}
+	if C.ncd_xchg_open(x.h, unsafe.Pointer(&flat[0])) != 0 {
+		return lastErr("ncd_xchg_open")
+	}
+	return nil
+}
+
+// ScanExchange enqueues the drift check and the exchange of its diff list (asynchronous).
+func (c *Ctx) ScanExchange(ctrl *Arena, shards []*Arena, mode uint32, x *Exchange) error {
+	c.mu.Lock()
+	defer c.mu.Unlock()
+	n := len(shards)
+	var arr **C.ncd_arena
+	if n > 0 {
+		arr = (**C.ncd_arena)(C.malloc(C.size_t(n) * C.size_t(unsafe.Sizeof(uintptr(0)))))
+		defer C.free(unsafe.Pointer(arr))
+		for i, s := range shards {
+			unsafe.Slice(arr, n)[i] = s.h
+		}
+	}
+	if C.ncd_scan_exchange(c.h, ctrl.h, arr, C.int(n), C.uint32_t(mode), x.h) != 0 {
+		return lastErr("ncd_scan_exchange")
+	}
+	return nil
+}
+
+// Fetch waits for the latest exchange and returns every rank's entries, in rank order.
+func (x *Exchange) Fetch() ([][]Entry, error) {
+	x.c.mu.Lock()
+	defer x.c.mu.Unlock()
+	words := 4 + 4*int(x.cap)
+	buf := make([]uint32, x.world*words)
+	if C.ncd_xchg_fetch(x.h, unsafe.Pointer(&buf[0]), C.uint64_t(4*len(buf))) != 0 {
+		return nil, lastErr("ncd_xchg_fetch")
+	}
+	out := make([][]Entry, x.world)
+	for r := 0; r < x.world; r++ {
+		slot := buf[r*words : (r+1)*words]
+		if slot[3] != 0 {
+			return nil, errors.New("ncd_xchg_fetch: a diff list exceeded the exchange capacity")
+		}
+		out[r] = make([]Entry, int(slot[0]))
+		copy(out[r], unsafe.Slice((*Entry)(unsafe.Pointer(&slot[4])), int(slot[0])))
+	}
+	return out, nil
+}
