@@ -304,10 +304,21 @@ def run_ours(args):
     sendbuf = torch.zeros(M.buffer_words(cap_entries), dtype=torch.int32, device=f"cuda:{local}")
     recvbuf = torch.zeros(world * sendbuf.numel(), dtype=torch.int32, device=f"cuda:{local}") if world > 1 else None
 
-    xchg = None
+    xchg, xchg_note = None, None
     if world > 1 and args.exchange == "peer":
-        xchg = M.PeerExchange(ctx, world, rank, cap_entries)
-        xchg.connect_group()
+        # peer memory needs CUDA IPC and peer access between all GPUs of the box; if any rank cannot
+        # map its peers, every rank takes the NCCL all-gather instead and the JSON line says so
+        try:
+            xchg = M.PeerExchange(ctx, world, rank, cap_entries)
+            xchg.connect_group()
+            ok = 1
+        except Exception as e:  # noqa: BLE001 - reported below
+            ok, xchg_note = 0, f"peer exchange unavailable on rank {rank}: {e}"
+        if not ok:  # connect_group fails on every rank or on none
+            if xchg is not None:
+                xchg.close()
+            xchg = None
+            print(f"[bench rank {rank}] {xchg_note}; using the NCCL all-gather", file=sys.stderr)
 
     def step():
         """One scan, fully asynchronous: the compaction kernel writes the diff list into the exchange
@@ -385,7 +396,7 @@ def run_ours(args):
                 "shards": S, "partition": f"ncd_keyhash(template key) % {world}" if world > 1 else "none",
                 "algorithmic_bytes": algo_all, "l2": "inputs >> 126 MB L2, no flush needed", "setup_s": round(setup_s, 2),
                 "diff_entries": ndiff_all, "diff_entries_after_allgather": gathered_total,
-                "exchange": None if world == 1 else ("peer-memory stores over NVLink (k_exchange)" if xchg is not None else "nccl all_gather_into_tensor"),
+                "exchange": None if world == 1 else ("peer-memory stores over NVLink (k_exchange)" if xchg is not None else "nccl all_gather_into_tensor" + (f" ({xchg_note})" if xchg_note else "")),
             },
             "gb_per_s": algo_all / (ms_per_step / 1e3) / 1e9,
             "roofline": {

@@ -259,9 +259,27 @@ k_sha256(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned i
 // The standard function, for callers that want digests other tools can reproduce.  It is serial
 // per record (four accumulators over 32-byte stripes), so the parallelism is across records: the
 // same persistent-lane scheme as k_sha256, one stripe per lane per iteration.
+// 64-bit arithmetic spelled in 32-bit halves, the way the integer pipes execute it: a rotate is two
+// funnel shifts, a product by a constant one wide multiply-add and two multiply-adds.
+__device__ __forceinline__ uint64_t pack64(uint32_t lo, uint32_t hi) { return (uint64_t)lo | ((uint64_t)hi << 32); }
+template <int R>
+__device__ __forceinline__ uint64_t xxh_rotl(uint64_t x) {
+  static_assert(R > 0 && R < 32, "rotations of XXH64 used on the stripe path are below 32");
+  const uint32_t lo = (uint32_t)x, hi = (uint32_t)(x >> 32);
+  return pack64(__funnelshift_l(hi, lo, R), __funnelshift_l(lo, hi, R));
+}
+// acc + x * C  (mod 2^64)
+__device__ __forceinline__ uint64_t xxh_mad(uint32_t xlo, uint32_t xhi, uint64_t C, uint64_t acc) {
+  const uint32_t clo = (uint32_t)C, chi = (uint32_t)(C >> 32);
+  const uint64_t p = (uint64_t)xlo * clo + acc;
+  return pack64((uint32_t)p, (uint32_t)(p >> 32) + xlo * chi + xhi * clo);
+}
+__device__ __forceinline__ uint64_t xxh_round2(uint64_t acc, uint32_t inlo, uint32_t inhi) {
+  acc = xxh_rotl<31>(xxh_mad(inlo, inhi, 14029467366897019727ull, acc));
+  return xxh_mad((uint32_t)acc, (uint32_t)(acc >> 32), 11400714785074694791ull, 0);
+}
 __device__ __forceinline__ uint64_t xxh_round(uint64_t acc, uint64_t in) {
-  acc += in * 14029467366897019727ull;
-  return rotl64(acc, 31) * 11400714785074694791ull;
+  return xxh_round2(acc, (uint32_t)in, (uint32_t)(in >> 32));
 }
 __device__ __forceinline__ uint64_t xxh_merge(uint64_t h, uint64_t v) {
   return (h ^ xxh_round(0, v)) * 11400714785074694791ull + 9650029242287828579ull;
@@ -366,18 +384,27 @@ k_xxh64(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned in
     if (have) {
       const uint4* row = win[lane];
       uint32_t w = 0;  // bytes of the window consumed
+      const uint32_t nfull = min((len - pos) >> 5, (uint32_t)(XXH_WIN / 32));  // whole stripes in this window
+      if (nfull == XXH_WIN / 32) {  // the common case, branch-free
 #pragma unroll
-      for (int k = 0; k < XXH_WIN / 32; ++k) {
-        if (len - pos >= 32) {
+        for (int k = 0; k < XXH_WIN / 32; ++k) {
           const uint4 x = row[2 * k], y = row[2 * k + 1];
-          v1 = xxh_round(v1, (uint64_t)x.x | ((uint64_t)x.y << 32));
-          v2 = xxh_round(v2, (uint64_t)x.z | ((uint64_t)x.w << 32));
-          v3 = xxh_round(v3, (uint64_t)y.x | ((uint64_t)y.y << 32));
-          v4 = xxh_round(v4, (uint64_t)y.z | ((uint64_t)y.w << 32));
-          pos += 32;
-          w += 32;
+          v1 = xxh_round2(v1, x.x, x.y);
+          v2 = xxh_round2(v2, x.z, x.w);
+          v3 = xxh_round2(v3, y.x, y.y);
+          v4 = xxh_round2(v4, y.z, y.w);
+        }
+      } else {
+        for (uint32_t k = 0; k < nfull; ++k) {
+          const uint4 x = row[2 * k], y = row[2 * k + 1];
+          v1 = xxh_round2(v1, x.x, x.y);
+          v2 = xxh_round2(v2, x.z, x.w);
+          v3 = xxh_round2(v3, y.x, y.y);
+          v4 = xxh_round2(v4, y.z, y.w);
         }
       }
+      pos += 32 * nfull;
+      w = 32 * nfull;
       const uint32_t rem = len - pos;
       if (rem < 32 && w + rem <= XXH_WIN) {  // the tail is inside this window: finish the record
         uint64_t h;

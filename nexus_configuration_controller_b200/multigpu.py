@@ -123,8 +123,19 @@ class PeerExchange:
             return
         handles: List[bytes] = [b""] * self.world
         dist.all_gather_object(handles, self.ipc_handle(), group=group)
-        self.open(handles)
-        dist.barrier(group=group)  # nobody pushes before every rank has mapped every buffer
+        err = ""
+        try:
+            self.open(handles)
+        except _ffi.NcdError as e:
+            err = str(e)
+        # doubles as the barrier: nobody pushes before every rank has mapped every buffer, and a
+        # rank that could not map its peers fails the set-up on every rank instead of leaving the
+        # others waiting
+        errs: List[str] = [""] * self.world
+        dist.all_gather_object(errs, err, group=group)
+        bad = [f"rank {r}: {e}" for r, e in enumerate(errs) if e]
+        if bad:
+            raise RuntimeError("peer exchange set-up failed: " + "; ".join(bad))
 
     def buffer(self) -> int:
         import ctypes as C

@@ -56,7 +56,7 @@ def run_config(ctx, name, modes):
 
 
 def test_cfg2_pure_compare_path_no_drift(ctx):
-    st, n = run_config(ctx, "cfg2_10k_templates_4KB_x8_nodrift", [A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256])
+    st, n = run_config(ctx, "cfg2_10k_templates_4KB_x8_nodrift", [A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64])
     assert n == 0 and st.pairs == 240_000 and st.algo_bytes == 783_360_000  # SURVEY.md 8(d) cfg 2
 
 
@@ -67,7 +67,7 @@ def test_cfg3_100k_configmaps_64KB_16_shards_1pct_drift(ctx):
 
 
 def test_cfg4_1M_mixed_objects_8_shards(ctx):
-    st, n = run_config(ctx, "cfg4_1M_mixed_1-16KB_x8", [A.MODE_DIRECT, A.MODE_HASH64])
+    st, n = run_config(ctx, "cfg4_1M_mixed_1-16KB_x8", [A.MODE_DIRECT, A.MODE_HASH64, A.MODE_XXH64])
     assert st.pairs == 8_000_016 and 8_000 < n < 10_500
     assert 77e9 < st.algo_bytes < 80e9
 

@@ -282,3 +282,94 @@ def test_scan_into_a_caller_buffer_matches_the_diff_object(ctx):
     assert (host[4 + 4 * small :] == 0xFFFFFFFF).all()
     for a in sas + [ca]:
         a.close()
+
+
+def long_key_clusters(seed: int, n_shards: int = 3):
+    """Keys longer than the 36 bytes an object line holds, many sharing everything but the last
+    bytes, keys of 35 / 36 / 37 bytes with a common prefix, and the Kubernetes maximum
+    (63-byte namespace + '/' + 253-byte name)."""
+    import random
+
+    rng = random.Random(seed)
+    ns_max, name_max = "n" * 63, "m" * 249
+    names = (
+        [f"{ns_max}/{name_max}{i:04d}" for i in range(40)]                 # 317 bytes, differ in the last 4
+        + ["default/" + "a" * k for k in (26, 27, 28, 29, 30)]             # 34 .. 38 bytes
+        + ["default/" + "b" * 28 + c for c in "XYZ"]                       # 37 bytes, differ at byte 36
+        + ["default/" + "c" * 27 + c for c in "XYZ"]                       # 36 bytes, differ at byte 35
+        + [f"team-{i}/" + "shared-long-object-name-with-a-common-prefix-" + "z" * (i % 7) for i in range(30)]
+    )
+    assert len(set(names)) == len(names)
+    secrets = [A.CachedObject(A.KIND_SECRET, k, rand_bytes(rng, rng.randint(1, 3000)), uid=f"c-{k}") for k in names]
+    cms = [A.CachedObject(A.KIND_CONFIGMAP, k, rand_bytes(rng, rng.randint(1, 3000)), uid=f"c-{k}") for k in names[::2]]
+    templates = []
+    for t, k in enumerate(names):
+        deps = [(A.KIND_SECRET, d) for d in rng.sample(names, 2)] + [(A.KIND_CONFIGMAP, d) for d in rng.sample(names, 2)]
+        templates.append(A.CachedObject(A.KIND_TEMPLATE, k, rand_bytes(rng, rng.randint(1, 5000)), uid=f"tuid-{t}", deps=deps))
+    ctrl = templates + secrets + cms
+    shards = []
+    for s in range(n_shards):
+        objs = []
+        for o in ctrl:
+            roll = rng.random()
+            if roll < 0.2:
+                continue  # absent
+            data = o.canon
+            if roll < 0.4:
+                b = bytearray(data)
+                b[rng.randrange(len(b))] ^= 0x40
+                data = bytes(b)
+            owners = []
+            if o.kind != A.KIND_TEMPLATE:
+                refs = [t for t in templates if (o.kind, o.key) in t.deps]
+                owners = [(True, f"s{s}-{t.uid}") for t in refs if rng.random() < 0.8]
+            objs.append(A.CachedObject(o.kind, o.key, data, uid=f"s{s}-{o.uid}", owners=owners))
+        # a near miss of a controller key on the shard only: same first 316 bytes
+        objs.append(A.CachedObject(A.KIND_SECRET, f"{ns_max}/{name_max}9999", b"orphan", uid=f"s{s}-orphan"))
+        rng.shuffle(objs)
+        shards.append(A.pack(objs))
+    return A.pack(ctrl), shards
+
+
+@pytest.mark.parametrize("seed", [1, 2])
+def test_long_keys_and_shared_prefixes(ctx, seed):
+    ctrl, shards = long_key_clusters(seed)
+    want_codes, want_ents = oracle.scan(ctrl, shards)
+    assert {0, 1, 2} <= set(np.unique(want_codes).tolist())
+    for mode in (A.MODE_DIRECT, A.MODE_HASH64):
+        codes, ents, _ = gpu_scan(ctx, ctrl, shards, mode)
+        np.testing.assert_array_equal(codes, want_codes)
+        np.testing.assert_array_equal(ents, want_ents)
+    # the orphan search walks the same keys from the shard side
+    ckeys = {(int(ctrl.kind[i]), ctrl.key(i)) for i in range(ctrl.nobj)}
+    want = [(s, i) for s, sh in enumerate(shards) for i in range(sh.nobj) if (int(sh.kind[i]), sh.key(i)) not in ckeys]
+    assert len(want) == len(shards)
+    ca = ctx.arena_from_host(ctrl)
+    sas = [ctx.arena_from_host(h) for h in shards]
+    np.testing.assert_array_equal(ctx.find_orphans(ca, sas), np.array(want, dtype=np.uint32).reshape(-1, 2))
+    for a in sas + [ca]:
+        a.close()
+
+
+def test_many_small_objects_fill_the_hash_table(ctx):
+    """60 000 keys per cache: long probe sequences and slots whose stored hash halves collide."""
+    import random
+
+    rng = random.Random(5)
+    n = 60000
+    keys = [f"ns{i % 97}/object-{i}" for i in range(n)]
+    datas = [rand_bytes(rng, 1 + (i * 7) % 48) for i in range(n)]
+    ctrl = A.pack([A.CachedObject(A.KIND_WORKGROUP, k, d, uid="u") for k, d in zip(keys, datas)])
+    order = list(range(n))
+    rng.shuffle(order)
+    drift = set(rng.sample(range(n), 500))
+    gone = set(rng.sample(range(n), 500)) - drift
+    shard = A.pack(
+        [A.CachedObject(A.KIND_WORKGROUP, keys[i], (datas[i][:-1] + bytes([datas[i][-1] ^ 1])) if i in drift else datas[i], uid="v")
+         for i in order if i not in gone]
+    )
+    want_codes, want_ents = oracle.scan(ctrl, [shard])
+    assert (want_codes != 0).sum() == len(drift) + len(gone)
+    codes, ents, _ = gpu_scan(ctx, ctrl, [shard], A.MODE_DIRECT)
+    np.testing.assert_array_equal(codes, want_codes)
+    np.testing.assert_array_equal(ents, want_ents)
