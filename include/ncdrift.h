@@ -67,8 +67,11 @@ enum {
   NCD_MODE_SHA256 = 2, /* FIPS 180-4 SHA-256 of every record, verdict from digest equality         */
   NCD_MODE_XXH64 = 3,  /* standard XXH64 (seed 0) of every record, verdict from digest equality    */
   NCD_MODE_CONFIRM = 0x100, /* OR with a hash mode: hash-equal pairs are re-checked by byte compare */
-  NCD_MODE_REHASH = 0x200   /* OR with a hash mode: recompute every digest (by default digests are
-                               kept with a committed arena and reused by later scans)              */
+  NCD_MODE_REHASH = 0x200,  /* OR with a hash mode: recompute every digest (by default digests are
+                               kept with a committed arena and reused by later scans; a value sync
+                               re-hashes only the records it rewrote)                              */
+  NCD_MODE_CACHED = 0x400   /* ncd_hash_arena only: return the digests the arena holds when they
+                               are valid instead of recomputing them                               */
 };
 
 typedef struct ncd_ctx ncd_ctx;
@@ -195,7 +198,9 @@ int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64
  * is added, deleted or re-owned needs ncd_arena_commit.  This is what an informer UpdateFunc
  * (controller.go:288-290, 301-303, 321-330, 344-353) turns into, instead of a full re-upload
  * on every 30 s resync (main.go:70-71).  obj_idx: host array of n distinct object indices;
- * new_payload_bytes: the used payload size after the rewrite (<= capacity). */
+ * new_payload_bytes: the used payload size after the rewrite (<= capacity).  Digests the arena
+ * holds (from a hash-mode scan or ncd_hash_arena) are brought up to date for the listed records
+ * and stay valid, so the next hash-mode scan hashes nothing. */
 int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint64_t new_payload_bytes);
 /* Commit after a structural change (objects added, deleted or re-owned: informer AddFunc /
  * DeleteFunc, controller.go:286-305, 319-355) WITHOUT re-uploading the payload that did not
@@ -313,6 +318,8 @@ int ncd_find_orphans(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const
 /* ------------------------------------------------------------------ hashing */
 /* Hashes every record of a committed arena on the GPU and copies the digests out.
  * mode NCD_MODE_HASH64 / NCD_MODE_XXH64: out is nobj x 8 bytes; NCD_MODE_SHA256: nobj x 32 bytes.
+ * Recomputes by default (it is also how the hash kernels are timed: kernel_ms); with
+ * | NCD_MODE_CACHED digests already valid for the arena are returned as they are (kernel_ms 0).
  * No counterpart in the reference (it never hashes, controller.go:539,600,725,795
  * call reflect.DeepEqual); this is the hash path BASELINE.json's north_star asks for. */
 int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* out, uint64_t out_bytes,

@@ -28,7 +28,7 @@ CODE_NAMES = {
     16: "ERR_MISSING_REF",
 }
 
-MODE_DIRECT, MODE_HASH64, MODE_SHA256, MODE_XXH64, MODE_CONFIRM, MODE_REHASH = 0, 1, 2, 3, 0x100, 0x200
+MODE_DIRECT, MODE_HASH64, MODE_SHA256, MODE_XXH64, MODE_CONFIRM, MODE_REHASH, MODE_CACHED = 0, 1, 2, 3, 0x100, 0x200, 0x400
 
 
 @dataclass

@@ -80,6 +80,8 @@ extern "C" void ncd_destroy(ncd_ctx* ctx) {
   if (ctx->d_shards) cudaFree(ctx->d_shards);
   if (ctx->d_jobs) cudaFree(ctx->d_jobs);
   if (ctx->d_counters) cudaFree(ctx->d_counters);
+  for (int i = 0; i < 4; ++i)
+    if (ctx->hpool_ptr[i]) cudaFreeHost(ctx->hpool_ptr[i]);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);
   for (int i = 0; i < 8; ++i) cudaEventDestroy(ctx->ev[i]);
   for (int r = 0; r < NCD_EV_RING; ++r)

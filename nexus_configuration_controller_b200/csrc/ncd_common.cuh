@@ -105,6 +105,10 @@ struct ncd_ctx {
   bool scan_pending;
   struct ncd_diff* pending;
   ncd_scan_stats stats;
+  // pinned host buffers of destroyed diff lists, reused by the next ones (pinning memory is slow
+  // and synchronises the device: a steady stream of scans must not do it per scan)
+  void* hpool_ptr[4];
+  size_t hpool_cap[4];
 };
 
 struct ncd_arena {
@@ -157,6 +161,7 @@ struct ncd_diff {
   uint64_t rows, nshards, n;
   ncd_entry* d_entries;  // device, capacity rows*nshards lazily bounded by n
   ncd_entry* h_entries;  // pinned, filled on first view
+  size_t h_cap;          // bytes of h_entries
   uint8_t* d_codes;      // device [rows*nshards]
   bool h_valid;
   uint32_t hdr[4];       // staging for ncd_diff_pack
@@ -221,6 +226,7 @@ int ncd_launch_compare_tma(ncd_ctx* ctx, const DevArena& dctrl, uint32_t S, cons
                            uint32_t* counters, uint32_t count_collisions);
 // ncd_hash.cu
 int ncd_hash_launch(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, uint32_t* launches);
+int ncd_hash_records(ncd_arena* a, const uint32_t* d_idx, uint64_t n);  // ncd_hash.cu: named records only
 int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint32_t mode, uint32_t* launches);
 
 // ------------------------------------------------------------------ device helpers

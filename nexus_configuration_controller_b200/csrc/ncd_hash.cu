@@ -33,6 +33,7 @@ struct HashJob {
   uint64_t ntiles;
   uint64_t rec_base;        // global index of this job's first record
   uint64_t nobj;
+  const uint32_t* rec_list; // non-null: hash only these records (entry i of the job is record rec_list[i])
 };
 constexpr int MAX_HASH_JOBS = 1025;
 
@@ -47,6 +48,67 @@ __device__ __forceinline__ int find_job(const uint64_t* base, int njobs, uint64_
   return lo;
 }
 
+// Contribution T of one tile (chunk-th 4 KiB of a record, nbytes of it real) to the record's digest;
+// the whole warp calls it, every lane returns T.  keys: (k0, k1) per vector position, in shared memory.
+__device__ __forceinline__ uint64_t h64_tile(const uint8_t* tile, uint32_t nbytes, uint32_t chunk, const uint4* keys,
+                                             uint32_t lane) {
+  constexpr int U = NCD_TILE_VECS / 32;
+  const uint32_t nvec = (nbytes + 15) >> 4;
+  const uint32_t tail = nbytes & 15;
+  const uint4* p = reinterpret_cast<const uint4*>(tile);
+  uint4 d[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const uint32_t v = lane + 32 * u;
+    d[u] = v < nvec ? ncd_ldg_stream(p + v) : make_uint4(0, 0, 0, 0);
+  }
+  // bytes past rec_len in the record's last vector do not belong to the value: clear them once,
+  // outside the accumulate loop (one lane of one tile of a record ever takes this branch)
+  if (tail && (nvec - 1) % 32 == lane) {
+    const uint32_t ut = (nvec - 1) / 32;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if ((uint32_t)u == ut) {
+        uint32_t w[4] = {d[u].x, d[u].y, d[u].z, d[u].w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int nb = (int)tail - 4 * i;
+          if (nb <= 0) w[i] = 0;
+          else if (nb < 4) w[i] &= (1u << (8 * nb)) - 1u;
+        }
+        d[u] = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  }
+  uint64_t A = 0, B = 0;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const uint32_t v = lane + 32 * u;
+    if (v < nvec) {
+      const uint4 x = d[u];
+      const uint4 k = keys[v];
+      const uint64_t d0 = (uint64_t)x.x | ((uint64_t)x.y << 32);
+      const uint64_t d1 = (uint64_t)x.z | ((uint64_t)x.w << 32);
+      A += (uint64_t)(x.x ^ k.x) * (uint64_t)(x.y ^ k.y) + d1;
+      B += (uint64_t)(x.z ^ k.z) * (uint64_t)(x.w ^ k.w) + d0;
+    }
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) {
+    A += __shfl_xor_sync(0xffffffffu, A, s);
+    B += __shfl_xor_sync(0xffffffffu, B, s);
+  }
+  return ncd_fmix64(ncd_fmix64(A + ncd_splitmix64(2ull * chunk)) + rotl64(B, 31) + ncd_splitmix64(2ull * chunk + 1));
+}
+
+__device__ __forceinline__ void h64_fill_keys(uint4* keys) {
+  for (uint32_t v = threadIdx.x; v < NCD_TILE_VECS; v += blockDim.x) {
+    const uint64_t k0 = ncd_splitmix64(0x6e63642d68363400ull + 2 * v);
+    const uint64_t k1 = ncd_splitmix64(0x6e63642d68363400ull + 2 * v + 1);
+    keys[v] = make_uint4((uint32_t)k0, (uint32_t)(k0 >> 32), (uint32_t)k1, (uint32_t)(k1 >> 32));
+  }
+}
+
 __global__ void __launch_bounds__(256)
 k_h64_tiles(const HashJob* __restrict__ jobs, int njobs, uint64_t ntiles) {
   __shared__ uint4 keys[NCD_TILE_VECS];  // (k0, k1) per vector position
@@ -57,16 +119,11 @@ k_h64_tiles(const HashJob* __restrict__ jobs, int njobs, uint64_t ntiles) {
     s_base[j] = jobs[j].tile_base;
     s_jobs[j] = jobs[j];
   }
-  for (uint32_t v = threadIdx.x; v < NCD_TILE_VECS; v += blockDim.x) {
-    const uint64_t k0 = ncd_splitmix64(0x6e63642d68363400ull + 2 * v);
-    const uint64_t k1 = ncd_splitmix64(0x6e63642d68363400ull + 2 * v + 1);
-    keys[v] = make_uint4((uint32_t)k0, (uint32_t)(k0 >> 32), (uint32_t)k1, (uint32_t)(k1 >> 32));
-  }
+  h64_fill_keys(keys);
   __syncthreads();
   const uint32_t lane = threadIdx.x & 31;
   const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-  constexpr int U = NCD_TILE_VECS / 32;
   for (uint64_t g = warp0; g < ntiles; g += nwarps) {
     const HashJob& a = s_jobs[find_job(s_base, njobs, g)];
     const uint64_t t = g - a.tile_base;
@@ -75,56 +132,8 @@ k_h64_tiles(const HashJob* __restrict__ jobs, int njobs, uint64_t ntiles) {
     const uint32_t len = a.rec_len[c];
     const uint64_t toff = (uint64_t)chunk * NCD_TILE_BYTES;
     const uint32_t nbytes = min(NCD_TILE_BYTES, len - (uint32_t)toff);
-    const uint32_t nvec = (nbytes + 15) >> 4;
-    const uint32_t tail = nbytes & 15;
-    const uint4* p = reinterpret_cast<const uint4*>(a.payload + a.rec_off[c] + toff);
-    uint4 d[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint32_t v = lane + 32 * u;
-      d[u] = v < nvec ? ncd_ldg_stream(p + v) : make_uint4(0, 0, 0, 0);
-    }
-    // bytes past rec_len in the record's last vector do not belong to the value: clear them once,
-    // outside the accumulate loop (one lane of one tile of a record ever takes this branch)
-    if (tail && (nvec - 1) % 32 == lane) {
-      const uint32_t ut = (nvec - 1) / 32;
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        if ((uint32_t)u == ut) {
-          uint32_t w[4] = {d[u].x, d[u].y, d[u].z, d[u].w};
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int nb = (int)tail - 4 * i;
-            if (nb <= 0) w[i] = 0;
-            else if (nb < 4) w[i] &= (1u << (8 * nb)) - 1u;
-          }
-          d[u] = make_uint4(w[0], w[1], w[2], w[3]);
-        }
-      }
-    }
-    uint64_t A = 0, B = 0;
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint32_t v = lane + 32 * u;
-      if (v < nvec) {
-        const uint4 x = d[u];
-        const uint4 k = keys[v];
-        const uint64_t d0 = (uint64_t)x.x | ((uint64_t)x.y << 32);
-        const uint64_t d1 = (uint64_t)x.z | ((uint64_t)x.w << 32);
-        A += (uint64_t)(x.x ^ k.x) * (uint64_t)(x.y ^ k.y) + d1;
-        B += (uint64_t)(x.z ^ k.z) * (uint64_t)(x.w ^ k.w) + d0;
-      }
-    }
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-      A += __shfl_xor_sync(0xffffffffu, A, s);
-      B += __shfl_xor_sync(0xffffffffu, B, s);
-    }
-    if (lane == 0) {
-      const uint64_t T = ncd_fmix64(ncd_fmix64(A + ncd_splitmix64(2ull * chunk)) + rotl64(B, 31) +
-                                    ncd_splitmix64(2ull * chunk + 1));
-      atomicAdd(&acc[c], (unsigned long long)T);
-    }
+    const uint64_t T = h64_tile(a.payload + a.rec_off[c] + toff, nbytes, chunk, keys, lane);
+    if (lane == 0) atomicAdd(&acc[c], (unsigned long long)T);
   }
 }
 
@@ -137,6 +146,34 @@ __global__ void k_h64_final(const HashJob* __restrict__ jobs, int njobs, uint64_
   const HashJob& a = jobs[find_job(s_base, njobs, g)];
   const uint64_t i = g - a.rec_base;
   a.acc[i] = ncd_fmix64((uint64_t)a.acc[i] + (uint64_t)a.rec_len[i] * 0x9E3779B185EBCA87ull);
+}
+
+// NCD-H64 of a few named records (after a value sync): block per record, its tiles dealt to the
+// warps, no atomics and no tile list — the digest equals the one k_h64_tiles + k_h64_final produce.
+__global__ void __launch_bounds__(256)
+k_h64_records(const uint32_t* __restrict__ idx, const uint8_t* __restrict__ payload, const uint64_t* __restrict__ rec_off,
+              const uint32_t* __restrict__ rec_len, unsigned long long* __restrict__ out) {
+  __shared__ uint4 keys[NCD_TILE_VECS];
+  __shared__ uint64_t part[8];
+  h64_fill_keys(keys);
+  __syncthreads();
+  const uint32_t c = idx[blockIdx.x];
+  const uint32_t len = rec_len[c];
+  const uint8_t* rec = payload + rec_off[c];
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t ntiles = (len + NCD_TILE_BYTES - 1) / NCD_TILE_BYTES;
+  uint64_t sum = 0;
+  for (uint32_t chunk = warp; chunk < ntiles; chunk += 8) {
+    const uint32_t toff = chunk * NCD_TILE_BYTES;
+    sum += h64_tile(rec + toff, min(NCD_TILE_BYTES, len - toff), chunk, keys, lane);
+  }
+  if (lane == 0) part[warp] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint64_t t = 0;
+    for (int w = 0; w < 8; ++w) t += part[w];
+    out[c] = ncd_fmix64(t + (uint64_t)len * 0x9E3779B185EBCA87ull);
+  }
 }
 
 // ------------------------------------------------------------------ SHA-256 (FIPS 180-4)
@@ -199,6 +236,7 @@ k_sha256(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned i
       if (!drained) {
         const HashJob& a = jobs[find_job(s_base, njobs, g)];
         rec = (uint32_t)(g - a.rec_base);
+        if (a.rec_list) rec = a.rec_list[rec];
         out = a.sha;
         len = a.rec_len[rec];
         p = reinterpret_cast<const uint4*>(a.payload + a.rec_off[rec]);
@@ -363,7 +401,8 @@ k_xxh64(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned in
       head = 0;
       for (uint32_t i = lane; i < qn; i += 32) {
         const HashJob& a = jobs[find_job(s_base, njobs, g0 + i)];
-        const uint32_t rec = (uint32_t)(g0 + i - a.rec_base);
+        uint32_t rec = (uint32_t)(g0 + i - a.rec_base);
+        if (a.rec_list) rec = a.rec_list[rec];
         qb[i] = a.payload + a.rec_off[rec];
         ql[i] = a.rec_len[rec];
         qo[i] = a.xxh + rec;
@@ -490,6 +529,7 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
     j.ntiles = a->ntiles;
     j.rec_base = recs;
     j.nobj = n;
+    j.rec_list = nullptr;
     tiles += a->ntiles;
     recs += n;
   }
@@ -540,6 +580,50 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
   return NCD_OK;
 }
 
+// Digests of the n records named by d_idx (device array), for every digest kind the arena
+// currently holds valid; the other records' digests are untouched.  Called by the value sync so
+// that cached digests stay valid across informer events.
+int ncd_hash_records(ncd_arena* a, const uint32_t* d_idx, uint64_t n) {
+  ncd_ctx* ctx = a->ctx;
+  cudaStream_t st = ctx->stream;
+  if (n == 0 || !(a->h64_valid || a->sha_valid || a->xxh_valid)) return NCD_OK;
+  if (a->h64_valid)
+    k_h64_records<<<(unsigned)n, 256, 0, st>>>(d_idx, a->d.payload, a->d.rec_off, a->d.rec_len, (unsigned long long*)a->h64);
+  if (a->sha_valid || a->xxh_valid) {
+    HashJob j;
+    memset(&j, 0, sizeof(j));
+    j.payload = a->d.payload;
+    j.rec_off = a->d.rec_off;
+    j.rec_len = a->d.rec_len;
+    j.sha = a->sha;
+    j.xxh = a->xxh;
+    j.nobj = n;
+    j.rec_list = d_idx;
+    if (ctx->d_jobs_cap < 1) {
+      NCD_CUDA(cudaMalloc(&ctx->d_jobs, sizeof(HashJob) * 32));
+      ctx->d_jobs_cap = 32;
+    }
+    NCD_CUDA(cudaMemcpyAsync(ctx->d_jobs, &j, sizeof(j), cudaMemcpyHostToDevice, st));  // pageable: staged now
+    const HashJob* dj = (const HashJob*)ctx->d_jobs;
+    unsigned int* next = reinterpret_cast<unsigned int*>(ctx->d_counters) + 8;
+    if (a->sha_valid) {
+      NCD_CUDA(cudaMemsetAsync(next, 0, 4, st));
+      const uint64_t want = (n + 127) / 128, cap = (uint64_t)ctx->sm_count * 16;
+      k_sha256<<<(unsigned)(want < cap ? want : cap), 128, sizeof(uint64_t), st>>>(dj, 1, (uint32_t)n, next);
+    }
+    if (a->xxh_valid) {
+      NCD_CUDA(cudaMemsetAsync(next, 0, 4, st));
+      const size_t xs = sizeof(XxhSmem) + sizeof(uint64_t);
+      NCD_CUDA(cudaFuncSetAttribute(k_xxh64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xs));
+      const uint64_t per_sm = (216u * 1024u) / xs ? (216u * 1024u) / xs : 1;
+      const uint64_t want = (n + 32 * XXH_WARPS - 1) / (32 * XXH_WARPS), cap = (uint64_t)ctx->sm_count * per_sm;
+      k_xxh64<<<(unsigned)(want < cap ? want : cap), 32 * XXH_WARPS, xs, st>>>(dj, 1, (uint32_t)n, next);
+    }
+  }
+  NCD_CUDA(cudaGetLastError());
+  return NCD_OK;
+}
+
 int ncd_hash_launch(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, uint32_t* launches) {
   return ncd_hash_launch_many(ctx, &a, 1, mode, launches);
 }
@@ -566,10 +650,12 @@ extern "C" int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* o
     return NCD_E_CAPACITY;
   }
   NCD_CUDA(cudaSetDevice(ctx->device));
-  // always recompute: this entry point is also the timing harness of the hash kernels
-  if (hm == NCD_MODE_HASH64) a->h64_valid = false;
-  else if (hm == NCD_MODE_SHA256) a->sha_valid = false;
-  else a->xxh_valid = false;
+  // recompute unless asked not to: this entry point is also the timing harness of the hash kernels
+  if (!(mode & NCD_MODE_CACHED)) {
+    if (hm == NCD_MODE_HASH64) a->h64_valid = false;
+    else if (hm == NCD_MODE_SHA256) a->sha_valid = false;
+    else a->xxh_valid = false;
+  }
   uint32_t launches = 0;
   NCD_CUDA(cudaEventRecord(ctx->ev[5], ctx->stream));
   NCD_TRY(ncd_hash_launch(ctx, a, hm, &launches));

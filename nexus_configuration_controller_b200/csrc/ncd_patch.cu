@@ -76,12 +76,21 @@ int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, ui
                                               new_payload_bytes, d_idx + n);
   uint32_t flags[2] = {0, 0};
   NCD_CUDA(cudaMemcpyAsync(flags, d_idx + n, 8, cudaMemcpyDeviceToHost, st));
+  NCD_CUDA(cudaStreamSynchronize(st));
+  a->payload_bytes = new_payload_bytes;
+  const uint32_t bad = flags[0];
+  // Digests the arena holds stay valid: only the rewritten records are hashed again, so a
+  // hash-mode scan after an informer event costs the changed bytes, not the fleet's.
+  int hrc = NCD_OK;
+  if (bad) a->h64_valid = a->sha_valid = a->xxh_valid = false;
+  else hrc = ncd_hash_records(a, d_idx, n);
   NCD_CUDA(cudaFreeAsync(d_idx, st));
   NCD_CUDA(cudaStreamSynchronize(st));
   NCD_CUDA(cudaGetLastError());
-  a->payload_bytes = new_payload_bytes;
-  a->h64_valid = a->sha_valid = a->xxh_valid = false;
-  const uint32_t bad = flags[0];
+  if (hrc != NCD_OK) {
+    a->h64_valid = a->sha_valid = a->xxh_valid = false;
+    return hrc;
+  }
   // same-length rewrites (the common event: a value changed in place) leave the tile lists and
   // the byte count as they are
   if (flags[1] || bad) NCD_TRY(ncd_rebuild_tiles(a));

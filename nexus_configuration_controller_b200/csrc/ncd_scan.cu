@@ -697,7 +697,22 @@ int ncd_diff_view(ncd_diff* d, const ncd_entry** entries, uint64_t* n) {
   }
   if (!d->h_valid) {
     NCD_CUDA(cudaSetDevice(d->ctx->device));
-    NCD_CUDA(cudaMallocHost((void**)&d->h_entries, (d->n ? d->n : 1) * sizeof(ncd_entry)));
+    // a pinned buffer from the context's pool if one is large enough, else a new one (power of two)
+    const size_t need = (size_t)(d->n ? d->n : 1) * sizeof(ncd_entry);
+    ncd_ctx* ctx = d->ctx;
+    int pick = -1;
+    for (int i = 0; i < 4; ++i)
+      if (ctx->hpool_ptr[i] && ctx->hpool_cap[i] >= need && (pick < 0 || ctx->hpool_cap[i] < ctx->hpool_cap[pick])) pick = i;
+    if (pick >= 0) {
+      d->h_entries = (ncd_entry*)ctx->hpool_ptr[pick];
+      d->h_cap = ctx->hpool_cap[pick];
+      ctx->hpool_ptr[pick] = nullptr;
+    } else {
+      size_t cap = 4096;
+      while (cap < need) cap <<= 1;
+      NCD_CUDA(cudaMallocHost((void**)&d->h_entries, cap));
+      d->h_cap = cap;
+    }
     if (d->n) {
       NCD_CUDA(cudaMemcpyAsync(d->h_entries, d->d_entries, d->n * sizeof(ncd_entry),
                                cudaMemcpyDeviceToHost, d->ctx->stream));
@@ -786,6 +801,27 @@ void ncd_diff_destroy(ncd_diff* d) {
   cudaSetDevice(d->ctx->device);
   if (d->d_entries) cudaFreeAsync(d->d_entries, d->ctx->stream);
   if (d->d_codes) cudaFreeAsync(d->d_codes, d->ctx->stream);
-  if (d->h_entries) cudaFreeHost(d->h_entries);
+  if (d->h_entries) {
+    // back to the pool: into a free slot, or in place of the smallest buffer if this one is larger
+    ncd_ctx* ctx = d->ctx;
+    int slot = -1;
+    for (int i = 0; i < 4 && slot < 0; ++i)
+      if (!ctx->hpool_ptr[i]) slot = i;
+    if (slot < 0) {
+      int smallest = 0;
+      for (int i = 1; i < 4; ++i)
+        if (ctx->hpool_cap[i] < ctx->hpool_cap[smallest]) smallest = i;
+      if (ctx->hpool_cap[smallest] < d->h_cap) {
+        cudaFreeHost(ctx->hpool_ptr[smallest]);
+        slot = smallest;
+      }
+    }
+    if (slot >= 0) {
+      ctx->hpool_ptr[slot] = d->h_entries;
+      ctx->hpool_cap[slot] = d->h_cap;
+    } else {
+      cudaFreeHost(d->h_entries);
+    }
+  }
   free(d);
 }

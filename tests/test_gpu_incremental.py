@@ -41,6 +41,7 @@ def test_rewritten_records_follow_to_the_device(ctx, seed):
     slack = 1 << 20
     arenas = [resident(ctx, h, slack) for h in [ctrl_h] + shard_hs]
     used = [h.payload_bytes for h in [ctrl_h] + shard_hs]
+    launches = {}
     try:
         for rnd in range(4):
             for k, a in enumerate(arenas):
@@ -63,17 +64,33 @@ def test_rewritten_records_follow_to_the_device(ctx, seed):
                 a.sync_records(np.array(picks, dtype=np.uint32), used[k])
             # also make a shard converge on the controller for some objects (drift goes away)
             want_codes, want_ents = oracle.scan(arenas[0].download(), [s.download() for s in arenas[1:]])
-            for mode in (A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256):
+            for mode in (A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64):
                 d = ctx.scan(arenas[0], arenas[1:], mode)
                 np.testing.assert_array_equal(d.codes(), want_codes)
                 np.testing.assert_array_equal(d.entries(), want_ents)
                 d.close()
+                # digests survive a value sync (only the rewritten records are hashed again, inside
+                # the sync), so from the second round on a hash-mode scan launches no hash kernel
+                launches.setdefault(mode, []).append(ctx.last_stats().launches)
+            # ... and the digests the arenas hold are those of the new contents
+            for a in arenas:
+                dev = a.download()
+                h64, ms = ctx.hash_arena(a, A.MODE_HASH64 | A.MODE_CACHED)
+                np.testing.assert_array_equal(h64, oracle.h64_arena(dev))
+                sha, _ = ctx.hash_arena(a, A.MODE_SHA256 | A.MODE_CACHED)
+                np.testing.assert_array_equal(sha, oracle.sha256_arena(dev))
+                xxh, _ = ctx.hash_arena(a, A.MODE_XXH64 | A.MODE_CACHED)
+                assert [int(v) for v in xxh] == [oracle.xxh64(dev.record(i)) for i in range(dev.nobj)]
             # the device copy is byte-identical to the pinned host arrays where records live
             for a in arenas:
                 arr, dev = a.host_arrays(), a.download()
                 for i in range(dev.nobj):
                     off, ln = int(arr["rec_off"][i]), int(arr["rec_len"][i])
                     assert dev.record(i) == arr["payload"][off : off + ln].tobytes()
+        for mode in (A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64):
+            first, later = launches[mode][0], launches[mode][1:]
+            assert all(n < first for n in later) and len(set(later)) == 1, (mode, launches[mode])
+            assert later[0] <= launches[A.MODE_DIRECT][-1]  # no hash kernel, and no compare kernel either
     finally:
         for a in arenas:
             a.close()
