@@ -216,6 +216,15 @@ int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint
  * ncd_arena_counts); any pointer in dst may be NULL to skip that array. */
 int ncd_arena_download(ncd_arena* a, ncd_arena_view* dst);
 int ncd_arena_counts(ncd_arena* a, ncd_arena_view* counts_only);
+/* Snapshot of a committed arena as a file, and back (offline
+ * diffing — compare what a cluster's caches held at some moment against another snapshot or a
+ * live arena).  The file carries every array of ncd_arena_view plus a checksum; it streams
+ * through a bounded pinned buffer.  ncd_arena_load creates the arena (flags as ncd_arena_create;
+ * payload_slack = spare payload capacity for later ncd_arena_sync_records on a HOST_PINNED one),
+ * verifies the checksum, validates the contents on the GPU like a commit does and builds the
+ * index.  No reference counterpart (the reference keeps no record of its caches). */
+int ncd_arena_save(ncd_arena* a, const char* path);
+int ncd_arena_load(ncd_ctx* ctx, const char* path, uint32_t flags, uint64_t payload_slack, ncd_arena** out);
 /* Rows of a committed arena when used as the controller side: one per template,
  * one per dependent reference of a template, one per workgroup. */
 int ncd_arena_rows(ncd_arena* a, uint64_t* rows);

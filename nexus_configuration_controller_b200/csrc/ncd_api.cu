@@ -1,6 +1,8 @@
 // ncd_api.cu — context and arena entry points of the C ABI (include/ncdrift.h).
 #include <stdarg.h>
+#include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "ncd_common.cuh"
 
@@ -367,5 +369,183 @@ extern "C" int ncd_arena_rows(ncd_arena* a, uint64_t* rows) {
     return NCD_E_STATE;
   }
   *rows = a->nrows;
+  return NCD_OK;
+}
+
+// ------------------------------------------------------------------ snapshots
+// One arena as a file, for offline diffing: what a cluster's caches held at some moment, compared
+// later (or elsewhere) against another snapshot or a live arena.  Layout, little-endian:
+//   header   "NCDARENA", u32 version (1), u32 field count (17), u64 nobj, payload_bytes,
+//            aux_bytes, nowner, ndep
+//   fields   in ncd_arena_view order; each: u64 byte count, the bytes, zero padding to 16
+//   trailer  u64 checksum of every field byte (word-wise multiply-xor), "NCDAEND\0"
+// Streams through a bounded pinned buffer, so a 10 GB arena needs no 10 GB of host memory.
+// No reference counterpart (the reference keeps no record of what its caches held).
+namespace {
+constexpr size_t kSnapChunk = 32u << 20;
+struct SnapHeader {
+  char magic[8];
+  uint32_t version, nfields;
+  uint64_t nobj, payload_bytes, aux_bytes, nowner, ndep;
+};
+inline uint64_t snap_mix(uint64_t h, const void* p, size_t n) {
+  const unsigned char* b = (const unsigned char*)p;
+  size_t i = 0;
+  for (; i + 8 <= n; i += 8) {
+    uint64_t w;
+    memcpy(&w, b + i, 8);
+    h = (h ^ w) * 0x9E3779B185EBCA87ull;
+    h ^= h >> 29;
+  }
+  uint64_t w = 0;
+  if (i < n) {
+    memcpy(&w, b + i, n - i);
+    h = (h ^ w ^ ((uint64_t)(n - i) << 56)) * 0x9E3779B185EBCA87ull;
+    h ^= h >> 29;
+  }
+  return h;
+}
+struct SnapFile {
+  FILE* f = nullptr;
+  void* stage = nullptr;
+  ~SnapFile() {
+    if (f) fclose(f);
+    if (stage) cudaFreeHost(stage);
+  }
+};
+}  // namespace
+
+extern "C" int ncd_arena_save(ncd_arena* a, const char* path) {
+  if (!a || !path) {
+    ncd_set_error("ncd_arena_save: null argument");
+    return NCD_E_INVALID;
+  }
+  if (!a->committed) {
+    ncd_set_error("ncd_arena_save: arena not committed");
+    return NCD_E_STATE;
+  }
+  NCD_CUDA(cudaSetDevice(a->ctx->device));
+  cudaStream_t st = a->ctx->stream;
+  SnapFile sf;
+  sf.f = fopen(path, "wb");
+  if (!sf.f) {
+    ncd_set_error("ncd_arena_save: cannot open %s for writing", path);
+    return NCD_E_INVALID;
+  }
+  NCD_CUDA(cudaMallocHost(&sf.stage, kSnapChunk));
+  SnapHeader h;
+  memset(&h, 0, sizeof(h));
+  memcpy(h.magic, "NCDARENA", 8);
+  h.version = 1;
+  h.nfields = kNumFields;
+  h.nobj = a->nobj;
+  h.payload_bytes = a->payload_bytes;
+  h.aux_bytes = a->aux_bytes;
+  h.nowner = a->nowner;
+  h.ndep = a->ndep;
+  bool ok = fwrite(&h, sizeof(h), 1, sf.f) == 1;
+  uint64_t sum = 0x6e6364615f736e61ull;
+  const char zeros[16] = {0};
+  for (int i = 0; i < kNumFields && ok; ++i) {
+    const Field& f = kFields[i];
+    uint64_t bytes = field_count(f, a->payload_bytes, a->nobj, a->aux_bytes, a->nowner, a->ndep) * f.elem;
+    if (f.cap_kind == 0) bytes = a->payload_bytes;
+    ok = fwrite(&bytes, 8, 1, sf.f) == 1;
+    const char* src = (const char*)*field_ptr(&a->d, f);
+    for (uint64_t off = 0; off < bytes && ok; off += kSnapChunk) {
+      const size_t n = (size_t)(bytes - off < kSnapChunk ? bytes - off : kSnapChunk);
+      NCD_CUDA(cudaMemcpyAsync(sf.stage, src + off, n, cudaMemcpyDeviceToHost, st));
+      NCD_CUDA(cudaStreamSynchronize(st));
+      sum = snap_mix(sum, sf.stage, n);
+      ok = fwrite(sf.stage, 1, n, sf.f) == n;
+    }
+    const size_t pad = (size_t)((16 - bytes % 16) % 16);
+    if (ok && pad) ok = fwrite(zeros, 1, pad, sf.f) == pad;
+  }
+  if (ok) ok = fwrite(&sum, 8, 1, sf.f) == 1 && fwrite("NCDAEND\0", 8, 1, sf.f) == 1;
+  if (ok) ok = fflush(sf.f) == 0;
+  if (!ok) {
+    ncd_set_error("ncd_arena_save: write to %s failed", path);
+    return NCD_E_INVALID;
+  }
+  return NCD_OK;
+}
+
+extern "C" int ncd_arena_load(ncd_ctx* ctx, const char* path, uint32_t flags, uint64_t payload_slack, ncd_arena** out) {
+  if (!ctx || !path || !out) {
+    ncd_set_error("ncd_arena_load: null argument");
+    return NCD_E_INVALID;
+  }
+  *out = nullptr;
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  SnapFile sf;
+  sf.f = fopen(path, "rb");
+  if (!sf.f) {
+    ncd_set_error("ncd_arena_load: cannot open %s", path);
+    return NCD_E_INVALID;
+  }
+  SnapHeader h;
+  if (fread(&h, sizeof(h), 1, sf.f) != 1 || memcmp(h.magic, "NCDARENA", 8) != 0 || h.version != 1 ||
+      h.nfields != (uint32_t)kNumFields) {
+    ncd_set_error("ncd_arena_load: %s is not an arena snapshot of version 1", path);
+    return NCD_E_INVALID;
+  }
+  ncd_arena* a = nullptr;
+  NCD_TRY(ncd_arena_create(ctx, h.payload_bytes + payload_slack, h.nobj, h.aux_bytes, h.nowner, h.ndep, flags, &a));
+  struct Guard {
+    ncd_arena* a;
+    ~Guard() {
+      if (a) ncd_arena_destroy(a);
+    }
+  } guard{a};
+  NCD_CUDA(cudaMallocHost(&sf.stage, kSnapChunk));
+  cudaStream_t st = ctx->stream;
+  uint64_t sum = 0x6e6364615f736e61ull;
+  for (int i = 0; i < kNumFields; ++i) {
+    const Field& f = kFields[i];
+    uint64_t want = field_count(f, h.payload_bytes, h.nobj, h.aux_bytes, h.nowner, h.ndep) * f.elem;
+    if (f.cap_kind == 0) want = h.payload_bytes;
+    uint64_t bytes = 0;
+    if (fread(&bytes, 8, 1, sf.f) != 1 || bytes != want) {
+      ncd_set_error("ncd_arena_load: %s: field %d holds %llu bytes, the header implies %llu", path, i,
+                    (unsigned long long)bytes, (unsigned long long)want);
+      return NCD_E_INVALID;
+    }
+    char* dev = (char*)*field_ptr(&a->d, f);
+    char* host = flags == NCD_ARENA_HOST_PINNED ? (char*)*field_ptr(&a->h, f) : nullptr;
+    for (uint64_t off = 0; off < bytes; off += kSnapChunk) {
+      const size_t n = (size_t)(bytes - off < kSnapChunk ? bytes - off : kSnapChunk);
+      void* into = host ? (void*)(host + off) : sf.stage;
+      if (fread(into, 1, n, sf.f) != n) {
+        ncd_set_error("ncd_arena_load: %s is truncated", path);
+        return NCD_E_INVALID;
+      }
+      sum = snap_mix(sum, into, n);
+      NCD_CUDA(cudaMemcpyAsync(dev + off, into, n, cudaMemcpyHostToDevice, st));
+      if (!host) NCD_CUDA(cudaStreamSynchronize(st));  // the staging buffer is reused
+    }
+    const size_t pad = (size_t)((16 - bytes % 16) % 16);
+    char skip[16];
+    if (pad && fread(skip, 1, pad, sf.f) != pad) {
+      ncd_set_error("ncd_arena_load: %s is truncated", path);
+      return NCD_E_INVALID;
+    }
+  }
+  uint64_t stored = 0;
+  char endm[8];
+  if (fread(&stored, 8, 1, sf.f) != 1 || fread(endm, 8, 1, sf.f) != 1 || memcmp(endm, "NCDAEND\0", 8) != 0) {
+    ncd_set_error("ncd_arena_load: %s has no trailer (truncated?)", path);
+    return NCD_E_INVALID;
+  }
+  if (stored != sum) {
+    ncd_set_error("ncd_arena_load: %s is corrupt (checksum %016llx, expected %016llx)", path, (unsigned long long)sum,
+                  (unsigned long long)stored);
+    return NCD_E_INVALID;
+  }
+  NCD_CUDA(cudaStreamSynchronize(st));
+  // the arrays are on the device already: validate them and build the index there
+  NCD_TRY(ncd_arena_commit_device(a, h.nobj, h.payload_bytes, h.aux_bytes, h.nowner, h.ndep));
+  guard.a = nullptr;
+  *out = a;
   return NCD_OK;
 }

@@ -8,6 +8,7 @@ computes lives in libncdrift.so; this file only moves pointers.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -144,6 +145,19 @@ class Arena:
         if self.handle:
             self.ctx.lib.ncd_arena_destroy(self.handle)
             self.handle = None
+
+    def save(self, path: str) -> None:
+        """Writes the committed arena to a snapshot file (ncd_arena_save)."""
+        check(self.ctx.lib.ncd_arena_save(self.handle, os.fsencode(path)))
+
+    @classmethod
+    def load(cls, ctx: "Context", path: str, device_only: bool = True, payload_slack: int = 0) -> "Arena":
+        """An arena from a snapshot file, checked, validated and indexed (ncd_arena_load)."""
+        h = C.c_void_p()
+        check(ctx.lib.ncd_arena_load(ctx.handle, os.fsencode(path), 1 if device_only else 0, payload_slack, C.byref(h)))
+        a = cls.__new__(cls)
+        a.ctx, a.handle = ctx, h
+        return a
 
     def host_view(self) -> ArenaView:
         v = ArenaView()
