@@ -202,6 +202,13 @@ int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64
  * holds (from a hash-mode scan or ncd_hash_arena) are brought up to date for the listed records
  * and stay valid, so the next hash-mode scan hashes nothing. */
 int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint64_t new_payload_bytes);
+/* The same for several arenas of one context in one call (a sweep syncs the controller and every
+ * shard cluster before it scans): every pull is enqueued first, then one host synchronisation
+ * reads all results back — one round trip instead of one per arena.  Arrays of `count` entries;
+ * an arena may appear once.  On a refused record the call still finishes the other arenas and
+ * returns the first error. */
+int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t* n,
+                            const uint32_t* const* obj_idx, const uint64_t* new_payload_bytes);
 /* Commit after a structural change (objects added, deleted or re-owned: informer AddFunc /
  * DeleteFunc, controller.go:286-305, 319-355) WITHOUT re-uploading the payload that did not
  * change.  The packer has rewritten the small per-object arrays in the pinned host arena (any

@@ -586,7 +586,7 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
 int ncd_hash_records(ncd_arena* a, const uint32_t* d_idx, uint64_t n) {
   ncd_ctx* ctx = a->ctx;
   cudaStream_t st = ctx->stream;
-  if (n == 0 || !(a->h64_valid || a->sha_valid || a->xxh_valid)) return NCD_OK;
+  if (n == 0 || a->nobj == 0 || !(a->h64_valid || a->sha_valid || a->xxh_valid)) return NCD_OK;
   if (a->h64_valid)
     k_h64_records<<<(unsigned)n, 256, 0, st>>>(d_idx, a->d.payload, a->d.rec_off, a->d.rec_len, (unsigned long long*)a->h64);
   if (a->sha_valid || a->xxh_valid) {

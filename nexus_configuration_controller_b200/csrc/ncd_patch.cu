@@ -13,13 +13,16 @@
 // One CTA per rewritten record.  h_* are the pinned host arrays (unified addressing makes them
 // readable from the device); the record lands at the same offset in the device payload.
 __global__ void __launch_bounds__(128)
-k_pull_records(const uint32_t* __restrict__ idx, const uint8_t* h_payload, const uint64_t* h_rec_off,
+k_pull_records(uint32_t* __restrict__ idx, const uint8_t* h_payload, const uint64_t* h_rec_off,
                const uint32_t* h_rec_len, uint8_t* __restrict__ d_payload, uint64_t* __restrict__ d_rec_off,
                uint32_t* __restrict__ d_rec_len, ObjMeta* __restrict__ meta, uint32_t nobj,
                uint64_t payload_limit, uint32_t* __restrict__ bad /*[0] refused, [1] lengths changed*/) {
   const uint32_t i = idx[blockIdx.x];
   if (i >= nobj) {
-    if (threadIdx.x == 0) atomicAdd(bad, 1u);
+    if (threadIdx.x == 0) {
+      atomicAdd(bad, 1u);
+      idx[blockIdx.x] = 0;  // the list is read again by the re-hash: keep it inside the arena
+    }
     return;
   }
   const uint64_t off = h_rec_off[i];
@@ -41,7 +44,8 @@ k_pull_records(const uint32_t* __restrict__ idx, const uint8_t* h_payload, const
   for (uint32_t v = threadIdx.x; v < (uint32_t)(padded >> 4); v += blockDim.x) dst[v] = src[v];
 }
 
-int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint64_t new_payload_bytes) {
+// Checks one arena's arguments for a sync (no CUDA calls).
+static int sync_check(const ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint64_t new_payload_bytes) {
   if (!a || (!obj_idx && n)) {
     ncd_set_error("ncd_arena_sync_records: null argument");
     return NCD_E_INVALID;
@@ -60,46 +64,111 @@ int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, ui
                   (unsigned long long)new_payload_bytes, (unsigned long long)a->payload_cap);
     return NCD_E_CAPACITY;
   }
-  if (n == 0) {
-    a->payload_bytes = new_payload_bytes;
-    return NCD_OK;
-  }
-  ncd_ctx* ctx = a->ctx;
-  NCD_CUDA(cudaSetDevice(ctx->device));
-  cudaStream_t st = ctx->stream;
-  uint32_t* d_idx = nullptr;
-  NCD_CUDA(cudaMallocAsync((void**)&d_idx, (n + 2) * 4, st));
-  NCD_CUDA(cudaMemcpyAsync(d_idx, obj_idx, n * 4, cudaMemcpyHostToDevice, st));
-  NCD_CUDA(cudaMemsetAsync(d_idx + n, 0, 8, st));
-  k_pull_records<<<(unsigned)n, 128, 0, st>>>(d_idx, a->h.payload, a->h.rec_off, a->h.rec_len, a->d.payload,
-                                              a->d.rec_off, a->d.rec_len, a->meta, (uint32_t)a->nobj,
-                                              new_payload_bytes, d_idx + n);
-  uint32_t flags[2] = {0, 0};
-  NCD_CUDA(cudaMemcpyAsync(flags, d_idx + n, 8, cudaMemcpyDeviceToHost, st));
-  NCD_CUDA(cudaStreamSynchronize(st));
-  a->payload_bytes = new_payload_bytes;
-  const uint32_t bad = flags[0];
-  // Digests the arena holds stay valid: only the rewritten records are hashed again, so a
-  // hash-mode scan after an informer event costs the changed bytes, not the fleet's.
-  int hrc = NCD_OK;
-  if (bad) a->h64_valid = a->sha_valid = a->xxh_valid = false;
-  else hrc = ncd_hash_records(a, d_idx, n);
-  NCD_CUDA(cudaFreeAsync(d_idx, st));
-  NCD_CUDA(cudaStreamSynchronize(st));
-  NCD_CUDA(cudaGetLastError());
-  if (hrc != NCD_OK) {
-    a->h64_valid = a->sha_valid = a->xxh_valid = false;
-    return hrc;
-  }
-  // same-length rewrites (the common event: a value changed in place) leave the tile lists and
-  // the byte count as they are
-  if (flags[1] || bad) NCD_TRY(ncd_rebuild_tiles(a));
-  if (bad) {
-    ncd_set_error("ncd_arena_sync_records: %u of %llu records were refused (index out of range, record "
-                  "not 16-byte aligned or outside the payload); commit the arena again", bad,
-                  (unsigned long long)n);
-    a->committed = false;
-    return NCD_E_INVALID;
+  if (n >= 0xFFFFFFFFull) {
+    ncd_set_error("ncd_arena_sync_records: more than 2^32 records named");
+    return NCD_E_CAPACITY;
   }
   return NCD_OK;
+}
+
+// Several arenas of one context in one pass: every pull (and the re-hash of the pulled records,
+// where an arena holds digests) is enqueued first, then ONE host synchronisation reads all the
+// flags back.  A sweep over S shard clusters + the controller pays one round trip, not S + 1.
+int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t* n, const uint32_t* const* obj_idx,
+                            const uint64_t* new_payload_bytes) {
+  if (count < 0 || (count > 0 && (!arenas || !n || !obj_idx || !new_payload_bytes))) {
+    ncd_set_error("ncd_arenas_sync_records: null argument");
+    return NCD_E_INVALID;
+  }
+  uint64_t total = 0;
+  ncd_ctx* ctx = nullptr;
+  for (int k = 0; k < count; ++k) {
+    NCD_TRY(sync_check(arenas[k], n[k], obj_idx[k], new_payload_bytes[k]));
+    for (int q = 0; q < k; ++q)
+      if (arenas[q] == arenas[k]) {
+        ncd_set_error("ncd_arenas_sync_records: arena %d is listed twice", k);
+        return NCD_E_INVALID;
+      }
+    if (ctx && arenas[k]->ctx != ctx) {
+      ncd_set_error("ncd_arenas_sync_records: arenas of different contexts");
+      return NCD_E_INVALID;
+    }
+    ctx = arenas[k]->ctx;
+    total += n[k];
+  }
+  if (total == 0) {
+    for (int k = 0; k < count; ++k) arenas[k]->payload_bytes = new_payload_bytes[k];
+    return NCD_OK;
+  }
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  // device: [indices of arena 0 | arena 1 | ...][2 flag words per arena]
+  uint32_t* d_idx = nullptr;
+  NCD_CUDA(cudaMallocAsync((void**)&d_idx, (total + 2 * (uint64_t)count) * 4, st));
+  uint32_t* d_flags = d_idx + total;
+  NCD_CUDA(cudaMemsetAsync(d_flags, 0, 8 * (size_t)count, st));
+  uint64_t at = 0;
+  int hrc = NCD_OK;
+  for (int k = 0; k < count; ++k) {
+    ncd_arena* a = arenas[k];
+    if (!n[k]) continue;
+    // pageable source: staged by the runtime before the call returns
+    NCD_CUDA(cudaMemcpyAsync(d_idx + at, obj_idx[k], n[k] * 4, cudaMemcpyHostToDevice, st));
+    k_pull_records<<<(unsigned)n[k], 128, 0, st>>>(d_idx + at, a->h.payload, a->h.rec_off, a->h.rec_len, a->d.payload,
+                                                  a->d.rec_off, a->d.rec_len, a->meta, (uint32_t)a->nobj,
+                                                  new_payload_bytes[k], d_flags + 2 * k);
+    // Digests the arena holds stay valid: only the rewritten records are hashed again, so a
+    // hash-mode scan after an informer event costs the changed bytes, not the fleet's.  (A
+    // refused index was replaced by the kernel above with a valid one; the arena is then
+    // uncommitted below anyway.)
+    if (hrc == NCD_OK) hrc = ncd_hash_records(a, d_idx + at, n[k]);
+    at += n[k];
+  }
+  uint32_t* flags = (uint32_t*)calloc((size_t)count * 2, sizeof(uint32_t));
+  if (!flags) {
+    cudaFreeAsync(d_idx, st);
+    ncd_set_error("ncd_arenas_sync_records: out of host memory");
+    return NCD_E_NOMEM;
+  }
+  cudaError_t e = cudaMemcpyAsync(flags, d_flags, 8 * (size_t)count, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaFreeAsync(d_idx, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    free(flags);
+    ncd_set_error("ncd_arenas_sync_records: %s", cudaGetErrorString(e));
+    return NCD_E_CUDA;
+  }
+  int rc = hrc;
+  for (int k = 0; k < count; ++k) {
+    ncd_arena* a = arenas[k];
+    a->payload_bytes = new_payload_bytes[k];
+    const uint32_t bad = flags[2 * k], len_changed = flags[2 * k + 1];
+    if (bad || hrc != NCD_OK) a->h64_valid = a->sha_valid = a->xxh_valid = false;
+    // same-length rewrites (the common event: a value changed in place) leave the tile lists and
+    // the byte count as they are
+    if (len_changed || bad) {
+      const int t = ncd_rebuild_tiles(a);
+      if (t != NCD_OK && rc == NCD_OK) rc = t;
+    }
+    if (bad) {
+      a->committed = false;
+      if (rc == NCD_OK || rc == hrc) {
+        ncd_set_error("ncd_arena_sync_records: %u of %llu records of arena %d were refused (index out of range, "
+                      "record not 16-byte aligned or outside the payload); commit the arena again",
+                      bad, (unsigned long long)n[k], k);
+        rc = NCD_E_INVALID;
+      }
+    }
+  }
+  free(flags);
+  return rc;
+}
+
+int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint64_t new_payload_bytes) {
+  if (!a) {
+    ncd_set_error("ncd_arena_sync_records: null argument");
+    return NCD_E_INVALID;
+  }
+  return ncd_arenas_sync_records(1, &a, &n, &obj_idx, &new_payload_bytes);
 }

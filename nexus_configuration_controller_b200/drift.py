@@ -86,6 +86,20 @@ class Context:
         arr = (C.c_void_p * max(len(shards), 1))(*[s.handle for s in shards])
         check(self.lib.ncd_scan_into(self.handle, ctrl.handle, arr, len(shards), mode, C.c_void_p(dev_ptr), cap_entries))
 
+    def sync_records_many(self, arenas: Sequence["Arena"], idx_lists: Sequence[np.ndarray], payload_bytes: Sequence[int]) -> None:
+        """ncd_arenas_sync_records: value rewrites of several resident arenas, one round trip."""
+        k = len(arenas)
+        idx = [np.ascontiguousarray(i, dtype=np.uint32) for i in idx_lists]
+        check(
+            self.lib.ncd_arenas_sync_records(
+                k,
+                (C.c_void_p * max(k, 1))(*[a.handle for a in arenas]),
+                (C.c_uint64 * max(k, 1))(*[len(i) for i in idx]),
+                (C.c_void_p * max(k, 1))(*[i.ctypes.data for i in idx]),
+                (C.c_uint64 * max(k, 1))(*[int(p) for p in payload_bytes]),
+            )
+        )
+
     def stats_back(self, back: int) -> ScanStats:
         st = ScanStats()
         check(self.lib.ncd_scan_stats_back(self.handle, back, C.byref(st)))

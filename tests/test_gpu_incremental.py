@@ -44,6 +44,7 @@ def test_rewritten_records_follow_to_the_device(ctx, seed):
     launches = {}
     try:
         for rnd in range(4):
+            batch = []
             for k, a in enumerate(arenas):
                 arr = a.host_arrays()
                 n = a.counts().nobj
@@ -61,7 +62,12 @@ def test_rewritten_records_follow_to_the_device(ctx, seed):
                     else:  # longer: appended behind the payload end
                         new = rand_bytes(rng, old + rng.randint(1, 9000))
                     used[k] = rewrite(rng, arr, used[k], i, new)
-                a.sync_records(np.array(picks, dtype=np.uint32), used[k])
+                if rnd % 2 == 0:
+                    a.sync_records(np.array(picks, dtype=np.uint32), used[k])
+                else:
+                    batch.append(np.array(picks, dtype=np.uint32))
+            if batch:  # odd rounds: every arena in one call (ncd_arenas_sync_records)
+                ctx.sync_records_many(arenas, batch, used)
             # also make a shard converge on the controller for some objects (drift goes away)
             want_codes, want_ents = oracle.scan(arenas[0].download(), [s.download() for s in arenas[1:]])
             for mode in (A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64):
@@ -116,6 +122,39 @@ def test_sync_refuses_what_it_cannot_place(ctx):
         dev_only.close()
     finally:
         a.close()
+
+
+def test_batched_sync_finishes_the_good_arenas_and_reports_the_bad_one(ctx):
+    """ncd_arenas_sync_records with one arena naming an object it does not have, while both hold
+    digests: the good arena is synced (and its digests follow), the bad one is refused and needs a
+    commit, nothing reads outside an arena."""
+    from nexus_configuration_controller_b200._ffi import NcdError
+
+    ctrl_h, shard_hs = random_clusters(9, n_templates=8, n_shards=2)
+    good, bad = resident(ctx, shard_hs[0], 1 << 16), resident(ctx, shard_hs[1], 1 << 16)
+    try:
+        for a in (good, bad):
+            ctx.hash_arena(a, A.MODE_HASH64)
+            ctx.hash_arena(a, A.MODE_XXH64)
+            ctx.hash_arena(a, A.MODE_SHA256)
+        arr = good.host_arrays()
+        i = next(k for k in range(shard_hs[0].nobj) if shard_hs[0].rec_len[k] > 0)
+        arr["payload"][int(arr["rec_off"][i])] ^= 0x11
+        with pytest.raises(NcdError, match="refused"):
+            ctx.sync_records_many([good, bad], [np.array([i], dtype=np.uint32), np.array([0, 10**6], dtype=np.uint32)],
+                                  [shard_hs[0].payload_bytes, shard_hs[1].payload_bytes])
+        dev = good.download()
+        assert dev.record(i) != shard_hs[0].record(i)
+        h64, _ = ctx.hash_arena(good, A.MODE_HASH64 | A.MODE_CACHED)
+        np.testing.assert_array_equal(h64, oracle.h64_arena(dev))
+        with pytest.raises(NcdError):
+            ctx.scan(bad, [], A.MODE_DIRECT)
+        with pytest.raises(NcdError):  # the same arena twice in one batch
+            ctx.sync_records_many([good, good], [np.array([i], dtype=np.uint32)] * 2, [shard_hs[0].payload_bytes] * 2)
+        ctx.sync_records_many([], [], [])  # nothing to do is not an error
+    finally:
+        good.close()
+        bad.close()
 
 
 def test_structural_change_recommits_without_the_old_payload(ctx):
