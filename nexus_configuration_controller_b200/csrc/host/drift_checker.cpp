@@ -114,7 +114,9 @@ struct ClusterImage {
 
   // Brings the resident arena up to date with the image.  `order` (controller image only)
   // receives the live objects in arena order.
-  void sync(ncd_ctx* ctx, std::vector<const CachedObject*>* order) {
+  // deferred: if given, a pure value sync is not issued here but left in pending_changed for the
+  // caller, which pushes the rewritten records of every cluster in one ncd_arenas_sync_records
+  void sync(ncd_ctx* ctx, std::vector<const CachedObject*>* order, std::vector<ClusterImage*>* deferred = nullptr) {
     // forget dead objects (their payload becomes unreferenced until the next full commit)
     if (structural) {
       std::vector<CachedObject> keep;
@@ -177,7 +179,7 @@ struct ClusterImage {
       structural = true;
       arena.reset();
       if (order) order->clear();
-      sync(ctx, order);
+      sync(ctx, order, deferred);
       return;
     }
     ncd_arena_view v;
@@ -191,11 +193,16 @@ struct ClusterImage {
       changed.push_back((uint32_t)i);
     }
     if (!changed.empty()) {
-      if (ncd_arena_sync_records(arena.a, changed.size(), changed.data(), payload_used) != NCD_OK)
-        throw std::runtime_error(ncd_err("ncd_arena_sync_records"));
       ++uploads_values;
+      if (deferred) {
+        pending_changed.swap(changed);
+        deferred->push_back(this);
+      } else if (ncd_arena_sync_records(arena.a, changed.size(), changed.data(), payload_used) != NCD_OK) {
+        throw std::runtime_error(ncd_err("ncd_arena_sync_records"));
+      }
     }
   }
+  std::vector<uint32_t> pending_changed;  // objects whose records a deferred value sync still has to push
 
  private:
   uint64_t aux_used = 0, own_used = 0, dep_used = 0;
@@ -364,11 +371,26 @@ int ncdh_scan(ncdh_checker* c) {
   if (!c) return fail("ncdh_scan: null checker");
   try {
     std::vector<const CachedObject*> order;
-    c->controller.sync(c->ctx, &order);
+    std::vector<ClusterImage*> deferred;
+    c->controller.sync(c->ctx, &order, &deferred);
     std::vector<const ncd_arena*> ptrs;
     for (ClusterImage& sh : c->shards) {
-      sh.sync(c->ctx, nullptr);
+      sh.sync(c->ctx, nullptr, &deferred);
       ptrs.push_back(sh.arena.a);
+    }
+    if (!deferred.empty()) {  // the value rewrites of every cluster: one round trip
+      std::vector<ncd_arena*> as;
+      std::vector<uint64_t> ns, pbs;
+      std::vector<const uint32_t*> idx;
+      for (ClusterImage* img : deferred) {
+        as.push_back(img->arena.a);
+        ns.push_back(img->pending_changed.size());
+        idx.push_back(img->pending_changed.data());
+        pbs.push_back(img->payload_used);
+      }
+      const int rc = ncd_arenas_sync_records((int)as.size(), as.data(), ns.data(), idx.data(), pbs.data());
+      for (ClusterImage* img : deferred) img->pending_changed.clear();
+      if (rc != NCD_OK) return fail(ncd_err("ncd_arenas_sync_records"));
     }
     ncd_diff* d = nullptr;
     if (ncd_scan(c->ctx, c->controller.arena.a, ptrs.data(), (int)ptrs.size(), c->mode, &d) != NCD_OK)
