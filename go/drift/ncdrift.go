@@ -124,6 +124,31 @@ func (a *Arena) SyncRecords(objs []uint32, payload uint64) error {
 	return nil
 }
 
+// Save writes the committed arena to a snapshot file; LoadArena brings one back, checked and indexed
+// (offline diffing, SURVEY section 8 row f-4).
+func (a *Arena) Save(path string) error {
+	cp := C.CString(path)
+	defer C.free(unsafe.Pointer(cp))
+	if C.ncd_arena_save(a.h, cp) != 0 {
+		return lastErr("ncd_arena_save")
+	}
+	return nil
+}
+
+func (c *Ctx) LoadArena(path string, deviceOnly bool, payloadSlack uint64) (*Arena, error) {
+	cp := C.CString(path)
+	defer C.free(unsafe.Pointer(cp))
+	flags := C.uint32_t(C.NCD_ARENA_HOST_PINNED)
+	if deviceOnly {
+		flags = C.uint32_t(C.NCD_ARENA_DEVICE_ONLY)
+	}
+	a := &Arena{}
+	if C.ncd_arena_load(c.h, cp, flags, C.uint64_t(payloadSlack), &a.h) != 0 {
+		return nil, lastErr("ncd_arena_load")
+	}
+	return a, nil
+}
+
 // Entry == ncd_entry.
 type Entry struct{ Obj, Dep, Shard, Code uint32 }
 
