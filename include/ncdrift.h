@@ -275,7 +275,8 @@ int ncd_scan_into(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* s
  *                                 needs peer access between the devices, or the same device)
  * Per step:       ncd_scan_exchange (asynchronous: scan, compaction into this rank's slot, one
  *                 kernel that stores the slot into every peer's buffer, flags it and waits for
- *                 the peers' flags), then ncd_xchg_fetch (host copy) or ncd_xchg_result + ncd_sync
+ *                 the peers' flags), then ncd_xchg_fetch (host copy: headers and the entries each
+ *                 slot really holds; the rest of host_out is left as it was) or ncd_xchg_result + ncd_sync
  *                 (device view): world x (16 + 16 * cap_entries) bytes, slot r = rank r's list in
  *                 ncd_diff_pack layout.
  * Rules: every rank calls ncd_scan_exchange the same number of times; use a gathered list (or

@@ -248,10 +248,22 @@ extern "C" int ncd_xchg_fetch(ncd_xchg* x, void* host_out, uint64_t bytes) {
     return NCD_E_CAPACITY;
   }
   NCD_CUDA(cudaSetDevice(x->ctx->device));
+  cudaStream_t st = x->ctx->stream;
   uint32_t err = 0;
-  NCD_CUDA(cudaMemcpyAsync(host_out, src, have, cudaMemcpyDeviceToHost, x->ctx->stream));
-  NCD_CUDA(cudaMemcpyAsync(&err, x->buf + x->err_off, sizeof(err), cudaMemcpyDeviceToHost, x->ctx->stream));
-  NCD_CUDA(cudaStreamSynchronize(x->ctx->stream));
+  // headers first (16 bytes per slot), then only the entries each slot really holds: the slots are
+  // sized for the worst case, the lists are usually a small part of that
+  NCD_CUDA(cudaMemcpy2DAsync(host_out, x->slot_bytes, src, x->slot_bytes, 16, (size_t)x->world, cudaMemcpyDeviceToHost, st));
+  NCD_CUDA(cudaMemcpyAsync(&err, x->buf + x->err_off, sizeof(err), cudaMemcpyDeviceToHost, st));
+  NCD_CUDA(cudaStreamSynchronize(st));
+  for (int r = 0; r < x->world; ++r) {
+    uint32_t found = 0;
+    memcpy(&found, (const char*)host_out + (size_t)r * x->slot_bytes, 4);
+    const uint64_t nent = found < x->cap ? found : x->cap;
+    if (nent)
+      NCD_CUDA(cudaMemcpyAsync((char*)host_out + (size_t)r * x->slot_bytes + 16, (const char*)src + (size_t)r * x->slot_bytes + 16,
+                               nent * sizeof(ncd_entry), cudaMemcpyDeviceToHost, st));
+  }
+  NCD_CUDA(cudaStreamSynchronize(st));
   if (err) {
     ncd_set_error("ncd_xchg_fetch: a peer's diff list did not arrive within %.1f s", x->timeout_ns * 1e-9);
     return NCD_E_STATE;
