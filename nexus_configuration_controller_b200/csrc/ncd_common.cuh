@@ -226,7 +226,8 @@ int ncd_launch_compare_tma(ncd_ctx* ctx, const DevArena& dctrl, uint32_t S, cons
                            uint32_t* counters, uint32_t count_collisions);
 // ncd_hash.cu
 int ncd_hash_launch(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, uint32_t* launches);
-int ncd_hash_records(ncd_arena* a, const uint32_t* d_idx, uint64_t n);  // ncd_hash.cu: named records only
+int ncd_hash_records_many(ncd_ctx* ctx, int count, ncd_arena* const* arenas, const uint32_t* const* d_idx,
+                          const uint64_t* n);  // ncd_hash.cu: named records only
 int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint32_t mode, uint32_t* launches);
 
 // ------------------------------------------------------------------ device helpers

@@ -6,6 +6,8 @@
 //   k_h64_tiles    striped 64-bit hash, one warp per 4 KB tile, HBM bound (all arenas of a scan in one launch)
 //   k_h64_final    one thread per object folds the tile sums and the length
 //   k_sha256       FIPS 180-4 SHA-256, persistent lanes pulling records, integer-pipe bound
+#include <vector>
+
 #include "ncd_common.cuh"
 #include "ncd_tma.cuh"
 
@@ -580,16 +582,20 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
   return NCD_OK;
 }
 
-// Digests of the n records named by d_idx (device array), for every digest kind the arena
-// currently holds valid; the other records' digests are untouched.  Called by the value sync so
-// that cached digests stay valid across informer events.
-int ncd_hash_records(ncd_arena* a, const uint32_t* d_idx, uint64_t n) {
-  ncd_ctx* ctx = a->ctx;
+// Digests of the records named by d_idx[k] (device arrays, n[k] entries) of each arena, for every
+// digest kind that arena currently holds valid; the other records' digests are untouched.  Called
+// by the value sync so that cached digests stay valid across informer events.  SHA-256 and XXH64
+// are serial inside a record, so all arenas go into ONE launch per kind: the pass then lasts as
+// long as its longest record, not the sum over arenas.
+int ncd_hash_records_many(ncd_ctx* ctx, int count, ncd_arena* const* arenas, const uint32_t* const* d_idx, const uint64_t* n) {
   cudaStream_t st = ctx->stream;
-  if (n == 0 || a->nobj == 0 || !(a->h64_valid || a->sha_valid || a->xxh_valid)) return NCD_OK;
-  if (a->h64_valid)
-    k_h64_records<<<(unsigned)n, 256, 0, st>>>(d_idx, a->d.payload, a->d.rec_off, a->d.rec_len, (unsigned long long*)a->h64);
-  if (a->sha_valid || a->xxh_valid) {
+  std::vector<HashJob> sha_jobs, xxh_jobs;
+  uint64_t sha_recs = 0, xxh_recs = 0;
+  for (int k = 0; k < count; ++k) {
+    ncd_arena* a = arenas[k];
+    if (n[k] == 0 || a->nobj == 0) continue;
+    if (a->h64_valid)
+      k_h64_records<<<(unsigned)n[k], 256, 0, st>>>(d_idx[k], a->d.payload, a->d.rec_off, a->d.rec_len, (unsigned long long*)a->h64);
     HashJob j;
     memset(&j, 0, sizeof(j));
     j.payload = a->d.payload;
@@ -597,27 +603,52 @@ int ncd_hash_records(ncd_arena* a, const uint32_t* d_idx, uint64_t n) {
     j.rec_len = a->d.rec_len;
     j.sha = a->sha;
     j.xxh = a->xxh;
-    j.nobj = n;
-    j.rec_list = d_idx;
-    if (ctx->d_jobs_cap < 1) {
-      NCD_CUDA(cudaMalloc(&ctx->d_jobs, sizeof(HashJob) * 32));
-      ctx->d_jobs_cap = 32;
-    }
-    NCD_CUDA(cudaMemcpyAsync(ctx->d_jobs, &j, sizeof(j), cudaMemcpyHostToDevice, st));  // pageable: staged now
-    const HashJob* dj = (const HashJob*)ctx->d_jobs;
-    unsigned int* next = reinterpret_cast<unsigned int*>(ctx->d_counters) + 8;
+    j.nobj = n[k];
+    j.rec_list = d_idx[k];
     if (a->sha_valid) {
-      NCD_CUDA(cudaMemsetAsync(next, 0, 4, st));
-      const uint64_t want = (n + 127) / 128, cap = (uint64_t)ctx->sm_count * 16;
-      k_sha256<<<(unsigned)(want < cap ? want : cap), 128, sizeof(uint64_t), st>>>(dj, 1, (uint32_t)n, next);
+      j.rec_base = sha_recs;
+      sha_jobs.push_back(j);
+      sha_recs += n[k];
     }
     if (a->xxh_valid) {
-      NCD_CUDA(cudaMemsetAsync(next, 0, 4, st));
-      const size_t xs = sizeof(XxhSmem) + sizeof(uint64_t);
+      j.rec_base = xxh_recs;
+      xxh_jobs.push_back(j);
+      xxh_recs += n[k];
+    }
+  }
+  const int njobs = (int)(sha_jobs.size() + xxh_jobs.size());
+  if (njobs) {
+    if (njobs > MAX_HASH_JOBS || sha_recs >= 0xFFFFFFFFull || xxh_recs >= 0xFFFFFFFFull) {
+      ncd_set_error("hash: too many arenas or records in one sync");
+      return NCD_E_CAPACITY;
+    }
+    if (njobs > ctx->d_jobs_cap) {
+      if (ctx->d_jobs) cudaFree(ctx->d_jobs);
+      ctx->d_jobs = nullptr;
+      ctx->d_jobs_cap = 0;
+      const int cap = njobs < 32 ? 32 : njobs;
+      NCD_CUDA(cudaMalloc(&ctx->d_jobs, sizeof(HashJob) * cap));
+      ctx->d_jobs_cap = cap;
+    }
+    HashJob* dj = (HashJob*)ctx->d_jobs;
+    unsigned int* next = reinterpret_cast<unsigned int*>(ctx->d_counters) + 8;  // two counters: SHA, XXH
+    NCD_CUDA(cudaMemsetAsync(next, 0, 8, st));
+    // pageable sources: staged by the runtime before each call returns
+    if (!sha_jobs.empty()) {
+      const int m = (int)sha_jobs.size();
+      NCD_CUDA(cudaMemcpyAsync(dj, sha_jobs.data(), sizeof(HashJob) * m, cudaMemcpyHostToDevice, st));
+      const uint64_t want = (sha_recs + 127) / 128, cap = (uint64_t)ctx->sm_count * 16;
+      k_sha256<<<(unsigned)(want < cap ? want : cap), 128, sizeof(uint64_t) * m, st>>>(dj, m, (uint32_t)sha_recs, next);
+    }
+    if (!xxh_jobs.empty()) {
+      const int m = (int)xxh_jobs.size();
+      HashJob* djx = dj + sha_jobs.size();
+      NCD_CUDA(cudaMemcpyAsync(djx, xxh_jobs.data(), sizeof(HashJob) * m, cudaMemcpyHostToDevice, st));
+      const size_t xs = sizeof(XxhSmem) + sizeof(uint64_t) * m;
       NCD_CUDA(cudaFuncSetAttribute(k_xxh64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xs));
       const uint64_t per_sm = (216u * 1024u) / xs ? (216u * 1024u) / xs : 1;
-      const uint64_t want = (n + 32 * XXH_WARPS - 1) / (32 * XXH_WARPS), cap = (uint64_t)ctx->sm_count * per_sm;
-      k_xxh64<<<(unsigned)(want < cap ? want : cap), 32 * XXH_WARPS, xs, st>>>(dj, 1, (uint32_t)n, next);
+      const uint64_t want = (xxh_recs + 32 * XXH_WARPS - 1) / (32 * XXH_WARPS), cap = (uint64_t)ctx->sm_count * per_sm;
+      k_xxh64<<<(unsigned)(want < cap ? want : cap), 32 * XXH_WARPS, xs, st>>>(djx, m, (uint32_t)xxh_recs, next + 1);
     }
   }
   NCD_CUDA(cudaGetLastError());

@@ -8,6 +8,8 @@
 // cross PCIe.  The packer rewrites a changed object's record in the pinned host arrays (in place
 // when it fits, else appended behind the payload end) and names the object here; one kernel
 // pulls exactly those records over PCIe from the pinned (device-mapped) host memory.
+#include <vector>
+
 #include "ncd_common.cuh"
 
 // One CTA per rewritten record.  h_* are the pinned host arrays (unified addressing makes them
@@ -108,7 +110,7 @@ int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t*
   uint32_t* d_flags = d_idx + total;
   NCD_CUDA(cudaMemsetAsync(d_flags, 0, 8 * (size_t)count, st));
   uint64_t at = 0;
-  int hrc = NCD_OK;
+  std::vector<const uint32_t*> d_lists((size_t)count, nullptr);
   for (int k = 0; k < count; ++k) {
     ncd_arena* a = arenas[k];
     if (!n[k]) continue;
@@ -117,13 +119,13 @@ int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t*
     k_pull_records<<<(unsigned)n[k], 128, 0, st>>>(d_idx + at, a->h.payload, a->h.rec_off, a->h.rec_len, a->d.payload,
                                                   a->d.rec_off, a->d.rec_len, a->meta, (uint32_t)a->nobj,
                                                   new_payload_bytes[k], d_flags + 2 * k);
-    // Digests the arena holds stay valid: only the rewritten records are hashed again, so a
-    // hash-mode scan after an informer event costs the changed bytes, not the fleet's.  (A
-    // refused index was replaced by the kernel above with a valid one; the arena is then
-    // uncommitted below anyway.)
-    if (hrc == NCD_OK) hrc = ncd_hash_records(a, d_idx + at, n[k]);
+    d_lists[k] = d_idx + at;
     at += n[k];
   }
+  // Digests the arenas hold stay valid: only the rewritten records are hashed again, so a
+  // hash-mode scan after an informer event costs the changed bytes, not the fleet's.  (A refused
+  // index was replaced by the kernel above with a valid one; that arena is uncommitted below anyway.)
+  const int hrc = ncd_hash_records_many(ctx, count, arenas, d_lists.data(), n);
   uint32_t* flags = (uint32_t*)calloc((size_t)count * 2, sizeof(uint32_t));
   if (!flags) {
     cudaFreeAsync(d_idx, st);
