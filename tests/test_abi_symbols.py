@@ -53,3 +53,28 @@ def test_keyhash_matches_the_spec_used_for_partitioning():
     lib = _ffi.load()
     for kind, key in [(0, b"nexus/t-0000000042"), (2, b"default/secret"), (3, b""), (1, b"a" * 300)]:
         assert lib.ncd_keyhash(kind, key, len(key)) == synth_spec.keyhash(kind, key)
+
+
+def test_headers_are_plain_c_and_sizes_agree_with_a_c_compiler(tmp_path):
+    """The boundary is a C ABI: both headers must compile as C99 on their own (no C++, no CUDA, no
+    torch types), and the struct sizes a C compiler computes are the ones the ctypes mirror uses."""
+    import shutil
+    import subprocess
+
+    cc = shutil.which("gcc") or shutil.which("cc")
+    assert cc, "no C compiler in the image"
+    src = tmp_path / "abi.c"
+    src.write_text(
+        '#include <stdio.h>\n#include "ncdrift.h"\n#include "ncdhost.h"\n'
+        "int main(void) {\n"
+        '  printf("%zu %zu %zu %zu %zu\\n", sizeof(ncd_arena_view), sizeof(ncd_entry), sizeof(ncd_scan_stats),\n'
+        "         sizeof(ncd_synth_cfg), sizeof(ncd_orphan));\n"
+        "  return 0;\n}\n"
+    )
+    exe = tmp_path / "abi"
+    res = subprocess.run([cc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", os.path.join(ROOT, "include"),
+                          str(src), "-o", str(exe)], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True).stdout.split()]
+    assert sizes[:4] == [C.sizeof(_ffi.ArenaView), C.sizeof(_ffi.Entry), C.sizeof(_ffi.ScanStats), C.sizeof(_ffi.SynthCfg)]
+    assert sizes[4] == 8
