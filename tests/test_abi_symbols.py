@@ -78,3 +78,29 @@ def test_headers_are_plain_c_and_sizes_agree_with_a_c_compiler(tmp_path):
     sizes = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True).stdout.split()]
     assert sizes[:4] == [C.sizeof(_ffi.ArenaView), C.sizeof(_ffi.Entry), C.sizeof(_ffi.ScanStats), C.sizeof(_ffi.SynthCfg)]
     assert sizes[4] == 8
+
+
+def test_go_binding_and_docs_only_name_functions_the_header_declares():
+    """go/ cannot be compiled here (no Go toolchain); at least every C function it calls, and every
+    ncd_* function the integration guide mentions, must exist in the header with that name, and
+    every constant the Go side reads must be defined."""
+    declared = set(declared_functions())
+    header = open(os.path.join(ROOT, "include", "ncdrift.h")).read()
+    host_header = open(os.path.join(ROOT, "include", "ncdhost.h")).read()
+    go_dir = os.path.join(ROOT, "go")
+    used, consts = set(), set()
+    for base, _, files in os.walk(go_dir):
+        for f in files:
+            if f.endswith(".go"):
+                src = open(os.path.join(base, f)).read()
+                used |= set(re.findall(r"\bC\.(ncd_[a-z0-9_]+)\s*\(", src))
+                consts |= set(re.findall(r"\bC\.(NCD_[A-Z0-9_]+)\b", src))
+    assert len(used) >= 20, "the Go binding went missing"
+    assert not (used - declared), f"go/ calls functions the header does not declare: {sorted(used - declared)}"
+    missing_consts = [c for c in consts if not re.search(rf"\b{c}\b", header)]
+    assert not missing_consts, f"go/ reads constants the header does not define: {missing_consts}"
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    host_declared = set(re.findall(r"\b(ncdh_[a-z0-9_]+)\s*\(", re.sub(r"/\*.*?\*/", "", host_header, flags=re.S)))
+    mentioned = set(re.findall(r"\b(ncdh?_[a-z0-9_]+)\s*\(", doc))
+    unknown = {m for m in mentioned if m not in declared and m not in host_declared}
+    assert not unknown, f"INTEGRATION.md mentions functions no header declares: {sorted(unknown)}"
