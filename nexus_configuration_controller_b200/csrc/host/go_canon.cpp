@@ -16,6 +16,7 @@
 #include <cmath>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <utility>
 #include <vector>
 
@@ -44,68 +45,93 @@ struct Cursor {
     p += 4;
     return v;
   }
-  void copy(std::string& out, uint64_t n) {
+  const uint8_t* take(uint64_t n) {
     need(n);
-    out.append(reinterpret_cast<const char*>(p), n);
+    const uint8_t* at = p;
     p += n;
+    return at;
   }
 };
 
-void encode(Cursor& in, std::string& out, int depth) {
+// Where encoded bytes go: into a string, or nowhere (a pass that only validates and measures).
+struct StrSink {
+  std::string& s;
+  void put(const void* b, uint64_t n) { s.append(reinterpret_cast<const char*>(b), n); }
+  void byte(uint8_t b) { s.push_back((char)b); }
+};
+struct NullSink {
+  void put(const void*, uint64_t) {}
+  void byte(uint8_t) {}
+};
+
+template <class Sink>
+void encode(Cursor& in, Sink& out, int depth) {
   if (depth > 200) throw std::runtime_error("value nested too deeply");
   const uint8_t tag = in.byte();
-  out.push_back((char)tag);
+  out.byte(tag);
   switch (tag) {
-    case T_BOOL: out.push_back(in.byte() ? 1 : 0); return;
-    case T_INT: in.copy(out, 9); return;
+    case T_BOOL: out.byte(in.byte() ? 1 : 0); return;
+    case T_INT: out.put(in.take(9), 9); return;
     case T_STRING:
     case T_BYTES: {
       const uint32_t n = in.len32();
-      out.append(reinterpret_cast<const char*>(&n), 4);
-      in.copy(out, n);
+      out.put(&n, 4);
+      out.put(in.take(n), n);
       return;
     }
     case T_NILBYTES: case T_NILSLICE: case T_NILMAP: case T_NILPTR: case T_NILIFACE: return;
     case T_SLICE:
     case T_STRUCT: {
       const uint32_t n = in.len32();
-      out.append(reinterpret_cast<const char*>(&n), 4);
+      out.put(&n, 4);
       for (uint32_t i = 0; i < n; ++i) encode(in, out, depth + 1);
       return;
     }
     case T_PTR: encode(in, out, depth + 1); return;
     case T_IFACE: {
       const uint32_t n = in.len32();
-      out.append(reinterpret_cast<const char*>(&n), 4);
-      in.copy(out, n);
+      out.put(&n, 4);
+      out.put(in.take(n), n);
       encode(in, out, depth + 1);
       return;
     }
     case T_FLOAT: {
-      in.need(8);
       double f;
-      memcpy(&f, in.p, 8);
-      in.p += 8;
+      memcpy(&f, in.take(8), 8);
       if (std::isnan(f)) throw std::runtime_error("NaN cannot be canonicalised: it is not DeepEqual to itself");
       if (f == 0) f = 0.0;
-      out.append(reinterpret_cast<const char*>(&f), 8);
+      out.put(&f, 8);
       return;
     }
     case T_MAP: {
+      // Keys are encoded apart (they order the entries); a value is only walked here — checked and
+      // measured — and encoded straight from the input once its place in the output is known, so
+      // a large value (a 1 MiB Secret) is copied once, not once per container it sits in.
+      struct Entry {
+        std::string key;
+        const uint8_t* vbegin;
+        const uint8_t* vend;
+      };
       const uint32_t n = in.len32();
-      std::vector<std::pair<std::string, std::string>> entries(n);
-      for (auto& e : entries) {
-        encode(in, e.first, depth + 1);
-        encode(in, e.second, depth + 1);
+      if ((uint64_t)n > (uint64_t)(in.end - in.p)) throw std::runtime_error("value is truncated");  // >= 1 byte per entry
+      std::vector<Entry> entries(n);
+      NullSink nowhere;
+      for (Entry& e : entries) {
+        StrSink ks{e.key};
+        encode(in, ks, depth + 1);
+        e.vbegin = in.p;
+        encode(in, nowhere, depth + 1);
+        e.vend = in.p;
       }
-      std::sort(entries.begin(), entries.end(),
-                [](const auto& a, const auto& b) { return a.first < b.first; });
+      std::sort(entries.begin(), entries.end(), [](const Entry& a, const Entry& b) { return a.key < b.key; });
       for (size_t i = 1; i < entries.size(); ++i)
-        if (entries[i].first == entries[i - 1].first) throw std::runtime_error("map holds a key twice");
-      out.append(reinterpret_cast<const char*>(&n), 4);
-      for (const auto& e : entries) {
-        out += e.first;
-        out += e.second;
+        if (entries[i].key == entries[i - 1].key) throw std::runtime_error("map holds a key twice");
+      if constexpr (std::is_same<Sink, NullSink>::value) return;  // checked above; nothing to write, no second walk
+      out.put(&n, 4);
+      for (const Entry& e : entries) {
+        out.put(e.key.data(), e.key.size());
+        Cursor v{e.vbegin, e.vend};
+        encode(v, out, depth + 1);
       }
       return;
     }
@@ -119,7 +145,8 @@ std::string canonicalise(const uint8_t* value, uint64_t len) {
   Cursor in{value, value + len};
   std::string out;
   out.reserve(len + 16);
-  encode(in, out, 0);
+  StrSink sink{out};
+  encode(in, sink, 0);
   if (in.p != in.end) throw std::runtime_error("bytes left over after the value");
   return out;
 }
