@@ -223,6 +223,84 @@ k_compare_grouped(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S
   }
 }
 
+// ------------------------------------------------------------------ k_compare_small
+// Records of a few hundred bytes (template and workgroup specs, small ConfigMaps): a whole warp
+// per tile leaves most lanes without a vector and the scan becomes bound per record, not per
+// byte (1M records x 8 shards in 1.5 ms whatever their length).  Here eight lanes share a tile,
+// so a warp walks four tiles at once: four times the tiles in flight for the same registers.
+// Correct for any tile size (a lane loops over vectors l, l + 8, ...); chosen only when tiles are small.
+__global__ void __launch_bounds__(256)
+k_compare_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
+                const uint32_t* __restrict__ tile_obj, const uint32_t* __restrict__ tile_chunk,
+                uint64_t ntiles, const uint64_t* __restrict__ sh_off, uint8_t* __restrict__ dv,
+                uint32_t* __restrict__ counters, uint32_t count_collisions) {
+  extern __shared__ const uint8_t* s_payload[];  // payload base of every shard
+  for (uint32_t s = threadIdx.x; s < S; s += blockDim.x) s_payload[s] = shards[s].payload;
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31, sub = lane >> 3, l8 = lane & 7;
+  const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t t0 = 4 * warp0; t0 < ntiles; t0 += 4 * nwarps) {
+    const uint64_t t = t0 + sub;
+    const bool have = t < ntiles;
+    uint32_t c = 0, nvec = 0, tail = 0;
+    uint64_t toff = 0;
+    const uint4* cp = nullptr;
+    if (have) {
+      c = tile_obj[t];
+      const uint32_t chunk = tile_chunk[t];
+      const uint32_t len = ctrl.rec_len[c];
+      toff = (uint64_t)chunk * NCD_TILE_BYTES;
+      const uint32_t nbytes = chunk + 1 == ncd_ctiles_of(len) ? len - (uint32_t)toff : NCD_TILE_BYTES;
+      nvec = (nbytes + 15) >> 4;
+      tail = nbytes & 15;
+      cp = reinterpret_cast<const uint4*>(ctrl.payload + ctrl.rec_off[c] + toff);
+    }
+    // the longest of the four tiles sets the trip count for the warp (shuffles below are warp-wide)
+    uint32_t maxvec = nvec;
+#pragma unroll
+    for (int d = 8; d < 32; d <<= 1) maxvec = max(maxvec, __shfl_xor_sync(0xffffffffu, maxvec, d));
+    for (uint32_t s0 = 0; s0 < S; s0 += CMP_G) {
+      const uint64_t my_off = (have && s0 + l8 < S) ? sh_off[(uint64_t)c * S + s0 + l8] : NCD_NO_OFF;
+      if (__all_sync(0xffffffffu, my_off == NCD_NO_OFF)) continue;  // nothing to read for any of the four tiles
+      const uint4* sp[CMP_G];
+      uint32_t x[CMP_G];
+#pragma unroll
+      for (int k = 0; k < CMP_G; ++k) {
+        const uint64_t off = __shfl_sync(0xffffffffu, my_off, k, 8);  // lane k of this tile's eight lanes
+        sp[k] = off == NCD_NO_OFF ? nullptr : reinterpret_cast<const uint4*>(s_payload[min(s0 + k, S - 1)] + off + toff);
+        x[k] = 0;
+      }
+      for (uint32_t v = l8; v < maxvec; v += 8) {
+        if (v >= nvec) continue;
+        uint4 a = ncd_ldg_stream(cp + v);
+        uint4 b[CMP_G];
+#pragma unroll
+        for (int k = 0; k < CMP_G; ++k) b[k] = sp[k] != nullptr ? ncd_ldg_stream(sp[k] + v) : a;
+        const bool last = tail && v == nvec - 1;
+        if (last) a = mask_tail(a, tail);
+#pragma unroll
+        for (int k = 0; k < CMP_G; ++k) {
+          uint4 bb = b[k];
+          if (last && sp[k] != nullptr) bb = mask_tail(bb, tail);
+          if (sp[k] != nullptr) x[k] |= (a.x ^ bb.x) | (a.y ^ bb.y) | (a.z ^ bb.z) | (a.w ^ bb.w);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < CMP_G; ++k) {
+        const uint32_t differs = (__ballot_sync(0xffffffffu, x[k] != 0) >> (8 * sub)) & 0xffu;  // this tile's lanes
+        if (differs && l8 == (uint32_t)k) {
+          const uint64_t p = (uint64_t)c * S + s0 + k;
+          uint32_t* word = reinterpret_cast<uint32_t*>(dv) + (p >> 2);
+          const uint32_t sh8 = 8u * (uint32_t)(p & 3);
+          const uint32_t old = atomicOr(word, (uint32_t)DV_DIFF << sh8);
+          if (count_collisions && ((old >> sh8) & 0xffu) == DV_EQUAL) atomicAdd(&counters[1], 1u);
+        }
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ k_classify
 __global__ void __launch_bounds__(256)
 k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint64_t nrows,
@@ -503,10 +581,11 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     //                                     producer / consumer warps, nothing staged in registers
     //   small records                     k_compare_grouped: controller + 8 shard copies in flight
     //                                     per warp, merged tail tiles
+    //   records of a few hundred bytes    k_compare_small: the same, eight lanes per tile, four tiles per warp
     int variant = ctx->compare_variant;
     if (variant < 0) {
       const uint64_t fill = ctrl->len_sum / ctrl->ntiles;
-      variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : 2);
+      variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : (fill >= 640 ? 2 : 16));
     }
     variant_used = (uint32_t)variant;
     const bool fixed_tiles = variant == 0 || variant == 8;
@@ -535,6 +614,12 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
         k_compare_grouped<4><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, t_obj, t_chunk, ntl, sh_off, dv,
                                                        counters, cc);
         break;
+      case 16: {  // eight lanes per tile
+        const uint64_t want4 = (ntl + 31) / 32;
+        k_compare_small<<<(unsigned)(want4 < cap ? want4 : cap), 256, smem, st>>>(dctrl, ctx->d_shards, S, t_obj, t_chunk,
+                                                                                  ntl, sh_off, dv, counters, cc);
+        break;
+      }
       default:
         k_compare<<<grid, 256, 0, st>>>(dctrl, ctx->d_shards, S, t_obj, t_chunk, ntl, sh_off, dv, counters, cc);
     }

@@ -223,10 +223,11 @@ def test_partition_by_key_hash_covers_everything_once(ctx):
     assert kept_total == 500
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 8])
+@pytest.mark.parametrize("variant", [0, 1, 2, 8, 16])
 def test_every_compare_variant_matches_oracle(variant, monkeypatch):
-    """The three data-movement shapes of the byte compare (register-staged per shard, grouped,
-    TMA bulk-copy pipeline) are picked per scan from the record shapes; forced here one by one."""
+    """The data-movement shapes of the byte compare (register-staged per shard, grouped, TMA
+    bulk-copy pipeline, eight lanes per tile) are picked per scan from the record shapes; forced
+    here one by one on records of every size."""
     from nexus_configuration_controller_b200.drift import Context
 
     monkeypatch.setenv("NCD_COMPARE_VARIANT", str(variant))
@@ -373,3 +374,37 @@ def test_many_small_objects_fill_the_hash_table(ctx):
     codes, ents, _ = gpu_scan(ctx, ctrl, [shard], A.MODE_DIRECT)
     np.testing.assert_array_equal(codes, want_codes)
     np.testing.assert_array_equal(ents, want_ents)
+
+
+def test_small_records_take_the_sub_warp_compare(ctx):
+    """Records of a few hundred bytes: the scan picks k_compare_small (variant 16) by itself and
+    decides like the oracle, tails and one-byte differences included."""
+    import random
+
+    rng = random.Random(31)
+    n = 3000
+    datas = [rand_bytes(rng, rng.choice([1, 15, 16, 17, 100, 255, 256, 257, 511, 512])) for _ in range(n)]
+    ctrl = A.pack([A.CachedObject(A.KIND_WORKGROUP, f"default/wg-{i}", d, uid="u") for i, d in enumerate(datas)])
+    shards = []
+    for s in range(9):  # more than one group of eight shards
+        objs = []
+        for i, d in enumerate(datas):
+            roll = rng.random()
+            if roll < 0.1:
+                continue
+            if roll < 0.3:
+                b = bytearray(d)
+                b[rng.choice([0, len(b) - 1, len(b) // 2])] ^= 1 << rng.randrange(8)
+                d = bytes(b)
+            elif roll < 0.35:
+                d = d + b"x"
+            objs.append(A.CachedObject(A.KIND_WORKGROUP, f"default/wg-{i}", d, uid="v"))
+        rng.shuffle(objs)
+        shards.append(A.pack(objs))
+    want_codes, want_ents = oracle.scan(ctrl, shards)
+    codes, ents, st = gpu_scan(ctx, ctrl, shards, A.MODE_DIRECT)
+    assert st.compare_variant == 16
+    np.testing.assert_array_equal(codes, want_codes)
+    np.testing.assert_array_equal(ents, want_ents)
+    codes, _, _ = gpu_scan(ctx, ctrl, shards, A.MODE_HASH64 | A.MODE_CONFIRM)
+    np.testing.assert_array_equal(codes, want_codes)
