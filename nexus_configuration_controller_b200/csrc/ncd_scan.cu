@@ -585,7 +585,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     int variant = ctx->compare_variant;
     if (variant < 0) {
       const uint64_t fill = ctrl->len_sum / ctrl->ntiles;
-      variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : (fill >= 640 ? 2 : 16));
+      variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : (fill >= 700 ? 2 : 16));
     }
     variant_used = (uint32_t)variant;
     const bool fixed_tiles = variant == 0 || variant == 8;
