@@ -171,6 +171,28 @@ def hbm_peak():
 
 
 # ----------------------------------------------------------------------------- CPU arm
+def deep_equal_walk_baseline(mean_len: int, threads: int, budget_s: float = 2.0) -> dict:
+    """Second CPU figure (SURVEY section 8d asks for both): reflect.DeepEqual restated on the value
+    model, walking `map[string][]byte{"token": <mean_len bytes>}` pairs that are already parsed and
+    separately allocated (a sweep streams from memory, as over an informer cache).  No lookup, no
+    ownership logic: compare it with the memcmp figure as the cost of the walk alone."""
+    import struct
+
+    import oracle
+
+    data = os.urandom(mean_len)
+    wire = (b"\x08" + struct.pack("<I", 1) + b"\x03" + struct.pack("<I", 5) + b"token" +
+            b"\x04" + struct.pack("<I", len(data)) + data)
+    npairs = max(1024, min(1 << 16, (256 << 20) // max(2 * mean_len, 1)))  # ~256 MB of values: beyond the caches
+    sec, eq = oracle.deep_equal_timed(wire, wire, npairs, 1, threads)  # warm-up, and sizes the repetitions
+    reps = max(1, min(64, int(budget_s / max(sec, 1e-4))))
+    sec, eq = oracle.deep_equal_timed(wire, wire, npairs, reps, threads)
+    return {"value": npairs * reps / sec, "unit": "pairs/s", "cores": threads, "gb_per_s": 2 * mean_len * npairs * reps / sec / 1e9,
+            "all_equal": bool(eq),
+            "sample": f"{npairs} pairs of map[string][]byte with one {mean_len}-byte value, {reps} sweep(s); "
+                      f"oracle DeepEqual on parsed values, no lookups"}
+
+
 class CpuArm:
     """The oracle (a port of the reference's lookup + DeepEqual walk) on a bounded sample of
     `workload`.  The sample is produced by the same generator as the GPU arm's input (on the GPU,
@@ -202,6 +224,8 @@ class CpuArm:
         self.identical = bool(np.array_equal(codes, self.gpu_codes))
         self.pairs = codes.size
         self.sweep_s = sec
+        mean_len = max(1, self.algo // max(1, self.ch.nobj * (1 + self.S)))
+        self.walk = deep_equal_walk_baseline(int(mean_len), threads)
 
     def time(self, budget_s: float):
         reps = max(1, min(200, int(budget_s / max(self.sweep_s, 1e-4))))
@@ -219,6 +243,7 @@ class CpuArm:
                       f"canonical records (an upper bound on a reflect.DeepEqual walk)",
             "gb_per_s": self.algo / sec / 1e9,
             "identical_to_gpu": self.identical,
+            "deep_equal_walk": self.walk,
         }
 
 

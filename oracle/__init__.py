@@ -50,12 +50,24 @@ def load() -> C.CDLL:
         lib.oracle_sha256_arena.restype = None
         lib.oracle_sha256_arena.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         lib.oracle_values_error.restype = C.c_char_p
+        lib.oracle_deep_equal_bench.restype = C.c_double
+        lib.oracle_deep_equal_bench.argtypes = [C.c_char_p, C.c_uint64, C.c_char_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(C.c_int)]
         lib.oracle_deep_equal.restype = C.c_int
         lib.oracle_deep_equal.argtypes = [C.c_char_p, C.c_uint64, C.c_char_p, C.c_uint64]
         lib.oracle_canon.restype = C.c_int64
         lib.oracle_canon.argtypes = [C.c_char_p, C.c_uint64, C.c_char_p, C.c_uint64]
         _lib = lib
     return _lib
+
+
+def deep_equal_timed(a_wire: bytes, b_wire: bytes, npairs: int, reps: int, nthreads: int) -> Tuple[float, bool]:
+    """Seconds `nthreads` threads take for `reps` sweeps of DeepEqual over `npairs` separately
+    allocated (already parsed) copies of the two values; and whether every comparison said equal."""
+    eq = C.c_int()
+    sec = load().oracle_deep_equal_bench(a_wire, len(a_wire), b_wire, len(b_wire), npairs, reps, nthreads, C.byref(eq))
+    if sec < 0:
+        raise ValueError(load().oracle_values_error().decode())
+    return sec, bool(eq.value)
 
 
 def deep_equal(a_wire: bytes, b_wire: bytes) -> bool:

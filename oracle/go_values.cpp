@@ -28,7 +28,9 @@
 #include <cmath>
 #include <memory>
 #include <stdexcept>
+#include <chrono>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -206,6 +208,48 @@ int oracle_deep_equal(const uint8_t* a, uint64_t alen, const uint8_t* b, uint64_
   } catch (const std::exception& e) {
     g_err = e.what();
     return -1;
+  }
+}
+
+// Timing helper for the CPU baseline: the walk reflect.DeepEqual does over values that are already
+// in memory (controller.go:539,600,725,795).  npairs separate copies of both values are parsed
+// first (untimed; separate allocations, so a sweep over them streams from memory like a sweep over
+// an informer cache does), then `nthreads` threads compare pair i of their share, `reps` sweeps.
+// Returns the wall-clock seconds of the sweeps only, or -1 on malformed input.
+double oracle_deep_equal_bench(const uint8_t* a, uint64_t alen, const uint8_t* b, uint64_t blen, uint64_t npairs,
+                               uint64_t reps, int nthreads, int* equal_out) {
+  try {
+    if (nthreads < 1) nthreads = 1;
+    std::vector<Node> as, bs;
+    as.reserve(npairs);
+    bs.reserve(npairs);
+    for (uint64_t i = 0; i < npairs; ++i) {
+      as.push_back(parse_all(a, alen));
+      bs.push_back(parse_all(b, blen));
+    }
+    std::vector<uint64_t> hits((size_t)nthreads, 0);
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t)
+      th.emplace_back([&, t] {
+        const uint64_t lo = npairs * (uint64_t)t / (uint64_t)nthreads, hi = npairs * (uint64_t)(t + 1) / (uint64_t)nthreads;
+        uint64_t h = 0;
+        for (uint64_t r = 0; r < reps; ++r)
+          for (uint64_t i = lo; i < hi; ++i) {
+            h += deep_equal(as[i], bs[i]) ? 1 : 0;
+            asm volatile("" ::: "memory");  // every comparison really walks the values
+          }
+        hits[(size_t)t] = h;
+      });
+    for (auto& x : th) x.join();
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    uint64_t total = 0;
+    for (uint64_t h : hits) total += h;
+    if (equal_out) *equal_out = total == npairs * reps ? 1 : 0;
+    return sec;
+  } catch (const std::exception& e) {
+    g_err = e.what();
+    return -1.0;
   }
 }
 

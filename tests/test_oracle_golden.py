@@ -131,3 +131,21 @@ def test_canon_refuses_nan():
     with pytest.raises(ValueError):
         oracle.canon(G.Float(float("nan")).wire())
     assert oracle.canon(G.Float(0.0).wire()) == oracle.canon(G.Float(-0.0).wire())
+
+
+def test_deep_equal_walk_timing_helper():
+    """The second CPU baseline figure (bench.py cpu_baseline.deep_equal_walk): the timing helper
+    really compares, says so when values differ, and the bench wrapper reports sane numbers."""
+    import bench
+    from tests import govalues as G
+
+    a = G.BytesMap({"token": bytes(range(200)) * 10}).wire()
+    b = G.BytesMap({"token": bytes(range(200)) * 9 + bytes(range(199)) + b"\x00"}).wire()
+    sec, eq = oracle.deep_equal_timed(a, a, 64, 2, 2)
+    assert sec > 0 and eq
+    sec, eq = oracle.deep_equal_timed(a, b, 64, 1, 3)
+    assert sec > 0 and not eq
+    with pytest.raises(ValueError):
+        oracle.deep_equal_timed(a[:-3], a, 4, 1, 1)
+    r = bench.deep_equal_walk_baseline(512, 2, budget_s=0.2)
+    assert r["all_equal"] and r["value"] > 1e4 and r["cores"] == 2 and r["unit"] == "pairs/s"
