@@ -261,6 +261,15 @@ int ncd_scan_stats_back(ncd_ctx* ctx, uint64_t back, ncd_scan_stats* out);
 int ncd_scan_into(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
                   uint32_t mode, void* dev_out, uint64_t cap_entries);
 
+/* The same drift check for a host-side caller that scans again and again (the DriftChecker of
+ * INTEGRATION.md): the diff list is delivered in pinned host memory the CONTEXT keeps, so a scan in
+ * steady state allocates nothing — ncd_scan's per-scan buffers (rows x shards x 17 bytes) and its
+ * ncd_diff are not used.  *entries (ordered like ncd_diff_view's) stays valid until the next scan on
+ * this context; SKIP decisions are simply absent from it.  The context's list buffer starts at
+ * 65 536 entries and is re-allocated, and the scan run again, only when a scan finds more. */
+int ncd_scan_host(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
+                  uint32_t mode, const ncd_entry** entries, uint64_t* n);
+
 /* ---- exchange of diff lists between GPUs through peer memory (ncd_exchange.cu) ----------------
  * The multi-GPU drift check partitions objects by key hash (ncd_keyhash % world) and ends with
  * every rank holding every rank's diff list.  An ncd_xchg is one rank's end of that exchange:
@@ -332,6 +341,20 @@ typedef struct ncd_orphan {
 int ncd_find_orphans(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
                      ncd_orphan* out, uint64_t cap, uint64_t* n);
 
+/* Controller-side adoption (the part of a resync sweep the per-shard decisions do not cover):
+ * adoptReferences (controller.go:647-695) gives every Secret / ConfigMap a template references on
+ * the CONTROLLER cluster an ownerReference to that template unless one with the template's UID is
+ * there already (isOwnedBy, controller.go:637-645: UID only).  This lists the (template,
+ * dependent) references that still lack it, ordered by (obj, dep): templates the sweep feed must
+ * still hand to templateSyncHandler although no shard drifted.  A reference to an object the
+ * controller does not hold is not listed (it is NCD_ERR_MISSING_REF in the diff list).  Writes at
+ * most cap entries; *n = the number found. */
+typedef struct ncd_adoption {
+  uint32_t obj; /* controller index of the template                    */
+  uint32_t dep; /* j+1 = its j-th dependent reference (as in ncd_entry) */
+} ncd_adoption;
+int ncd_find_unadopted(ncd_ctx* ctx, const ncd_arena* ctrl, ncd_adoption* out, uint64_t cap, uint64_t* n);
+
 /* ------------------------------------------------------------------ hashing */
 /* Hashes every record of a committed arena on the GPU and copies the digests out.
  * mode NCD_MODE_HASH64 / NCD_MODE_XXH64: out is nobj x 8 bytes; NCD_MODE_SHA256: nobj x 32 bytes.
@@ -350,7 +373,9 @@ int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* out, uint64_
  * to its own pool, a handler that cannot afford cudaMalloc's device-wide synchronisation or
  * an out-of-memory failure mid-reconcile.  The caller owns every buffer it passes (all DEVICE
  * pointers, on the device that is current when the call is made):
- *   dev_payload  records, each starting on a 16-byte boundary (arena payload layout)
+ *   dev_payload  records, each starting on a 16-byte boundary (arena payload layout); the kernels
+ *                read whole 16-byte vectors, so the buffer must be readable up to the 16-byte
+ *                padded end of every record (the bytes past dev_rec_len are ignored)
  *   dev_rec_off  byte offset of record i (multiple of 16), dev_rec_len its length
  *   dev_out      nrec x uint64, receives the NCD-H64 digests, identical to
  *                ncd_hash_arena(NCD_MODE_HASH64) on the same records

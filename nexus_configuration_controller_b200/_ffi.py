@@ -121,6 +121,8 @@ PROTOTYPES = {
     "ncd_scan_last_stats": (C.c_int, [VP, C.POINTER(ScanStats)]),
     "ncd_scan_stats_back": (C.c_int, [VP, C.c_uint64, C.POINTER(ScanStats)]),
     "ncd_scan_into": (C.c_int, [VP, VP, C.POINTER(VP), C.c_int, C.c_uint32, VP, C.c_uint64]),
+    "ncd_scan_host": (C.c_int, [VP, VP, C.POINTER(VP), C.c_int, C.c_uint32, C.POINTER(C.POINTER(Entry)), u64p]),
+    "ncd_find_unadopted": (C.c_int, [VP, VP, u32p, C.c_uint64, u64p]),
     "ncd_arenas_sync_records": (C.c_int, [C.c_int, C.POINTER(VP), u64p, C.POINTER(VP), u64p]),
     "ncd_arena_save": (C.c_int, [VP, C.c_char_p]),
     "ncd_arena_load": (C.c_int, [VP, C.c_char_p, C.c_uint32, C.c_uint64, C.POINTER(VP)]),

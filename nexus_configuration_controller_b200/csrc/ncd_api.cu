@@ -55,7 +55,16 @@ extern "C" int ncd_init(int device, ncd_ctx** out) {
   ctx->sm_count = prop.multiProcessorCount;
   ctx->compare_variant = -1;  // -1: chosen per scan from the mean tile fill
   ctx->compare_ctas_per_sm = 8;
-  if (const char* v = getenv("NCD_COMPARE_VARIANT")) ctx->compare_variant = atoi(v);
+  if (const char* v = getenv("NCD_COMPARE_VARIANT")) {
+    // experiment knob: only the kernels that exist may be named (ncd_scan_stats.compare_variant)
+    const int k = atoi(v);
+    if (k != -1 && k != 0 && k != 1 && k != 2 && k != 4 && k != 8 && k != 16) {
+      ncd_set_error("ncd_init: NCD_COMPARE_VARIANT=%s is not one of -1, 0, 1, 2, 4, 8, 16", v);
+      free(ctx);
+      return NCD_E_INVALID;
+    }
+    ctx->compare_variant = k;
+  }
   if (const char* v = getenv("NCD_COMPARE_CTAS")) ctx->compare_ctas_per_sm = atoi(v) > 0 ? atoi(v) : 8;
   NCD_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   for (int i = 0; i < 8; ++i) NCD_CUDA(cudaEventCreate(&ctx->ev[i]));
@@ -82,6 +91,8 @@ extern "C" void ncd_destroy(ncd_ctx* ctx) {
   if (ctx->d_shards) cudaFree(ctx->d_shards);
   if (ctx->d_jobs) cudaFree(ctx->d_jobs);
   if (ctx->d_counters) cudaFree(ctx->d_counters);
+  if (ctx->list_dev) cudaFree(ctx->list_dev);
+  if (ctx->list_host) cudaFreeHost(ctx->list_host);
   for (int i = 0; i < 4; ++i)
     if (ctx->hpool_ptr[i]) cudaFreeHost(ctx->hpool_ptr[i]);
   if (ctx->h_counters) cudaFreeHost(ctx->h_counters);

@@ -109,6 +109,11 @@ struct ncd_ctx {
   // and synchronises the device: a steady stream of scans must not do it per scan)
   void* hpool_ptr[4];
   size_t hpool_cap[4];
+  // ncd_scan_host: the diff list buffer (device, header + entries) and its pinned host mirror,
+  // kept between scans and grown only when a scan finds more than they hold
+  void* list_dev;
+  void* list_host;
+  uint64_t list_cap;  // entries
 };
 
 struct ncd_arena {

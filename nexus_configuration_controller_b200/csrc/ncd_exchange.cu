@@ -265,6 +265,9 @@ extern "C" int ncd_xchg_fetch(ncd_xchg* x, void* host_out, uint64_t bytes) {
   }
   NCD_CUDA(cudaStreamSynchronize(st));
   if (err) {
+    // reported once: the word is cleared so that one slow peer does not fail every later step
+    cudaMemsetAsync(x->buf + x->err_off, 0, sizeof(uint32_t), st);
+    cudaStreamSynchronize(st);
     ncd_set_error("ncd_xchg_fetch: a peer's diff list did not arrive within %.1f s", x->timeout_ns * 1e-9);
     return NCD_E_STATE;
   }

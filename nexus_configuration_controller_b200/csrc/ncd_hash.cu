@@ -507,15 +507,18 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
       return NCD_E_CAPACITY;
     }
     const uint64_t n = a->nobj;
+    // digest buffers are allocated once and kept across commits: sized for the arena's object
+    // CAPACITY, because a later commit / recommit may hold more objects than the first hashed one
+    const size_t dcap = (size_t)(a->nobj_cap > n ? a->nobj_cap : (n ? n : 1));
     if (mode == NCD_MODE_HASH64) {
-      if (!a->h64) NCD_CUDA(cudaMalloc((void**)&a->h64, (size_t)(n ? n : 1) * 8));
+      if (!a->h64) NCD_CUDA(cudaMalloc((void**)&a->h64, dcap * 8));
       NCD_CUDA(cudaMemsetAsync(a->h64, 0, (size_t)(n ? n : 1) * 8, st));
       a->h64_valid = true;
     } else if (mode == NCD_MODE_SHA256) {
-      if (!a->sha) NCD_CUDA(cudaMalloc((void**)&a->sha, (size_t)(n ? n : 1) * 32));
+      if (!a->sha) NCD_CUDA(cudaMalloc((void**)&a->sha, dcap * 32));
       a->sha_valid = true;
     } else {
-      if (!a->xxh) NCD_CUDA(cudaMalloc((void**)&a->xxh, (size_t)(n ? n : 1) * 8));
+      if (!a->xxh) NCD_CUDA(cudaMalloc((void**)&a->xxh, dcap * 8));
       a->xxh_valid = true;
     }
     HashJob& j = jobs[njobs++];

@@ -6,6 +6,8 @@
 //     reference loop structure controller.go:790-831 with :505,:567 for the dependents),
 //   the tile list the compare and hash kernels iterate over.
 // Also the device exclusive scan used here and by the synthetic generator.
+#include <atomic>
+
 #include "ncd_common.cuh"
 
 // ------------------------------------------------------------------ exclusive scan
@@ -417,11 +419,11 @@ int ncd_rebuild_tiles(ncd_arena* a) {
   return NCD_OK;
 }
 
-static uint64_t g_generation = 0;
+static std::atomic<uint64_t> g_generation{0};  // contexts of different GPUs may commit from different threads
 
 int ncd_build_index(ncd_arena* a) {
   ncd_ctx* ctx = a->ctx;
-  a->generation = ++g_generation;  // keys may have changed: join caches built on the old index are stale
+  a->generation = g_generation.fetch_add(1) + 1;  // keys may have changed: join caches built on the old index are stale
   cudaStream_t st = ctx->stream;
   const uint32_t n = (uint32_t)a->nobj;
   const unsigned blocks = (n + 255) / 256;

@@ -588,7 +588,9 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
       variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : (fill >= 700 ? 2 : 16));
     }
     variant_used = (uint32_t)variant;
-    const bool fixed_tiles = variant == 0 || variant == 8;
+    // the merged tile list (tiles up to 6144 B) belongs to the kernels that walk a tile to its end;
+    // k_compare and k_compare_tma compare at most 4096 B per tile and take the fixed 4 KB cut
+    const bool fixed_tiles = !(variant == 1 || variant == 2 || variant == 4 || variant == 16);
     const uint64_t ntl = fixed_tiles ? ctrl->ntiles : ctrl->nctiles;
     const uint32_t* t_obj = fixed_tiles ? ctrl->tile_obj : ctrl->ctile_obj;
     const uint32_t* t_chunk = fixed_tiles ? ctrl->tile_chunk : ctrl->ctile_chunk;
@@ -728,6 +730,73 @@ int ncd_scan_into(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* s
   NCD_CUDA(cudaSetDevice(ctx->device));
   return scan_enqueue(ctx, ctrl, shards, nshards, mode, nullptr, (ncd_entry*)((char*)dev_out + 16), cap_entries,
                       (uint32_t*)dev_out);
+}
+
+// (Re)allocates the context's list buffers for `cap` entries.
+static int list_reserve(ncd_ctx* ctx, uint64_t cap) {
+  if (cap <= ctx->list_cap) return NCD_OK;
+  NCD_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (ctx->list_dev) cudaFree(ctx->list_dev);
+  if (ctx->list_host) cudaFreeHost(ctx->list_host);
+  ctx->list_dev = ctx->list_host = nullptr;
+  ctx->list_cap = 0;
+  const size_t bytes = 16 + (size_t)cap * sizeof(ncd_entry);
+  cudaError_t e = cudaMalloc(&ctx->list_dev, bytes);
+  if (e == cudaSuccess) e = cudaMallocHost(&ctx->list_host, bytes);
+  if (e != cudaSuccess) {
+    ncd_set_error("ncd_scan_host: diff list buffers of %zu bytes: %s", bytes, cudaGetErrorString(e));
+    if (ctx->list_dev) cudaFree(ctx->list_dev);
+    ctx->list_dev = nullptr;
+    return NCD_E_NOMEM;
+  }
+  ctx->list_cap = cap;
+  return NCD_OK;
+}
+
+int ncd_scan_host(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards, uint32_t mode,
+                  const ncd_entry** entries, uint64_t* n) {
+  if (!entries || !n) {
+    ncd_set_error("ncd_scan_host: null output");
+    return NCD_E_INVALID;
+  }
+  NCD_TRY(check_scan_args(ctx, ctrl, shards, nshards, mode));
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  NCD_TRY(list_reserve(ctx, 1u << 16));
+  // The list is usually a tiny part of the decisions.  One copy brings the header and the first
+  // entries back; a longer list needs a second copy, a list beyond the buffer a larger buffer and
+  // the scan again (the codes are recomputed, nothing is kept from the short run).
+  constexpr uint64_t FIRST = 4096;
+  for (int attempt = 0;; ++attempt) {
+    NCD_TRY(scan_enqueue(ctx, ctrl, shards, nshards, mode, nullptr, (ncd_entry*)((char*)ctx->list_dev + 16), ctx->list_cap,
+                         (uint32_t*)ctx->list_dev));
+    const uint64_t first = ctx->list_cap < FIRST ? ctx->list_cap : FIRST;
+    NCD_CUDA(cudaMemcpyAsync(ctx->list_host, ctx->list_dev, 16 + first * sizeof(ncd_entry), cudaMemcpyDeviceToHost, st));
+    cudaError_t e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) {
+      ncd_set_error("scan failed on the GPU: %s", cudaGetErrorString(e));
+      return NCD_E_CUDA;
+    }
+    const uint64_t found = ((const uint32_t*)ctx->list_host)[0];
+    if (found > ctx->list_cap) {
+      if (attempt) {
+        ncd_set_error("ncd_scan_host: the list grew between two scans of the same arenas");
+        return NCD_E_STATE;
+      }
+      NCD_TRY(list_reserve(ctx, found + found / 2));
+      continue;
+    }
+    if (found > first) {
+      NCD_CUDA(cudaMemcpyAsync((char*)ctx->list_host + 16 + first * sizeof(ncd_entry),
+                               (const char*)ctx->list_dev + 16 + first * sizeof(ncd_entry),
+                               (found - first) * sizeof(ncd_entry), cudaMemcpyDeviceToHost, st));
+      NCD_CUDA(cudaStreamSynchronize(st));
+    }
+    NCD_TRY(stats_of(ctx, 0, &ctx->stats));
+    *entries = (const ncd_entry*)((const char*)ctx->list_host + 16);
+    *n = found;
+    return NCD_OK;
+  }
 }
 
 int ncd_scan_finish(ncd_ctx* ctx, ncd_diff** out) {

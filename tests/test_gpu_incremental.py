@@ -242,3 +242,37 @@ def test_structural_change_recommits_without_the_old_payload(ctx):
     finally:
         for x in arenas + [a, other]:
             x.close()
+
+
+def test_digests_follow_an_arena_that_grows_between_commits(ctx):
+    """An arena made with spare object capacity is hashed while it holds few objects, then committed
+    again with more (an informer AddFunc that still fits: ncd_arena_commit / ncd_arena_recommit inside
+    nobj_cap).  The digest buffers the arena keeps must be large enough for the later commit: every
+    digest kind is checked against the oracle after the growth, and the digests of a neighbouring
+    arena allocated right after the first hash stay intact."""
+    rng = random.Random(404)
+    objs = [A.CachedObject(A.KIND_SECRET, f"default/s{i}", rand_bytes(rng, rng.randint(1, 6000))) for i in range(600)]
+    small, big = A.pack(objs[:40]), A.pack(objs)
+    a = Arena(ctx, big.payload_bytes + 4096, big.nobj + 8, big.aux_bytes + 64, big.nowner + 1, big.ndep + 1, device_only=False)
+    try:
+        a.fill_from(small)
+        a.commit(small.nobj, small.payload_bytes, small.aux_bytes, small.nowner, small.ndep)
+        for mode in (A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64):
+            ctx.hash_arena(a, mode)
+        # a neighbour whose own digests would sit right behind a too-small buffer
+        nb = ctx.arena_from_host(small)
+        nb_want = {m: ctx.hash_arena(nb, m)[0].copy() for m in (A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64)}
+        a.fill_from(big)
+        a.commit(big.nobj, big.payload_bytes, big.aux_bytes, big.nowner, big.ndep)
+        dev = a.download()
+        h64, _ = ctx.hash_arena(a, A.MODE_HASH64)
+        np.testing.assert_array_equal(h64, oracle.h64_arena(dev))
+        sha, _ = ctx.hash_arena(a, A.MODE_SHA256)
+        np.testing.assert_array_equal(sha, oracle.sha256_arena(dev))
+        xxh, _ = ctx.hash_arena(a, A.MODE_XXH64)
+        assert [int(v) for v in xxh] == [oracle.xxh64(dev.record(i)) for i in range(dev.nobj)]
+        for m, want in nb_want.items():
+            np.testing.assert_array_equal(ctx.hash_arena(nb, m | A.MODE_CACHED)[0], want)
+        nb.close()
+    finally:
+        a.close()
