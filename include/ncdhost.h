@@ -45,6 +45,45 @@ int ncdh_cluster_add(ncdh_checker* c, int cluster, uint32_t kind, const char* ns
                      const char* const* configmap_names, int nconfigmaps);
 int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char* ns, const char* name);
 
+/* The same as a batch: informer events that arrived since the last call (AddFunc / UpdateFunc /
+ * DeleteFunc of the four informers, controller.go:286-359), applied in order.  The values are
+ * canonicalised on `threads` threads (<= 0: one per host core), then the cache images are updated
+ * under the checker's lock.  An event that fails (malformed value) stops the batch: the events
+ * before it are applied, the call returns -1. */
+enum { NCDH_EV_PUT = 0, NCDH_EV_DELETE = 1 };
+typedef struct ncdh_event {
+  int32_t cluster;  /* -1 controller, s >= 0 shard s                         */
+  uint32_t kind;    /* NCD_KIND_*                                            */
+  uint32_t op;      /* NCDH_EV_PUT | NCDH_EV_DELETE                          */
+  int32_t nowners, nsecrets, nconfigmaps;
+  const char* ns;
+  const char* name;
+  const char* uid;
+  const uint8_t* value; /* transport form of .Spec / .Data (PUT only)        */
+  uint64_t value_len;
+  const char* const* owner_kinds;
+  const char* const* owner_uids;
+  const char* const* secret_names;
+  const char* const* configmap_names;
+} ncdh_event;
+int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int threads);
+
+/* Threading and freshness (the reference's handlers run on `workers` goroutines at once,
+ * controller.go:875-877, and read LIVE caches, :766,792,507,516):
+ *   - every function here may be called from any thread.  ncdh_cluster_add / _remove /
+ *     ncdh_apply_events take the checker's cache lock for the update only; ncdh_scan runs one at a
+ *     time and holds that lock only while it lays changed records out in pinned memory, not while
+ *     the GPU works; ncdh_lookup / ncdh_plan_* / ncdh_sweep_queue read the snapshot the last
+ *     finished scan published (swapped in atomically) and never wait for a scan in flight.
+ *   - a snapshot is only as fresh as its scan.  Every put / remove is stamped with a counter; a
+ *     lookup or plan whose template, any of its dependents, or any shard's copy of those was put or
+ *     removed AFTER the snapshot's scan began answers NCDH_STALE instead of a decision the live
+ *     caches no longer support (a Secret rotated one second after a scan is never answered SKIP).
+ *     The caller then runs ncdh_scan (cheap: only the changed records cross PCIe) and asks again,
+ *     or falls back to its own lister.Get + reflect.DeepEqual for that object. */
+#define NCDH_NOT_FOUND 1
+#define NCDH_STALE 2
+
 /* DriftChecker.Scan: bring every cluster's resident arena up to date with what was added /
  * removed since the last Scan (only changed records or the small per-object arrays cross PCIe,
  * a full upload happens on the first Scan or when an arena runs out of room), then ncd_scan.
@@ -52,8 +91,9 @@ int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char*
 int ncdh_scan(ncdh_checker* c);
 
 /* DriftChecker.Lookup: the decision of the last Scan for (template or workgroup kind/ns/name,
- * dep = 0 the object itself | j+1 its j-th dependent, shard).  Returns 0 and *code, or 1 when
- * the object is not in the controller cache (controller.go:769-772). */
+ * dep = 0 the object itself | j+1 its j-th dependent, shard).  Returns 0 and *code,
+ * NCDH_NOT_FOUND when the object is not in the controller cache (controller.go:769-772),
+ * NCDH_STALE when the caches changed under the snapshot (see above), -1 on a bad argument. */
 int ncdh_lookup(ncdh_checker* c, uint32_t kind, const char* ns, const char* name, int dep, int shard,
                 uint32_t* code);
 
@@ -61,7 +101,8 @@ int ncdh_lookup(ncdh_checker* c, uint32_t kind, const char* ns, const char* name
  * (controller.go:790-831, with :504-626) or workgroupSyncHandler (:720-745) would issue, in
  * order, stopping where the handler would return an error.  Output, one line per action:
  *   "<shard>\t<nexus|kube>\t<verb>\t<resource>\t<name>\n"   then   "error\t<text>\n" if it failed.
- * Returns the text length (written only if it fits cap) or -1. */
+ * Returns the text length (written only if it fits cap), -1 on error, or -NCDH_STALE (-2) when
+ * anything the replay reads was put or removed after the snapshot's scan began. */
 int64_t ncdh_plan_template(ncdh_checker* c, const char* ns, const char* name, char* out, uint64_t cap);
 int64_t ncdh_plan_workgroup(ncdh_checker* c, const char* ns, const char* name, char* out, uint64_t cap);
 
@@ -72,6 +113,29 @@ int64_t ncdh_plan_workgroup(ncdh_checker* c, const char* ns, const char* name, c
  *   "<template|workgroup>\t<namespace/name>\n"   (Element{objRef, objTypeName}, controller.go:88-91).
  * Returns the text length (written only if it fits cap) or -1. */
 int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap);
+
+/* adoptReferences (controller.go:647-695) as a plan: the controller-cluster Secrets / ConfigMaps
+ * the template references that do not carry an ownerReference with its UID yet (decided on the GPU
+ * by ncd_find_unadopted at the last Scan).  One line per Update the handler would issue on the
+ * CONTROLLER cluster: "kube\tupdate-owner\t<secrets|configmaps>\t<name>\n".  Same return values as
+ * ncdh_plan_template.  Templates with such references are part of ncdh_sweep_queue. */
+int64_t ncdh_plan_adoption(ncdh_checker* c, const char* ns, const char* name, char* out, uint64_t cap);
+
+/* Where the time and the bytes of the last Scan went (host clock, milliseconds). */
+typedef struct ncdh_scan_timing {
+  double canon_ms;    /* canonicalisation done by ncdh_cluster_add / ncdh_apply_events since the previous Scan */
+  double pack_ms;     /* laying changed records out in the pinned arenas (under the cache lock)                */
+  double upload_ms;   /* ncd_arena_commit / _recommit / ncd_arenas_sync_records                                */
+  double scan_ms;     /* ncd_scan_host: kernels + diff list to the host                                        */
+  double publish_ms;  /* building and swapping in the snapshot                                                 */
+  double total_ms;    /* the whole ncdh_scan call                                                              */
+  double gpu_scan_ms; /* device time of the scan kernels (CUDA events)                                         */
+  uint64_t h2d_bytes; /* bytes this Scan moved host -> device                                                  */
+  uint64_t d2h_bytes; /* bytes it read back                                                                    */
+  uint64_t records_synced, full_uploads, structural_uploads;
+  uint64_t events;    /* puts / removes that changed something since the previous Scan                         */
+} ncdh_scan_timing;
+int ncdh_last_timing(ncdh_checker* c, ncdh_scan_timing* out);
 
 /* How a cluster's data has reached the GPU so far: scans that needed a full arena upload
  * (ncd_arena_commit), a structural one (ncd_arena_recommit: per-object arrays + new records) or

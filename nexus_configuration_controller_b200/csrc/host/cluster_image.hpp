@@ -1,0 +1,191 @@
+// cluster_image.hpp — one cluster's informer caches as the host layer keeps them, and the packer
+// that lays them out as an arena (include/ncdrift.h "arenas").
+//
+// Stands in for the four listers of a cluster (controller.go:268-278; shards.Shard's listers): an
+// insertion-ordered store keyed by (kind, "namespace/name").  Informer events map onto three costs:
+//   value of an existing object changed (UpdateFunc)   -> ncd_arena_sync_records: that record only
+//   object added / deleted / re-owned (Add/DeleteFunc) -> ncd_arena_recommit: small arrays + new records
+//   first scan, or the arena ran out of room           -> ncd_arena_commit of a fresh, larger arena
+// Every put / remove that changes something is stamped with the checker's event counter; the
+// stamps are what Lookup's freshness rule reads (include/ncdhost.h).
+#pragma once
+#include <stdint.h>
+#include <string.h>
+
+#include <iterator>
+#include <memory>
+#include <stdexcept>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../../../include/ncdrift.h"
+
+namespace ncdh {
+
+struct OwnerRef {
+  std::string kind, uid;
+  bool operator==(const OwnerRef& o) const { return kind == o.kind && uid == o.uid; }
+};
+
+// Everything about an object except its compared value.  Immutable once made: a put that changes
+// any of it makes a new one, so snapshots can share it with the live image without copying.
+struct ObjInfo {
+  uint32_t kind = 0;
+  std::string key;  // "namespace/name" (cache.ObjectName.String())
+  std::string name, uid;
+  std::vector<OwnerRef> owners;
+  std::vector<std::string> secrets, configmaps;  // GetSecretNames() / GetConfigMapNames() (templates)
+  bool same_structure(const ObjInfo& o) const {
+    return uid == o.uid && owners == o.owners && secrets == o.secrets && configmaps == o.configmaps;
+  }
+};
+
+struct CachedObject {
+  std::shared_ptr<const ObjInfo> info;
+  std::string canon;  // canonical bytes of .Spec / .Data
+  bool live = true;
+  uint64_t gen = 0;  // event counter value of the last put that changed this object
+  // where the record lives in the resident arena's payload (-1: not placed yet)
+  int64_t rec_off = -1;
+  uint64_t rec_cap = 0;      // padded bytes reserved at rec_off
+  bool value_dirty = false;  // canon changed since the device copy was written
+};
+
+inline std::string store_key(uint32_t kind, const std::string& key) { return std::string(1, (char)('0' + kind)) + key; }
+inline uint64_t pad16(uint64_t n) { return (n + 15) & ~15ull; }
+inline std::string ncd_err(const char* op) { return std::string(op) + ": " + ncd_last_error(); }
+
+struct ArenaHandle {
+  ncd_arena* a = nullptr;
+  ArenaHandle() = default;
+  ArenaHandle(const ArenaHandle&) = delete;
+  ArenaHandle& operator=(const ArenaHandle&) = delete;
+  ArenaHandle(ArenaHandle&& o) noexcept : a(o.a) { o.a = nullptr; }
+  void reset() {
+    if (a) ncd_arena_destroy(a);
+    a = nullptr;
+  }
+  ~ArenaHandle() { reset(); }
+};
+
+// Runs fn(i) for i in [0, n) on up to `threads` threads (the packer's record copies and the
+// canonicaliser are memory-bound loops over independent records).
+template <class Fn>
+void parallel_for(size_t n, int threads, size_t min_per_thread, Fn fn) {
+  size_t t = threads < 1 ? 1 : (size_t)threads;
+  if (min_per_thread && n / min_per_thread < t) t = n / min_per_thread;
+  if (t <= 1) {
+    for (size_t i = 0; i < n; ++i) fn(i);
+    return;
+  }
+  std::vector<std::thread> th;
+  std::vector<std::exception_ptr> errs(t);
+  for (size_t k = 0; k < t; ++k)
+    th.emplace_back([&, k] {
+      try {
+        for (size_t i = n * k / t; i < n * (k + 1) / t; ++i) fn(i);
+      } catch (...) {
+        errs[k] = std::current_exception();
+      }
+    });
+  for (auto& x : th) x.join();
+  for (auto& e : errs)
+    if (e) std::rethrow_exception(e);
+}
+
+// What one Scan has to send to the GPU for a cluster, decided while the cache lock is held and
+// carried out after it is released.
+enum class Upload { None, Values, Structural, Full };
+
+struct ClusterImage {
+  std::vector<CachedObject> objs;
+  std::unordered_map<std::string, size_t> index;   // store_key -> position in objs (live objects)
+  std::unordered_map<std::string, uint64_t> tomb;  // store_key -> stamp of the removal
+  std::vector<uint32_t> dirty;                     // positions whose value changed since the last Scan
+  uint64_t last_change = 0;                        // stamp of the latest put / remove that changed anything
+  ArenaHandle arena;
+  uint64_t payload_used = 0, payload_cap = 0, nobj_cap = 0, aux_cap = 0, nowner_cap = 0, ndep_cap = 0;
+  bool structural = true;  // keys / owners / dependents changed since the last commit
+  uint64_t uploads_full = 0, uploads_structural = 0, uploads_values = 0;
+  std::vector<uint32_t> pending_changed;  // records a prepared Values upload still has to push
+
+  // ---- events (caller holds the cache lock exclusively)
+  // Returns true when the put changed anything.
+  bool put(std::shared_ptr<const ObjInfo> info, std::string&& canon, uint64_t stamp) {
+    const std::string k = store_key(info->kind, info->key);
+    auto it = index.find(k);
+    if (it == index.end()) {
+      index.emplace(k, objs.size());
+      CachedObject o;
+      o.info = std::move(info);
+      o.canon = std::move(canon);
+      o.gen = stamp;
+      objs.push_back(std::move(o));
+      tomb.erase(k);
+      structural = true;
+      last_change = stamp;
+      return true;
+    }
+    CachedObject& old = objs[it->second];
+    bool changed = false;
+    if (!old.info->same_structure(*info)) {
+      structural = true;
+      changed = true;
+      old.info = std::move(info);
+    } else if (old.info->name != info->name) {
+      old.info = std::move(info);
+    }
+    if (old.canon != canon) {
+      old.canon = std::move(canon);
+      if (!old.value_dirty) dirty.push_back((uint32_t)it->second);
+      old.value_dirty = true;
+      changed = true;
+    }
+    if (changed) old.gen = last_change = stamp;
+    return changed;
+  }
+  bool drop(uint32_t kind, const std::string& key, uint64_t stamp) {
+    const std::string k = store_key(kind, key);
+    auto it = index.find(k);
+    if (it == index.end()) return false;
+    objs[it->second].live = false;
+    index.erase(it);
+    tomb[k] = stamp;
+    structural = true;
+    last_change = stamp;
+    return true;
+  }
+  const CachedObject* get(uint32_t kind, const std::string& key) const {
+    auto it = index.find(store_key(kind, key));
+    return it == index.end() ? nullptr : &objs[it->second];
+  }
+  // Stamp of the last event that touched this key (0: none the image remembers).
+  uint64_t changed_at(const std::string& skey) const {
+    auto it = index.find(skey);
+    if (it != index.end()) return objs[it->second].gen;
+    auto t = tomb.find(skey);
+    return t == tomb.end() ? 0 : t->second;
+  }
+  // After a failed Scan: nothing about the resident copy is trusted any more.
+  void invalidate() {
+    arena.reset();
+    structural = true;
+    pending_changed.clear();
+    for (CachedObject& o : objs) o.rec_off = -1;
+  }
+
+  Upload prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uint64_t* h2d);
+  void upload(Upload what);
+
+ private:
+  uint64_t aux_used = 0, own_used = 0, dep_used = 0, objs_committed = 0, dirty_from = 0;
+  ncd_arena_view host_view();
+  Upload prepare_structural(ncd_ctx* ctx, int threads, uint64_t* h2d);
+  void assign(CachedObject& o, bool force_append);
+  static void copy_record(ncd_arena_view& v, CachedObject& o);
+  void write_all(ncd_arena_view& v, int threads);
+};
+
+}  // namespace ncdh
