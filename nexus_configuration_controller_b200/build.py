@@ -25,11 +25,11 @@ def host_sources():
 
 def build_host(force: bool = False) -> str:
     """libncdhost.so: the C++ host layer (canonicaliser, packer, DriftChecker, replay) over libncdrift.so."""
-    deps = host_sources() + glob.glob(os.path.join(HERE, "..", "include", "*.h")) + [OUT]
+    deps = host_sources() + glob.glob(os.path.join(CSRC, "host", "*.hpp")) + glob.glob(os.path.join(HERE, "..", "include", "*.h")) + [OUT]
     if not force and os.path.exists(HOST_OUT) and all(os.path.getmtime(p) <= os.path.getmtime(HOST_OUT) for p in deps):
         return HOST_OUT
     cxx = shutil.which("g++") or "g++"
-    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-Wextra"] + host_sources() + [
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-pthread", "-Wall", "-Wextra"] + host_sources() + [
         "-L" + os.path.dirname(OUT), "-lncdrift", "-Wl,-rpath,$ORIGIN", "-o", HOST_OUT]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:

@@ -1,14 +1,28 @@
-// drift_checker.cpp — packer, DriftChecker (Scan / Lookup) and handler replay over libncdrift.so.
+// drift_checker.cpp — DriftChecker (Scan / Lookup) and handler replay over libncdrift.so.
 //
 // This is the C++ stand-in for the Go layer of INTEGRATION.md.  It decides nothing about drift:
-// it lays the informer caches out as arenas (canonicalising the compared values), calls
-// ncd_scan, and reads decision codes back.  The replay functions walk a template's / workgroup's
-// slice of those codes in the order the reference's handlers walk the shards
+// it lays the informer caches out as arenas (canonicalising the compared values), calls the
+// scan on the GPU, and reads decision codes back.  The replay functions walk a template's /
+// workgroup's slice of those codes in the order the reference's handlers walk the shards
 // (controller.go:790-831 with :504-626; :720-745) and stop where the handler would return.
+//
+// Concurrency (the reference runs its handlers on `workers` goroutines, controller.go:875-877,
+// while informer callbacks update the caches, :286-359):
+//   cache_mu   shared_mutex over the cluster images.  Event writers take it exclusively for the
+//              update; a Scan takes it exclusively only while it lays changed records out in
+//              pinned memory; readers take it shared for the freshness check.
+//   scan_mu    one Scan at a time; also serialises every call on the ncd_ctx.
+//   snap       the result of the last finished Scan, an immutable object swapped in atomically:
+//              Lookup / plan never wait for a Scan in flight and never see half a result.
 #include <stdint.h>
 #include <string.h>
 
+#include <algorithm>
+#include <atomic>
+#include <chrono>
 #include <memory>
+#include <mutex>
+#include <shared_mutex>
 #include <stdexcept>
 #include <string>
 #include <unordered_map>
@@ -16,10 +30,12 @@
 
 #include "../../../include/ncdhost.h"
 #include "../../../include/ncdrift.h"
+#include "cluster_image.hpp"
 
 namespace ncdh {
 std::string canonicalise(const uint8_t* value, uint64_t len);
 }
+using namespace ncdh;
 
 namespace {
 
@@ -28,236 +44,41 @@ int fail(const std::string& m) {
   g_err = m;
   return -1;
 }
-std::string ncd_err(const char* op) { return std::string(op) + ": " + ncd_last_error(); }
+double ms_since(std::chrono::steady_clock::time_point t0) {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+}
 
-struct OwnerRef {
-  std::string kind, uid;
-  bool operator==(const OwnerRef& o) const { return kind == o.kind && uid == o.uid; }
-};
-struct CachedObject {
-  uint32_t kind = 0;
-  std::string key;  // "namespace/name"
-  std::string name, uid;
-  std::string canon;  // canonical bytes of .Spec / .Data
-  std::vector<OwnerRef> owners;
-  std::vector<std::string> secrets, configmaps;  // dependent names (templates)
-  bool live = true;
-  // where the record lives in the resident arena's payload (-1: not placed yet)
-  int64_t rec_off = -1;
-  uint64_t rec_cap = 0;     // padded bytes reserved at rec_off
-  bool value_dirty = false; // canon changed since the device copy was written
+// The controller objects the rows of a scan were made from, in arena order.  Shared between
+// snapshots while the controller's structure does not change (value updates keep it).
+struct RowDirectory {
+  std::vector<std::shared_ptr<const ObjInfo>> objs;  // by controller arena index
+  std::vector<uint64_t> row0;                        // first row of object i (templates / workgroups)
+  std::unordered_map<std::string, uint32_t> by_key;  // store_key -> arena index, templates and workgroups
+  uint64_t rows = 0;
 };
 
-std::string store_key(uint32_t kind, const std::string& key) { return std::string(1, (char)('0' + kind)) + key; }
-inline uint64_t pad16(uint64_t n) { return (n + 15) & ~15ull; }
+// What one finished Scan published.
+struct Snapshot {
+  uint64_t clock = 0;  // event counter when the Scan began: everything stamped later is not in it
+  size_t nshards = 0;
+  uint64_t rows = 0;
+  std::shared_ptr<const RowDirectory> dir;
+  std::vector<ncd_entry> entries;       // the diff list, ordered by (obj, dep, shard); SKIP is absent
+  std::vector<ncd_adoption> unadopted;  // ordered by (obj, dep)
 
-struct ArenaHandle {
-  ncd_arena* a = nullptr;
-  ArenaHandle() = default;
-  ArenaHandle(const ArenaHandle&) = delete;
-  ArenaHandle& operator=(const ArenaHandle&) = delete;
-  ArenaHandle(ArenaHandle&& o) noexcept : a(o.a) { o.a = nullptr; }
-  void reset() {
-    if (a) ncd_arena_destroy(a);
-    a = nullptr;
-  }
-  ~ArenaHandle() { reset(); }
-};
-
-// One cluster's informer caches (all four listers), insertion ordered, plus its resident arena.
-// Informer events map onto three costs (include/ncdrift.h):
-//   value of an existing object changed (UpdateFunc)   -> ncd_arena_sync_records: that record only
-//   object added / deleted / re-owned (Add/DeleteFunc) -> ncd_arena_recommit: small arrays + new records
-//   first scan, or the arena ran out of room           -> ncd_arena_commit of a fresh, larger arena
-struct ClusterImage {
-  std::vector<CachedObject> objs;
-  std::unordered_map<std::string, size_t> index;
-  ArenaHandle arena;
-  uint64_t payload_used = 0, payload_cap = 0, nobj_cap = 0, aux_cap = 0, nowner_cap = 0, ndep_cap = 0;
-  bool structural = true;  // keys / owners / dependents changed since the last commit
-  uint64_t uploads_full = 0, uploads_structural = 0, uploads_values = 0;  // how each scan got its data across
-
-  void put(CachedObject&& o) {
-    const std::string k = store_key(o.kind, o.key);
-    auto it = index.find(k);
-    if (it == index.end()) {
-      index.emplace(k, objs.size());
-      objs.push_back(std::move(o));
-      structural = true;
-      return;
-    }
-    CachedObject& old = objs[it->second];
-    if (old.uid != o.uid || !(old.owners == o.owners) || old.secrets != o.secrets || old.configmaps != o.configmaps)
-      structural = true;
-    if (old.canon != o.canon) {
-      old.canon = std::move(o.canon);
-      old.value_dirty = true;
-    }
-    old.name = std::move(o.name);
-    old.uid = std::move(o.uid);
-    old.owners = std::move(o.owners);
-    old.secrets = std::move(o.secrets);
-    old.configmaps = std::move(o.configmaps);
-  }
-  bool drop(uint32_t kind, const std::string& key) {
-    auto it = index.find(store_key(kind, key));
-    if (it == index.end()) return false;
-    objs[it->second].live = false;
-    index.erase(it);
-    structural = true;
-    return true;
-  }
-  const CachedObject* get(uint32_t kind, const std::string& key) const {
-    auto it = index.find(store_key(kind, key));
-    return it == index.end() ? nullptr : &objs[it->second];
-  }
-
-  // Brings the resident arena up to date with the image.  `order` (controller image only)
-  // receives the live objects in arena order.
-  // deferred: if given, a pure value sync is not issued here but left in pending_changed for the
-  // caller, which pushes the rewritten records of every cluster in one ncd_arenas_sync_records
-  void sync(ncd_ctx* ctx, std::vector<const CachedObject*>* order, std::vector<ClusterImage*>* deferred = nullptr) {
-    // forget dead objects (their payload becomes unreferenced until the next full commit)
-    if (structural) {
-      std::vector<CachedObject> keep;
-      for (CachedObject& o : objs)
-        if (o.live) keep.push_back(std::move(o));
-      objs.swap(keep);
-      index.clear();
-      for (size_t i = 0; i < objs.size(); ++i) index.emplace(store_key(objs[i].kind, objs[i].key), i);
-    }
-    if (order)
-      for (const CachedObject& o : objs) order->push_back(&o);
-
-    if (!arena.a || structural) {
-      uint64_t aux = 0, nowner = 0, ndep = 0, append = 0, compact = 0;
-      for (const CachedObject& o : objs) {
-        aux += o.key.size() + o.uid.size();
-        for (const OwnerRef& r : o.owners) aux += r.uid.size();
-        nowner += o.owners.size();
-        for (const auto& s : o.secrets) aux += o.key.size() + s.size();  // "namespace/" + name <= key + name
-        for (const auto& s : o.configmaps) aux += o.key.size() + s.size();
-        ndep += o.secrets.size() + o.configmaps.size();
-        compact += pad16(o.canon.size());
-        if (o.rec_off < 0 || o.value_dirty) append += pad16(o.canon.size());
-      }
-      const bool fits = arena.a && objs.size() <= nobj_cap && aux <= aux_cap && nowner <= nowner_cap &&
-                        ndep <= ndep_cap && payload_used + append <= payload_cap;
-      if (!fits) {
-        // a fresh arena with room to grow; every record is placed again, compactly
-        arena.reset();
-        payload_cap = compact + compact / 2 + (64 << 10);
-        nobj_cap = objs.size() + objs.size() / 2 + 16;
-        aux_cap = aux + aux / 2 + 1024;
-        nowner_cap = nowner + nowner / 2 + 16;
-        ndep_cap = ndep + ndep / 2 + 16;
-        if (ncd_arena_create(ctx, payload_cap, nobj_cap, aux_cap, nowner_cap, ndep_cap, NCD_ARENA_HOST_PINNED,
-                             &arena.a) != NCD_OK)
-          throw std::runtime_error(ncd_err("ncd_arena_create"));
-        payload_used = 0;
-        for (CachedObject& o : objs) o.rec_off = -1;
-      }
-      ncd_arena_view v;
-      if (ncd_arena_host_view(arena.a, &v) != NCD_OK) throw std::runtime_error(ncd_err("ncd_arena_host_view"));
-      const uint64_t dirty_from = payload_used;
-      write_all(v);
-      const uint64_t n = objs.size();
-      const int rc = fits ? ncd_arena_recommit(arena.a, n, payload_used, aux_used, own_used, dep_used, dirty_from)
-                          : ncd_arena_commit(arena.a, n, payload_used, aux_used, own_used, dep_used);
-      if (rc != NCD_OK) throw std::runtime_error(ncd_err(fits ? "ncd_arena_recommit" : "ncd_arena_commit"));
-      ++(fits ? uploads_structural : uploads_full);
-      structural = false;
-      return;
-    }
-
-    // same objects, some values changed: rewrite those records and push only them
-    std::vector<uint32_t> changed;
-    uint64_t append = 0;
-    for (const CachedObject& o : objs)
-      if (o.value_dirty && pad16(o.canon.size()) > o.rec_cap) append += pad16(o.canon.size());
-    if (payload_used + append > payload_cap) {  // no room to append: start over with a larger arena
-      structural = true;
-      arena.reset();
-      if (order) order->clear();
-      sync(ctx, order, deferred);
-      return;
-    }
-    ncd_arena_view v;
-    if (ncd_arena_host_view(arena.a, &v) != NCD_OK) throw std::runtime_error(ncd_err("ncd_arena_host_view"));
-    for (size_t i = 0; i < objs.size(); ++i) {
-      CachedObject& o = objs[i];
-      if (!o.value_dirty) continue;
-      place(v, o, /*force_append=*/false);
-      v.rec_off[i] = (uint64_t)o.rec_off;
-      v.rec_len[i] = (uint32_t)o.canon.size();
-      changed.push_back((uint32_t)i);
-    }
-    if (!changed.empty()) {
-      ++uploads_values;
-      if (deferred) {
-        pending_changed.swap(changed);
-        deferred->push_back(this);
-      } else if (ncd_arena_sync_records(arena.a, changed.size(), changed.data(), payload_used) != NCD_OK) {
-        throw std::runtime_error(ncd_err("ncd_arena_sync_records"));
-      }
-    }
-  }
-  std::vector<uint32_t> pending_changed;  // objects whose records a deferred value sync still has to push
-
- private:
-  uint64_t aux_used = 0, own_used = 0, dep_used = 0;
-
-  // Writes o's record into the pinned payload: where it already is if it fits, else at the end.
-  void place(ncd_arena_view& v, CachedObject& o, bool force_append) {
-    const uint64_t need = pad16(o.canon.size());
-    if (o.rec_off < 0 || need > o.rec_cap || force_append) {
-      o.rec_off = (int64_t)payload_used;
-      o.rec_cap = need;
-      payload_used += need;
-    }
-    memcpy(v.payload + o.rec_off, o.canon.data(), o.canon.size());
-    memset(v.payload + o.rec_off + o.canon.size(), 0, need - o.canon.size());
-    o.value_dirty = false;
-  }
-
-  // Every per-object array from scratch (arena layout: ncdrift.h "arenas"); records that are
-  // already on the device and did not change keep their place, the others are appended.
-  void write_all(ncd_arena_view& v) {
-    uint64_t ax = 0, oi = 0, di = 0, i = 0;
-    auto put_aux = [&](const std::string& s, uint32_t* o, uint32_t* l) {
-      memcpy(v.aux + ax, s.data(), s.size());
-      *o = (uint32_t)ax;
-      *l = (uint32_t)s.size();
-      ax += s.size();
+  uint32_t code(uint32_t obj, uint32_t dep, uint32_t shard) const {
+    auto lt = [](const ncd_entry& e, const ncd_entry& k) {
+      return e.obj != k.obj ? e.obj < k.obj : (e.dep != k.dep ? e.dep < k.dep : e.shard < k.shard);
     };
-    for (CachedObject& o : objs) {
-      if (o.rec_off < 0 || o.value_dirty) place(v, o, /*force_append=*/true);  // only appended payload is re-uploaded
-      v.rec_off[i] = (uint64_t)o.rec_off;
-      v.rec_len[i] = (uint32_t)o.canon.size();
-      v.kind[i] = (uint8_t)o.kind;
-      put_aux(o.key, &v.key_off[i], &v.key_len[i]);
-      put_aux(o.uid, &v.uid_off[i], &v.uid_len[i]);
-      v.own_start[i] = (uint32_t)oi;
-      for (const OwnerRef& r : o.owners) {
-        v.own_is_template[oi] = r.kind == "NexusAlgorithmTemplate";  // the Kind test of controller.go:490
-        put_aux(r.uid, &v.own_uid_off[oi], &v.own_uid_len[oi]);
-        ++oi;
-      }
-      v.dep_start[i] = (uint32_t)di;
-      const std::string ns = o.key.substr(0, o.key.find('/') + 1);
-      for (int pass = 0; pass < 2; ++pass)  // secrets first, then configmaps (:817 before :825)
-        for (const std::string& name : pass == 0 ? o.secrets : o.configmaps) {
-          v.dep_kind[di] = pass == 0 ? NCD_KIND_SECRET : NCD_KIND_CONFIGMAP;
-          put_aux(ns + name, &v.dep_key_off[di], &v.dep_key_len[di]);
-          ++di;
-        }
-      ++i;
-    }
-    v.own_start[i] = (uint32_t)oi;
-    v.dep_start[i] = (uint32_t)di;
-    aux_used = ax;
-    own_used = oi;
-    dep_used = di;
+    const ncd_entry key{obj, dep, shard, 0};
+    auto it = std::lower_bound(entries.begin(), entries.end(), key, lt);
+    return (it != entries.end() && it->obj == obj && it->dep == dep && it->shard == shard) ? it->code : (uint32_t)NCD_SKIP;
+  }
+  bool needs_adoption(uint32_t obj, uint32_t dep) const {
+    auto lt = [](const ncd_adoption& e, const ncd_adoption& k) { return e.obj != k.obj ? e.obj < k.obj : e.dep < k.dep; };
+    const ncd_adoption key{obj, dep};
+    auto it = std::lower_bound(unadopted.begin(), unadopted.end(), key, lt);
+    return it != unadopted.end() && it->obj == obj && it->dep == dep;
   }
 };
 
@@ -266,21 +87,28 @@ struct ClusterImage {
 struct ncdh_checker {
   ncd_ctx* ctx = nullptr;
   uint32_t mode = 0;
+  int threads = 1;
+  std::shared_mutex cache_mu;
+  std::mutex scan_mu;
+  std::atomic<uint64_t> clock{0};
+  std::atomic<uint64_t> events_since_scan{0};
+  std::atomic<uint64_t> canon_ns_since_scan{0};
   ClusterImage controller;
   std::vector<ClusterImage> shards;
-  // snapshot of the last Scan
-  bool scanned = false;
-  std::vector<uint8_t> codes;                          // rows x nshards
-  std::unordered_map<std::string, uint64_t> first_row;  // store_key -> first row of a template / workgroup
-  std::unordered_map<std::string, CachedObject> snap;   // the controller objects the rows were made from
-  std::vector<std::string> dirty;                       // sweep feed of the last Scan: "<type>\t<ns/name>"
-  uint64_t rows = 0, ndiff = 0;
+  std::shared_ptr<const Snapshot> snap;  // read / written with std::atomic_load / atomic_store
+  // scan thread only
+  std::shared_ptr<const RowDirectory> dir;
+  std::vector<ncd_adoption> unadopted;  // of the controller arena as last committed
+  bool unadopted_valid = false;
+  std::mutex timing_mu;
+  ncdh_scan_timing timing{};
 
   ClusterImage* image(int cluster) {
     if (cluster == -1) return &controller;
     if (cluster >= 0 && (size_t)cluster < shards.size()) return &shards[cluster];
     return nullptr;
   }
+  std::shared_ptr<const Snapshot> snapshot() const { return std::atomic_load(&snap); }
 };
 
 namespace {
@@ -300,6 +128,56 @@ int64_t render(const std::vector<Action>& acts, const std::string& error, char* 
   if (!error.empty()) s += "error\t" + error + "\n";
   if (out && s.size() <= cap) memcpy(out, s.data(), s.size());
   return (int64_t)s.size();
+}
+
+// One event, canonicalised and ready to be put under the lock.
+struct Prepared {
+  int cluster = 0;
+  uint32_t op = NCDH_EV_PUT;
+  std::shared_ptr<const ObjInfo> info;
+  std::string canon;
+};
+
+void prepare_event(const ncdh_event& e, Prepared* p) {
+  if (!e.ns || !e.name) throw std::runtime_error("null namespace / name");
+  if (e.kind > NCD_KIND_CONFIGMAP) throw std::runtime_error("unknown kind");
+  auto info = std::make_shared<ObjInfo>();
+  info->kind = e.kind;
+  info->key = std::string(e.ns) + "/" + e.name;  // cache.ObjectName.String()
+  info->name = e.name;
+  p->cluster = e.cluster;
+  p->op = e.op;
+  if (e.op == NCDH_EV_PUT) {
+    if (!e.uid || (!e.value && e.value_len)) throw std::runtime_error("null uid / value");
+    if (e.nowners < 0 || e.nsecrets < 0 || e.nconfigmaps < 0) throw std::runtime_error("negative count");
+    info->uid = e.uid;
+    for (int i = 0; i < e.nowners; ++i) info->owners.push_back({e.owner_kinds[i], e.owner_uids[i]});
+    for (int i = 0; i < e.nsecrets; ++i) info->secrets.push_back(e.secret_names[i]);
+    for (int i = 0; i < e.nconfigmaps; ++i) info->configmaps.push_back(e.configmap_names[i]);
+    p->canon = canonicalise(e.value, e.value_len);
+  } else if (e.op != NCDH_EV_DELETE) {
+    throw std::runtime_error("unknown event op");
+  }
+  p->info = std::move(info);
+}
+
+// Applies prepared events in order.  Caller holds cache_mu exclusively.
+int apply_locked(ncdh_checker* c, std::vector<Prepared>& evs, size_t count, int* removed_missing) {
+  for (size_t i = 0; i < count; ++i) {
+    Prepared& p = evs[i];
+    ClusterImage* img = c->image(p.cluster);
+    if (!img) return fail("no such cluster");
+    const uint64_t stamp = c->clock.fetch_add(1) + 1;
+    bool changed;
+    if (p.op == NCDH_EV_PUT) {
+      changed = img->put(std::move(p.info), std::move(p.canon), stamp);
+    } else {
+      changed = img->drop(p.info->kind, p.info->key, stamp);
+      if (!changed && removed_missing) ++*removed_missing;
+    }
+    if (changed) c->events_since_scan.fetch_add(1, std::memory_order_relaxed);
+  }
+  return 0;
 }
 
 }  // namespace
@@ -324,6 +202,8 @@ int ncdh_checker_create(int device, uint32_t mode, int nshards, ncdh_checker** o
   if (ncd_init(device, &c->ctx) != NCD_OK) return fail(ncd_err("ncd_init"));  // no GPU: an error, not a fallback
   c->mode = mode;
   c->shards.resize(nshards);
+  const unsigned hc = std::thread::hardware_concurrency();
+  c->threads = hc ? (int)(hc > 32 ? 32 : hc) : 4;
   *out = c.release();
   return 0;
 }
@@ -336,162 +216,316 @@ void ncdh_checker_destroy(ncdh_checker* c) {
   delete c;
 }
 
+int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int threads) {
+  if (!c || (!events && n)) return fail("ncdh_apply_events: null argument");
+  if (n == 0) return 0;
+  if (threads <= 0) threads = c->threads;
+  const auto t0 = std::chrono::steady_clock::now();
+  // canonicalise outside the lock, in parallel; remember the first event that cannot be
+  std::vector<Prepared> evs(n);
+  std::vector<std::string> errs(n);
+  std::atomic<uint64_t> first_bad{n};
+  parallel_for(n, threads, 8, [&](size_t i) {
+    try {
+      prepare_event(events[i], &evs[i]);
+    } catch (const std::exception& e) {
+      errs[i] = e.what();
+      uint64_t cur = first_bad.load();
+      while (i < cur && !first_bad.compare_exchange_weak(cur, i)) {
+      }
+    }
+  });
+  c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t0) * 1e6), std::memory_order_relaxed);
+  const uint64_t good = first_bad.load();
+  int rc;
+  {
+    std::unique_lock<std::shared_mutex> lk(c->cache_mu);
+    rc = apply_locked(c, evs, good, nullptr);
+  }
+  if (rc != 0) return fail("ncdh_apply_events: " + g_err);
+  if (good < n) return fail("ncdh_apply_events: event " + std::to_string(good) + ": " + errs[good]);
+  return 0;
+}
+
 int ncdh_cluster_add(ncdh_checker* c, int cluster, uint32_t kind, const char* ns, const char* name, const char* uid,
                      const uint8_t* value, uint64_t value_len, const char* const* owner_kinds,
                      const char* const* owner_uids, int nowners, const char* const* secret_names, int nsecrets,
                      const char* const* configmap_names, int nconfigmaps) {
   if (!c || !ns || !name || !uid || (!value && value_len)) return fail("ncdh_cluster_add: null argument");
-  ClusterImage* img = c->image(cluster);
-  if (!img) return fail("ncdh_cluster_add: no such cluster");
+  if (!c->image(cluster)) return fail("ncdh_cluster_add: no such cluster");
   if (kind > NCD_KIND_CONFIGMAP) return fail("ncdh_cluster_add: unknown kind");
+  ncdh_event e;
+  memset(&e, 0, sizeof(e));
+  e.cluster = cluster;
+  e.kind = kind;
+  e.op = NCDH_EV_PUT;
+  e.ns = ns;
+  e.name = name;
+  e.uid = uid;
+  e.value = value;
+  e.value_len = value_len;
+  e.owner_kinds = owner_kinds;
+  e.owner_uids = owner_uids;
+  e.nowners = nowners;
+  e.secret_names = secret_names;
+  e.nsecrets = nsecrets;
+  e.configmap_names = configmap_names;
+  e.nconfigmaps = nconfigmaps;
   try {
-    CachedObject o;
-    o.kind = kind;
-    o.key = std::string(ns) + "/" + name;  // cache.ObjectName.String()
-    o.name = name;
-    o.uid = uid;
-    o.canon = ncdh::canonicalise(value, value_len);
-    for (int i = 0; i < nowners; ++i) o.owners.push_back({owner_kinds[i], owner_uids[i]});
-    for (int i = 0; i < nsecrets; ++i) o.secrets.push_back(secret_names[i]);
-    for (int i = 0; i < nconfigmaps; ++i) o.configmaps.push_back(configmap_names[i]);
-    img->put(std::move(o));
-  } catch (const std::exception& e) {
-    return fail(std::string("ncdh_cluster_add: ") + e.what());
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<Prepared> one(1);
+    prepare_event(e, &one[0]);  // canonicalised on the caller's thread, outside the lock
+    c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t0) * 1e6), std::memory_order_relaxed);
+    std::unique_lock<std::shared_mutex> lk(c->cache_mu);
+    return apply_locked(c, one, 1, nullptr);
+  } catch (const std::exception& ex) {
+    return fail(std::string("ncdh_cluster_add: ") + ex.what());
   }
-  return 0;
 }
 
 int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char* ns, const char* name) {
-  ClusterImage* img = c ? c->image(cluster) : nullptr;
-  if (!img || !ns || !name) return fail("ncdh_cluster_remove: bad argument");
-  return img->drop(kind, std::string(ns) + "/" + name) ? 0 : 1;
+  if (!c || !c->image(cluster) || !ns || !name || kind > NCD_KIND_CONFIGMAP) return fail("ncdh_cluster_remove: bad argument");
+  std::vector<Prepared> one(1);
+  auto info = std::make_shared<ObjInfo>();
+  info->kind = kind;
+  info->key = std::string(ns) + "/" + name;
+  one[0].cluster = cluster;
+  one[0].op = NCDH_EV_DELETE;
+  one[0].info = std::move(info);
+  int missing = 0;
+  std::unique_lock<std::shared_mutex> lk(c->cache_mu);
+  if (apply_locked(c, one, 1, &missing) != 0) return -1;
+  return missing ? 1 : 0;
 }
 
 int ncdh_scan(ncdh_checker* c) {
   if (!c) return fail("ncdh_scan: null checker");
+  std::lock_guard<std::mutex> scan_lock(c->scan_mu);
+  const auto t_all = std::chrono::steady_clock::now();
+  ncdh_scan_timing tm;
+  memset(&tm, 0, sizeof(tm));
   try {
-    std::vector<const CachedObject*> order;
-    std::vector<ClusterImage*> deferred;
-    c->controller.sync(c->ctx, &order, &deferred);
-    std::vector<const ncd_arena*> ptrs;
-    for (ClusterImage& sh : c->shards) {
-      sh.sync(c->ctx, nullptr, &deferred);
-      ptrs.push_back(sh.arena.a);
+    const size_t S = c->shards.size();
+    std::vector<ClusterImage*> imgs;
+    imgs.push_back(&c->controller);
+    for (ClusterImage& sh : c->shards) imgs.push_back(&sh);
+    std::vector<Upload> ups(imgs.size(), Upload::None);
+    auto snap = std::make_shared<Snapshot>();
+    const std::shared_ptr<const Snapshot> prev = c->snapshot();
+    {
+      // ---- under the cache lock: stamp the scan, lay the changes out in pinned memory
+      std::unique_lock<std::shared_mutex> lk(c->cache_mu);
+      const auto t0 = std::chrono::steady_clock::now();
+      snap->clock = c->clock.load();
+      tm.events = c->events_since_scan.exchange(0);
+      tm.canon_ms = (double)c->canon_ns_since_scan.exchange(0) / 1e6;
+      for (size_t k = 0; k < imgs.size(); ++k) ups[k] = imgs[k]->prepare(c->ctx, c->threads, prev ? prev->clock : 0, &tm.h2d_bytes);
+      if (ups[0] == Upload::Full || ups[0] == Upload::Structural || !c->dir) {
+        // row numbering: arena order, one row per template + one per dependent, one per workgroup
+        auto dir = std::make_shared<RowDirectory>();
+        const std::vector<CachedObject>& objs = c->controller.objs;
+        dir->objs.reserve(objs.size());
+        dir->row0.assign(objs.size(), 0);
+        uint64_t row = 0;
+        for (size_t i = 0; i < objs.size(); ++i) {
+          const ObjInfo& f = *objs[i].info;
+          dir->objs.push_back(objs[i].info);
+          if (f.kind == NCD_KIND_TEMPLATE || f.kind == NCD_KIND_WORKGROUP) {
+            dir->row0[i] = row;
+            dir->by_key.emplace(store_key(f.kind, f.key), (uint32_t)i);
+            row += 1 + (f.kind == NCD_KIND_TEMPLATE ? f.secrets.size() + f.configmaps.size() : 0);
+          }
+        }
+        dir->rows = row;
+        c->dir = std::move(dir);
+        c->unadopted_valid = false;
+      }
+      tm.pack_ms = ms_since(t0);
     }
-    if (!deferred.empty()) {  // the value rewrites of every cluster: one round trip
-      std::vector<ncd_arena*> as;
-      std::vector<uint64_t> ns, pbs;
-      std::vector<const uint32_t*> idx;
-      for (ClusterImage* img : deferred) {
+    // ---- GPU: uploads, then the scan (the cache lock is free: events and lookups go on)
+    const auto t_up = std::chrono::steady_clock::now();
+    std::vector<ncd_arena*> as;
+    std::vector<uint64_t> ns, pbs;
+    std::vector<const uint32_t*> idx;
+    for (size_t k = 0; k < imgs.size(); ++k) {
+      ClusterImage* img = imgs[k];
+      if (ups[k] == Upload::Full) ++tm.full_uploads;
+      if (ups[k] == Upload::Structural) ++tm.structural_uploads;
+      if (ups[k] == Upload::Values) {  // the value rewrites of every cluster: one round trip
         as.push_back(img->arena.a);
         ns.push_back(img->pending_changed.size());
         idx.push_back(img->pending_changed.data());
         pbs.push_back(img->payload_used);
+        tm.records_synced += img->pending_changed.size();
+      } else {
+        img->upload(ups[k]);
       }
+    }
+    if (!as.empty()) {
       const int rc = ncd_arenas_sync_records((int)as.size(), as.data(), ns.data(), idx.data(), pbs.data());
-      for (ClusterImage* img : deferred) img->pending_changed.clear();
-      if (rc != NCD_OK) return fail(ncd_err("ncd_arenas_sync_records"));
+      for (ClusterImage* img : imgs) img->pending_changed.clear();
+      if (rc != NCD_OK) throw std::runtime_error(ncd_err("ncd_arenas_sync_records"));
+      tm.d2h_bytes += 8 * as.size();
     }
-    ncd_diff* d = nullptr;
-    if (ncd_scan(c->ctx, c->controller.arena.a, ptrs.data(), (int)ptrs.size(), c->mode, &d) != NCD_OK)
-      return fail(ncd_err("ncd_scan"));
-    ncd_scan_stats st;
-    ncd_scan_last_stats(c->ctx, &st);
-    c->rows = st.rows;
-    c->ndiff = st.ndiff;
-    c->codes.assign(st.rows * ptrs.size(), 0);
-    int rc = ncd_diff_codes(d, c->codes.data(), c->codes.size());
-    std::vector<uint32_t> dirty_idx;
-    if (rc == NCD_OK) {
-      uint64_t nd = 0;
-      rc = ncd_diff_dirty_objects(d, nullptr, 0, &nd);
-      dirty_idx.resize(nd);
-      if (rc == NCD_OK && nd) rc = ncd_diff_dirty_objects(d, dirty_idx.data(), nd, &nd);
-    }
-    ncd_diff_destroy(d);
-    if (rc != NCD_OK) return fail(ncd_err("ncd_diff_codes"));
-    // row numbering: arena order, one row per template + one per dependent, one per workgroup
-    c->first_row.clear();
-    c->snap.clear();
-    uint64_t row = 0;
-    for (const CachedObject* o : order) {
-      if (o->kind == NCD_KIND_TEMPLATE || o->kind == NCD_KIND_WORKGROUP) {
-        c->first_row[store_key(o->kind, o->key)] = row;
-        c->snap[store_key(o->kind, o->key)] = *o;
-        row += 1 + (o->kind == NCD_KIND_TEMPLATE ? o->secrets.size() + o->configmaps.size() : 0);
+    if (!c->unadopted_valid) {  // ownerReferences only change with a structural upload of the controller
+      uint64_t n = 0;
+      c->unadopted.resize(1024);
+      if (ncd_find_unadopted(c->ctx, c->controller.arena.a, c->unadopted.data(), c->unadopted.size(), &n) != NCD_OK)
+        throw std::runtime_error(ncd_err("ncd_find_unadopted"));
+      if (n > c->unadopted.size()) {
+        c->unadopted.resize(n);
+        if (ncd_find_unadopted(c->ctx, c->controller.arena.a, c->unadopted.data(), c->unadopted.size(), &n) != NCD_OK)
+          throw std::runtime_error(ncd_err("ncd_find_unadopted"));
       }
+      c->unadopted.resize(n);
+      c->unadopted_valid = true;
+      tm.d2h_bytes += 8 + n * sizeof(ncd_adoption);
     }
-    if (row != st.rows) return fail("ncdh_scan: row count disagrees with the library");
-    c->dirty.clear();
-    for (uint32_t i : dirty_idx) {
-      if (i >= order.size()) return fail("ncdh_scan: dirty object index out of range");
-      c->dirty.push_back(std::string(order[i]->kind == NCD_KIND_TEMPLATE ? "template" : "workgroup") + "\t" + order[i]->key);
-    }
-    c->scanned = true;
+    tm.upload_ms = ms_since(t_up);
+    const auto t_scan = std::chrono::steady_clock::now();
+    std::vector<const ncd_arena*> ptrs;
+    for (ClusterImage& sh : c->shards) ptrs.push_back(sh.arena.a);
+    const ncd_entry* ents = nullptr;
+    uint64_t nent = 0;
+    if (ncd_scan_host(c->ctx, c->controller.arena.a, ptrs.data(), (int)S, c->mode, &ents, &nent) != NCD_OK)
+      throw std::runtime_error(ncd_err("ncd_scan_host"));
+    ncd_scan_stats st;
+    if (ncd_scan_last_stats(c->ctx, &st) != NCD_OK) throw std::runtime_error(ncd_err("ncd_scan_last_stats"));
+    tm.scan_ms = ms_since(t_scan);
+    tm.gpu_scan_ms = st.total_ms;
+    tm.d2h_bytes += 16 + nent * sizeof(ncd_entry);
+    // ---- publish
+    const auto t_pub = std::chrono::steady_clock::now();
+    if (st.rows != c->dir->rows) throw std::runtime_error("row count disagrees with the library");
+    snap->nshards = S;
+    snap->rows = st.rows;
+    snap->dir = c->dir;
+    snap->entries.assign(ents, ents + nent);
+    snap->unadopted = c->unadopted;
+    for (const ncd_entry& e : snap->entries)
+      if (e.obj >= snap->dir->objs.size()) throw std::runtime_error("diff entry names an object the controller does not hold");
+    std::atomic_store(&c->snap, std::shared_ptr<const Snapshot>(std::move(snap)));
+    tm.publish_ms = ms_since(t_pub);
   } catch (const std::exception& e) {
-    return fail(std::string("ncdh_scan: ") + e.what());
+    // whatever was laid out for this Scan may not have reached the GPU: the next Scan uploads
+    // every cluster in full again rather than trust a half-updated resident copy
+    const std::string what = e.what();
+    std::unique_lock<std::shared_mutex> lk(c->cache_mu);
+    c->controller.invalidate();
+    for (ClusterImage& sh : c->shards) sh.invalidate();
+    c->dir.reset();
+    return fail("ncdh_scan: " + what);
   }
+  tm.total_ms = ms_since(t_all);
+  std::lock_guard<std::mutex> tl(c->timing_mu);
+  c->timing = tm;
   return 0;
 }
 
+}  // extern "C"
+
+namespace {
+
+// Freshness of everything a decision about template / workgroup `f` on `shards` [s0, s1) rests on:
+// the controller's copy of the object and of each dependent it names, and every listed shard's
+// copies of the same keys (the shard template's UID decides ownership, controller.go:529).
+// True when any of them was put or removed after the snapshot's Scan began.  Caller holds
+// cache_mu (shared).
+bool stale_for(ncdh_checker* c, const Snapshot& s, const std::string& skey, const ObjInfo* f, size_t s0, size_t s1) {
+  bool any = c->controller.last_change > s.clock;
+  for (size_t k = s0; k < s1 && !any; ++k) any = c->shards[k].last_change > s.clock;
+  if (!any) return false;  // nothing at all changed in the clusters involved: the common case
+  std::vector<std::string> keys;
+  keys.push_back(skey);
+  if (f && f->kind == NCD_KIND_TEMPLATE) {
+    const std::string ns = f->key.substr(0, f->key.find('/') + 1);
+    for (const std::string& n : f->secrets) keys.push_back(store_key(NCD_KIND_SECRET, ns + n));
+    for (const std::string& n : f->configmaps) keys.push_back(store_key(NCD_KIND_CONFIGMAP, ns + n));
+  }
+  for (const std::string& k : keys) {
+    if (c->controller.changed_at(k) > s.clock) return true;
+    for (size_t sh = s0; sh < s1; ++sh)
+      if (c->shards[sh].changed_at(k) > s.clock) return true;
+  }
+  return false;
+}
+
+}  // namespace
+
+extern "C" {
+
 int ncdh_lookup(ncdh_checker* c, uint32_t kind, const char* ns, const char* name, int dep, int shard, uint32_t* code) {
   if (!c || !ns || !name || !code) return fail("ncdh_lookup: null argument");
-  if (!c->scanned) return fail("ncdh_lookup: no scan yet");
-  if (shard < 0 || (size_t)shard >= c->shards.size()) return fail("ncdh_lookup: no such shard");
+  const std::shared_ptr<const Snapshot> s = c->snapshot();
+  if (!s) return fail("ncdh_lookup: no scan yet");
+  if (shard < 0 || (size_t)shard >= s->nshards) return fail("ncdh_lookup: no such shard");
   const std::string k = store_key(kind, std::string(ns) + "/" + name);
-  auto it = c->first_row.find(k);
-  if (it == c->first_row.end()) return 1;
-  const CachedObject& o = c->snap[k];
-  const size_t ndeps = o.kind == NCD_KIND_TEMPLATE ? o.secrets.size() + o.configmaps.size() : 0;
+  auto it = s->dir->by_key.find(k);
+  std::shared_lock<std::shared_mutex> lk(c->cache_mu);
+  if (it == s->dir->by_key.end())  // not in the snapshot: gone for good, or added since
+    return c->controller.changed_at(k) > s->clock ? NCDH_STALE : NCDH_NOT_FOUND;
+  const ObjInfo& f = *s->dir->objs[it->second];
+  const size_t ndeps = f.kind == NCD_KIND_TEMPLATE ? f.secrets.size() + f.configmaps.size() : 0;
   if (dep < 0 || (size_t)dep > ndeps) return fail("ncdh_lookup: no such dependent");
-  *code = c->codes[(it->second + dep) * c->shards.size() + shard];
+  if (stale_for(c, *s, k, &f, (size_t)shard, (size_t)shard + 1)) return NCDH_STALE;
+  *code = s->code(it->second, (uint32_t)dep, (uint32_t)shard);
   return 0;
 }
 
 int64_t ncdh_plan_template(ncdh_checker* c, const char* ns, const char* name, char* out, uint64_t cap) {
   if (!c || !ns || !name) return fail("ncdh_plan_template: null argument");
-  if (!c->scanned) return fail("ncdh_plan_template: no scan yet");
+  const std::shared_ptr<const Snapshot> s = c->snapshot();
+  if (!s) return fail("ncdh_plan_template: no scan yet");
   std::vector<Action> acts;
   std::string error;
   const std::string k = store_key(NCD_KIND_TEMPLATE, std::string(ns) + "/" + name);
-  auto it = c->snap.find(k);
-  if (it == c->snap.end()) return render(acts, error, out, cap);  // :769-772: gone from the cache, nil
-  const CachedObject& t = it->second;
-  const size_t S = c->shards.size(), nsec = t.secrets.size(), ndeps = nsec + t.configmaps.size();
-  const uint64_t row0 = c->first_row[k];
+  auto it = s->dir->by_key.find(k);
+  const size_t S = s->nshards;
+  {
+    std::shared_lock<std::shared_mutex> lk(c->cache_mu);
+    if (it == s->dir->by_key.end()) {
+      if (c->controller.changed_at(k) > s->clock) return -NCDH_STALE;
+      return render(acts, error, out, cap);  // :769-772: gone from the cache, nil
+    }
+    if (stale_for(c, *s, k, s->dir->objs[it->second].get(), 0, S)) return -NCDH_STALE;
+  }
+  const uint32_t obj = it->second;
+  const ObjInfo& t = *s->dir->objs[obj];
+  const size_t nsec = t.secrets.size(), ndeps = nsec + t.configmaps.size();
   auto dep_name = [&](size_t j) { return j < nsec ? t.secrets[j] : t.configmaps[j - nsec]; };
   auto dep_res = [&](size_t j) { return j < nsec ? "secrets" : "configmaps"; };
   // adoptReferences (:783 -> :647-676) fails the handler before any shard when a referenced
   // object is missing on the controller; ERR_MISSING_REF does not depend on the shard
   if (S > 0) {
     for (size_t j = 0; j < ndeps; ++j)
-      if (c->codes[(row0 + 1 + j) * S] == NCD_ERR_MISSING_REF) {
+      if (s->code(obj, (uint32_t)j + 1, 0) == NCD_ERR_MISSING_REF) {
         error = std::string("missing ") + dep_res(j) + " " + dep_name(j);
         return render(acts, error, out, cap);
       }
   } else {
+    std::shared_lock<std::shared_mutex> lk(c->cache_mu);
     for (size_t j = 0; j < ndeps; ++j)
       if (!c->controller.get(j < nsec ? NCD_KIND_SECRET : NCD_KIND_CONFIGMAP, std::string(ns) + "/" + dep_name(j))) {
         error = std::string("missing ") + dep_res(j) + " " + dep_name(j);
         return render(acts, error, out, cap);
       }
   }
-  for (size_t s = 0; s < S && error.empty(); ++s) {  // :790
-    const uint32_t tc = c->codes[row0 * S + s];
-    if (tc & NCD_UPDATE_DATA) acts.push_back({(int)s, "nexus", "update", "NexusAlgorithmTemplates", t.name});  // :795-797
-    if (tc == NCD_CREATE) acts.push_back({(int)s, "nexus", "create", "NexusAlgorithmTemplates", t.name});      // :805-808
+  for (size_t sh = 0; sh < S && error.empty(); ++sh) {  // :790
+    const uint32_t tc = s->code(obj, 0, (uint32_t)sh);
+    if (tc & NCD_UPDATE_DATA) acts.push_back({(int)sh, "nexus", "update", "NexusAlgorithmTemplates", t.name});  // :795-797
+    if (tc == NCD_CREATE) acts.push_back({(int)sh, "nexus", "create", "NexusAlgorithmTemplates", t.name});      // :805-808
     for (size_t j = 0; j < ndeps; ++j) {  // :817 then :825
-      const uint32_t code = c->codes[(row0 + 1 + j) * S + s];
+      const uint32_t code = s->code(obj, (uint32_t)j + 1, (uint32_t)sh);
       if (code == NCD_ERR_ROGUE) {  // :529-535 / :591-597
         error = "Resource \"" + dep_name(j) + "\" already exists and is not managed by any Algorithm";
         break;
       }
       if (code == NCD_CREATE) {  // :518-520 / :580-582
-        acts.push_back({(int)s, "kube", "create", dep_res(j), dep_name(j)});
+        acts.push_back({(int)sh, "kube", "create", dep_res(j), dep_name(j)});
         continue;
       }
-      if (code & NCD_UPDATE_DATA) acts.push_back({(int)s, "kube", "update-data", dep_res(j), dep_name(j)});    // :539-541 / :600-602
-      if (code & NCD_UPDATE_OWNER) acts.push_back({(int)s, "kube", "update-owner", dep_res(j), dep_name(j)});  // :550-552 / :612-614
+      if (code & NCD_UPDATE_DATA) acts.push_back({(int)sh, "kube", "update-data", dep_res(j), dep_name(j)});    // :539-541 / :600-602
+      if (code & NCD_UPDATE_OWNER) acts.push_back({(int)sh, "kube", "update-owner", dep_res(j), dep_name(j)});  // :550-552 / :612-614
     }
   }
   return render(acts, error, out, cap);
@@ -499,32 +533,77 @@ int64_t ncdh_plan_template(ncdh_checker* c, const char* ns, const char* name, ch
 
 int64_t ncdh_plan_workgroup(ncdh_checker* c, const char* ns, const char* name, char* out, uint64_t cap) {
   if (!c || !ns || !name) return fail("ncdh_plan_workgroup: null argument");
-  if (!c->scanned) return fail("ncdh_plan_workgroup: no scan yet");
+  const std::shared_ptr<const Snapshot> s = c->snapshot();
+  if (!s) return fail("ncdh_plan_workgroup: no scan yet");
   std::vector<Action> acts;
   const std::string k = store_key(NCD_KIND_WORKGROUP, std::string(ns) + "/" + name);
-  auto it = c->snap.find(k);
-  if (it == c->snap.end()) return render(acts, "", out, cap);  // :705-708
-  const size_t S = c->shards.size();
-  const uint64_t row0 = c->first_row[k];
-  for (size_t s = 0; s < S; ++s) {  // :720
-    const uint32_t code = c->codes[row0 * S + s];
-    if (code & NCD_UPDATE_DATA) acts.push_back({(int)s, "nexus", "update", "NexusAlgorithmWorkgroups", it->second.name});  // :725-727
-    if (code == NCD_CREATE) acts.push_back({(int)s, "nexus", "create", "NexusAlgorithmWorkgroups", it->second.name});      // :735-738
+  auto it = s->dir->by_key.find(k);
+  const size_t S = s->nshards;
+  {
+    std::shared_lock<std::shared_mutex> lk(c->cache_mu);
+    if (it == s->dir->by_key.end()) {
+      if (c->controller.changed_at(k) > s->clock) return -NCDH_STALE;
+      return render(acts, "", out, cap);  // :705-708
+    }
+    if (stale_for(c, *s, k, s->dir->objs[it->second].get(), 0, S)) return -NCDH_STALE;
+  }
+  const std::string& wname = s->dir->objs[it->second]->name;
+  for (size_t sh = 0; sh < S; ++sh) {  // :720
+    const uint32_t code = s->code(it->second, 0, (uint32_t)sh);
+    if (code & NCD_UPDATE_DATA) acts.push_back({(int)sh, "nexus", "update", "NexusAlgorithmWorkgroups", wname});  // :725-727
+    if (code == NCD_CREATE) acts.push_back({(int)sh, "nexus", "create", "NexusAlgorithmWorkgroups", wname});      // :735-738
   }
   return render(acts, "", out, cap);
 }
 
+int64_t ncdh_plan_adoption(ncdh_checker* c, const char* ns, const char* name, char* out, uint64_t cap) {
+  if (!c || !ns || !name) return fail("ncdh_plan_adoption: null argument");
+  const std::shared_ptr<const Snapshot> s = c->snapshot();
+  if (!s) return fail("ncdh_plan_adoption: no scan yet");
+  const std::string k = store_key(NCD_KIND_TEMPLATE, std::string(ns) + "/" + name);
+  auto it = s->dir->by_key.find(k);
+  std::string text;
+  {
+    std::shared_lock<std::shared_mutex> lk(c->cache_mu);
+    if (it == s->dir->by_key.end()) return c->controller.changed_at(k) > s->clock ? -NCDH_STALE : 0;
+    if (stale_for(c, *s, k, s->dir->objs[it->second].get(), 0, 0)) return -NCDH_STALE;
+  }
+  const ObjInfo& t = *s->dir->objs[it->second];
+  const size_t nsec = t.secrets.size(), ndeps = nsec + t.configmaps.size();
+  for (size_t j = 0; j < ndeps; ++j)  // :648 secrets, then :671 configmaps
+    if (s->needs_adoption(it->second, (uint32_t)j + 1))
+      text += std::string("kube\tupdate-owner\t") + (j < nsec ? "secrets" : "configmaps") + "\t" +
+              (j < nsec ? t.secrets[j] : t.configmaps[j - nsec]) + "\n";
+  if (out && text.size() <= cap) memcpy(out, text.data(), text.size());
+  return (int64_t)text.size();
+}
+
 int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap) {
-  if (!c || !c->scanned) return fail("ncdh_sweep_queue: no scan yet");
-  std::string s;
-  for (const std::string& line : c->dirty) s += line + "\n";
-  if (out && s.size() <= cap) memcpy(out, s.data(), s.size());
-  return (int64_t)s.size();
+  if (!c) return fail("ncdh_sweep_queue: null checker");
+  const std::shared_ptr<const Snapshot> s = c->snapshot();
+  if (!s) return fail("ncdh_sweep_queue: no scan yet");
+  // objects with a shard decision != SKIP, merged with templates that still have references to
+  // adopt on the controller cluster; both lists are ordered by controller index
+  std::string text;
+  size_t i = 0, j = 0;
+  uint32_t last = 0xFFFFFFFFu;
+  while (i < s->entries.size() || j < s->unadopted.size()) {
+    uint32_t obj;
+    if (j >= s->unadopted.size() || (i < s->entries.size() && s->entries[i].obj <= s->unadopted[j].obj)) obj = s->entries[i++].obj;
+    else obj = s->unadopted[j++].obj;
+    if (obj == last) continue;
+    last = obj;
+    const ObjInfo& f = *s->dir->objs[obj];
+    text += std::string(f.kind == NCD_KIND_TEMPLATE ? "template" : "workgroup") + "\t" + f.key + "\n";
+  }
+  if (out && text.size() <= cap) memcpy(out, text.data(), text.size());
+  return (int64_t)text.size();
 }
 
 int ncdh_upload_counts(ncdh_checker* c, int cluster, uint64_t* full, uint64_t* structural, uint64_t* values) {
   ClusterImage* img = c ? c->image(cluster) : nullptr;
   if (!img) return fail("ncdh_upload_counts: no such cluster");
+  std::shared_lock<std::shared_mutex> lk(c->cache_mu);
   if (full) *full = img->uploads_full;
   if (structural) *structural = img->uploads_structural;
   if (values) *values = img->uploads_values;
@@ -532,9 +611,18 @@ int ncdh_upload_counts(ncdh_checker* c, int cluster, uint64_t* full, uint64_t* s
 }
 
 int ncdh_last_counts(ncdh_checker* c, uint64_t* ndiff, uint64_t* decisions) {
-  if (!c || !c->scanned) return fail("ncdh_last_counts: no scan yet");
-  if (ndiff) *ndiff = c->ndiff;
-  if (decisions) *decisions = c->rows * c->shards.size();
+  if (!c) return fail("ncdh_last_counts: null checker");
+  const std::shared_ptr<const Snapshot> s = c->snapshot();
+  if (!s) return fail("ncdh_last_counts: no scan yet");
+  if (ndiff) *ndiff = s->entries.size();
+  if (decisions) *decisions = s->rows * s->nshards;
+  return 0;
+}
+
+int ncdh_last_timing(ncdh_checker* c, ncdh_scan_timing* out) {
+  if (!c || !out) return fail("ncdh_last_timing: null argument");
+  std::lock_guard<std::mutex> tl(c->timing_mu);
+  *out = c->timing;
   return 0;
 }
 
