@@ -570,10 +570,13 @@ int64_t ncdh_plan_adoption(ncdh_checker* c, const char* ns, const char* name, ch
   }
   const ObjInfo& t = *s->dir->objs[it->second];
   const size_t nsec = t.secrets.size(), ndeps = nsec + t.configmaps.size();
-  for (size_t j = 0; j < ndeps; ++j)  // :648 secrets, then :671 configmaps
+  for (size_t j = 0; j < ndeps; ++j) {  // :648 secrets, then :671 configmaps
+    // a reference the controller does not hold ends adoptReferences with an error (:649-653, :672-676)
+    if (s->nshards > 0 && s->code(it->second, (uint32_t)j + 1, 0) == NCD_ERR_MISSING_REF) break;
     if (s->needs_adoption(it->second, (uint32_t)j + 1))
       text += std::string("kube\tupdate-owner\t") + (j < nsec ? "secrets" : "configmaps") + "\t" +
               (j < nsec ? t.secrets[j] : t.configmaps[j - nsec]) + "\n";
+  }
   if (out && text.size() <= cap) memcpy(out, text.data(), text.size());
   return (int64_t)text.size();
 }

@@ -39,6 +39,8 @@ def load() -> C.CDLL:
         lib.oracle_scan.argtypes = [avp, C.POINTER(avp), C.c_int, C.POINTER(C.c_uint8), C.POINTER(Entry), C.c_int, C.POINTER(C.c_uint64)]
         lib.oracle_scan_timed.restype = C.c_double
         lib.oracle_scan_timed.argtypes = [avp, C.POINTER(avp), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_int, C.POINTER(C.c_uint64)]
+        lib.oracle_unadopted.restype = C.c_uint64
+        lib.oracle_unadopted.argtypes = [avp, C.POINTER(C.c_uint32), C.c_uint64]
         lib.oracle_h64.restype = C.c_uint64
         lib.oracle_h64.argtypes = [C.c_char_p, C.c_uint64]
         lib.oracle_sha256.restype = None
@@ -149,3 +151,13 @@ def sha256_arena(a) -> np.ndarray:
     out = np.zeros(max(a.nobj, 1) * 32, dtype=np.uint8)
     load().oracle_sha256_arena(a.payload.ctypes.data, a.rec_off.ctypes.data, a.rec_len.ctypes.data, a.nobj, out.ctypes.data)
     return out[: a.nobj * 32].reshape(a.nobj, 32)
+
+
+def unadopted(ctrl) -> np.ndarray:
+    """uint32[n, 2] of (template index, dep) whose controller-side dependent lacks the template's ownerReference."""
+    lib = load()
+    cv = ctrl.view()
+    n = lib.oracle_unadopted(C.byref(cv), None, 0)
+    out = np.zeros((max(n, 1), 2), dtype=np.uint32)
+    lib.oracle_unadopted(C.byref(cv), out.ctypes.data_as(C.POINTER(C.c_uint32)), n)
+    return out[:n]

@@ -116,3 +116,21 @@ def workgroup_sync(ctrl: Cluster, shards: List[Cluster], ns: str, name: str) -> 
         if sw is None:  # :735
             res.nexus_actions[s].append(("create", RESOURCE[WORKGROUP], name))  # :737
     return res
+
+
+def adopt_references(ctrl: Cluster, ns: str, name: str) -> List[Tuple[str, str, str]]:
+    """adoptReferences (controller.go:647-695): the Updates issued on the CONTROLLER cluster, in order — one
+    per referenced Secret, then ConfigMap, that no ownerReference ties to the template yet (isOwnedBy,
+    :637-645: UID only).  Stops at the first reference the controller does not hold (:649-653, :672-676)."""
+    t = ctrl.get((TEMPLATE, ns, name))
+    out: List[Tuple[str, str, str]] = []
+    if t is None:
+        return out
+    for kind, names in ((SECRET, t.secret_names), (CONFIGMAP, t.configmap_names)):
+        for n in names:
+            dep = ctrl.get((kind, ns, n))
+            if dep is None:
+                return out
+            if not any(uid == t.uid for _, uid in dep.owner_refs):  # :639
+                out.append(("update-owner", RESOURCE[kind], n))
+    return out

@@ -205,3 +205,31 @@ extern "C" double oracle_scan_timed(const ncd_arena_view* ctrl, const ncd_arena_
   if (bytes_out) *bytes_out = total_bytes.load() / (reps > 0 ? reps : 1);
   return std::chrono::duration<double>(t1 - t0).count() / (reps > 0 ? reps : 1);
 }
+
+// adoptReferences, controller.go:647-695, as a list: the (template, dependent) references whose
+// controller-side Secret / ConfigMap carries no ownerReference with the template's UID (isOwnedBy,
+// :637-645: UID only, any Kind).  A reference to an object the controller does not hold is not
+// listed (the handler errors out at :649-653 / :672-676).  out: pairs {obj, dep} in (obj, dep)
+// order, capacity cap; returns the number found.
+extern "C" uint64_t oracle_unadopted(const ncd_arena_view* c, uint32_t* out, uint64_t cap) {
+  const Store cstore = build_store(c);
+  uint64_t n = 0;
+  for (uint32_t t = 0; t < c->nobj; ++t) {
+    if (c->kind[t] != NCD_KIND_TEMPLATE) continue;
+    std::string_view tuid = sv(c, c->uid_off[t], c->uid_len[t]);
+    for (uint32_t d = c->dep_start[t]; d < c->dep_start[t + 1]; ++d) {
+      const uint32_t cd = store_get(cstore, c->dep_kind[d], sv(c, c->dep_key_off[d], c->dep_key_len[d]));
+      if (cd == 0xFFFFFFFFu) continue;
+      bool owned = false;
+      for (uint32_t o = c->own_start[cd]; o < c->own_start[cd + 1] && !owned; ++o)
+        owned = sv(c, c->own_uid_off[o], c->own_uid_len[o]) == tuid;  // :639
+      if (owned) continue;
+      if (n < cap) {
+        out[2 * n] = t;
+        out[2 * n + 1] = d - c->dep_start[t] + 1;
+      }
+      ++n;
+    }
+  }
+  return n;
+}

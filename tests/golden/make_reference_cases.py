@@ -36,18 +36,22 @@ def obj_json(o):
     }
 
 
-def case(name, source, sync, controller, shards, nexus, kube, error, pinned=True, note=""):
+def case(name, source, sync, controller, shards, nexus, kube, error, pinned=True, note="", adopt=()):
+    """adopt: the Updates adoptReferences issues on the CONTROLLER cluster (controller.go:647-695), as the Go
+    tests expect them through expectedControllerUpdateActions (controller_test.go:733-740); empty where a test
+    expects none."""
     return {
         "name": name, "source": source, "pinned": pinned, "note": note,
         "sync": {"kind": sync[0], "namespace": NS, "name": sync[1]},
         "controller": [obj_json(o) for o in controller],
         "shards": [[obj_json(o) for o in sh] for sh in shards],
-        "expect": {"error": error, "nexus": nexus, "kube": kube},
+        "expect": {"error": error, "nexus": nexus, "kube": kube, "adopt": [list(a) for a in adopt]},
     }
 
 
 def build():
     cases = []
+    BOTH = [["update-owner", S, "test-secret"], ["update-owner", C, "test-config"]]  # expectedControllerUpdateActions :733-740
     # provisionControllerResources (:747-752)
     secret, config = new_secret("test-secret", None), new_configmap("test-config", None)
     template = new_template("test", secret, config)
@@ -55,13 +59,14 @@ def build():
     # TestCreatesTemplate :800-843 — empty shard; expectShardActions(..., false) :835-839
     cases.append(case("TestCreatesTemplate", "controller_test.go:800-843", ("template", "test"),
                       [template, secret, config], [[]],
-                      nexus=[[["create", T, "test"]]], kube=[[["create", S, "test-secret"], ["create", C, "test-config"]]], error=False))
+                      nexus=[[["create", T, "test"]]], kube=[[["create", S, "test-secret"], ["create", C, "test-config"]]], error=False,
+                      adopt=BOTH))  # :833
 
     # TestDetectsRogue :846-886 — shard holds the un-owned secret (:863-865); template created, then
     # fail-fast: "no actions expected" for secret/configmap (:875-880); f.run(..., true) expects error
     cases.append(case("TestDetectsRogue", "controller_test.go:846-886", ("template", "test"),
                       [template, secret, config], [[secret]],
-                      nexus=[[["create", T, "test"]]], kube=[[]], error=True))
+                      nexus=[[["create", T, "test"]]], kube=[[]], error=True, adopt=BOTH))  # :882
 
     # TestHandlesNotExistingResource :889-909 — template not in the controller cache: nil, no actions
     cases.append(case("TestHandlesNotExistingResource", "controller_test.go:889-909", ("template", "test"),
@@ -90,14 +95,14 @@ def build():
                       [t1, t2, own1_s, own1_c], [[t1_shard, s_shard1, c_shard1]],
                       nexus=[[["create", T, "test2"]]],  # :1084
                       kube=[[["update-owner", S, "test-secret"], ["update-owner", C, "test-config"]]],  # :1085-1087
-                      error=False))
+                      error=False, adopt=BOTH))  # :1083: template2 is appended to the owners template1 left
 
     # TestTakesOwnership :1094-1140 — shard template differs in *bool MountDatadogSocket (:1099-1100)
     rogue_t = with_uid(new_template("test", secret, config, mount_datadog_socket=False), "")
     cases.append(case("TestTakesOwnership", "controller_test.go:1094-1140", ("template", "test"),
                       [template, secret, config], [[rogue_t]],
                       nexus=[[["update", T, "test"]]],  # expectShardActions(..., true) :1132-1136
-                      kube=[[["create", S, "test-secret"], ["create", C, "test-config"]]], error=False))
+                      kube=[[["create", S, "test-secret"], ["create", C, "test-config"]]], error=False, adopt=BOTH))  # :1131
 
     # TestCreatesWorkgroup :1193-1231
     wg = new_workgroup("test-workgroup", "shard0")
@@ -132,13 +137,14 @@ def build():
     sec_nil = Obj(K_SECRET, NS, "test-secret", "", BytesMap(None).wire(), owner_refs=[("NexusAlgorithmTemplate", "test")])
     cases.append(case("NilVsEmptyMap", "reflect.DeepEqual map rule (no reference test)", ("template", "test"),
                       [template, secret, config], [[tmpl_shard, sec_nil, with_owners(config, [tmpl_shard])]],
-                      nexus=[[]], kube=[[["update-data", S, "test-secret"]]], error=False, pinned=False, note="extrapolated"))
+                      nexus=[[]], kube=[[["update-data", S, "test-secret"]]], error=False, pinned=False, note="extrapolated",
+                      adopt=BOTH))
     # rogue on the SECOND shard: first shard's actions stand, the handler stops at the rogue (fail-fast :819-822)
     cases.append(case("RogueOnSecondShard_failfast", "controller.go:790-831 fail-fast (no reference test)", ("template", "test"),
                       [template, secret, config], [[], [tmpl_shard, secret], []],
                       nexus=[[["create", T, "test"]], [], []],
                       kube=[[["create", S, "test-secret"], ["create", C, "test-config"]], [], []],
-                      error=True, pinned=False, note="extrapolated: third shard is never visited"))
+                      error=True, pinned=False, note="extrapolated: third shard is never visited", adopt=BOTH))
     return {"generated_by": "tests/golden/make_reference_cases.py", "cases": cases}
 
 
