@@ -1,0 +1,312 @@
+"""The host layer (csrc/host: packer, DriftChecker, replay) on two backends.
+
+``fake``  the CPU test double of libncdrift (tests/fake_backend): arenas in plain memory, decisions from
+          the oracle.  Runs without a GPU, so the host logic — what goes into the arenas, which upload
+          path an event takes, the snapshot and its freshness rule, locking — is covered by the CPU suite.
+``gpu``   the real libncdhost.so over libncdrift.so: the same assertions with decisions from the GPU.
+
+The reference's handler tests (tests/golden/reference_cases.json, transcribed from controller_test.go)
+are run through both.
+"""
+import ctypes as C
+import os
+import random
+import subprocess
+import threading
+
+import pytest
+
+from nexus_configuration_controller_b200 import arena as A
+from nexus_configuration_controller_b200 import host as Hst
+from oracle import handlers as H
+from tests.reference_fixtures import NS, new_configmap, new_secret, new_template, new_workgroup, with_owners
+from tests.test_oracle_golden import CASES
+
+_fake = {}
+
+
+def fake_lib():
+    if "lib" not in _fake:
+        from tests.fake_backend.build import build
+
+        _fake["paths"] = build(tsan=False)
+        _fake["lib"] = Hst.bind(C.CDLL(_fake["paths"]["lib"]))
+    return _fake["lib"]
+
+
+@pytest.fixture(params=["fake", pytest.param("gpu", marks=pytest.mark.gpu)])
+def make_checker(request):
+    def make(nshards, mode=0):
+        return Hst.DriftChecker(nshards, mode=mode, lib=fake_lib() if request.param == "fake" else None)
+
+    return make
+
+
+def fill(checker, case):
+    for cluster, objs in [(-1, case["controller"])] + list(enumerate(case["shards"])):
+        for o in objs:
+            checker.add(cluster, o["kind"], o["namespace"], o["name"], o["uid"], bytes.fromhex(o["value_wire"]),
+                        [tuple(r) for r in o["owner_refs"]], o["secret_names"], o["configmap_names"])
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c["name"] for c in CASES])
+def test_reference_case_through_the_host_layer(make_checker, case):
+    """controller_test.go's handler tests: shard actions in order, error or not, and the controller-side
+    adoption Updates (expectedControllerUpdateActions, controller_test.go:733-740)."""
+    with make_checker(len(case["shards"])) as f:
+        fill(f, case)
+        f.scan()
+        sync = case["sync"]
+        plan = f.plan_template if sync["kind"] == "template" else f.plan_workgroup
+        nexus, kube, error = plan(sync["namespace"], sync["name"])
+        adopt = f.plan_adoption(sync["namespace"], sync["name"]) if sync["kind"] == "template" else []
+    exp = case["expect"]
+    assert (error is not None) == exp["error"], error
+    assert nexus == exp["nexus"]
+    assert kube == exp["kube"]
+    assert adopt == exp["adopt"]
+
+
+class Fleet:
+    """Controller + shards as plain object dicts, mirrored into a DriftChecker."""
+
+    def __init__(self, nshards, checker):
+        self.clusters = {c: {} for c in range(-1, nshards)}
+        self.f = checker
+
+    def put(self, cluster, o: H.Obj):
+        self.clusters[cluster][(o.kind, o.namespace, o.name)] = o
+        self.f.add(cluster, o.kind, o.namespace, o.name, o.uid, o.value, o.owner_refs, o.secret_names, o.configmap_names)
+
+    def remove(self, cluster, o: H.Obj):
+        del self.clusters[cluster][(o.kind, o.namespace, o.name)]
+        assert self.f.remove(cluster, o.kind, o.namespace, o.name)
+
+    def check(self):
+        self.f.scan()
+        ctrl = self.clusters[-1]
+        shards = [self.clusters[s] for s in range(len(self.clusters) - 1)]
+        dirty = []
+        for (kind, ns, name), o in ctrl.items():
+            adopt = []
+            if kind == H.TEMPLATE:
+                want = H.template_sync(ctrl, shards, ns, name)
+                nexus, kube, err = self.f.plan_template(ns, name)
+                adopt = self.f.plan_adoption(ns, name)
+                assert adopt == [list(a) for a in H.adopt_references(ctrl, ns, name)], name
+            elif kind == H.WORKGROUP:
+                want = H.workgroup_sync(ctrl, shards, ns, name)
+                nexus, kube, err = self.f.plan_workgroup(ns, name)
+            else:
+                continue
+            assert nexus == [[list(a) for a in sh] for sh in want.nexus_actions], name
+            assert kube == [[list(a) for a in sh] for sh in want.kube_actions], name
+            assert (err is not None) == (want.error is not None), name
+            if any(nexus) or any(kube) or err or adopt:
+                dirty.append(("template" if kind == H.TEMPLATE else "workgroup", f"{ns}/{name}"))
+        # the sweep feed names exactly the objects whose handler would do something: a shard write, an
+        # error, or an adoption Update on the controller cluster
+        assert sorted(self.f.sweep_queue()) == sorted(dirty)
+
+
+def test_resident_arenas_follow_informer_events(make_checker):
+    rng = random.Random(5)
+    with make_checker(2) as f:
+        fleet = Fleet(2, f)
+        templates, secrets, configs = [], [], []
+        for i in range(6):
+            t = new_template(f"algo-{i}", new_secret(f"sec-{i}", None), new_configmap(f"cfg-{i}", None), version_tag=f"v1.{i}")
+            templates.append(t)
+            # the controller's dependents already carry their template's ownerReference, except the last two
+            owner = t if i < 4 else None
+            secrets.append(new_secret(f"sec-{i}", owner, {"k": bytes(rng.getrandbits(8) for _ in range(50 + 40 * i))}))
+            configs.append(new_configmap(f"cfg-{i}", owner, {"k": "v" * (10 + 30 * i)}))
+        for o in secrets + configs + templates + [new_workgroup("wg", "shard0")]:
+            fleet.put(-1, o)
+        for s in (0, 1):
+            for i in range(6):
+                if (i + s) % 3 == 0:
+                    continue  # this shard lacks template i and its dependents
+                fleet.put(s, templates[i])
+                fleet.put(s, with_owners(secrets[i], [templates[i]]))
+                fleet.put(s, with_owners(configs[i], [templates[i]]))
+            fleet.put(s, new_workgroup("wg", "shard0"))
+        fleet.check()
+        assert f.upload_counts(-1) == (1, 0, 0) and f.upload_counts(0) == (1, 0, 0)
+        t = f.timing()
+        assert t["full_uploads"] == 3 and t["records_synced"] == 0 and t["h2d_bytes"] > 0 and t["events"] > 0
+
+        # UpdateFunc: values change, same keys and owners -> only those records are pushed
+        fleet.put(-1, new_secret("sec-1", templates[1], {"k": b"rotated"}))  # shorter: rewritten in place
+        fleet.put(-1, new_configmap("cfg-2", templates[2], {"k": "w" * 5000}))  # longer: appended
+        fleet.put(0, with_owners(new_secret("sec-1", None, {"k": b"rotated"}), [templates[1]]))  # shard 0 already converged
+        fleet.check()
+        assert f.upload_counts(-1) == (1, 0, 1) and f.upload_counts(0) == (1, 0, 1) and f.upload_counts(1) == (1, 0, 0)
+        t = f.timing()
+        assert (t["full_uploads"], t["structural_uploads"], t["records_synced"], t["events"]) == (0, 0, 3, 3)
+        # a put that changes nothing (the 30 s resync re-delivers every object) is no event at all
+        fleet.put(-1, new_secret("sec-1", templates[1], {"k": b"rotated"}))
+        fleet.check()
+        assert f.timing()["events"] == 0 and f.upload_counts(-1) == (1, 0, 1)
+
+        # AddFunc / DeleteFunc / re-owning: the small arrays are re-committed, old records stay put
+        fleet.put(1, templates[2])  # shard 1 gets the template it lacked
+        fleet.put(1, new_secret("sec-2", None))  # ... and an un-owned (rogue) secret of that name
+        fleet.remove(0, with_owners(configs[4], [templates[4]]))
+        fleet.put(0, with_owners(secrets[5], [templates[0]]))  # owned by another template only
+        fleet.check()
+        assert f.upload_counts(0) == (1, 1, 1) and f.upload_counts(1) == (1, 1, 0)
+        # adoption done on the controller cluster (what the handler's Update would cause): the feed shrinks
+        fleet.put(-1, with_owners(secrets[5], [templates[5]]))
+        fleet.put(-1, with_owners(configs[5], [templates[5]]))
+        fleet.check()
+
+        # growth beyond the arena's spare room -> one fresh full upload, then back to cheap syncs
+        for i in range(6, 40):
+            sec, cfg = new_secret(f"sec-{i}", None, {"k": b"x" * 3000}), new_configmap(f"cfg-{i}", None, {"k": "y" * 3000})
+            for o in (sec, cfg, new_template(f"algo-{i}", sec, cfg)):
+                fleet.put(-1, o)
+        fleet.check()
+        assert f.upload_counts(-1)[0] == 2
+        fleet.put(-1, new_secret("sec-7", None, {"k": b"z" * 3000}))
+        fleet.check()
+        full, structural, values = f.upload_counts(-1)
+        assert (full, values) == (2, 2)
+
+
+def test_a_snapshot_never_outlives_the_caches_it_was_made_from(make_checker):
+    """The reference's handlers read live caches (controller.go:766,792,507,516).  A Secret rotated after a
+    scan, a template added or removed after it, a shard copy changed after it: every one of them must be
+    answered 'stale', never with the old decision, until the next scan."""
+    case = next(c for c in CASES if c["name"] == "TwoShards_converged_and_drifted")
+    with make_checker(2) as f:
+        fill(f, case)
+        f.scan()
+        assert f.lookup(A.KIND_TEMPLATE, NS, "test", 1, 0) == A.SKIP
+        assert f.lookup(A.KIND_TEMPLATE, NS, "test", 1, 1) == A.UPDATE_DATA
+        ctrl_secret = next(o for o in case["controller"] if o["kind"] == A.KIND_SECRET)
+        owners = [tuple(r) for r in ctrl_secret["owner_refs"]]
+        # the same object delivered again (a resync) changes nothing: still fresh
+        f.add(-1, A.KIND_SECRET, NS, ctrl_secret["name"], ctrl_secret["uid"], bytes.fromhex(ctrl_secret["value_wire"]), owners)
+        assert f.lookup(A.KIND_TEMPLATE, NS, "test", 1, 0) == A.SKIP
+        # rotation on the controller cluster
+        rotated = new_secret(ctrl_secret["name"], None, {"secret.file": b"rotated-again"})
+        f.add(-1, A.KIND_SECRET, NS, rotated.name, "", rotated.value, owners)
+        for shard in (0, 1):
+            with pytest.raises(Hst.Stale):
+                f.lookup(A.KIND_TEMPLATE, NS, "test", 1, shard)
+            with pytest.raises(Hst.Stale):  # the template row too: one of its dependents moved
+                f.lookup(A.KIND_TEMPLATE, NS, "test", 0, shard)
+        with pytest.raises(Hst.Stale):
+            f.plan_template(NS, "test")
+        f.scan()
+        assert f.lookup(A.KIND_TEMPLATE, NS, "test", 1, 0) == A.UPDATE_DATA  # shard 0 was converged on the old value
+        # a change on ONE shard stales that shard's answers only
+        shard_cm = next(o for o in case["shards"][1] if o["kind"] == A.KIND_CONFIGMAP)
+        f.add(1, A.KIND_CONFIGMAP, NS, shard_cm["name"], "", new_configmap("x", None, {"other": "value"}).value,
+              [tuple(r) for r in shard_cm["owner_refs"]])
+        assert f.lookup(A.KIND_TEMPLATE, NS, "test", 2, 0) == A.SKIP
+        with pytest.raises(Hst.Stale):
+            f.lookup(A.KIND_TEMPLATE, NS, "test", 2, 1)
+        f.scan()
+        # a template created after the scan is not 'absent from the cache': it is not in the snapshot yet
+        assert f.lookup(A.KIND_TEMPLATE, NS, "newcomer", 0, 0) is None
+        t2 = new_template("newcomer", None, None)
+        f.add(-1, A.KIND_TEMPLATE, NS, "newcomer", t2.uid, t2.value)
+        with pytest.raises(Hst.Stale):
+            f.lookup(A.KIND_TEMPLATE, NS, "newcomer", 0, 0)
+        with pytest.raises(Hst.Stale):
+            f.plan_template(NS, "newcomer")
+        f.scan()
+        assert f.lookup(A.KIND_TEMPLATE, NS, "newcomer", 0, 0) == A.CREATE
+        # removed after the scan: not NOT_FOUND from the live cache mixed with a code from the old snapshot
+        assert f.remove(-1, A.KIND_TEMPLATE, NS, "newcomer")
+        with pytest.raises(Hst.Stale):
+            f.lookup(A.KIND_TEMPLATE, NS, "newcomer", 0, 0)
+        f.scan()
+        assert f.lookup(A.KIND_TEMPLATE, NS, "newcomer", 0, 0) is None
+        # the shard's copy of the TEMPLATE replaced (new UID): ownership of the dependents hangs on it
+        shard_t = next(o for o in case["shards"][0] if o["kind"] == A.KIND_TEMPLATE)
+        f.add(0, A.KIND_TEMPLATE, NS, "test", "another-uid", bytes.fromhex(shard_t["value_wire"]), [], shard_t["secret_names"],
+              shard_t["configmap_names"])
+        with pytest.raises(Hst.Stale):
+            f.lookup(A.KIND_TEMPLATE, NS, "test", 1, 0)
+        f.scan()
+        assert f.lookup(A.KIND_TEMPLATE, NS, "test", 1, 0) & A.UPDATE_OWNER
+
+
+def test_batched_events_equal_single_puts(make_checker):
+    case = next(c for c in CASES if c["name"] == "DataAndOwner_both")
+    with make_checker(1) as one, make_checker(1) as batch:
+        fill(one, case)
+        keep, evs = [], []
+        for cluster, objs in [(-1, case["controller"])] + list(enumerate(case["shards"])):
+            for o in objs:
+                evs.append(Hst.make_event(cluster, o["kind"], o["namespace"], o["name"], o["uid"], bytes.fromhex(o["value_wire"]),
+                                          [tuple(r) for r in o["owner_refs"]], o["secret_names"], o["configmap_names"], keep=keep))
+        # something to delete again, in the same batch
+        evs.append(Hst.make_event(0, A.KIND_SECRET, NS, "short-lived", "", new_secret("x", None).value, keep=keep))
+        evs.append(Hst.make_event(0, A.KIND_SECRET, NS, "short-lived", op=Hst.EV_DELETE, keep=keep))
+        batch.apply_events(evs, threads=3)
+        one.scan()
+        batch.scan()
+        assert batch.plan_template(NS, "test") == one.plan_template(NS, "test")
+        assert batch.counts() == one.counts()
+        # a malformed value stops the batch at that event: the ones before it are in, the rest is not
+        good = new_workgroup("wg-a", "shard0")
+        bad = [Hst.make_event(-1, A.KIND_WORKGROUP, NS, "wg-a", "u", good.value, keep=keep),
+               Hst.make_event(-1, A.KIND_WORKGROUP, NS, "wg-b", "u", b"\xff\x00garbage", keep=keep),
+               Hst.make_event(-1, A.KIND_WORKGROUP, NS, "wg-c", "u", good.value, keep=keep)]
+        with pytest.raises(Hst.HostError, match="event 1"):
+            batch.apply_events(bad, threads=2)
+        batch.scan()
+        assert batch.lookup(A.KIND_WORKGROUP, NS, "wg-a", 0, 0) == A.CREATE
+        assert batch.lookup(A.KIND_WORKGROUP, NS, "wg-c", 0, 0) is None
+
+
+def test_lookups_from_threads_while_another_thread_scans(make_checker):
+    """Python threads release the GIL inside the ctypes calls, so this really overlaps lookups, puts and
+    scans in the host layer (the native stress test below does it harder and under ThreadSanitizer)."""
+    case = next(c for c in CASES if c["name"] == "TwoShards_converged_and_drifted")
+    errors, stop = [], threading.Event()
+    with make_checker(2) as f:
+        fill(f, case)
+        f.scan()
+
+        def reader():
+            while not stop.is_set():
+                try:
+                    code = f.lookup(A.KIND_TEMPLATE, NS, "test", 2, 1)
+                    if code != A.UPDATE_DATA:
+                        errors.append(f"configmap on shard 1 answered {code}")
+                    f.plan_template(NS, "test")
+                except Hst.Stale:
+                    pass
+                except Exception as e:  # noqa: BLE001
+                    errors.append(repr(e))
+
+        threads = [threading.Thread(target=reader) for _ in range(3)]
+        for t in threads:
+            t.start()
+        wg = new_workgroup("wg", "shard0")
+        for k in range(30):
+            f.add(-1, A.KIND_WORKGROUP, NS, f"wg-{k % 4}", "u", wg.value)  # unrelated to template "test"
+            f.scan()
+        stop.set()
+        for t in threads:
+            t.join()
+    assert not errors, errors[:3]
+
+
+def test_host_layer_under_thread_sanitizer():
+    """csrc/host + the CPU backend double built with -fsanitize=thread: writers, scanners and readers at
+    once; any data race report fails the run (exit code 66), as does any wrong answer (exit code 1)."""
+    from tests.fake_backend.build import build
+
+    paths = build(tsan=True)
+    env = dict(os.environ, TSAN_OPTIONS="exitcode=66 halt_on_error=0", NCD_FAKE_SCAN_SLEEP_US="300")
+    plain = subprocess.run([paths["stress"], "80"], capture_output=True, text=True, timeout=300, env=env)
+    assert plain.returncode == 0, plain.stdout + plain.stderr
+    tsan = subprocess.run([paths["stress_tsan"], "40"], capture_output=True, text=True, timeout=600, env=env)
+    assert tsan.returncode == 0, (tsan.stdout + tsan.stderr)[-4000:]
+    assert "0 failures" in tsan.stdout
