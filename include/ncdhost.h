@@ -145,6 +145,25 @@ int ncdh_upload_counts(ncdh_checker* c, int cluster, uint64_t* full, uint64_t* s
 /* Number of diff-list entries and decisions of the last Scan. */
 int ncdh_last_counts(ncdh_checker* c, uint64_t* ndiff, uint64_t* decisions);
 
+/* ------------------------------------------------------------------ synthetic events
+ * Bench / test utility, not part of the drop-in surface (like ncd_synth_fill): informer events made
+ * from objects laid out like an arena (struct ncd_arena_view of ncdrift.h with HOST pointers, e.g.
+ * the synthetic generator's output downloaded with ncd_arena_download).  Names, UIDs,
+ * ownerReferences and dependent names come from `meta`; the value of object i is record i of
+ * `values` (NULL = meta; another cluster's arrays model "the shard received the controller's
+ * value") wrapped as a Go value in transport form: map[string][]byte{"data": rec} for a Secret,
+ * map[string]string{"data": rec} for a ConfigMap, struct{[]byte; string} for a template or
+ * workgroup spec.  salt != 0 flips one byte of every value at a position derived from (salt,
+ * kind, key): the same salt gives the same bytes for every cluster's copy of an object.
+ * obj_idx = NULL takes every object of meta.  The batch owns everything its events point to. */
+struct ncd_arena_view;
+typedef struct ncdh_event_batch ncdh_event_batch;
+int ncdh_batch_from_arrays(const struct ncd_arena_view* meta, const struct ncd_arena_view* values, int cluster,
+                           const uint32_t* obj_idx, uint64_t n, uint64_t salt, int threads, ncdh_event_batch** out);
+const ncdh_event* ncdh_batch_events(const ncdh_event_batch* b, uint64_t* n);
+uint64_t ncdh_batch_value_bytes(const ncdh_event_batch* b);
+void ncdh_batch_free(ncdh_event_batch* b);
+
 #ifdef __cplusplus
 }
 #endif

@@ -52,6 +52,10 @@ PROTOTYPES = {
     "ncdh_apply_events": (C.c_int, [VP, C.POINTER(Event), C.c_uint64, C.c_int]),
     "ncdh_plan_adoption": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
     "ncdh_last_timing": (C.c_int, [VP, C.POINTER(ScanTiming)]),
+    "ncdh_batch_from_arrays": (C.c_int, [C.POINTER(_ffi.ArenaView), C.POINTER(_ffi.ArenaView), C.c_int, _ffi.u32p, C.c_uint64, C.c_uint64, C.c_int, C.POINTER(VP)]),
+    "ncdh_batch_events": (C.POINTER(Event), [VP, C.POINTER(C.c_uint64)]),
+    "ncdh_batch_value_bytes": (C.c_uint64, [VP]),
+    "ncdh_batch_free": (None, [VP]),
     "ncdh_scan": (C.c_int, [VP]),
     "ncdh_lookup": (C.c_int, [VP, C.c_uint32, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint32)]),
     "ncdh_plan_template": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
@@ -125,6 +129,38 @@ def make_event(cluster: int, kind: int, namespace: str, name: str, uid: str = ""
     return e
 
 
+class EventBatch:
+    """ncdh_event_batch: synthetic informer events made from arena-shaped host arrays (bench / tests)."""
+
+    def __init__(self, meta, values=None, cluster: int = -1, obj_idx=None, salt: int = 0, threads: int = 0, lib=None):
+        """meta / values: HostArena (arena.py); obj_idx: uint32 indices or None for every object."""
+        import numpy as np
+
+        self.lib = lib if lib is not None else load()
+        mv = meta.view()
+        vv = values.view() if values is not None else None
+        idx = None if obj_idx is None else np.ascontiguousarray(obj_idx, dtype=np.uint32)
+        h = VP()
+        rc = self.lib.ncdh_batch_from_arrays(C.byref(mv), C.byref(vv) if vv is not None else None, cluster,
+                                             idx.ctypes.data_as(_ffi.u32p) if idx is not None else None,
+                                             0 if idx is None else len(idx), salt, threads, C.byref(h))
+        if rc != 0:
+            raise HostError("ncdh_batch_from_arrays: bad arrays or index")
+        self.h = h
+        n = C.c_uint64()
+        self.events = self.lib.ncdh_batch_events(self.h, C.byref(n))
+        self.n = n.value
+        self.value_bytes = self.lib.ncdh_batch_value_bytes(self.h)
+
+    def close(self):
+        if self.h:
+            self.lib.ncdh_batch_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+
 class DriftChecker:
     def __init__(self, nshards: int, device: int = 0, mode: int = 0, lib: Optional[C.CDLL] = None):
         """lib: another build of the same ABI (the CPU test double of tests/fake_backend); default libncdhost.so."""
@@ -139,8 +175,11 @@ class DriftChecker:
 
     def apply_events(self, events: Sequence[Event], threads: int = 0) -> None:
         """ncdh_apply_events: a batch of informer events, canonicalised on `threads` threads."""
-        arr = (Event * max(len(events), 1))(*events)
-        if self.lib.ncdh_apply_events(self.h, arr, len(events), threads) != 0:
+        if isinstance(events, EventBatch):
+            arr, n = events.events, events.n
+        else:
+            arr, n = (Event * max(len(events), 1))(*events), len(events)
+        if self.lib.ncdh_apply_events(self.h, arr, n, threads) != 0:
             raise self._e()
 
     def timing(self) -> dict:

@@ -310,3 +310,76 @@ def test_host_layer_under_thread_sanitizer():
     tsan = subprocess.run([paths["stress_tsan"], "40"], capture_output=True, text=True, timeout=600, env=env)
     assert tsan.returncode == 0, (tsan.stdout + tsan.stderr)[-4000:]
     assert "0 failures" in tsan.stdout
+
+
+@pytest.mark.parametrize("seed", [11, 12])
+def test_synthetic_event_batches_decide_like_the_oracle_on_the_raw_arenas(make_checker, request, seed):
+    """ncdh_batch_from_arrays wraps every record of arena-shaped arrays as a Go value; equality of the wrapped
+    values is equality of the records, so after the events went through canonicaliser, packer and scan every
+    decision must equal the oracle's on the raw arenas — shared dependents, dangling references, rogue and
+    foreign owners, per-shard object order included.  Then churn: new controller values by salt, shards follow."""
+    import oracle
+    from tests.helpers import random_clusters
+
+    lib = fake_lib() if "fake" in request.node.name else None
+    ctrl, shards = random_clusters(seed, n_templates=14, n_shards=3)
+
+    def check(f, ctrl_h, shard_hs):
+        want, _ = oracle.scan(ctrl_h, shard_hs)
+        row = 0
+        for i in range(ctrl_h.nobj):
+            kind = int(ctrl_h.kind[i])
+            if kind not in (A.KIND_TEMPLATE, A.KIND_WORKGROUP):
+                continue
+            ns, name = ctrl_h.key(i).split("/", 1)
+            ndeps = int(ctrl_h.dep_start[i + 1] - ctrl_h.dep_start[i]) if kind == A.KIND_TEMPLATE else 0
+            for dep in range(ndeps + 1):
+                for s in range(len(shard_hs)):
+                    assert f.lookup(kind, ns, name, dep, s) == want[row, s], (name, dep, s)
+                row += 1
+        assert row == want.shape[0]
+
+    with make_checker(3) as f:
+        batches = [Hst.EventBatch(ctrl, cluster=-1, threads=2, lib=lib)] + [Hst.EventBatch(h, cluster=s, threads=2, lib=lib) for s, h in enumerate(shards)]
+        for b in batches:
+            f.apply_events(b, threads=2)
+        f.scan()
+        check(f, ctrl, shards)
+        # churn on the controller: a third of its objects get a new value (one byte, same length)
+        rng = random.Random(seed)
+        idx = sorted(rng.sample(range(ctrl.nobj), ctrl.nobj // 3))
+        upd = Hst.EventBatch(ctrl, cluster=-1, obj_idx=idx, salt=7, threads=2, lib=lib)
+        f.apply_events(upd)
+        f.scan()
+        t = f.timing()
+        assert t["full_uploads"] == 0 and t["structural_uploads"] == 0
+        changed = [i for i in idx if ctrl.rec_len[i] > 0]
+        assert t["records_synced"] == len(changed) and t["events"] == len(changed)
+        # the oracle sees the same change when the raw records are patched the same way
+        # (ncdh_batch_from_arrays: byte h % len of the record ^= 1 + (h >> 32) % 255, h = mix(salt * P ^ fnv(kind, key)))
+        M = (1 << 64) - 1
+
+        def mix(x):
+            x = (x + 0x9E3779B97F4A7C15) & M
+            x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & M
+            x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & M
+            return x ^ (x >> 31)
+
+        def patch(h, i, salt):
+            key = h.key(i).encode()
+            k = 0xCBF29CE484222325 ^ int(h.kind[i])
+            for b in key:
+                k = ((k ^ b) * 0x100000001B3) & M
+            v = mix(((salt * 0x100000001B3) & M) ^ k)
+            ln = int(h.rec_len[i])
+            if ln:
+                h.payload[int(h.rec_off[i]) + v % ln] ^= 1 + (v >> 32) % 255
+
+        import copy
+
+        ctrl2 = copy.deepcopy(ctrl)
+        for i in idx:
+            patch(ctrl2, i, 7)
+        check(f, ctrl2, shards)
+        for b in batches + [upd]:
+            b.close()
