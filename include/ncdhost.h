@@ -145,6 +145,13 @@ int ncdh_upload_counts(ncdh_checker* c, int cluster, uint64_t* full, uint64_t* s
 /* Number of diff-list entries and decisions of the last Scan. */
 int ncdh_last_counts(ncdh_checker* c, uint64_t* ndiff, uint64_t* decisions);
 
+/* A checksum of the last Scan's diff list that does not depend on arena layout: the sum over the
+ * entries of mix(fnv1a(kind digit + "namespace/name") ^ dep * 0x9E3779B185EBCA87 ^ shard *
+ * 0xC2B2AE3D27D4EB4F ^ code * 0x165667B19E3779F9) (mix = the MurmurHash3 64-bit finaliser).  Two
+ * implementations fed the same events can be compared by it (bench.py compares the GPU arm with the
+ * CPU arm's sweep over parsed values).  dirty_objects (optional) = objects with at least one entry. */
+int ncdh_diff_digest(ncdh_checker* c, uint64_t* digest, uint64_t* dirty_objects);
+
 /* ------------------------------------------------------------------ synthetic events
  * Bench / test utility, not part of the drop-in surface (like ncd_synth_fill): informer events made
  * from objects laid out like an arena (struct ncd_arena_view of ncdrift.h with HOST pointers, e.g.

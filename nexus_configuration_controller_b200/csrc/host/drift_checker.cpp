@@ -622,6 +622,35 @@ int ncdh_last_counts(ncdh_checker* c, uint64_t* ndiff, uint64_t* decisions) {
   return 0;
 }
 
+int ncdh_diff_digest(ncdh_checker* c, uint64_t* digest, uint64_t* dirty_objects) {
+  if (!c || !digest) return fail("ncdh_diff_digest: null argument");
+  const std::shared_ptr<const Snapshot> s = c->snapshot();
+  if (!s) return fail("ncdh_diff_digest: no scan yet");
+  auto fmix = [](uint64_t x) {
+    x ^= x >> 33;
+    x *= 0xff51afd7ed558ccdull;
+    x ^= x >> 33;
+    x *= 0xc4ceb9fe1a85ec53ull;
+    return x ^ (x >> 33);
+  };
+  uint64_t sum = 0, dirty = 0, kh = 0;
+  uint32_t last = 0xFFFFFFFFu;
+  for (const ncd_entry& e : s->entries) {
+    if (e.obj != last) {  // the key hash is per object: entries of one object are adjacent
+      const ObjInfo& f = *s->dir->objs[e.obj];
+      kh = 0xcbf29ce484222325ull;
+      for (unsigned char ch : store_key(f.kind, f.key)) kh = (kh ^ ch) * 0x100000001b3ull;
+      last = e.obj;
+      ++dirty;
+    }
+    sum += fmix(kh ^ ((uint64_t)e.dep * 0x9E3779B185EBCA87ull) ^ ((uint64_t)e.shard * 0xC2B2AE3D27D4EB4Full) ^
+                ((uint64_t)e.code * 0x165667B19E3779F9ull));
+  }
+  *digest = sum;
+  if (dirty_objects) *dirty_objects = dirty;
+  return 0;
+}
+
 int ncdh_last_timing(ncdh_checker* c, ncdh_scan_timing* out) {
   if (!c || !out) return fail("ncdh_last_timing: null argument");
   std::lock_guard<std::mutex> tl(c->timing_mu);

@@ -56,6 +56,7 @@ PROTOTYPES = {
     "ncdh_batch_events": (C.POINTER(Event), [VP, C.POINTER(C.c_uint64)]),
     "ncdh_batch_value_bytes": (C.c_uint64, [VP]),
     "ncdh_batch_free": (None, [VP]),
+    "ncdh_diff_digest": (C.c_int, [VP, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "ncdh_scan": (C.c_int, [VP]),
     "ncdh_lookup": (C.c_int, [VP, C.c_uint32, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_uint32)]),
     "ncdh_plan_template": (C.c_int64, [VP, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]),
@@ -181,6 +182,13 @@ class DriftChecker:
             arr, n = (Event * max(len(events), 1))(*events), len(events)
         if self.lib.ncdh_apply_events(self.h, arr, n, threads) != 0:
             raise self._e()
+
+    def diff_digest(self) -> Tuple[int, int]:
+        """(layout-independent checksum of the last scan's diff list, objects with at least one entry)."""
+        d, n = C.c_uint64(), C.c_uint64()
+        if self.lib.ncdh_diff_digest(self.h, C.byref(d), C.byref(n)) != 0:
+            raise self._e()
+        return d.value, n.value
 
     def timing(self) -> dict:
         t = ScanTiming()

@@ -41,6 +41,14 @@ def load() -> C.CDLL:
         lib.oracle_scan_timed.argtypes = [avp, C.POINTER(avp), C.c_int, C.POINTER(C.c_uint8), C.c_int, C.c_int, C.POINTER(C.c_uint64)]
         lib.oracle_unadopted.restype = C.c_uint64
         lib.oracle_unadopted.argtypes = [avp, C.POINTER(C.c_uint32), C.c_uint64]
+        lib.oracle_fleet_create.restype = C.c_void_p
+        lib.oracle_fleet_create.argtypes = [C.c_int]
+        lib.oracle_fleet_destroy.restype = None
+        lib.oracle_fleet_destroy.argtypes = [C.c_void_p]
+        lib.oracle_fleet_apply.restype = C.c_int
+        lib.oracle_fleet_apply.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int]
+        lib.oracle_fleet_sweep.restype = C.c_double
+        lib.oracle_fleet_sweep.argtypes = [C.c_void_p, C.c_int] + [C.POINTER(C.c_uint64)] * 4
         lib.oracle_h64.restype = C.c_uint64
         lib.oracle_h64.argtypes = [C.c_char_p, C.c_uint64]
         lib.oracle_sha256.restype = None
@@ -161,3 +169,27 @@ def unadopted(ctrl) -> np.ndarray:
     out = np.zeros((max(n, 1), 2), dtype=np.uint32)
     lib.oracle_unadopted(C.byref(cv), out.ctypes.data_as(C.POINTER(C.c_uint32)), n)
     return out[:n]
+
+
+class Fleet:
+    """Every cluster's cache as parsed objects + the handlers' sweep over them (oracle/go_values.cpp "fleet"):
+    the CPU arm of the steady-state bench.  Events are ncdh_event arrays (include/ncdhost.h)."""
+
+    def __init__(self, nshards: int):
+        self.lib = load()
+        self.h = C.c_void_p(self.lib.oracle_fleet_create(nshards))
+
+    def close(self):
+        if self.h:
+            self.lib.oracle_fleet_destroy(self.h)
+            self.h = None
+
+    def apply(self, events_ptr, n: int, threads: int = 1) -> None:
+        if self.lib.oracle_fleet_apply(self.h, C.cast(events_ptr, C.c_void_p), n, threads) != 0:
+            raise ValueError(self.lib.oracle_values_error().decode())
+
+    def sweep(self, threads: int = 1):
+        """(seconds, decisions, diff entries, dirty objects, diff-list checksum)."""
+        v = [C.c_uint64() for _ in range(4)]
+        sec = self.lib.oracle_fleet_sweep(self.h, threads, *[C.byref(x) for x in v])
+        return (sec,) + tuple(x.value for x in v)

@@ -268,3 +268,190 @@ int64_t oracle_canon(const uint8_t* v, uint64_t vlen, uint8_t* out, uint64_t cap
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ fleet: the handlers over parsed values
+// The CPU arm of the steady-state bench and a second, independent statement of the decisions:
+// every cluster's informer cache as a map of PARSED objects (what a lister holds), informer events
+// applied to it, and a sweep that walks every template and workgroup of the controller cache over
+// every shard the way templateSyncHandler / workgroupSyncHandler do (controller.go:790-831 with
+// :504-626 and :484-502; :720-745) — lister lookups by key and reflect.DeepEqual on the value
+// trees, no canonical bytes, no arenas.  Events arrive in the same ncdh_event records the GPU arm's
+// host layer takes (include/ncdhost.h is included for that struct alone).
+#include <atomic>
+#include <unordered_map>
+
+#include "../include/ncdhost.h"
+#include "../include/ncdrift.h"
+
+namespace {
+
+struct FleetObj {
+  uint32_t kind = 0;
+  std::string key, uid;
+  Node value;
+  std::vector<std::pair<std::string, std::string>> owners;  // (Kind, UID)
+  std::vector<std::string> deps;                            // "ns/name", secrets first
+  uint32_t nsecrets = 0;
+};
+using FleetStore = std::unordered_map<std::string, FleetObj>;  // (kind digit + "ns/name") -> object
+
+inline std::string fkey(uint32_t kind, const std::string& key) { return std::string(1, (char)('0' + kind)) + key; }
+
+inline uint64_t fmix(uint64_t x) {
+  x ^= x >> 33;
+  x *= 0xff51afd7ed558ccdull;
+  x ^= x >> 33;
+  x *= 0xc4ceb9fe1a85ec53ull;
+  return x ^ (x >> 33);
+}
+inline uint64_t key_fnv(const std::string& skey) {
+  uint64_t h = 0xcbf29ce484222325ull;
+  for (unsigned char c : skey) h = (h ^ c) * 0x100000001b3ull;
+  return h;
+}
+// The checksum both arms compute over their diff lists: order independent, keyed by NAME (not by
+// arena index), so two implementations with different layouts can be compared.
+inline uint64_t entry_digest(const std::string& skey, uint32_t dep, uint32_t shard, uint32_t code) {
+  return fmix(key_fnv(skey) ^ ((uint64_t)dep * 0x9E3779B185EBCA87ull) ^ ((uint64_t)shard * 0xC2B2AE3D27D4EB4Full) ^
+              ((uint64_t)code * 0x165667B19E3779F9ull));
+}
+
+// isMissingOwnership, controller.go:484-502
+uint32_t fleet_ownership(const FleetObj& dep, const FleetObj* shard_tmpl) {
+  if (dep.owners.empty()) return NCD_ERR_ROGUE;  // :494-499
+  if (shard_tmpl)
+    for (const auto& o : dep.owners)  // :489-492
+      if (o.first == "NexusAlgorithmTemplate" && o.second == shard_tmpl->uid) return 0;
+  return NCD_UPDATE_OWNER;  // :501
+}
+
+}  // namespace
+
+struct oracle_fleet {
+  FleetStore controller;
+  std::vector<FleetStore> shards;
+};
+
+extern "C" {
+
+oracle_fleet* oracle_fleet_create(int nshards) {
+  oracle_fleet* f = new oracle_fleet();
+  f->shards.resize(nshards < 0 ? 0 : nshards);
+  return f;
+}
+void oracle_fleet_destroy(oracle_fleet* f) { delete f; }
+
+// Applies informer events in order: values are parsed (in parallel, the analogue of an informer
+// decoding an object), then stored.  Returns 0, or -1 on a malformed value (nothing applied).
+int oracle_fleet_apply(oracle_fleet* f, const ncdh_event* ev, uint64_t n, int nthreads) {
+  if (nthreads < 1) nthreads = 1;
+  std::vector<FleetObj> objs(n);
+  std::atomic<int> bad{0};
+  auto work = [&](uint64_t lo, uint64_t hi) {
+    for (uint64_t i = lo; i < hi; ++i) {
+      const ncdh_event& e = ev[i];
+      FleetObj& o = objs[i];
+      o.kind = e.kind;
+      o.key = std::string(e.ns) + "/" + e.name;
+      if (e.op != NCDH_EV_PUT) continue;
+      try {
+        o.value = parse_all(e.value, e.value_len);
+      } catch (const std::exception& ex) {
+        g_err = ex.what();
+        bad.store(1);
+        return;
+      }
+      o.uid = e.uid;
+      for (int k = 0; k < e.nowners; ++k) o.owners.emplace_back(e.owner_kinds[k], e.owner_uids[k]);
+      for (int k = 0; k < e.nsecrets; ++k) o.deps.push_back(std::string(e.ns) + "/" + e.secret_names[k]);
+      for (int k = 0; k < e.nconfigmaps; ++k) o.deps.push_back(std::string(e.ns) + "/" + e.configmap_names[k]);
+      o.nsecrets = (uint32_t)e.nsecrets;
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; ++t) th.emplace_back(work, n * t / nthreads, n * (t + 1) / nthreads);
+  for (auto& x : th) x.join();
+  if (bad.load()) return -1;
+  for (uint64_t i = 0; i < n; ++i) {
+    const int c = ev[i].cluster;
+    if (c < -1 || c >= (int)f->shards.size()) return -1;
+    FleetStore& st = c < 0 ? f->controller : f->shards[c];
+    const std::string k = fkey(objs[i].kind, objs[i].key);
+    if (ev[i].op == NCDH_EV_PUT) st[k] = std::move(objs[i]);
+    else st.erase(k);
+  }
+  return 0;
+}
+
+// One resync sweep: every template (with its dependents) and workgroup of the controller cache on
+// every shard.  Returns the seconds the sweep took; decisions = (row, shard) pairs decided, ndiff =
+// those != SKIP, dirty = templates / workgroups with at least one, digest = checksum of the diff list.
+double oracle_fleet_sweep(oracle_fleet* f, int nthreads, uint64_t* decisions, uint64_t* ndiff, uint64_t* dirty, uint64_t* digest) {
+  if (nthreads < 1) nthreads = 1;
+  std::vector<const FleetObj*> heads;
+  for (const auto& kv : f->controller)
+    if (kv.second.kind == NCD_KIND_TEMPLATE || kv.second.kind == NCD_KIND_WORKGROUP) heads.push_back(&kv.second);
+  const size_t S = f->shards.size();
+  std::atomic<uint64_t> t_dec{0}, t_diff{0}, t_dirty{0}, t_dig{0};
+  const auto t0 = std::chrono::steady_clock::now();
+  auto work = [&](size_t lo, size_t hi) {
+    uint64_t dec = 0, nd = 0, dirt = 0, dig = 0;
+    for (size_t h = lo; h < hi; ++h) {
+      const FleetObj& t = *heads[h];
+      const std::string tk = fkey(t.kind, t.key);
+      bool any = false;
+      for (size_t s = 0; s < S; ++s) {  // :790 / :720
+        const FleetStore& sh = f->shards[s];
+        auto sti = sh.find(tk);  // :792 / :722
+        const FleetObj* st = sti == sh.end() ? nullptr : &sti->second;
+        uint32_t code = !st ? (uint32_t)NCD_CREATE : (deep_equal(st->value, t.value) ? (uint32_t)NCD_SKIP : (uint32_t)NCD_UPDATE_DATA);  // :795 / :725
+        ++dec;
+        if (code) {
+          ++nd;
+          any = true;
+          dig += entry_digest(tk, 0, (uint32_t)s, code);
+        }
+        if (t.kind != NCD_KIND_TEMPLATE) continue;
+        for (size_t j = 0; j < t.deps.size(); ++j) {  // :505 / :567
+          const uint32_t dk = j < t.nsecrets ? NCD_KIND_SECRET : NCD_KIND_CONFIGMAP;
+          const std::string k = fkey(dk, t.deps[j]);
+          auto cdi = f->controller.find(k);  // :507 / :569
+          if (cdi == f->controller.end()) {
+            code = NCD_ERR_MISSING_REF;  // :509-514 / :571-576
+          } else {
+            auto sdi = sh.find(k);  // :516 / :578
+            if (sdi == sh.end()) {
+              code = NCD_CREATE;  // :518-520 / :580-582
+            } else {
+              const uint32_t own = fleet_ownership(sdi->second, st);  // :529 / :591
+              if (own == NCD_ERR_ROGUE) code = NCD_ERR_ROGUE;
+              else code = (deep_equal(cdi->second.value, sdi->second.value) ? 0u : (uint32_t)NCD_UPDATE_DATA) | own;  // :539 / :600
+            }
+          }
+          ++dec;
+          if (code) {
+            ++nd;
+            any = true;
+            dig += entry_digest(tk, (uint32_t)j + 1, (uint32_t)s, code);
+          }
+        }
+      }
+      if (any) ++dirt;
+    }
+    t_dec += dec;
+    t_diff += nd;
+    t_dirty += dirt;
+    t_dig += dig;
+  };
+  std::vector<std::thread> th;
+  for (int t = 0; t < nthreads; ++t) th.emplace_back(work, heads.size() * t / nthreads, heads.size() * (t + 1) / nthreads);
+  for (auto& x : th) x.join();
+  const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  if (decisions) *decisions = t_dec.load();
+  if (ndiff) *ndiff = t_diff.load();
+  if (dirty) *dirty = t_dirty.load();
+  if (digest) *digest = t_dig.load();
+  return sec;
+}
+
+}  // extern "C"

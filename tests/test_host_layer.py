@@ -383,3 +383,38 @@ def test_synthetic_event_batches_decide_like_the_oracle_on_the_raw_arenas(make_c
         check(f, ctrl2, shards)
         for b in batches + [upd]:
             b.close()
+
+
+@pytest.mark.parametrize("seed", [21, 22, 23])
+def test_host_layer_and_the_sweep_over_parsed_values_agree(make_checker, request, seed):
+    """Two statements of the same sweep fed the same events: the host layer (canonical bytes, arenas, scan)
+    and the oracle's fleet (parsed value trees, map lookups, reflect.DeepEqual restated) must produce the
+    same diff list — compared by count, by dirty objects and by the layout-independent checksum."""
+    import oracle
+    from tests.helpers import random_clusters
+
+    lib = fake_lib() if "fake" in request.node.name else None
+    ctrl, shards = random_clusters(seed, n_templates=16, n_shards=3)
+    _, want_ents = oracle.scan(ctrl, shards)
+    fleet = oracle.Fleet(3)
+    with make_checker(3) as f:
+        rng = random.Random(seed)
+        for step in range(3):
+            if step == 0:
+                batches = [Hst.EventBatch(ctrl, cluster=-1, lib=lib)] + [Hst.EventBatch(h, cluster=s, lib=lib) for s, h in enumerate(shards)]
+            else:  # churn: some controller objects change, some shard objects change
+                batches = [Hst.EventBatch(ctrl, cluster=-1, obj_idx=rng.sample(range(ctrl.nobj), ctrl.nobj // 4), salt=step, lib=lib)]
+                batches += [Hst.EventBatch(h, cluster=s, obj_idx=rng.sample(range(h.nobj), h.nobj // 5), salt=10 + step, lib=lib)
+                            for s, h in enumerate(shards)]
+            for b in batches:
+                f.apply_events(b, threads=2)
+                fleet.apply(b.events, b.n, threads=2)
+            f.scan()
+            _, decisions, ndiff, dirty, digest = fleet.sweep(threads=3)
+            assert f.counts() == (ndiff, decisions)
+            assert f.diff_digest() == (digest, dirty)
+            if step == 0:
+                assert ndiff == len(want_ents)
+            for b in batches:
+                b.close()
+    fleet.close()
