@@ -10,13 +10,23 @@ fits one GPU: 1M mixed objects (templates, Secrets, ConfigMaps, canonical length
 At N>1 the same 1M objects are partitioned by ncd_keyhash(template key) % N (strong scaling,
 as the north_star states it) and the per-GPU diff lists are exchanged with ONE NCCL all-gather.
 
-A step = one full scan (join + compare + classify + compaction [+ all-gather]) over inputs
+A step = one full scan (join + compare + classify + compaction [+ exchange]) over inputs
 already resident in HBM.  Inputs (>= 9.8 GB per GPU) are far larger than the 126 MB L2, so no
-flush is needed between steps.  `e2e` is the same metric through the C ABI with HOST (pinned)
-arenas: every step uploads the arenas, builds their index, scans, and reads the diff list back.
+flush is needed between steps.
 
---impl reference times the CPU oracle (a port of the reference's lookup + DeepEqual walk; the Go
-reference cannot be built in this image) on the box's host cores, on a bounded sample.
+`e2e` is the same metric through the API the controller would call — the DriftChecker of
+INTEGRATION.md (libncdhost.so): per step one interval's informer events (1 % of the controller's
+objects changed, every shard catching up with the previous interval) are canonicalised and applied,
+the changed records are packed into pinned memory and pulled over PCIe, every pair is scanned, the
+diff list is read back, the sweep queue and a few lookups are served; host wall clock around the
+whole call sequence, with the pack / upload / scan split and the bytes moved (bench_steady.py).
+`e2e_by_churn` repeats it at 0.1 %, 1 %, 10 % and 100 % churn, `e2e_cold` is the stateless extreme
+(every arena uploaded and indexed again every step through the C ABI), `break_even_churn` says where
+the GPU arm stops beating the CPU arm.
+
+--impl reference times the CPU arm: the reference's handlers restated over parsed objects (map
+lookups + reflect.DeepEqual; the Go reference cannot be built in this image), fed the same events,
+on the box's host cores, on a bounded sample.
 """
 from __future__ import annotations
 
@@ -193,58 +203,73 @@ def deep_equal_walk_baseline(mean_len: int, threads: int, budget_s: float = 2.0)
                       f"oracle DeepEqual on parsed values, no lookups"}
 
 
+STEADY_LEVELS = [0.001, 0.01, 0.1, 1.0]
+HEADLINE_CHURN = 0.01
+
+
+def sized_groups(want: int, shards: int, copies: float) -> int:
+    """Shrinks a sample so that `copies` host copies of it fit comfortably in the box's free memory."""
+    import bench_steady as BS
+
+    per_group = 3 * 8704 * (1 + shards)
+    fit = int(0.6 * BS.mem_available_gb() * 1e9 / (per_group * copies))
+    return max(1000, min(want, fit))
+
+
 class CpuArm:
-    """The oracle (a port of the reference's lookup + DeepEqual walk) on a bounded sample of
-    `workload`.  The sample is produced by the same generator as the GPU arm's input (on the GPU,
-    then copied to host memory); only the CPU walk is timed."""
+    """The reference's walk restated on the CPU (the Go reference cannot be built here), on a bounded sample of
+    `workload`, fed the SAME informer events as the GPU arm's end-to-end leg (bench_steady.py): every cluster's
+    cache as parsed objects, events parsed and stored, then a full sweep of every template and workgroup over
+    every shard with map lookups and reflect.DeepEqual on the parsed values (oracle fleet).  The sample comes
+    from the same generator as the GPU arm's input (on the GPU, then copied to host memory)."""
 
-    def __init__(self, workload: str, sample_groups: int, threads: int):
-        import numpy as np
+    def __init__(self, workload: str, sample_groups: int, threads: int, with_gpu_check: bool = True):
+        import bench_steady as BS
 
-        import oracle
-        from nexus_configuration_controller_b200.drift import Context
+        self.BS, self.workload, self.threads = BS, workload, threads
+        _, S = make_cfg(workload)
+        self.groups = sized_groups(sample_groups, S, 3.0)
+        cfg, self.S = BS.converged_cfg(make_cfg, workload, self.groups)
+        self.device = int(os.environ.get("LOCAL_RANK", "0"))
+        self.hosts = BS.download_clusters(self.device, cfg, self.S)
+        ctrl = self.hosts[0]
+        self.algo = int(ctrl.rec_len[: ctrl.nobj].astype("uint64").sum()) * (1 + self.S)
+        self.mean_len = max(1, self.algo // max(1, ctrl.nobj * (1 + self.S)))
+        self.cpu = BS.SteadyCpu(self.hosts, threads)
+        # the GPU arm on the same sample and the same events, outside any timed region: parity of the two arms
+        self.gpu = BS.SteadyGpu(self.hosts, self.device, threads) if with_gpu_check else None
+        self.rows = None
 
-        self.oracle, self.np = oracle, np
-        self.workload, self.groups, self.threads = workload, sample_groups, threads
-        cfg, S = make_cfg(workload, groups=sample_groups)
-        self.S = S
-        with Context(int(os.environ.get("LOCAL_RANK", "0"))) as ctx:
-            ca = ctx.synth_arena(cfg, -1)
-            sas = [ctx.synth_arena(cfg, s) for s in range(S)]
-            d = ctx.scan(ca, sas, 0)
-            self.gpu_codes = d.codes().copy()
-            d.close()
-            self.ch, self.shs = ca.download(), [s.download() for s in sas]
-            for a in sas + [ca]:
-                a.close()
-        self.algo = int(self.ch.rec_len[: self.ch.nobj].astype("uint64").sum()) + sum(
-            int(s.rec_len[: s.nobj].astype("uint64").sum()) for s in self.shs
-        )
-        sec, codes, _ = oracle.scan_timed(self.ch, self.shs, threads, 1)  # warm-up + parity
-        self.identical = bool(np.array_equal(codes, self.gpu_codes))
-        self.pairs = codes.size
-        self.sweep_s = sec
-        mean_len = max(1, self.algo // max(1, self.ch.nobj * (1 + self.S)))
-        self.walk = deep_equal_walk_baseline(int(mean_len), threads)
+    def run(self, levels=None, steps_for=None) -> dict:
+        BS = self.BS
+        self.rows = BS.run_levels(self.gpu, self.cpu, self.hosts, levels or STEADY_LEVELS, steps_for or BS.default_steps, self.threads)
+        return self.rows
 
-    def time(self, budget_s: float):
-        reps = max(1, min(200, int(budget_s / max(self.sweep_s, 1e-4))))
-        sec, _, _ = self.oracle.scan_timed(self.ch, self.shs, self.threads, reps)
-        return sec, reps
-
-    def report(self, sec: float, reps: int) -> dict:
-        return {
-            "value": self.pairs / sec,
-            "unit": UNIT,
-            "cores": self.threads,
-            "kind": "port",
-            "sample": f"{self.workload}: first {self.groups} groups = {self.ch.nobj} objects x {self.S} shards, "
-                      f"{self.algo / 1e9:.2f} GB, {reps} sweep(s) of {sec * 1e3:.1f} ms; hash-map lookup + memcmp of "
-                      f"canonical records (an upper bound on a reflect.DeepEqual walk)",
-            "gb_per_s": self.algo / sec / 1e9,
-            "identical_to_gpu": self.identical,
-            "deep_equal_walk": self.walk,
+    def report(self) -> dict:
+        rows = self.rows
+        head = rows[HEADLINE_CHURN]
+        ctrl = self.hosts[0]
+        out = {
+            "value": head["cpu_decisions_per_s"], "unit": UNIT, "cores": self.threads, "kind": "port",
+            "sample": f"{self.workload} shapes, converged fleet: first {self.groups} groups = {ctrl.nobj} objects x {self.S} shards "
+                      f"({self.algo / 1e9:.2f} GB of values as parsed objects); a step = apply one interval's informer events "
+                      f"({HEADLINE_CHURN:.1%} of the controller's objects changed + the shards catching up: {head['events_per_step']} events) "
+                      f"then sweep every template / workgroup over every shard: map lookups + reflect.DeepEqual restated on parsed values; "
+                      f"median of {head['steps']} steps of {head['cpu_ms_per_step']:.1f} ms",
+            "ms_per_step": head["cpu_ms_per_step"],
+            "gb_per_s": self.algo / (head["cpu_ms_per_step"] / 1e3) / 1e9,
+            "by_churn": {f"{c:g}": {"decisions_per_s": r["cpu_decisions_per_s"], "ms_per_step": r["cpu_ms_per_step"],
+                                    "events_per_step": r["events_per_step"]} for c, r in rows.items()},
         }
+        if self.gpu is not None:
+            out["identical_to_gpu"] = all(r.get("identical_to_cpu", False) for r in rows.values())
+        out["deep_equal_walk"] = deep_equal_walk_baseline(int(self.mean_len), self.threads)
+        return out
+
+    def close(self):
+        self.cpu.close()
+        if self.gpu is not None:
+            self.gpu.close()
 
 
 def run_reference(args):
@@ -254,23 +279,23 @@ def run_reference(args):
     threads = os.cpu_count() or 1
     t0 = time.time()
     arm = CpuArm(args.workload, args.cpu_sample_groups, threads)
-    per_step = []
-    for i in range(args.warmup + args.steps):
-        sec, reps = arm.time(budget_s=1.0)
-        if i >= args.warmup:
-            per_step.append(sec)
-    sec = sum(per_step) / len(per_step)
-    base = arm.report(sec, reps)
+    # --steps / --warmup are honoured for the headline churn; the other levels keep their short defaults
+    import bench_steady as BS
+
+    arm.run(steps_for=lambda c: (args.steps, args.warmup) if c == HEADLINE_CHURN else BS.default_steps(c))
+    base = arm.report()
+    arm.close()
     value = base["value"]
     _, S = make_cfg(args.workload)
     line = {
         "impl": "reference",
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "ms_per_step": base["ms_per_step"], "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic",
         "config": {"workload": args.workload, "shards": S,
-                   "note": "CPU port of the reference walk on all host threads (the Go reference cannot be built here: "
-                           "no Go toolchain, dependencies un-vendored); a step = one sweep over the bounded sample"},
+                   "note": "CPU port of the reference's handlers on all host threads (the Go reference cannot be built here: "
+                           "no Go toolchain, dependencies un-vendored); a step = one interval's informer events applied to the "
+                           "caches + one resync sweep over the bounded sample, the same step the GPU arm's e2e leg makes"},
         "cpu_baseline": base,
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": time.time() - t0,
@@ -442,22 +467,46 @@ def run_ours(args):
     for a in sas + [ca]:
         a.close()
     if not args.skip_e2e:
-        # the resident e2e steps accumulate drift, so their exchange buffer is sized generously
-        e2e_cap = 1 << 18
         if world > 1:
+            e2e_cap = 1 << 18
             e2e_send = torch.zeros(M.buffer_words(e2e_cap), dtype=torch.int32, device=f"cuda:{local}")
             e2e_recv = torch.zeros(world * e2e_send.numel(), dtype=torch.int32, device=f"cuda:{local}")
             gather = lambda d: M.gather_diffs(d, e2e_send, e2e_recv, ext, e2e_cap)  # noqa: E731
         else:
             gather = lambda d: None  # noqa: E731
-        e2e_cold, e2e_res = run_e2e(ctx, args, mode & 0xFF, world, rank, dist, ext, gather)
+        e2e_cold = run_e2e_cold(ctx, args, mode & 0xFF, world, rank, dist, ext, gather)
         if rank == 0:
-            result["e2e"] = e2e_cold
-            result["e2e_resident"] = e2e_res
+            result["e2e_cold"] = e2e_cold
     ctx.close()
+    if not args.skip_e2e:
+        steady = run_steady(args, world, rank, local, dist)
+        if rank == 0:
+            head = steady["rows"][HEADLINE_CHURN]
+            result["e2e"] = {
+                "value": head["decisions_per_s"], "unit": UNIT, "h2d_bytes_per_step": head["h2d_bytes_per_step"],
+                "d2h_bytes_per_step": head["d2h_bytes_per_step"], "ms_per_step": head["ms_per_step"], "churn": HEADLINE_CHURN,
+                "events_per_step": head["events_per_step"], "value_bytes_per_step": head["value_bytes_per_step"],
+                "split_ms": head["split_ms"], "diff_entries": head["diff_entries"],
+                "api": "DriftChecker of INTEGRATION.md (libncdhost.so over libncdrift.so): ncdh_apply_events -> ncdh_scan -> "
+                       "ncdh_sweep_queue + ncdh_lookup",
+                "sample": steady["sample"],
+            }
+            result["e2e_by_churn"] = {f"{c:g}": r for c, r in steady["rows"].items()}
+            result["e2e_first_scan"] = steady["first_scan"]
     if rank == 0 and world == 1 and not args.skip_cpu:
         arm = CpuArm(args.workload, args.cpu_sample_groups, os.cpu_count() or 1)
-        result["cpu_baseline"] = arm.report(*arm.time(args.cpu_budget_s))
+        arm.run()
+        result["cpu_baseline"] = arm.report()
+        arm.close()
+        if "e2e_by_churn" in result:
+            import bench_steady as BS
+
+            cpu_by = result["cpu_baseline"]["by_churn"]
+            rows = list(result["e2e_by_churn"].values())
+            # level by level against the CPU arm at the same churn (the CPU arm's own cost grows with churn too)
+            ratios = {k: r["decisions_per_s"] / cpu_by[k]["decisions_per_s"] for k, r in result["e2e_by_churn"].items() if k in cpu_by}
+            result["e2e_vs_cpu_by_churn"] = {k: round(v, 3) for k, v in ratios.items()}
+            result["break_even_churn"] = BS.break_even(rows, result["cpu_baseline"]["value"])
     if rank == 0:
         print(json.dumps(result), flush=True)
     if dist:
@@ -465,60 +514,29 @@ def run_ours(args):
     return 0
 
 
-def run_e2e(ctx, args, mode, world, rank, dist, ext, gather):
-    """The same metric through the C ABI with HOST (pinned) arenas, two ways:
-
-    cold      every step uploads every arena of this rank (H2D), rebuilds its index, scans and reads
-              the diff list back: what a controller without resident state would pay per sweep.
-    resident  arenas stay in HBM; every step the host rewrites a small fraction of the records in the
-              pinned arrays (what informer UpdateFunc events amount to between two resyncs), the
-              library pulls just those records over PCIe (ncd_arena_sync_records), scans, and the
-              diff list is read back.
-    Timed with CUDA events on the library's stream around the whole region (host gaps included),
-    barrier on both sides, max over ranks.
-    """
-    import numpy as np
+def run_e2e_cold(ctx, args, mode, world, rank, dist, ext, gather):
+    """The same metric through the C ABI with HOST (pinned) arenas and NO resident state: every step uploads
+    every arena of this rank (H2D), rebuilds its index, scans and reads the diff list back — what a controller
+    that kept nothing on the GPU would pay per sweep (100 % churn without even the canonicaliser).  Timed with
+    CUDA events on the library's stream around the whole region (host gaps included), barrier on both sides,
+    max over ranks."""
     import torch
 
-    from nexus_configuration_controller_b200 import arena as A
     from nexus_configuration_controller_b200._ffi import check
     from nexus_configuration_controller_b200.drift import Arena
 
     cfg, S = make_cfg(args.workload, groups=args.e2e_groups, part_mod=world if world > 1 else 0, part_rem=rank)
     hosts = []
-    slack = 1 << 20
     for r in range(-1, S):
         a = ctx.synth_arena(cfg, r)
         c = a.counts()
-        h = Arena(ctx, c.payload_bytes + slack, c.nobj, c.aux_bytes, c.nowner, c.ndep, device_only=False)
+        h = Arena(ctx, c.payload_bytes, c.nobj, c.aux_bytes, c.nowner, c.ndep, device_only=False)
         v = h.host_view()
         check(ctx.lib.ncd_arena_download(a.handle, C.byref(v)))  # fills the pinned host arrays
         hosts.append((h, c))
         a.close()
     h2d_cold = sum(c.payload_bytes + c.aux_bytes + c.nobj * 29 + 8 + c.nowner * 9 + c.ndep * 9 for _, c in hosts)
     arenas = [h for h, _ in hosts]
-
-    def timed(step, reps, warm):
-        """Median step time: the box is shared (PCIe and host memory traffic of other tenants shows up
-        as single slow steps), every step is bracketed by its own events on the library's stream."""
-        for _ in range(warm):
-            out = step()
-        torch.cuda.synchronize()
-        if dist:
-            dist.barrier()
-        evs = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
-        evs[0].record(ext)
-        for i in range(reps):
-            out = step()
-            evs[i + 1].record(ext)
-        torch.cuda.synchronize()
-        per_step = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(reps))
-        ms = per_step[len(per_step) // 2]
-        if dist:
-            t = torch.tensor([ms], device=f"cuda:{ctx.device}")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, out
 
     def total(x):
         if not dist:
@@ -538,7 +556,24 @@ def run_e2e(ctx, args, mode, world, rank, dist, ext, gather):
         return st, ents
 
     reps = max(1, args.e2e_steps)
-    cold_ms, (st, ents) = timed(cold_step, reps, 2)
+    for _ in range(1):
+        out = cold_step()
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(reps + 1)]
+    evs[0].record(ext)
+    for i in range(reps):
+        out = cold_step()
+        evs[i + 1].record(ext)
+    torch.cuda.synchronize()
+    per_step = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(reps))
+    cold_ms = per_step[len(per_step) // 2]
+    if dist:
+        t = torch.tensor([cold_ms], device=f"cuda:{ctx.device}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        cold_ms = float(t.item())
+    st, ents = out
     pairs, algo = total(st.pairs), total(st.algo_bytes)
     result = {
         "value": pairs / (cold_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(total(h2d_cold)),
@@ -547,59 +582,64 @@ def run_e2e(ctx, args, mode, world, rank, dist, ext, gather):
                   f"host arenas{' split over ' + str(world) + ' ranks by key hash' if world > 1 else ''}; "
                   f"step = H2D of every arena + index build + scan + diff list D2H; median of {reps} steps",
     }
-
-    # resident: rewrite ~0.1 % of the records of every cluster per step, pull them, scan
-    rng = np.random.default_rng(1234 + rank)
-    views = [h.host_arrays() for h in arenas]
-    pulled = [0]
-
-    step_mode = [mode]
-
-    def resident_step():
-        pulled[0] = 0
-        batch = []
-        for h, (hh, c), arr in zip(arenas, hosts, views):
-            k = max(1, int(c.nobj * args.resident_fraction))
-            idx = rng.choice(c.nobj, size=k, replace=False).astype(np.uint32)
-            off = arr["rec_off"][idx].astype(np.int64)
-            ln = arr["rec_len"][idx].astype(np.int64)
-            pos = off + (rng.integers(0, 1 << 62, size=k) % np.maximum(ln, 1))
-            arr["payload"][pos] ^= 0x5A  # the event: one byte of the value changed, same length
-            batch.append(idx)
-            pulled[0] += int(((ln + 15) // 16 * 16).sum()) + 4 * k
-        # every cluster's rewritten records in one call: one PCIe round trip for the sweep
-        ctx.sync_records_many(arenas, batch, [c.payload_bytes for _, c in hosts])
-        d = ctx.scan(arenas[0], arenas[1:], step_mode[0])
-        gather(d)
-        ents = d.entries()
-        st = ctx.last_stats()
-        d.close()
-        return st, ents
-
-    res_ms, (st, ents) = timed(resident_step, max(3, reps), 2)
-    # the same steps with cached digests (NCD-H64): the sync re-hashes the rewritten records, the
-    # scan compares digests; verdicts are probabilistic (2^-64 per differing pair), so this is
-    # reported beside the exact figure, never instead of it
-    cached = {}
-    for name, hmode in (("hash64", A.MODE_HASH64), ("sha256", A.MODE_SHA256)):
-        step_mode[0] = hmode
-        resident_step()  # the first scan in a hash mode computes every digest once
-        hms, (_, hents) = timed(resident_step, max(3, reps), 2)
-        cached[name] = {"value": pairs / (hms / 1e3), "unit": UNIT, "ms_per_step": hms, "diff_entries_last_step": int(total(len(hents)))}
-    result_res = {
-        "value": pairs / (res_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(total(pulled[0])),
-        "d2h_bytes_per_step": int(total(ents.nbytes + 64)), "ms_per_step": res_ms, "gb_per_s": algo / (res_ms / 1e3) / 1e9,
-        "diff_entries_last_step": int(total(len(ents))),
-        "sample": f"same sample, arenas resident in HBM; step = host rewrites {args.resident_fraction:.2%} of the records of every "
-                  f"cluster in the pinned arrays + ncd_arenas_sync_records (only those records cross PCIe) + scan + diff list D2H",
-        "cached_digests": dict(cached["hash64"], mode="hash64", sha256=cached["sha256"],
-                               note="same steps with the verdict taken from digests the arenas keep (the sync re-hashes only the "
-                                    "rewritten records, the scan is join + classify): NCD-H64 leaves 2^-64 per differing pair, the "
-                                    "sha256 entry is the cryptographic variant; both reported beside the byte-compare figure"),
-    }
     for h in arenas:
         h.close()
-    return result, result_res
+    return result
+
+
+def run_steady(args, world, rank, local, dist):
+    """The end-to-end legs: steady-state sweeps through the DriftChecker API at several churn levels (bench_steady.py)."""
+    import torch
+
+    import bench_steady as BS
+
+    _, S0 = make_cfg(args.workload)
+    threads = max(1, (os.cpu_count() or 1) // world)
+    groups = sized_groups(args.e2e_groups, S0, 4.5 * world)
+    cfg, S = BS.converged_cfg(make_cfg, args.workload, groups, part_mod=world if world > 1 else 0, part_rem=rank)
+    hosts = BS.download_clusters(local, cfg, S)
+    for h in hosts[1:]:
+        h.payload = __import__("numpy").zeros(16, dtype="uint8")  # shard events take their values from the controller's records
+    arm = BS.SteadyGpu(hosts, local, threads)
+    if dist:  # the ranks sweep in lockstep: one tiny all-reduce per step stands for the exchange of the diff lists
+        flag = torch.zeros(1, device=f"cuda:{local}")
+        step0 = arm.step
+
+        def step(batches):
+            t0 = time.perf_counter()
+            _, tm, n = step0(batches)
+            dist.all_reduce(flag)
+            torch.cuda.synchronize()
+            return time.perf_counter() - t0, tm, n
+
+        arm.step = step
+        dist.barrier()
+    levels = [c for c in STEADY_LEVELS if c <= args.max_churn]
+    rows = BS.run_levels(arm, None, hosts, levels, BS.default_steps, threads)
+    decisions, nobj = float(arm.decisions), float(hosts[0].nobj)
+    first = dict(arm.first, load_s=round(arm.load_s, 2))
+    arm.close()
+    if dist:
+        t = torch.tensor([decisions, nobj], dtype=torch.float64, device=f"cuda:{local}")
+        dist.all_reduce(t)
+        decisions, nobj = [float(x) for x in t.tolist()]
+        for c, r in rows.items():  # max over ranks of the step time, sums of the bytes
+            t = torch.tensor([r["ms_per_step"]], dtype=torch.float64, device=f"cuda:{local}")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            r["ms_per_step"] = float(t.item())
+            t = torch.tensor([float(r[k]) for k in ("h2d_bytes_per_step", "d2h_bytes_per_step", "events_per_step", "value_bytes_per_step", "diff_entries", "records_synced")],
+                             dtype=torch.float64, device=f"cuda:{local}")
+            dist.all_reduce(t)
+            for k, v in zip(("h2d_bytes_per_step", "d2h_bytes_per_step", "events_per_step", "value_bytes_per_step", "diff_entries", "records_synced"), t.tolist()):
+                r[k] = int(v)
+            r["decisions_per_s"] = decisions / (r["ms_per_step"] / 1e3)
+    sample = (f"{args.workload} shapes, converged fleet: first {groups} groups = {int(nobj)} objects x {S} shards resident behind the "
+              f"DriftChecker{' split over ' + str(world) + ' ranks by key hash' if world > 1 else ''}; a step = one interval's informer "
+              f"events (a fraction `churn` of the controller's objects changed + every shard catching up with the previous interval) "
+              f"applied through ncdh_apply_events (values canonicalised on {threads} threads), then ncdh_scan (changed records packed into "
+              f"pinned memory, pulled over PCIe, full scan of every pair, diff list to the host), ncdh_sweep_queue and 64 ncdh_lookup; "
+              f"host wall clock, median over the steps")
+    return {"rows": rows, "sample": sample, "first_scan": first}
 
 
 def main():
@@ -614,11 +654,10 @@ def main():
     ap.add_argument("--mode", default="direct", choices=["direct", "hash64", "sha256", "xxh64"])
     ap.add_argument("--groups", type=int, default=None, help="override the number of template groups (smaller runs)")
     ap.add_argument("--gather-cap", type=int, default=None, help="entries per rank in the all-gather buffer (default: sized from a first scan)")
-    ap.add_argument("--cpu-sample-groups", type=int, default=6000)
-    ap.add_argument("--cpu-budget-s", type=float, default=12.0)
+    ap.add_argument("--cpu-sample-groups", type=int, default=30000, help="template groups of the CPU arm's sample")
+    ap.add_argument("--max-churn", type=float, default=1.0, help="largest churn level of the end-to-end legs")
     ap.add_argument("--e2e-groups", type=int, default=100000)
     ap.add_argument("--e2e-steps", type=int, default=5)
-    ap.add_argument("--resident-fraction", type=float, default=0.001, help="records rewritten per cluster per resident e2e step")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--allow-short-warmup", action="store_true")

@@ -86,7 +86,7 @@ Upload ClusterImage::prepare_structural(ncd_ctx* ctx, int threads, uint64_t* h2d
   if (!fits) {
     // a fresh arena with room to grow; every record is placed again, compactly
     arena.reset();
-    payload_cap = compact + compact / 2 + (64 << 10);
+    payload_cap = compact + compact / 4 + (64 << 10);  // pinned and device memory both: a quarter of spare room
     nobj_cap = objs.size() + objs.size() / 2 + 16;
     aux_cap = aux + aux / 2 + 1024;
     nowner_cap = nowner + nowner / 2 + 16;
