@@ -9,6 +9,8 @@ ncd_arena_view ClusterImage::host_view() {
   return v;
 }
 
+void ClusterImage::bind_arena() { host_payload = arena.a ? host_view().payload : nullptr; }
+
 // Brings the pinned host arrays up to date with the image and says what has to be uploaded.
 // Caller holds the cache lock exclusively; no GPU work here except creating a larger arena.
 // h2d: bytes that upload will move.  tomb_floor: removals at or before this stamp are part of the
@@ -16,7 +18,7 @@ ncd_arena_view ClusterImage::host_view() {
 Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uint64_t* h2d) {
   for (auto it = tomb.begin(); it != tomb.end();)
     it = it->second <= tomb_floor ? tomb.erase(it) : std::next(it);
-  if (structural) {  // forget dead objects (their payload becomes unreferenced until the next full commit)
+  if (structural) {  // forget dead objects (their payload becomes unreferenced until the arena is re-made)
     bool any_dead = false;
     for (const CachedObject& o : objs) any_dead = any_dead || !o.live;
     if (any_dead) {
@@ -27,30 +29,37 @@ Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uin
       objs.swap(keep);
       index.clear();
       for (size_t i = 0; i < objs.size(); ++i) index.emplace(store_key(objs[i].info->kind, objs[i].info->key), i);
+      ++layout;
     }
     dirty.clear();
   }
-  if (!arena.a || structural) return prepare_structural(ctx, threads, h2d);
+  if (!arena.a || structural || force_full) return prepare_structural(ctx, threads, h2d);
   if (dirty.empty()) return Upload::None;
 
   // same objects, some values changed: rewrite those records, to be pushed alone
   uint64_t append = 0;
   for (uint32_t i : dirty)
-    if (pad16(objs[i].canon.size()) > objs[i].rec_cap) append += pad16(objs[i].canon.size());
-  if (payload_used + append > payload_cap) {  // no room to append: start over with a larger arena
-    arena.reset();
+    if (pad16(objs[i].len) > objs[i].rec_cap) append += pad16(objs[i].len);
+  if (payload_used + append > payload_cap) {  // no room to append: move to a larger arena
     dirty.clear();
-    return prepare_structural(ctx, threads, h2d);
+    return prepare_structural(ctx, threads, h2d, /*regrow=*/true);
   }
   ncd_arena_view v = host_view();
   for (uint32_t i : dirty) {  // offsets first (serial), bytes after (parallel)
     CachedObject& o = objs[i];
     assign(o, /*force_append=*/false);
     v.rec_off[i] = (uint64_t)o.rec_off;
-    v.rec_len[i] = (uint32_t)o.canon.size();
-    *h2d += pad16(o.canon.size()) + 4;
+    v.rec_len[i] = o.len;
+    *h2d += pad16(o.len) + 4;
   }
-  parallel_for(dirty.size(), threads, 64, [&](size_t k) { copy_record(v, objs[dirty[k]]); });
+  parallel_for(dirty.size(), threads, 64, [&](size_t k) {
+    CachedObject& o = objs[dirty[k]];
+    copy_record(v, o, o.pending);
+  });
+  for (uint32_t i : dirty) {  // the arena holds the bytes now: the events' memory is released
+    objs[i].pending = nullptr;
+    objs[i].hold.reset();
+  }
   pending_changed.swap(dirty);
   dirty.clear();
   ++uploads_values;
@@ -62,13 +71,14 @@ void ClusterImage::upload(Upload what) {
   if (what == Upload::Full) {
     if (ncd_arena_commit(arena.a, objs_committed, payload_used, aux_used, own_used, dep_used) != NCD_OK)
       throw std::runtime_error(ncd_err("ncd_arena_commit"));
+    force_full = false;
   } else if (what == Upload::Structural) {
     if (ncd_arena_recommit(arena.a, objs_committed, payload_used, aux_used, own_used, dep_used, dirty_from) != NCD_OK)
       throw std::runtime_error(ncd_err("ncd_arena_recommit"));
   }
 }
 
-Upload ClusterImage::prepare_structural(ncd_ctx* ctx, int threads, uint64_t* h2d) {
+Upload ClusterImage::prepare_structural(ncd_ctx* ctx, int threads, uint64_t* h2d, bool regrow) {
   uint64_t aux = 0, nowner = 0, ndep = 0, append = 0, compact = 0;
   for (const CachedObject& o : objs) {
     const ObjInfo& f = *o.info;
@@ -78,38 +88,47 @@ Upload ClusterImage::prepare_structural(ncd_ctx* ctx, int threads, uint64_t* h2d
     for (const auto& s : f.secrets) aux += f.key.size() + s.size();  // "namespace/" + name <= key + name
     for (const auto& s : f.configmaps) aux += f.key.size() + s.size();
     ndep += f.secrets.size() + f.configmaps.size();
-    compact += pad16(o.canon.size());
-    if (o.rec_off < 0 || o.value_dirty) append += pad16(o.canon.size());
+    compact += pad16(o.len);
+    if (o.pending) append += pad16(o.len);
   }
-  const bool fits = arena.a && objs.size() <= nobj_cap && aux <= aux_cap && nowner <= nowner_cap && ndep <= ndep_cap &&
+  const bool fits = arena.a && !regrow && objs.size() <= nobj_cap && aux <= aux_cap && nowner <= nowner_cap && ndep <= ndep_cap &&
                     payload_used + append <= payload_cap;
+  ArenaHandle old;  // the arena being left: the only copy of the records that are not pending
+  const uint8_t* old_payload = host_payload;
   if (!fits) {
     // a fresh arena with room to grow; every record is placed again, compactly
-    arena.reset();
-    payload_cap = compact + compact / 4 + (64 << 10);  // pinned and device memory both: a quarter of spare room
-    nobj_cap = objs.size() + objs.size() / 2 + 16;
-    aux_cap = aux + aux / 2 + 1024;
-    nowner_cap = nowner + nowner / 2 + 16;
-    ndep_cap = ndep + ndep / 2 + 16;
-    if (ncd_arena_create(ctx, payload_cap, nobj_cap, aux_cap, nowner_cap, ndep_cap, NCD_ARENA_HOST_PINNED, &arena.a) != NCD_OK)
-      throw std::runtime_error(ncd_err("ncd_arena_create"));
+    ncd_arena* fresh = nullptr;
+    const uint64_t p_cap = compact + compact / 4 + (64 << 10);  // pinned and device memory both: a quarter of spare room
+    const uint64_t n_cap = objs.size() + objs.size() / 2 + 16, a_cap = aux + aux / 2 + 1024, o_cap = nowner + nowner / 2 + 16,
+                   d_cap = ndep + ndep / 2 + 16;
+    if (ncd_arena_create(ctx, p_cap, n_cap, a_cap, o_cap, d_cap, NCD_ARENA_HOST_PINNED, &fresh) != NCD_OK)
+      throw std::runtime_error(ncd_err("ncd_arena_create"));  // the old arena, if any, is untouched
+    old.a = arena.a;
+    arena.a = fresh;
+    payload_cap = p_cap;
+    nobj_cap = n_cap;
+    aux_cap = a_cap;
+    nowner_cap = o_cap;
+    ndep_cap = d_cap;
     payload_used = 0;
-    for (CachedObject& o : objs) o.rec_off = -1;
+    bind_arena();
   }
   ncd_arena_view v = host_view();
-  dirty_from = payload_used;
-  write_all(v, threads);
+  dirty_from = fits ? payload_used : 0;
+  write_all(v, threads, old.a ? old_payload : nullptr, !fits);
+  old.reset();
   objs_committed = objs.size();
-  *h2d += (payload_used - dirty_from) + aux_used + objs_committed * 29 + 8 + own_used * 9 + dep_used * 9;
-  ++(fits ? uploads_structural : uploads_full);
+  const bool full = !fits || force_full;
+  *h2d += (full ? payload_used : payload_used - dirty_from) + aux_used + objs_committed * 29 + 8 + own_used * 9 + dep_used * 9;
+  ++(full ? uploads_full : uploads_structural);
   structural = false;
   dirty.clear();
-  return fits ? Upload::Structural : Upload::Full;
+  return full ? Upload::Full : Upload::Structural;
 }
 
 // Gives o a place in the payload: where it already is if it fits, else at the end.
 void ClusterImage::assign(CachedObject& o, bool force_append) {
-  const uint64_t need = pad16(o.canon.size());
+  const uint64_t need = pad16(o.len);
   if (o.rec_off < 0 || need > o.rec_cap || force_append) {
     o.rec_off = (int64_t)payload_used;
     o.rec_cap = need;
@@ -117,16 +136,17 @@ void ClusterImage::assign(CachedObject& o, bool force_append) {
   }
 }
 
-void ClusterImage::copy_record(ncd_arena_view& v, CachedObject& o) {
-  const uint64_t need = pad16(o.canon.size());
-  memcpy(v.payload + o.rec_off, o.canon.data(), o.canon.size());
-  memset(v.payload + o.rec_off + o.canon.size(), 0, need - o.canon.size());
-  o.value_dirty = false;
+void ClusterImage::copy_record(ncd_arena_view& v, CachedObject& o, const uint8_t* src) {
+  const uint64_t need = pad16(o.len);
+  memcpy(v.payload + o.rec_off, src, o.len);
+  memset(v.payload + o.rec_off + o.len, 0, need - o.len);
 }
 
-// Every per-object array from scratch (arena layout: ncdrift.h "arenas"); records that are
-// already on the device and did not change keep their place, the others are appended.
-void ClusterImage::write_all(ncd_arena_view& v, int threads) {
+// Every per-object array from scratch (arena layout: ncdrift.h "arenas").  Same arena: records
+// already in it keep their place and only pending ones are appended (only appended payload is
+// re-uploaded).  New arena (replace_all): every record is placed again, pending ones from their
+// events' memory, the others from the arena being left (old_payload).
+void ClusterImage::write_all(ncd_arena_view& v, int threads, const uint8_t* old_payload, bool replace_all) {
   uint64_t ax = 0, oi = 0, di = 0, i = 0;
   auto put_aux = [&](const std::string& s, uint32_t* o, uint32_t* l) {
     memcpy(v.aux + ax, s.data(), s.size());
@@ -134,15 +154,24 @@ void ClusterImage::write_all(ncd_arena_view& v, int threads) {
     *l = (uint32_t)s.size();
     ax += s.size();
   };
-  std::vector<uint32_t> to_copy;
+  struct Copy {
+    uint32_t obj;
+    const uint8_t* src;
+  };
+  std::vector<Copy> to_copy;
   for (CachedObject& o : objs) {
     const ObjInfo& f = *o.info;
-    if (o.rec_off < 0 || o.value_dirty) {  // only appended payload is re-uploaded
+    if (o.pending || replace_all) {
+      const uint8_t* src = o.pending;
+      if (!src) {
+        if (!old_payload || o.rec_off < 0) throw std::runtime_error("packer: a record has no bytes anywhere");
+        src = old_payload + o.rec_off;
+      }
       assign(o, /*force_append=*/true);
-      to_copy.push_back((uint32_t)i);
+      to_copy.push_back({(uint32_t)i, src});
     }
     v.rec_off[i] = (uint64_t)o.rec_off;
-    v.rec_len[i] = (uint32_t)o.canon.size();
+    v.rec_len[i] = o.len;
     v.kind[i] = (uint8_t)f.kind;
     put_aux(f.key, &v.key_off[i], &v.key_len[i]);
     put_aux(f.uid, &v.uid_off[i], &v.uid_len[i]);
@@ -167,7 +196,11 @@ void ClusterImage::write_all(ncd_arena_view& v, int threads) {
   aux_used = ax;
   own_used = oi;
   dep_used = di;
-  parallel_for(to_copy.size(), threads, 64, [&](size_t k) { copy_record(v, objs[to_copy[k]]); });
+  parallel_for(to_copy.size(), threads, 64, [&](size_t k) { copy_record(v, objs[to_copy[k].obj], to_copy[k].src); });
+  for (const Copy& c : to_copy) {
+    objs[c.obj].pending = nullptr;
+    objs[c.obj].hold.reset();
+  }
 }
 
 }  // namespace ncdh

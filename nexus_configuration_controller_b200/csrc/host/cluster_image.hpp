@@ -42,15 +42,20 @@ struct ObjInfo {
   }
 };
 
+// The compared value's canonical bytes live in exactly one place: in memory the event brought
+// (`pending`, kept alive by `hold`: a batch's slab or a single buffer) until the next Scan lays the
+// record out in the arena's pinned payload, and only there afterwards.  The pinned arena IS the
+// cache of values: no second host copy is kept.
 struct CachedObject {
   std::shared_ptr<const ObjInfo> info;
-  std::string canon;  // canonical bytes of .Spec / .Data
+  uint32_t len = 0;                  // canonical length of the current value
+  const uint8_t* pending = nullptr;  // its bytes while they are not in the arena yet
+  std::shared_ptr<const void> hold;  // owner of `pending`
   bool live = true;
   uint64_t gen = 0;  // event counter value of the last put that changed this object
   // where the record lives in the resident arena's payload (-1: not placed yet)
   int64_t rec_off = -1;
-  uint64_t rec_cap = 0;      // padded bytes reserved at rec_off
-  bool value_dirty = false;  // canon changed since the device copy was written
+  uint64_t rec_cap = 0;  // padded bytes reserved at rec_off
 };
 
 inline std::string store_key(uint32_t kind, const std::string& key) { return std::string(1, (char)('0' + kind)) + key; }
@@ -105,42 +110,79 @@ struct ClusterImage {
   std::unordered_map<std::string, uint64_t> tomb;  // store_key -> stamp of the removal
   std::vector<uint32_t> dirty;                     // positions whose value changed since the last Scan
   uint64_t last_change = 0;                        // stamp of the latest put / remove that changed anything
+  uint64_t layout = 0;                             // bumped whenever positions in objs are reassigned
   ArenaHandle arena;
+  const uint8_t* host_payload = nullptr;           // the arena's pinned payload (where placed records are read back from)
   uint64_t payload_used = 0, payload_cap = 0, nobj_cap = 0, aux_cap = 0, nowner_cap = 0, ndep_cap = 0;
-  bool structural = true;  // keys / owners / dependents changed since the last commit
+  bool structural = true;   // keys / owners / dependents changed since the last commit
+  bool force_full = false;  // the resident device copy is not trusted: upload everything again
   uint64_t uploads_full = 0, uploads_structural = 0, uploads_values = 0;
   std::vector<uint32_t> pending_changed;  // records a prepared Values upload still has to push
 
+  const uint8_t* bytes_of(const CachedObject& o) const { return o.pending ? o.pending : host_payload + o.rec_off; }
+
+  // What a batch found out about an event ahead of the update, in parallel and under the SHARED lock
+  // (looking the object up and comparing the value's bytes are the expensive parts of a put): valid
+  // only while positions were not reassigned (same layout) and the object has not changed (same gen).
+  struct PutHint {
+    bool found = false, same_value = false, same_structure = false;
+    uint64_t seen_gen = 0, layout = 0;
+    size_t pos = 0;
+  };
+  PutHint precheck(const std::string& skey, const ObjInfo& info, const uint8_t* bytes, uint32_t len) const {
+    PutHint h;
+    auto it = index.find(skey);
+    if (it == index.end()) return h;
+    const CachedObject& o = objs[it->second];
+    h.found = true;
+    h.pos = it->second;
+    h.layout = layout;
+    h.seen_gen = o.gen;
+    h.same_value = o.len == len && memcmp(bytes_of(o), bytes, len) == 0;
+    h.same_structure = o.info->same_structure(info);
+    return h;
+  }
+
   // ---- events (caller holds the cache lock exclusively)
-  // Returns true when the put changed anything.
-  bool put(std::shared_ptr<const ObjInfo> info, std::string&& canon, uint64_t stamp) {
-    const std::string k = store_key(info->kind, info->key);
-    auto it = index.find(k);
-    if (it == index.end()) {
-      index.emplace(k, objs.size());
-      CachedObject o;
-      o.info = std::move(info);
-      o.canon = std::move(canon);
-      o.gen = stamp;
-      objs.push_back(std::move(o));
-      tomb.erase(k);
-      structural = true;
-      last_change = stamp;
-      return true;
+  // Returns true when the put changed anything.  k = store_key(kind, key); bytes / len = the canonical
+  // value, owned by `hold`.
+  bool put(const std::string& k, std::shared_ptr<const ObjInfo> info, const uint8_t* bytes, uint32_t len,
+           const std::shared_ptr<const void>& hold, uint64_t stamp, const PutHint* hint = nullptr) {
+    size_t pos = 0;
+    bool hinted = hint && hint->found && hint->layout == layout && hint->pos < objs.size() && objs[hint->pos].live &&
+                  objs[hint->pos].gen == hint->seen_gen;
+    if (hinted) {
+      pos = hint->pos;
+    } else {
+      auto it = index.find(k);
+      if (it == index.end()) {
+        index.emplace(k, objs.size());
+        CachedObject o;
+        o.info = std::move(info);
+        o.len = len;
+        o.pending = bytes;
+        o.hold = hold;
+        o.gen = stamp;
+        objs.push_back(std::move(o));
+        tomb.erase(k);
+        structural = true;
+        last_change = stamp;
+        return true;
+      }
+      pos = it->second;
     }
-    CachedObject& old = objs[it->second];
+    CachedObject& old = objs[pos];
     bool changed = false;
-    if (!old.info->same_structure(*info)) {
+    if (!(hinted ? hint->same_structure : old.info->same_structure(*info))) {
       structural = true;
       changed = true;
       old.info = std::move(info);
-    } else if (old.info->name != info->name) {
-      old.info = std::move(info);
     }
-    if (old.canon != canon) {
-      old.canon = std::move(canon);
-      if (!old.value_dirty) dirty.push_back((uint32_t)it->second);
-      old.value_dirty = true;
+    if (!(hinted ? hint->same_value : (old.len == len && memcmp(bytes_of(old), bytes, len) == 0))) {
+      if (!old.pending) dirty.push_back((uint32_t)pos);
+      old.pending = bytes;
+      old.hold = hold;
+      old.len = len;
       changed = true;
     }
     if (changed) old.gen = last_change = stamp;
@@ -168,12 +210,12 @@ struct ClusterImage {
     auto t = tomb.find(skey);
     return t == tomb.end() ? 0 : t->second;
   }
-  // After a failed Scan: nothing about the resident copy is trusted any more.
+  // After a failed Scan: the resident DEVICE copy is not trusted any more.  The pinned arena keeps
+  // the values (it is their only copy), so the next Scan commits the same arena again in full.
   void invalidate() {
-    arena.reset();
     structural = true;
+    force_full = true;
     pending_changed.clear();
-    for (CachedObject& o : objs) o.rec_off = -1;
   }
 
   Upload prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uint64_t* h2d);
@@ -182,10 +224,11 @@ struct ClusterImage {
  private:
   uint64_t aux_used = 0, own_used = 0, dep_used = 0, objs_committed = 0, dirty_from = 0;
   ncd_arena_view host_view();
-  Upload prepare_structural(ncd_ctx* ctx, int threads, uint64_t* h2d);
+  Upload prepare_structural(ncd_ctx* ctx, int threads, uint64_t* h2d, bool regrow = false);
   void assign(CachedObject& o, bool force_append);
-  static void copy_record(ncd_arena_view& v, CachedObject& o);
-  void write_all(ncd_arena_view& v, int threads);
+  static void copy_record(ncd_arena_view& v, CachedObject& o, const uint8_t* src);
+  void bind_arena();
+  void write_all(ncd_arena_view& v, int threads, const uint8_t* old_payload, bool replace_all);
 };
 
 }  // namespace ncdh

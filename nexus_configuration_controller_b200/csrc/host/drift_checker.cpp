@@ -15,6 +15,8 @@
 //   snap       the result of the last finished Scan, an immutable object swapped in atomically:
 //              Lookup / plan never wait for a Scan in flight and never see half a result.
 #include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -34,6 +36,7 @@
 
 namespace ncdh {
 std::string canonicalise(const uint8_t* value, uint64_t len);
+uint64_t canonicalise_into(const uint8_t* value, uint64_t len, uint8_t* out, uint64_t cap);
 }
 using namespace ncdh;
 
@@ -135,10 +138,44 @@ struct Prepared {
   int cluster = 0;
   uint32_t op = NCDH_EV_PUT;
   std::shared_ptr<const ObjInfo> info;
-  std::string canon;
+  std::string skey;
+  const uint8_t* bytes = nullptr;  // canonical value, inside the batch's slab
+  uint32_t len = 0;
+  ClusterImage::PutHint hint;
+  bool hinted = false;
 };
 
-void prepare_event(const ncdh_event& e, Prepared* p) {
+// Memory the canonical values of a batch of events are written into, one buffer per batch.  The
+// cached objects keep it alive (shared_ptr) until the next Scan has laid their records out in the
+// pinned arena; then it returns to the pool and the next batch reuses it — already mapped, so the
+// canonicaliser does not pay a page fault per 4 KiB of output the way fresh allocations do.
+struct SlabPool {
+  std::mutex mu;
+  std::vector<std::vector<uint8_t>> free_list;
+  static constexpr size_t kKeepBytes = 1ull << 30;  // buffers beyond this in total are returned to the system
+  std::vector<uint8_t> take(size_t bytes) {
+    std::lock_guard<std::mutex> lk(mu);
+    int best = -1;
+    for (size_t i = 0; i < free_list.size(); ++i)
+      if (free_list[i].size() >= bytes && (best < 0 || free_list[i].size() < free_list[best].size())) best = (int)i;
+    std::vector<uint8_t> out;
+    if (best >= 0) {
+      out.swap(free_list[best]);
+      free_list.erase(free_list.begin() + best);
+    }
+    return out;  // empty: the caller allocates
+  }
+  void give(std::vector<uint8_t>&& buf) {
+    std::lock_guard<std::mutex> lk(mu);
+    size_t kept = 0;
+    for (const auto& b : free_list) kept += b.size();
+    if (kept + buf.size() <= kKeepBytes) free_list.push_back(std::move(buf));
+  }
+};
+SlabPool g_pool;
+
+// out / cap: where the canonical value goes (cap >= e.value_len always suffices).
+void prepare_event(const ncdh_event& e, Prepared* p, uint8_t* out, uint64_t cap) {
   if (!e.ns || !e.name) throw std::runtime_error("null namespace / name");
   if (e.kind > NCD_KIND_CONFIGMAP) throw std::runtime_error("unknown kind");
   auto info = std::make_shared<ObjInfo>();
@@ -154,15 +191,19 @@ void prepare_event(const ncdh_event& e, Prepared* p) {
     for (int i = 0; i < e.nowners; ++i) info->owners.push_back({e.owner_kinds[i], e.owner_uids[i]});
     for (int i = 0; i < e.nsecrets; ++i) info->secrets.push_back(e.secret_names[i]);
     for (int i = 0; i < e.nconfigmaps; ++i) info->configmaps.push_back(e.configmap_names[i]);
-    p->canon = canonicalise(e.value, e.value_len);
+    if (e.value_len >= 0xFFFFFFFFull) throw std::runtime_error("value longer than 4 GiB");
+    p->len = (uint32_t)canonicalise_into(e.value, e.value_len, out, cap);
+    p->bytes = out;
   } else if (e.op != NCDH_EV_DELETE) {
     throw std::runtime_error("unknown event op");
   }
+  p->skey = store_key(info->kind, info->key);
   p->info = std::move(info);
 }
 
 // Applies prepared events in order.  Caller holds cache_mu exclusively.
-int apply_locked(ncdh_checker* c, std::vector<Prepared>& evs, size_t count, int* removed_missing) {
+int apply_locked(ncdh_checker* c, std::vector<Prepared>& evs, size_t count, const std::shared_ptr<const void>& hold,
+                 int* removed_missing) {
   for (size_t i = 0; i < count; ++i) {
     Prepared& p = evs[i];
     ClusterImage* img = c->image(p.cluster);
@@ -170,7 +211,7 @@ int apply_locked(ncdh_checker* c, std::vector<Prepared>& evs, size_t count, int*
     const uint64_t stamp = c->clock.fetch_add(1) + 1;
     bool changed;
     if (p.op == NCDH_EV_PUT) {
-      changed = img->put(std::move(p.info), std::move(p.canon), stamp);
+      changed = img->put(p.skey, std::move(p.info), p.bytes, p.len, hold, stamp, p.hinted ? &p.hint : nullptr);
     } else {
       changed = img->drop(p.info->kind, p.info->key, stamp);
       if (!changed && removed_missing) ++*removed_missing;
@@ -221,26 +262,46 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
   if (n == 0) return 0;
   if (threads <= 0) threads = c->threads;
   const auto t0 = std::chrono::steady_clock::now();
-  // canonicalise outside the lock, in parallel; remember the first event that cannot be
+  // one slab for the canonical values of the whole batch (a canonical form is as long as its transport form)
+  std::vector<uint64_t> off(n + 1, 0);
+  for (uint64_t i = 0; i < n; ++i) off[i + 1] = off[i] + (events[i].op == NCDH_EV_PUT ? events[i].value_len : 0);
+  auto slab = std::make_shared<std::vector<uint8_t>>(g_pool.take(off[n]));
+  if (slab->size() < off[n]) slab->resize(off[n]);
+  const std::shared_ptr<const void> hold(slab.get(), [slab](const void*) mutable {
+    g_pool.give(std::move(*slab));  // the last cached object that pointed into it is gone
+    slab.reset();
+  });
+  // canonicalise in parallel, outside the exclusive lock, and look every object up and compare its
+  // value with what the cache holds under the SHARED lock: readers and other batches go on, only the
+  // short update below is exclusive.  The first event that cannot be canonicalised ends the batch.
   std::vector<Prepared> evs(n);
   std::vector<std::string> errs(n);
   std::atomic<uint64_t> first_bad{n};
-  parallel_for(n, threads, 8, [&](size_t i) {
-    try {
-      prepare_event(events[i], &evs[i]);
-    } catch (const std::exception& e) {
-      errs[i] = e.what();
-      uint64_t cur = first_bad.load();
-      while (i < cur && !first_bad.compare_exchange_weak(cur, i)) {
+  {
+    std::shared_lock<std::shared_mutex> rd(c->cache_mu);
+    parallel_for(n, threads, 8, [&](size_t i) {
+      try {
+        Prepared& p = evs[i];
+        prepare_event(events[i], &p, slab->data() + off[i], off[i + 1] - off[i]);
+        ClusterImage* img = c->image(p.cluster);
+        if (img && p.op == NCDH_EV_PUT) {
+          p.hint = img->precheck(p.skey, *p.info, p.bytes, p.len);
+          p.hinted = true;
+        }
+      } catch (const std::exception& e) {
+        errs[i] = e.what();
+        uint64_t cur = first_bad.load();
+        while (i < cur && !first_bad.compare_exchange_weak(cur, i)) {
+        }
       }
-    }
-  });
+    });
+  }
   c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t0) * 1e6), std::memory_order_relaxed);
   const uint64_t good = first_bad.load();
   int rc;
   {
     std::unique_lock<std::shared_mutex> lk(c->cache_mu);
-    rc = apply_locked(c, evs, good, nullptr);
+    rc = apply_locked(c, evs, good, hold, nullptr);
   }
   if (rc != 0) return fail("ncdh_apply_events: " + g_err);
   if (good < n) return fail("ncdh_apply_events: event " + std::to_string(good) + ": " + errs[good]);
@@ -274,10 +335,11 @@ int ncdh_cluster_add(ncdh_checker* c, int cluster, uint32_t kind, const char* ns
   try {
     const auto t0 = std::chrono::steady_clock::now();
     std::vector<Prepared> one(1);
-    prepare_event(e, &one[0]);  // canonicalised on the caller's thread, outside the lock
+    auto buf = std::make_shared<std::vector<uint8_t>>(value_len ? value_len : 1);
+    prepare_event(e, &one[0], buf->data(), value_len);  // canonicalised on the caller's thread, outside the lock
     c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t0) * 1e6), std::memory_order_relaxed);
     std::unique_lock<std::shared_mutex> lk(c->cache_mu);
-    return apply_locked(c, one, 1, nullptr);
+    return apply_locked(c, one, 1, std::shared_ptr<const void>(buf, buf->data()), nullptr);
   } catch (const std::exception& ex) {
     return fail(std::string("ncdh_cluster_add: ") + ex.what());
   }
@@ -294,7 +356,7 @@ int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char*
   one[0].info = std::move(info);
   int missing = 0;
   std::unique_lock<std::shared_mutex> lk(c->cache_mu);
-  if (apply_locked(c, one, 1, &missing) != 0) return -1;
+  if (apply_locked(c, one, 1, nullptr, &missing) != 0) return -1;
   return missing ? 1 : 0;
 }
 

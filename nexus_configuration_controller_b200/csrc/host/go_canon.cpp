@@ -59,6 +59,19 @@ struct StrSink {
   void put(const void* b, uint64_t n) { s.append(reinterpret_cast<const char*>(b), n); }
   void byte(uint8_t b) { s.push_back((char)b); }
 };
+struct BufSink {  // a caller-sized buffer: the canonical form is never longer than the transport form
+  uint8_t* p;
+  uint8_t* end;
+  void put(const void* b, uint64_t n) {
+    if ((uint64_t)(end - p) < n) throw std::runtime_error("canonical form does not fit the buffer");
+    memcpy(p, b, n);
+    p += n;
+  }
+  void byte(uint8_t b) {
+    if (p == end) throw std::runtime_error("canonical form does not fit the buffer");
+    *p++ = b;
+  }
+};
 struct NullSink {
   void put(const void*, uint64_t) {}
   void byte(uint8_t) {}
@@ -149,6 +162,16 @@ std::string canonicalise(const uint8_t* value, uint64_t len) {
   encode(in, sink, 0);
   if (in.p != in.end) throw std::runtime_error("bytes left over after the value");
   return out;
+}
+
+// The same into a buffer of `cap` bytes (cap = len always suffices: every node's canonical form is
+// exactly as long as its transport form, map entries are only reordered).  Returns the bytes written.
+uint64_t canonicalise_into(const uint8_t* value, uint64_t len, uint8_t* out, uint64_t cap) {
+  Cursor in{value, value + len};
+  BufSink sink{out, out + cap};
+  encode(in, sink, 0);
+  if (in.p != in.end) throw std::runtime_error("bytes left over after the value");
+  return (uint64_t)(sink.p - out);
 }
 
 }  // namespace ncdh

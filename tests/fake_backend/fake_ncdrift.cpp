@@ -172,9 +172,17 @@ int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t*
   return NCD_OK;
 }
 
+// Test hook: the next `n` scans fail the way a CUDA error would (after the uploads went through).
+static int g_fail_scans = 0;
+void ncd_fake_fail_next_scans(int n) { g_fail_scans = n; }
+
 int ncd_scan_host(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards, uint32_t mode,
                   const ncd_entry** entries, uint64_t* n) {
   (void)mode;
+  if (g_fail_scans > 0) {
+    --g_fail_scans;
+    return fail(NCD_E_CUDA, "fake: injected scan failure");
+  }
   if (!ctx || !ctrl || !entries || !n || !ctrl->committed) return fail(NCD_E_STATE, "fake: scan of an uncommitted arena");
   std::vector<const ncd_arena_view*> sv;
   for (int s = 0; s < nshards; ++s) {

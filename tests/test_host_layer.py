@@ -418,3 +418,35 @@ def test_host_layer_and_the_sweep_over_parsed_values_agree(make_checker, request
             for b in batches:
                 b.close()
     fleet.close()
+
+
+def test_a_failed_scan_costs_a_full_upload_not_the_cached_values():
+    """The pinned arenas are the only copy of the values once a record has been laid out.  A Scan that fails
+    on the GPU (here: injected into the CPU double) must leave them intact: the next Scan commits the same
+    arenas again in full and decides correctly, including for values that changed before the failure."""
+    lib = fake_lib()
+    case = next(c for c in CASES if c["name"] == "TwoShards_converged_and_drifted")
+    with Hst.DriftChecker(2, lib=lib) as f:
+        fill(f, case)
+        f.scan()
+        want = f.plan_template(NS, "test")
+        ctrl_cm = next(o for o in case["controller"] if o["kind"] == A.KIND_CONFIGMAP)
+        f.add(-1, A.KIND_CONFIGMAP, NS, ctrl_cm["name"], "", new_configmap("x", None, {"brand": "new"}).value,
+              [tuple(r) for r in ctrl_cm["owner_refs"]])
+        lib.ncd_fake_fail_next_scans(1)
+        with pytest.raises(Hst.HostError, match="injected"):
+            f.scan()
+        with pytest.raises(Hst.Stale):  # the old snapshot is still there, and still honest about its age
+            f.plan_template(NS, "test")
+        f.scan()
+        assert f.upload_counts(-1)[0] == 2 and f.upload_counts(0)[0] == 2  # every cluster committed again in full
+        nexus, kube, err = f.plan_template(NS, "test")
+        assert nexus == want[0] and err is None
+        assert kube[0] == [["update-data", "configmaps", "test-config"]]  # shard 0 held the old value
+        assert kube[1] == want[1][1]
+        # and the cheap paths work again afterwards
+        f.add(-1, A.KIND_CONFIGMAP, NS, ctrl_cm["name"], "", new_configmap("x", None, {"brand": "newer"}).value,
+              [tuple(r) for r in ctrl_cm["owner_refs"]])
+        f.scan()
+        assert f.upload_counts(-1)[0] == 2 and f.upload_counts(-1)[2] >= 1
+        assert f.plan_template(NS, "test")[1][0] == [["update-data", "configmaps", "test-config"]]
