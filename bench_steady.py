@@ -71,8 +71,9 @@ class Steps:
     """The event batches of the steps of one churn level (prebuilt: they are the steps' input)."""
 
     def __init__(self, hosts, churn, nsteps, seed, first_salt, prev_idx=None, prev_salt=0, threads=0, lib=None):
-        from nexus_configuration_controller_b200.host import EventBatch
+        from nexus_configuration_controller_b200.host import Event, EventBatch
 
+        self._owners = []
         rng = np.random.default_rng(seed)
         ctrl, n = hosts[0], hosts[0].nobj
         k = max(1, int(round(n * churn)))
@@ -85,17 +86,25 @@ class Steps:
             if idx_prev is not None:  # the shards catch up with the previous interval's controller values
                 batches += [EventBatch(h, values=ctrl, cluster=c, obj_idx=idx_prev, salt=salt_prev, threads=threads, lib=lib)
                             for c, h in enumerate(hosts[1:])]
-            self.steps.append(batches)
+            # one array per step: an interval's events of every cluster go through ONE ncdh_apply_events call
+            total = sum(b.n for b in batches)
+            merged = (Event * max(total, 1))()
+            at = 0
+            for b in batches:
+                C.memmove(C.byref(merged, at * C.sizeof(Event)), b.events, b.n * C.sizeof(Event))
+                at += b.n
+            self.steps.append((merged, total))
+            self._owners.append(batches)
             idx_prev, salt_prev = idx, salt
         self.last_idx, self.last_salt = idx_prev, salt_prev
-        self.value_bytes = sum(b.value_bytes for b in self.steps[-1])
-        self.events = sum(b.n for b in self.steps[-1])
+        self.value_bytes = sum(b.value_bytes for b in self._owners[-1])
+        self.events = self.steps[-1][1]
 
     def close(self):
-        for batches in self.steps:
+        for batches in self._owners:
             for b in batches:
                 b.close()
-        self.steps = []
+        self.steps, self._owners = [], []
 
 
 class SteadyGpu:
@@ -124,14 +133,15 @@ class SteadyGpu:
     def step(self, batches):
         """One timed step.  Returns (seconds, timing dict of the scan)."""
         f, lib = self.f, self.f.lib
+        events, n = batches
         t0 = time.perf_counter()
-        for b in batches:
-            f.apply_events(b, self.threads)
+        if lib.ncdh_apply_events(f.h, events, n, self.threads) != 0:
+            raise RuntimeError(lib.ncdh_last_error().decode())
         f.scan()
-        n = lib.ncdh_sweep_queue(f.h, None, 0)  # the work-queue feed
+        n = lib.ncdh_sweep_queue(f.h, self.qbuf, len(self.qbuf))  # the work-queue feed
         if n > len(self.qbuf):
             self.qbuf = C.create_string_buffer(int(n * 2))
-        lib.ncdh_sweep_queue(f.h, self.qbuf, len(self.qbuf))
+            lib.ncdh_sweep_queue(f.h, self.qbuf, len(self.qbuf))
         code = C.c_uint32()
         for kind, ns, name in self.lookup_keys:  # what handlers ask for: (template, dependent, shard)
             lib.ncdh_lookup(f.h, kind, ns, name, 0, 0, C.byref(code))
@@ -158,9 +168,9 @@ class SteadyCpu:
         self.last = self.fleet.sweep(threads)  # warm-up sweep
 
     def step(self, batches):
+        events, n = batches
         t0 = time.perf_counter()
-        for b in batches:
-            self.fleet.apply(b.events, b.n, self.threads)
+        self.fleet.apply(events, n, self.threads)
         self.last = self.fleet.sweep(self.threads)
         return time.perf_counter() - t0
 
