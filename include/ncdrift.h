@@ -151,7 +151,8 @@ typedef struct ncd_scan_stats {
   uint64_t ndiff;     /* entries in the diff list                    */
   uint64_t hash_collisions; /* CONFIRM only: hash-equal pairs whose bytes differ */
   uint32_t launches;  /* kernels launched by the scan                */
-  uint32_t compare_variant; /* which byte-compare kernel ran: 0 k_compare, 2 k_compare_grouped, 8 k_compare_tma, 16 k_compare_small */
+  uint32_t compare_variant; /* which byte-compare kernel ran: 0 k_compare, 2 k_compare_grouped, 8 k_compare_tma, 16 k_compare_small,
+                               32 k_scan_small (join and compare fused, small records in direct mode) */
 } ncd_scan_stats;
 
 /* ------------------------------------------------------------------ context */

@@ -55,6 +55,8 @@ extern "C" int ncd_init(int device, ncd_ctx** out) {
   ctx->sm_count = prop.multiProcessorCount;
   ctx->compare_variant = -1;  // -1: chosen per scan from the mean tile fill
   ctx->compare_ctas_per_sm = 8;
+  ctx->fuse_small = 1;
+  if (const char* v = getenv("NCD_FUSE_SMALL")) ctx->fuse_small = atoi(v) != 0;  // experiment knob: 0 = k_join + k_compare_small
   if (const char* v = getenv("NCD_COMPARE_VARIANT")) {
     // experiment knob: only the kernels that exist may be named (ncd_scan_stats.compare_variant)
     const int k = atoi(v);

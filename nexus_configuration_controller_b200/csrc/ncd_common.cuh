@@ -29,7 +29,15 @@ __host__ __device__ __forceinline__ uint32_t ncd_ctiles_of(uint32_t len) {
 
 // Everything a probe needs about one object, in one 64-byte line: the join reads the table
 // slot, then this, and nothing else unless the key is longer than NCD_KEY_INLINE bytes.
-constexpr uint32_t NCD_KEY_INLINE = 36;
+// The first 32-byte sector holds everything a scan needs once the join is cached (record
+// offset / length and the ownership tag); the second sector is the inline key for probes.
+constexpr uint32_t NCD_KEY_INLINE = 32;
+// Ownership tag of an object, interned at commit: what isMissingOwnership (controller.go:484-502)
+// needs, in one word.  Template: the id of its own metadata.uid.  Any other object: its single
+// ownerReference packed as (Kind == NexusAlgorithmTemplate) << 31 | uid id, NCD_TAG_ROGUE when it
+// has none, NCD_TAG_MANY when it has several (the decision kernel then walks the list).
+#define NCD_TAG_ROGUE 0xFFFFFFFFu
+#define NCD_TAG_MANY 0xFFFFFFFEu
 struct __align__(16) ObjMeta {
   uint64_t keyhash;
   uint64_t rec_off;
@@ -38,6 +46,7 @@ struct __align__(16) ObjMeta {
   uint16_t key_len;
   uint8_t kind;
   uint8_t pad;
+  uint32_t tag;
   uint8_t key[NCD_KEY_INLINE];  // first bytes of the key, zero padded
 };
 static_assert(sizeof(ObjMeta) == 64, "ObjMeta must be one 64-byte line");
@@ -87,6 +96,7 @@ struct ncd_ctx {
   int sm_count;
   int compare_variant;      // -1 = pick per scan, 0 = per-shard loop, 1/2/4 = grouped with CH vectors per lane
   int compare_ctas_per_sm;  // grid = sm_count * this
+  int fuse_small;           // 1: small records in direct mode take k_scan_small (join + compare in one kernel)
   cudaStream_t stream;
   cudaEvent_t ev[8];                        // ev[5], ev[6]: ncd_hash_arena
   cudaEvent_t evr[NCD_EV_RING][5];          // per-scan phase events, ring indexed by scan_seq
@@ -282,10 +292,11 @@ __device__ __forceinline__ uint32_t ncd_probe_meta(const DevArena& t, const ObjM
     if ((uint32_t)(e >> 32) == hi) {
       const uint32_t idx = (uint32_t)e;
       const uint4* mw = reinterpret_cast<const uint4*>(&t.meta[idx]);
-      // words 0-1: keyhash; word 6: key_len | kind | pad; words 7-15: inline key (zero padded)
+      // words 0-1: keyhash; word 6: key_len | kind | pad; word 7: tag (not part of the key);
+      // words 8-15: inline key (zero padded)
       const uint4 m0 = mw[0], m1 = mw[1], m2 = mw[2], m3 = mw[3];
       const uint4 q0 = qw[0], q1 = qw[1], q2 = qw[2], q3 = qw[3];
-      const uint32_t diff = (m0.x ^ q0.x) | (m0.y ^ q0.y) | ((m1.z ^ q1.z) & 0x00FFFFFFu) | (m1.w ^ q1.w) |
+      const uint32_t diff = (m0.x ^ q0.x) | (m0.y ^ q0.y) | ((m1.z ^ q1.z) & 0x00FFFFFFu) |
                             (m2.x ^ q2.x) | (m2.y ^ q2.y) | (m2.z ^ q2.z) | (m2.w ^ q2.w) |
                             (m3.x ^ q3.x) | (m3.y ^ q3.y) | (m3.z ^ q3.z) | (m3.w ^ q3.w);
       if (diff == 0) {

@@ -138,6 +138,12 @@ __global__ void k_meta_build(DevArena a, ObjMeta* __restrict__ meta) {
   m.key_len = (uint16_t)klen;
   m.kind = a.kind[i];
   m.pad = 0;
+  if (m.kind == NCD_KIND_TEMPLATE) {
+    m.tag = a.uid_id[i];
+  } else {
+    const uint32_t o0 = a.own_start[i], o1 = a.own_start[i + 1];
+    m.tag = o0 == o1 ? NCD_TAG_ROGUE : (o1 - o0 == 1 ? a.own_packed[o0] : NCD_TAG_MANY);
+  }
 #pragma unroll
   for (uint32_t b = 0; b < NCD_KEY_INLINE; ++b) m.key[b] = b < klen ? key[b] : 0;
   const uint4* src = reinterpret_cast<const uint4*>(&m);
@@ -480,6 +486,7 @@ int ncd_build_index(ncd_arena* a) {
       k_uid_resolve<<<ublocks, 256, 0, st>>>(da, (uint32_t)nstr, utable, usize - 1, a->uid_id, a->own_packed);
       NCD_CUDA(cudaFreeAsync(utable, st));
     }
+    ncd_fill_dev_arena(a, &da);  // uid_id / own_packed were (re)allocated above: the object lines carry tags made from them
     k_meta_build<<<blocks, 256, 0, st>>>(da, a->meta);
     k_table_build<<<blocks, 256, 0, st>>>(da, (unsigned long long*)a->table, d_small + 1);
     k_row_counts<<<blocks, 256, 0, st>>>(da, counts);

@@ -20,7 +20,7 @@
 // ------------------------------------------------------------------ k_join
 __global__ void __launch_bounds__(256)
 k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t mode,
-       uint32_t* __restrict__ sh_idx, uint64_t* __restrict__ sh_off, uint8_t* __restrict__ dv) {
+       uint32_t* __restrict__ sh_idx, uint64_t* __restrict__ sh_off, uint8_t* __restrict__ dv, uint32_t* __restrict__ tag) {
   const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= (uint64_t)ctrl.nobj * S) return;
   const uint32_t c = (uint32_t)(p / S), s = (uint32_t)(p % S);
@@ -37,6 +37,8 @@ k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t 
   }
   uint8_t v;
   uint64_t off = NCD_NO_OFF;
+  uint32_t tg = NCD_TAG_ROGUE;
+  if (idx != NCD_NOTFOUND) tg = sh.meta[idx].tag;
   if (idx == NCD_NOTFOUND) {
     v = DV_NOTFOUND;
   } else if (sh.meta[idx].rec_len != q.rec_len) {
@@ -61,6 +63,7 @@ k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t 
   sh_idx[p] = idx;
   sh_off[p] = off;
   dv[p] = v;
+  tag[p] = tg;
 }
 
 // ------------------------------------------------------------------ k_compare
@@ -301,12 +304,111 @@ k_compare_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
   }
 }
 
+// ------------------------------------------------------------------ k_scan_small
+// Small records (a few hundred bytes: template and workgroup specs, small ConfigMaps), direct mode:
+// the join and the byte compare in ONE kernel.  With k_join + k_compare_small every 64-256 bytes
+// of payload sat behind two dependent load levels (tile list -> record offset/length -> shard
+// offsets written by the join), and the join itself had already touched the object's line.  Here
+// eight lanes own one controller object.  Per group of up to eight shards, lane l looks the object
+// up in shard l (lister.Get: the cached answer of the previous scan, or a probe of the shard's
+// table) and reads the FIRST 32-byte sector of the shard object's line — record offset, length and
+// ownership tag; then the eight lanes walk the record together, vector v of the controller copy
+// against vector v of every shard copy, all loads of a step issued before any is used.  Verdict,
+// shard index and tag go out for k_classify; no tile list, no offsets round trip.
+// Correct for any record length (the lanes loop over the whole record); chosen when records are small.
+template <int G>
+__global__ void __launch_bounds__(256, G == 8 ? 3 : 4)
+k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t* __restrict__ sh_idx,
+             uint8_t* __restrict__ dv, uint32_t* __restrict__ tag) {
+  struct ShardRef {
+    const uint8_t* payload;
+    const ObjMeta* meta;
+    const uint32_t* join_cache;
+    uint32_t* join_cache_out;
+  };
+  extern __shared__ __align__(16) uint8_t s_raw[];
+  ShardRef* s_sh = reinterpret_cast<ShardRef*>(s_raw);
+  for (uint32_t s = threadIdx.x; s < S; s += blockDim.x)
+    s_sh[s] = ShardRef{shards[s].payload, shards[s].meta, shards[s].join_cache, shards[s].join_cache_out};
+  __syncthreads();
+  const uint32_t lane = threadIdx.x & 31, l8 = lane & 7;
+  const uint32_t gmask = 0xFFu << (lane & 24);  // the eight lanes of this object
+  const uint64_t group0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const uint64_t ngroups = ((uint64_t)gridDim.x * blockDim.x) >> 3;
+  for (uint64_t c = group0; c < ctrl.nobj; c += ngroups) {
+    const ObjMeta& q = ctrl.meta[c];
+    const uint32_t len = q.rec_len;
+    const uint32_t nvec = (len + 15) >> 4, tail = len & 15;
+    const uint4* cp = reinterpret_cast<const uint4*>(ctrl.payload + q.rec_off);
+    for (uint32_t s0 = 0; s0 < S; s0 += G) {
+      // ---- join: lane l8 < G answers for shard s0 + l8
+      const uint32_t s = s0 + l8;
+      uint32_t idx = NCD_NOTFOUND, tg = NCD_TAG_ROGUE;
+      uint8_t v = DV_NOTFOUND;
+      const uint4* mine = nullptr;  // this lane's shard copy, when its bytes have to be compared
+      if (l8 < G && s < S) {
+        const ShardRef sr = s_sh[s];
+        if (sr.join_cache) {
+          idx = sr.join_cache[c];
+        } else {
+          idx = ncd_probe_meta(shards[s], q, ctrl.aux);
+          if (sr.join_cache_out) sr.join_cache_out[c] = idx;
+        }
+        if (idx != NCD_NOTFOUND) {
+          const uint4* line = reinterpret_cast<const uint4*>(sr.meta + idx);
+          const uint4 w0 = line[0], w1 = line[1];  // keyhash | rec_off ; rec_len key_off key_len/kind tag
+          tg = w1.w;
+          if (w1.x != len) {
+            v = DV_DIFF;  // the encoding is injective: different lengths cannot be DeepEqual
+          } else {
+            v = DV_EQUAL;
+            mine = reinterpret_cast<const uint4*>(sr.payload + ((uint64_t)w0.z | ((uint64_t)w0.w << 32)));
+          }
+        }
+      }
+      // ---- compare: the eight lanes walk the record against the G shard copies together
+      const uint4* sp[G];
+      uint32_t x[G];
+#pragma unroll
+      for (int k = 0; k < G; ++k) {
+        const unsigned long long p = __shfl_sync(gmask, (unsigned long long)mine, (lane & 24) + k);
+        sp[k] = reinterpret_cast<const uint4*>(p);
+        x[k] = 0;
+      }
+      for (uint32_t vv = l8; vv < nvec; vv += 8) {
+        uint4 a = ncd_ldg_stream(cp + vv);
+        uint4 b[G];
+#pragma unroll
+        for (int k = 0; k < G; ++k) b[k] = sp[k] != nullptr ? ncd_ldg_stream(sp[k] + vv) : a;
+        if (tail && vv == nvec - 1) {
+          a = mask_tail(a, tail);
+#pragma unroll
+          for (int k = 0; k < G; ++k) b[k] = mask_tail(b[k], tail);
+        }
+#pragma unroll
+        for (int k = 0; k < G; ++k) x[k] |= (a.x ^ b[k].x) | (a.y ^ b[k].y) | (a.z ^ b[k].z) | (a.w ^ b[k].w);
+      }
+#pragma unroll
+      for (int k = 0; k < G; ++k) {
+        const uint32_t differs = __ballot_sync(gmask, x[k] != 0) & gmask;
+        if (differs && l8 == (uint32_t)k) v = DV_DIFF;  // sp[k] was null for every lane unless lane k set it
+      }
+      if (l8 < G && s < S) {
+        const uint64_t p = c * S + s;
+        sh_idx[p] = idx;
+        dv[p] = v;
+        tag[p] = tg;
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ k_classify
 __global__ void __launch_bounds__(256)
 k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint64_t nrows,
            const uint32_t* __restrict__ row_obj, const uint32_t* __restrict__ row_dep,
            const uint32_t* __restrict__ row_cidx, const uint32_t* __restrict__ sh_idx,
-           const uint8_t* __restrict__ dv, uint8_t* __restrict__ codes,
+           const uint8_t* __restrict__ dv, const uint32_t* __restrict__ tag, uint8_t* __restrict__ codes,
            uint32_t* __restrict__ blk_cnt, uint32_t* __restrict__ blk_off, uint32_t* __restrict__ counters,
            uint32_t fuse_scan) {
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -326,10 +428,12 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
       if (v == DV_NOTFOUND) {
         code = NCD_CREATE;  // :518-520, :580-582
       } else {
-        const DevArena& sh = shards[s];
-        const uint32_t j = sh_idx[p];
-        const uint32_t o0 = sh.own_start[j], o1 = sh.own_start[j + 1];
-        if (o0 == o1) {
+        // The join left each shard object's ownership tag beside its verdict (ObjMeta.tag): the
+        // single ownerReference of a dependent, the interned UID of a template.  The common cases
+        // are decided from those two words; only a dependent with several ownerReferences walks
+        // its list in the shard's arena.
+        const uint32_t mine = tag[p];
+        if (mine == NCD_TAG_ROGUE) {
           code = NCD_ERR_ROGUE;  // :494-499, checked before the data compare (:529 before :539)
         } else {
           // isMissingOwnership(:484-502) against the shard's copy of the owning template.  A
@@ -340,9 +444,15 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
           bool missing = true;
           if (dv[tp] != DV_NOTFOUND) {
             // UIDs were interned at commit: equal ids <=> byte-equal strings (ncd_index.cu)
-            const uint32_t want = sh.uid_id[sh_idx[tp]] | 0x80000000u;  // Kind == NexusAlgorithmTemplate && same UID
-            for (uint32_t o = o0; o < o1 && missing; ++o)
-              if (sh.own_packed[o] == want) missing = false;
+            const uint32_t want = tag[tp] | 0x80000000u;  // Kind == NexusAlgorithmTemplate && same UID
+            if (mine != NCD_TAG_MANY) {
+              missing = mine != want;
+            } else {
+              const DevArena& sh = shards[s];
+              const uint32_t j = sh_idx[p];
+              for (uint32_t o = sh.own_start[j]; o < sh.own_start[j + 1] && missing; ++o)
+                if (sh.own_packed[o] == want) missing = false;
+            }
           }
           code = (v == DV_DIFF ? NCD_UPDATE_DATA : 0u) | (missing ? NCD_UPDATE_OWNER : 0u);
         }
@@ -539,11 +649,12 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   }
   algo += ctrl->len_sum;
 
-  // scratch: sh_off u64[npairs] | sh_idx u32[npairs] | blk_cnt u32[nblk+1] | blk_off u32[nblk+1] | dv u8[npairs]
+  // scratch: sh_off u64[npairs] | sh_idx u32[npairs] | tag u32[npairs] | blk_cnt u32[nblk+1] | blk_off u32[nblk+1] | dv u8[npairs]
   const uint64_t nblk = (nq + 255) / 256;
   size_t o_off = 0;
   size_t o_idx = o_off + ncd_align_up(npairs * 8, 256);
-  size_t o_cnt = o_idx + ncd_align_up(npairs * 4, 256);
+  size_t o_tag = o_idx + ncd_align_up(npairs * 4, 256);
+  size_t o_cnt = o_tag + ncd_align_up(npairs * 4, 256);
   size_t o_bo = o_cnt + ncd_align_up((nblk + 1) * 4, 256);
   size_t o_dv = o_bo + ncd_align_up((nblk + 2) * 4, 256);
   size_t o_codes = o_dv + ncd_align_up(npairs, 256);
@@ -552,6 +663,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   NCD_TRY(ncd_ctx_scratch(ctx, total, &base));
   uint64_t* sh_off = (uint64_t*)((char*)base + o_off);
   uint32_t* sh_idx = (uint32_t*)((char*)base + o_idx);
+  uint32_t* tag = (uint32_t*)((char*)base + o_tag);
   uint32_t* blk_cnt = (uint32_t*)((char*)base + o_cnt);
   uint32_t* blk_off = (uint32_t*)((char*)base + o_bo);
   uint8_t* dv = (uint8_t*)((char*)base + o_dv);
@@ -560,18 +672,37 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   uint32_t* counters = (uint32_t*)ctx->d_counters;
   NCD_CUDA(cudaMemsetAsync(counters, 0, 8 * sizeof(uint64_t), st));
 
-  if (npairs) {
+  // Which byte-compare kernel this scan takes, from the mean tile fill (see below); small records
+  // in direct mode take ONE kernel for join and compare together (k_scan_small).
+  int variant = ctx->compare_variant;
+  if (variant < 0 && ctrl->ntiles) {
+    const uint64_t fill = ctrl->len_sum / ctrl->ntiles;
+    variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : (fill >= 700 ? 2 : 16));
+  }
+  const bool fused_small = npairs && variant == 16 && hm == NCD_MODE_DIRECT && ctx->fuse_small;
+  if (npairs && !fused_small) {
     k_join<<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(dctrl, ctx->d_shards, S, mode, sh_idx,
-                                                             sh_off, dv);
+                                                             sh_off, dv, tag);
     ++launches;
+  }
+  NCD_CUDA(cudaEventRecord(evs[2], st));
+  if (fused_small) {
+    const uint64_t want = (nc * 8 + 255) / 256, cap = (uint64_t)ctx->sm_count * 16;
+    const size_t smem = (size_t)S * 32;
+    if (S <= 4)
+      k_scan_small<4><<<(unsigned)(want < cap ? want : cap), 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+    else
+      k_scan_small<8><<<(unsigned)(want < cap ? want : cap), 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+    ++launches;
+    variant_used = 32;
+  }
+  if (npairs)
     for (ncd_arena* sa : jc_filled) {
       sa->jc_ctrl = ctrl;
       sa->jc_ctrl_gen = ctrl->generation;
       sa->jc_gen = sa->generation;
     }
-  }
-  NCD_CUDA(cudaEventRecord(evs[2], st));
-  const bool do_compare = (hm == NCD_MODE_DIRECT) || (mode & NCD_MODE_CONFIRM);
+  const bool do_compare = !fused_small && ((hm == NCD_MODE_DIRECT) || (mode & NCD_MODE_CONFIRM));
   if (do_compare && npairs && ctrl->ntiles) {
     // Three data-movement shapes for the same compare, picked from the mean tile fill
     // (measured on B200, profiles/r01_variants_and_shapes.txt):
@@ -582,11 +713,6 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     //   small records                     k_compare_grouped: controller + 8 shard copies in flight
     //                                     per warp, merged tail tiles
     //   records of a few hundred bytes    k_compare_small: the same, eight lanes per tile, four tiles per warp
-    int variant = ctx->compare_variant;
-    if (variant < 0) {
-      const uint64_t fill = ctrl->len_sum / ctrl->ntiles;
-      variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : (fill >= 700 ? 2 : 16));
-    }
     variant_used = (uint32_t)variant;
     // the merged tile list (tiles up to 6144 B) belongs to the kernels that walk a tile to its end;
     // k_compare and k_compare_tma compare at most 4096 B per tile and take the fixed 4 KB cut
@@ -631,7 +757,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   if (nq) {
     const bool fuse = nblk <= 4096;
     k_classify<<<(unsigned)nblk, 256, 0, st>>>(dctrl, ctx->d_shards, S, nrows, ctrl->row_obj,
-                                               ctrl->row_dep, ctrl->row_cidx, sh_idx, dv, codes,
+                                               ctrl->row_dep, ctrl->row_cidx, sh_idx, dv, tag, codes,
                                                blk_cnt, blk_off, counters, fuse ? 1u : 0u);
     if (!fuse) {
       NCD_TRY(ncd_exclusive_scan_u32(ctx, blk_cnt, blk_off, nblk, counters));

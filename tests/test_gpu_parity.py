@@ -223,13 +223,16 @@ def test_partition_by_key_hash_covers_everything_once(ctx):
     assert kept_total == 500
 
 
-@pytest.mark.parametrize("variant", [0, 1, 2, 8, 16])
+@pytest.mark.parametrize("variant", [0, 1, 2, 8, 16, "16-unfused"])
 def test_every_compare_variant_matches_oracle(variant, monkeypatch):
     """The data-movement shapes of the byte compare (register-staged per shard, grouped, TMA
     bulk-copy pipeline, eight lanes per tile) are picked per scan from the record shapes; forced
     here one by one on records of every size."""
     from nexus_configuration_controller_b200.drift import Context
 
+    if variant == "16-unfused":  # k_join + k_compare_small instead of the fused k_scan_small
+        variant = 16
+        monkeypatch.setenv("NCD_FUSE_SMALL", "0")
     monkeypatch.setenv("NCD_COMPARE_VARIANT", str(variant))
     with Context(0) as c2:
         for seed, nshards in ((7, 3), (8, 9), (9, 17)):
@@ -377,8 +380,10 @@ def test_many_small_objects_fill_the_hash_table(ctx):
 
 
 def test_small_records_take_the_sub_warp_compare(ctx):
-    """Records of a few hundred bytes: the scan picks k_compare_small (variant 16) by itself and
-    decides like the oracle, tails and one-byte differences included."""
+    """Records of a few hundred bytes: the scan picks the fused join + compare kernel (k_scan_small, variant
+    32) by itself in direct mode, k_compare_small (16) behind the hash path's confirm pass, and decides like
+    the oracle, tails and one-byte differences included — on the first scan (probing) and on the second
+    (join answered from the cache the first one filled)."""
     import random
 
     rng = random.Random(31)
@@ -403,8 +408,18 @@ def test_small_records_take_the_sub_warp_compare(ctx):
         shards.append(A.pack(objs))
     want_codes, want_ents = oracle.scan(ctrl, shards)
     codes, ents, st = gpu_scan(ctx, ctrl, shards, A.MODE_DIRECT)
-    assert st.compare_variant == 16
+    assert st.compare_variant == 32
     np.testing.assert_array_equal(codes, want_codes)
     np.testing.assert_array_equal(ents, want_ents)
-    codes, _, _ = gpu_scan(ctx, ctrl, shards, A.MODE_HASH64 | A.MODE_CONFIRM)
+    ca = ctx.arena_from_host(ctrl)
+    sas = [ctx.arena_from_host(h) for h in shards]
+    for _ in range(2):  # the second scan reads the join cache
+        d = ctx.scan(ca, sas, A.MODE_DIRECT)
+        np.testing.assert_array_equal(d.codes(), want_codes)
+        np.testing.assert_array_equal(d.entries(), want_ents)
+        d.close()
+    for a in sas + [ca]:
+        a.close()
+    codes, _, st = gpu_scan(ctx, ctrl, shards, A.MODE_HASH64 | A.MODE_CONFIRM)
+    assert st.compare_variant == 16
     np.testing.assert_array_equal(codes, want_codes)
