@@ -12,8 +12,12 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <algorithm>
+#include <condition_variable>
+#include <functional>
 #include <iterator>
 #include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
 #include <thread>
@@ -75,8 +79,109 @@ struct ArenaHandle {
   ~ArenaHandle() { reset(); }
 };
 
+// A small pool of worker threads shared by every checker of the process: the canonicaliser, the
+// packer's record copies and the per-cluster cache updates are short parallel loops run many times
+// a second, and creating threads for each of them cost more than the loops themselves.  One loop at
+// a time (callers queue on job_mu; lock order is always cache lock, then job_mu); the calling thread
+// works too.  Never destroyed: the workers sleep on a condition variable until the process exits.
+class Workers {
+ public:
+  static Workers& get() {
+    static Workers* w = new Workers();
+    return *w;
+  }
+  int size() const { return (int)threads_.size() + 1; }
+
+  // fn(chunk) for chunk in [0, chunks), on up to `width` threads including the caller.
+  template <class Fn>
+  void run(size_t chunks, int width, Fn&& fn) {
+    if (chunks == 0) return;
+    if (chunks == 1 || width <= 1 || threads_.empty()) {
+      for (size_t k = 0; k < chunks; ++k) fn(k);
+      return;
+    }
+    std::lock_guard<std::mutex> job(job_mu_);
+    std::exception_ptr err;
+    std::mutex err_mu;
+    std::function<void(size_t)> body = [&](size_t k) {
+      try {
+        fn(k);
+      } catch (...) {
+        std::lock_guard<std::mutex> lk(err_mu);
+        if (!err) err = std::current_exception();
+      }
+    };
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      body_ = &body;
+      chunks_ = chunks;
+      next_ = 0;
+      done_ = 0;
+      helpers_ = std::min<size_t>((size_t)width - 1, std::min(threads_.size(), chunks - 1));
+      woken_ = 0;
+      ++epoch_;
+    }
+    cv_.notify_all();
+    work(body, chunks);
+    {
+      std::unique_lock<std::mutex> lk(mu_);
+      idle_.wait(lk, [&] { return done_ == chunks_ && active_ == 0; });
+      body_ = nullptr;
+    }
+    if (err) std::rethrow_exception(err);
+  }
+
+ private:
+  Workers() {
+    unsigned hc = std::thread::hardware_concurrency();
+    if (hc == 0) hc = 4;
+    if (hc > 32) hc = 32;
+    for (unsigned i = 1; i < hc; ++i) threads_.emplace_back([this] { loop(); });
+    for (auto& t : threads_) t.detach();
+  }
+  void work(std::function<void(size_t)>& body, size_t chunks) {
+    for (;;) {
+      size_t k;
+      {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (next_ >= chunks) return;
+        k = next_++;
+      }
+      body(k);
+      std::lock_guard<std::mutex> lk(mu_);
+      if (++done_ == chunks_) idle_.notify_all();
+    }
+  }
+  void loop() {
+    uint64_t seen = 0;
+    for (;;) {
+      std::function<void(size_t)>* body;
+      size_t chunks;
+      {
+        std::unique_lock<std::mutex> lk(mu_);
+        cv_.wait(lk, [&] { return epoch_ != seen; });
+        seen = epoch_;
+        if (!body_ || woken_ >= helpers_) continue;  // this loop needs fewer helpers than there are workers
+        ++woken_;
+        ++active_;
+        body = body_;
+        chunks = chunks_;
+      }
+      work(*body, chunks);
+      std::lock_guard<std::mutex> lk(mu_);
+      if (--active_ == 0) idle_.notify_all();
+    }
+  }
+  std::vector<std::thread> threads_;
+  std::mutex job_mu_, mu_;
+  std::condition_variable cv_, idle_;
+  std::function<void(size_t)>* body_ = nullptr;
+  size_t chunks_ = 0, next_ = 0, done_ = 0, helpers_ = 0, woken_ = 0, active_ = 0;
+  uint64_t epoch_ = 0;
+};
+
 // Runs fn(i) for i in [0, n) on up to `threads` threads (the packer's record copies and the
-// canonicaliser are memory-bound loops over independent records).
+// canonicaliser are memory-bound loops over independent records), in contiguous slices.
 template <class Fn>
 void parallel_for(size_t n, int threads, size_t min_per_thread, Fn fn) {
   size_t t = threads < 1 ? 1 : (size_t)threads;
@@ -85,19 +190,10 @@ void parallel_for(size_t n, int threads, size_t min_per_thread, Fn fn) {
     for (size_t i = 0; i < n; ++i) fn(i);
     return;
   }
-  std::vector<std::thread> th;
-  std::vector<std::exception_ptr> errs(t);
-  for (size_t k = 0; k < t; ++k)
-    th.emplace_back([&, k] {
-      try {
-        for (size_t i = n * k / t; i < n * (k + 1) / t; ++i) fn(i);
-      } catch (...) {
-        errs[k] = std::current_exception();
-      }
-    });
-  for (auto& x : th) x.join();
-  for (auto& e : errs)
-    if (e) std::rethrow_exception(e);
+  const size_t slices = t * 4;  // finer than the thread count: a slow thread does not hold the loop up
+  Workers::get().run(slices, (int)t, [&](size_t k) {
+    for (size_t i = n * k / slices; i < n * (k + 1) / slices; ++i) fn(i);
+  });
 }
 
 // What one Scan has to send to the GPU for a cluster, decided while the cache lock is held and

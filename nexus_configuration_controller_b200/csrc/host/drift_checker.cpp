@@ -18,6 +18,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <sys/mman.h>
 
 #include <algorithm>
 #include <atomic>
@@ -149,27 +150,50 @@ struct Prepared {
 // cached objects keep it alive (shared_ptr) until the next Scan has laid their records out in the
 // pinned arena; then it returns to the pool and the next batch reuses it — already mapped, so the
 // canonicaliser does not pay a page fault per 4 KiB of output the way fresh allocations do.
+struct Slab {
+  uint8_t* p = nullptr;
+  size_t cap = 0;
+};
 struct SlabPool {
   std::mutex mu;
-  std::vector<std::vector<uint8_t>> free_list;
-  static constexpr size_t kKeepBytes = 1ull << 30;  // buffers beyond this in total are returned to the system
-  std::vector<uint8_t> take(size_t bytes) {
-    std::lock_guard<std::mutex> lk(mu);
-    int best = -1;
-    for (size_t i = 0; i < free_list.size(); ++i)
-      if (free_list[i].size() >= bytes && (best < 0 || free_list[i].size() < free_list[best].size())) best = (int)i;
-    std::vector<uint8_t> out;
-    if (best >= 0) {
-      out.swap(free_list[best]);
-      free_list.erase(free_list.begin() + best);
+  std::vector<Slab> free_list;
+  static constexpr size_t kKeepBytes = 4ull << 30;  // buffers beyond this in total go back to the system
+  // At least `bytes`, with headroom so that the next batch of about the same size fits too.  A fresh
+  // buffer is NOT cleared (the canonicaliser's threads touch it first, in parallel) and asks for
+  // huge pages.
+  Slab take(size_t bytes) {
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      int best = -1;
+      for (size_t i = 0; i < free_list.size(); ++i)
+        if (free_list[i].cap >= bytes && (best < 0 || free_list[i].cap < free_list[best].cap)) best = (int)i;
+      if (best >= 0) {
+        Slab out = free_list[best];
+        free_list.erase(free_list.begin() + best);
+        return out;
+      }
     }
-    return out;  // empty: the caller allocates
+    Slab out;
+    out.cap = (bytes + bytes / 8 + (2u << 20)) & ~((size_t)(2u << 20) - 1);
+    void* mem = nullptr;
+    if (posix_memalign(&mem, 2u << 20, out.cap) != 0) throw std::bad_alloc();
+#ifdef MADV_HUGEPAGE
+    madvise(mem, out.cap, MADV_HUGEPAGE);
+#endif
+    out.p = (uint8_t*)mem;
+    return out;
   }
-  void give(std::vector<uint8_t>&& buf) {
-    std::lock_guard<std::mutex> lk(mu);
-    size_t kept = 0;
-    for (const auto& b : free_list) kept += b.size();
-    if (kept + buf.size() <= kKeepBytes) free_list.push_back(std::move(buf));
+  void give(Slab s) {
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      size_t kept = 0;
+      for (const Slab& b : free_list) kept += b.cap;
+      if (kept + s.cap <= kKeepBytes) {
+        free_list.push_back(s);
+        return;
+      }
+    }
+    free(s.p);
   }
 };
 SlabPool g_pool;
@@ -265,12 +289,9 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
   // one slab for the canonical values of the whole batch (a canonical form is as long as its transport form)
   std::vector<uint64_t> off(n + 1, 0);
   for (uint64_t i = 0; i < n; ++i) off[i + 1] = off[i] + (events[i].op == NCDH_EV_PUT ? events[i].value_len : 0);
-  auto slab = std::make_shared<std::vector<uint8_t>>(g_pool.take(off[n]));
-  if (slab->size() < off[n]) slab->resize(off[n]);
-  const std::shared_ptr<const void> hold(slab.get(), [slab](const void*) mutable {
-    g_pool.give(std::move(*slab));  // the last cached object that pointed into it is gone
-    slab.reset();
-  });
+  const Slab slab = g_pool.take(off[n] ? off[n] : 1);
+  const std::shared_ptr<const void> hold(slab.p, [slab](const void*) { g_pool.give(slab); });  // back to the pool when the
+                                                                                               // last cached object lets go
   // canonicalise in parallel, outside the exclusive lock, and look every object up and compare its
   // value with what the cache holds under the SHARED lock: readers and other batches go on, only the
   // short update below is exclusive.  The first event that cannot be canonicalised ends the batch.
@@ -282,7 +303,7 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     parallel_for(n, threads, 8, [&](size_t i) {
       try {
         Prepared& p = evs[i];
-        prepare_event(events[i], &p, slab->data() + off[i], off[i + 1] - off[i]);
+        prepare_event(events[i], &p, slab.p + off[i], off[i + 1] - off[i]);
         ClusterImage* img = c->image(p.cluster);
         if (img && p.op == NCDH_EV_PUT) {
           p.hint = img->precheck(p.skey, *p.info, p.bytes, p.len);
@@ -298,12 +319,31 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
   }
   c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t0) * 1e6), std::memory_order_relaxed);
   const uint64_t good = first_bad.load();
-  int rc;
+  for (uint64_t i = 0; i < good; ++i)
+    if (!c->image(evs[i].cluster)) return fail("ncdh_apply_events: event " + std::to_string(i) + ": no such cluster");
+  // The update itself: the events of different clusters touch different images, so each cluster's
+  // events are applied, in order, by their own worker.
+  std::vector<std::vector<uint32_t>> by_cluster(c->shards.size() + 1);
+  for (uint64_t i = 0; i < good; ++i) by_cluster[(size_t)(evs[i].cluster + 1)].push_back((uint32_t)i);
   {
     std::unique_lock<std::shared_mutex> lk(c->cache_mu);
-    rc = apply_locked(c, evs, good, hold, nullptr);
+    Workers::get().run(by_cluster.size(), threads, [&](size_t k) {
+      ClusterImage* img = c->image((int)k - 1);
+      uint64_t changed_events = 0;
+      for (uint32_t i : by_cluster[k]) {
+        Prepared& p = evs[i];
+        const uint64_t stamp = c->clock.fetch_add(1) + 1;
+        const bool changed = p.op == NCDH_EV_PUT ? img->put(p.skey, std::move(p.info), p.bytes, p.len, hold, stamp, p.hinted ? &p.hint : nullptr)
+                                                 : img->drop(p.info->kind, p.info->key, stamp);
+        changed_events += changed ? 1 : 0;
+      }
+      c->events_since_scan.fetch_add(changed_events, std::memory_order_relaxed);
+    });
   }
-  if (rc != 0) return fail("ncdh_apply_events: " + g_err);
+  parallel_for(n, threads, 256, [&](size_t i) {  // what the events still own is released in parallel too
+    evs[i].info.reset();
+    std::string().swap(evs[i].skey);
+  });
   if (good < n) return fail("ncdh_apply_events: event " + std::to_string(good) + ": " + errs[good]);
   return 0;
 }
