@@ -434,7 +434,7 @@ def run_ours(args):
         peak, peak_src = hbm_peak()
         kern_ms = sum(cmp_ms) / len(cmp_ms)
         achieved = st.algo_bytes / (kern_ms / 1e3) / 1e9  # this rank's kernel over this rank's bytes
-        kernel_name = ({0: "k_compare", 1: "k_compare_grouped<1>", 2: "k_compare_grouped<2>", 4: "k_compare_grouped<4>", 8: "k_compare_tma", 16: "k_compare_small"}.get(st.compare_variant, "k_compare")
+        kernel_name = ({0: "k_compare", 1: "k_compare_grouped<1>", 2: "k_compare_grouped<2>", 4: "k_compare_grouped<4>", 8: "k_compare_tma", 16: "k_compare_small", 32: "k_scan_small"}.get(st.compare_variant, "k_compare")
                        if mode == A.MODE_DIRECT else {"hash64": "k_h64_tiles", "sha256": "k_sha256", "xxh64": "k_xxh64"}[args.mode])
         traffic, traffic_src = ncu_traffic(args.workload, kernel_name, world, args.groups is None and not os.environ.get("NCD_BENCH_LEN"))
         result = {

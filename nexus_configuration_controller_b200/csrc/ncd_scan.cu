@@ -316,10 +316,16 @@ k_compare_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
 // against vector v of every shard copy, all loads of a step issued before any is used.  Verdict,
 // shard index and tag go out for k_classify; no tile list, no offsets round trip.
 // Correct for any record length (the lanes loop over the whole record); chosen when records are small.
-template <int G>
+// LPO lanes own one object (4 for records up to about a hundred bytes, where eight lanes would
+// leave half of them without a vector; 8 otherwise); a lane answers the join for G / LPO shards.
+// When the join is cached and the shards fit one group, the cached indices of the NEXT object are
+// requested while the current one is compared, which takes one level out of the dependent chain
+// (index -> object line -> payload) every object otherwise waits through.
+template <int G, int LPO>
 __global__ void __launch_bounds__(256, G == 8 ? 3 : 4)
 k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t* __restrict__ sh_idx,
              uint8_t* __restrict__ dv, uint32_t* __restrict__ tag) {
+  constexpr int SLOTS = G / LPO;  // shards a lane joins per group of G
   struct ShardRef {
     const uint8_t* payload;
     const ObjMeta* meta;
@@ -331,51 +337,77 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
   for (uint32_t s = threadIdx.x; s < S; s += blockDim.x)
     s_sh[s] = ShardRef{shards[s].payload, shards[s].meta, shards[s].join_cache, shards[s].join_cache_out};
   __syncthreads();
-  const uint32_t lane = threadIdx.x & 31, l8 = lane & 7;
-  const uint32_t gmask = 0xFFu << (lane & 24);  // the eight lanes of this object
-  const uint64_t group0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-  const uint64_t ngroups = ((uint64_t)gridDim.x * blockDim.x) >> 3;
+  const uint32_t lane = threadIdx.x & 31, l = lane & (LPO - 1), base = lane & ~(uint32_t)(LPO - 1);
+  const uint32_t gmask = (LPO == 8 ? 0xFFu : 0xFu) << base;  // the lanes of this object
+  const uint64_t group0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LPO;
+  const uint64_t ngroups = ((uint64_t)gridDim.x * blockDim.x) / LPO;
+  const bool prefetch = S <= (uint32_t)G && S > 0 && s_sh[0].join_cache != nullptr;  // all shards cached or none (ncd_scan)
+  uint32_t idx_next[SLOTS];
+#pragma unroll
+  for (int j = 0; j < SLOTS; ++j) {
+    const uint32_t s = l + j * LPO;
+    idx_next[j] = (prefetch && s < S && group0 < ctrl.nobj) ? s_sh[s].join_cache[group0] : NCD_NOTFOUND;
+  }
   for (uint64_t c = group0; c < ctrl.nobj; c += ngroups) {
     const ObjMeta& q = ctrl.meta[c];
     const uint32_t len = q.rec_len;
     const uint32_t nvec = (len + 15) >> 4, tail = len & 15;
     const uint4* cp = reinterpret_cast<const uint4*>(ctrl.payload + q.rec_off);
+    uint32_t idx_cur[SLOTS];
+#pragma unroll
+    for (int j = 0; j < SLOTS; ++j) idx_cur[j] = idx_next[j];
+    if (prefetch && c + ngroups < ctrl.nobj) {
+#pragma unroll
+      for (int j = 0; j < SLOTS; ++j) {
+        const uint32_t s = l + j * LPO;
+        if (s < S) idx_next[j] = s_sh[s].join_cache[c + ngroups];
+      }
+    }
     for (uint32_t s0 = 0; s0 < S; s0 += G) {
-      // ---- join: lane l8 < G answers for shard s0 + l8
-      const uint32_t s = s0 + l8;
-      uint32_t idx = NCD_NOTFOUND, tg = NCD_TAG_ROGUE;
-      uint8_t v = DV_NOTFOUND;
-      const uint4* mine = nullptr;  // this lane's shard copy, when its bytes have to be compared
-      if (l8 < G && s < S) {
-        const ShardRef sr = s_sh[s];
-        if (sr.join_cache) {
-          idx = sr.join_cache[c];
-        } else {
-          idx = ncd_probe_meta(shards[s], q, ctrl.aux);
-          if (sr.join_cache_out) sr.join_cache_out[c] = idx;
-        }
-        if (idx != NCD_NOTFOUND) {
-          const uint4* line = reinterpret_cast<const uint4*>(sr.meta + idx);
-          const uint4 w0 = line[0], w1 = line[1];  // keyhash | rec_off ; rec_len key_off key_len/kind tag
-          tg = w1.w;
-          if (w1.x != len) {
-            v = DV_DIFF;  // the encoding is injective: different lengths cannot be DeepEqual
+      // ---- join: this lane answers for shards s0 + l, s0 + l + LPO, ...
+      uint32_t idx[SLOTS], tg[SLOTS];
+      uint8_t v[SLOTS];
+      const uint4* mine[SLOTS];  // this lane's shard copies, where bytes have to be compared
+#pragma unroll
+      for (int j = 0; j < SLOTS; ++j) {
+        const uint32_t s = s0 + l + j * LPO;
+        idx[j] = NCD_NOTFOUND;
+        tg[j] = NCD_TAG_ROGUE;
+        v[j] = DV_NOTFOUND;
+        mine[j] = nullptr;
+        if (s < S) {
+          const ShardRef sr = s_sh[s];
+          if (prefetch) {
+            idx[j] = idx_cur[j];
+          } else if (sr.join_cache) {
+            idx[j] = sr.join_cache[c];
           } else {
-            v = DV_EQUAL;
-            mine = reinterpret_cast<const uint4*>(sr.payload + ((uint64_t)w0.z | ((uint64_t)w0.w << 32)));
+            idx[j] = ncd_probe_meta(shards[s], q, ctrl.aux);
+            if (sr.join_cache_out) sr.join_cache_out[c] = idx[j];
+          }
+          if (idx[j] != NCD_NOTFOUND) {
+            const uint4* line = reinterpret_cast<const uint4*>(sr.meta + idx[j]);
+            const uint4 w0 = line[0], w1 = line[1];  // keyhash | rec_off ; rec_len key_off key_len/kind tag
+            tg[j] = w1.w;
+            if (w1.x != len) {
+              v[j] = DV_DIFF;  // the encoding is injective: different lengths cannot be DeepEqual
+            } else {
+              v[j] = DV_EQUAL;
+              mine[j] = reinterpret_cast<const uint4*>(sr.payload + ((uint64_t)w0.z | ((uint64_t)w0.w << 32)));
+            }
           }
         }
       }
-      // ---- compare: the eight lanes walk the record against the G shard copies together
+      // ---- compare: the lanes walk the record against the G shard copies together
       const uint4* sp[G];
       uint32_t x[G];
 #pragma unroll
-      for (int k = 0; k < G; ++k) {
-        const unsigned long long p = __shfl_sync(gmask, (unsigned long long)mine, (lane & 24) + k);
+      for (int k = 0; k < G; ++k) {  // shard s0 + k was joined by lane k % LPO in its slot k / LPO
+        const unsigned long long p = __shfl_sync(gmask, (unsigned long long)mine[k / LPO], base + (k % LPO));
         sp[k] = reinterpret_cast<const uint4*>(p);
         x[k] = 0;
       }
-      for (uint32_t vv = l8; vv < nvec; vv += 8) {
+      for (uint32_t vv = l; vv < nvec; vv += LPO) {
         uint4 a = ncd_ldg_stream(cp + vv);
         uint4 b[G];
 #pragma unroll
@@ -391,19 +423,64 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
 #pragma unroll
       for (int k = 0; k < G; ++k) {
         const uint32_t differs = __ballot_sync(gmask, x[k] != 0) & gmask;
-        if (differs && l8 == (uint32_t)k) v = DV_DIFF;  // sp[k] was null for every lane unless lane k set it
+        if (differs && l == (uint32_t)(k % LPO)) v[k / LPO] = DV_DIFF;  // sp[k] is null unless that lane found bytes to compare
       }
-      if (l8 < G && s < S) {
-        const uint64_t p = c * S + s;
-        sh_idx[p] = idx;
-        dv[p] = v;
-        tag[p] = tg;
+#pragma unroll
+      for (int j = 0; j < SLOTS; ++j) {
+        const uint32_t s = s0 + l + j * LPO;
+        if (s < S) {
+          const uint64_t p = c * S + s;
+          sh_idx[p] = idx[j];
+          dv[p] = v[j];
+          tag[p] = tg[j];
+        }
       }
     }
   }
 }
 
 // ------------------------------------------------------------------ k_classify
+// One thread per ROW, walking the row's shards: the row's controller index, dependent entry and
+// owning template are read once, the verdicts and tags of its S pairs are contiguous, and the grid
+// is rows / 256 blocks instead of rows x shards / 256 (the compaction's block scan stays in one
+// block for up to a million rows).
+__device__ __forceinline__ uint32_t decide_pair(const DevArena* __restrict__ shards, uint32_t S, uint32_t s, uint32_t obj,
+                                                uint32_t dep, uint32_t cidx, const uint32_t* __restrict__ sh_idx,
+                                                const uint8_t* __restrict__ dv, const uint32_t* __restrict__ tag) {
+  if (dep == NCD_NOTFOUND) {
+    // template (:792-808) or workgroup (:722-738) row
+    const uint8_t v = dv[(uint64_t)cidx * S + s];
+    return v == DV_NOTFOUND ? NCD_CREATE : (v == DV_DIFF ? NCD_UPDATE_DATA : NCD_SKIP);
+  }
+  if (cidx == NCD_NOTFOUND) return NCD_ERR_MISSING_REF;  // :509-514, :571-576
+  const uint64_t p = (uint64_t)cidx * S + s;
+  const uint8_t v = dv[p];
+  if (v == DV_NOTFOUND) return NCD_CREATE;  // :518-520, :580-582
+  // The join left each shard object's ownership tag beside its verdict (ObjMeta.tag): the single
+  // ownerReference of a dependent, the interned UID of a template.  The common cases are decided
+  // from those two words; only a dependent with several ownerReferences walks its list.
+  const uint32_t mine = tag[p];
+  if (mine == NCD_TAG_ROGUE) return NCD_ERR_ROGUE;  // :494-499, checked before the data compare (:529 before :539)
+  // isMissingOwnership(:484-502) against the shard's copy of the owning template.  A template that
+  // is about to be created on this shard has a UID no existing ownerReference can carry, so the
+  // reference is missing by definition.
+  const uint64_t tp = (uint64_t)obj * S + s;
+  bool missing = true;
+  if (dv[tp] != DV_NOTFOUND) {
+    // UIDs were interned at commit: equal ids <=> byte-equal strings (ncd_index.cu)
+    const uint32_t want = tag[tp] | 0x80000000u;  // Kind == NexusAlgorithmTemplate && same UID
+    if (mine != NCD_TAG_MANY) {
+      missing = mine != want;
+    } else {
+      const DevArena& sh = shards[s];
+      const uint32_t j = sh_idx[p];
+      for (uint32_t o = sh.own_start[j]; o < sh.own_start[j + 1] && missing; ++o)
+        if (sh.own_packed[o] == want) missing = false;
+    }
+  }
+  return (v == DV_DIFF ? NCD_UPDATE_DATA : 0u) | (missing ? NCD_UPDATE_OWNER : 0u);
+}
+
 __global__ void __launch_bounds__(256)
 k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint64_t nrows,
            const uint32_t* __restrict__ row_obj, const uint32_t* __restrict__ row_dep,
@@ -411,64 +488,32 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
            const uint8_t* __restrict__ dv, const uint32_t* __restrict__ tag, uint8_t* __restrict__ codes,
            uint32_t* __restrict__ blk_cnt, uint32_t* __restrict__ blk_off, uint32_t* __restrict__ counters,
            uint32_t fuse_scan) {
-  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t code = NCD_SKIP;
-  if (q < nrows * S) {
-    const uint32_t r = (uint32_t)(q / S), s = (uint32_t)(q % S);
-    const uint32_t cidx = row_cidx[r], dep = row_dep[r];
-    if (dep == NCD_NOTFOUND) {
-      // template (:792-808) or workgroup (:722-738) row
-      const uint8_t v = dv[(uint64_t)cidx * S + s];
-      code = v == DV_NOTFOUND ? NCD_CREATE : (v == DV_DIFF ? NCD_UPDATE_DATA : NCD_SKIP);
-    } else if (cidx == NCD_NOTFOUND) {
-      code = NCD_ERR_MISSING_REF;  // :509-514, :571-576
-    } else {
-      const uint64_t p = (uint64_t)cidx * S + s;
-      const uint8_t v = dv[p];
-      if (v == DV_NOTFOUND) {
-        code = NCD_CREATE;  // :518-520, :580-582
-      } else {
-        // The join left each shard object's ownership tag beside its verdict (ObjMeta.tag): the
-        // single ownerReference of a dependent, the interned UID of a template.  The common cases
-        // are decided from those two words; only a dependent with several ownerReferences walks
-        // its list in the shard's arena.
-        const uint32_t mine = tag[p];
-        if (mine == NCD_TAG_ROGUE) {
-          code = NCD_ERR_ROGUE;  // :494-499, checked before the data compare (:529 before :539)
-        } else {
-          // isMissingOwnership(:484-502) against the shard's copy of the owning template.  A
-          // template that is about to be created on this shard has a UID no existing
-          // ownerReference can carry, so the reference is missing by definition.
-          const uint32_t obj = row_obj[r];
-          const uint64_t tp = (uint64_t)obj * S + s;
-          bool missing = true;
-          if (dv[tp] != DV_NOTFOUND) {
-            // UIDs were interned at commit: equal ids <=> byte-equal strings (ncd_index.cu)
-            const uint32_t want = tag[tp] | 0x80000000u;  // Kind == NexusAlgorithmTemplate && same UID
-            if (mine != NCD_TAG_MANY) {
-              missing = mine != want;
-            } else {
-              const DevArena& sh = shards[s];
-              const uint32_t j = sh_idx[p];
-              for (uint32_t o = sh.own_start[j]; o < sh.own_start[j + 1] && missing; ++o)
-                if (sh.own_packed[o] == want) missing = false;
-            }
-          }
-          code = (v == DV_DIFF ? NCD_UPDATE_DATA : 0u) | (missing ? NCD_UPDATE_OWNER : 0u);
-        }
-      }
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t mine = 0;
+  if (r < nrows) {
+    const uint32_t obj = row_obj[r], dep = row_dep[r], cidx = row_cidx[r];
+    for (uint32_t s = 0; s < S; ++s) {
+      const uint32_t code = decide_pair(shards, S, s, obj, dep, cidx, sh_idx, dv, tag);
+      codes[r * S + s] = (uint8_t)code;
+      mine += code != NCD_SKIP;
     }
-    codes[q] = (uint8_t)code;
   }
-  const int cnt = __syncthreads_count(code != NCD_SKIP);
+  // entries this block will emit
+  __shared__ uint32_t wsum[8];
+  uint32_t w = mine;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) w += __shfl_xor_sync(0xffffffffu, w, d);
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = w;
+  __syncthreads();
   // Small grids (launch-latency bound scans): the block that finishes last turns the per-block
   // counts into offsets (exclusive scan) and the total into counters[0], so the ordered compaction
-  // needs no separate scan launches.  Large grids keep the three-launch scan: a fence and a
-  // ticket per block cost more there than the launches do.
+  // needs no separate scan launches.  Large grids keep the three-launch scan.
   __shared__ bool is_last;
   __shared__ uint32_t part[256];
   if (threadIdx.x == 0) {
-    blk_cnt[blockIdx.x] = (uint32_t)cnt;
+    uint32_t cnt = 0;
+    for (int k = 0; k < 8; ++k) cnt += wsum[k];
+    blk_cnt[blockIdx.x] = cnt;
     if (!fuse_scan) return;
     __threadfence();
     is_last = atomicAdd(&counters[2], 1u) == gridDim.x - 1;
@@ -504,8 +549,9 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
 }
 
 // ------------------------------------------------------------------ k_emit
-// Same block shape as k_classify; blk_off is the exclusive scan of blk_cnt, so the list comes
-// out in (row, shard) order — the order the reference walks (template, then its dependents).
+// Same block shape as k_classify (a thread per row); blk_off is the exclusive scan of blk_cnt, so
+// the list comes out in (row, shard) order — the order the reference walks (template, then its
+// dependents, shard by shard).
 __global__ void __launch_bounds__(256)
 k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ row_obj,
        const uint32_t* __restrict__ row_dep, const uint8_t* __restrict__ codes,
@@ -520,23 +566,34 @@ k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ r
     hdr[3] = n > cap ? 1u : 0u;
   }
   __shared__ uint32_t warp_cnt[8];
-  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t code = q < nrows * S ? codes[q] : 0u;
-  const uint32_t bal = __ballot_sync(0xffffffffu, code != 0);
-  if (lane == 0) warp_cnt[warp] = __popc(bal);
+  uint32_t mine = 0;
+  if (r < nrows)
+    for (uint32_t s = 0; s < S; ++s) mine += codes[r * S + s] != 0;
+  // exclusive scan of the per-row counts inside the block
+  uint32_t incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= (uint32_t)d) incl += o;
+  }
+  if (lane == 31) warp_cnt[warp] = incl;
   __syncthreads();
-  if (code != 0) {
-    uint32_t pos = blk_off[blockIdx.x] + __popc(bal & ((1u << lane) - 1u));
-    for (uint32_t w = 0; w < warp; ++w) pos += warp_cnt[w];
-    const uint32_t r = (uint32_t)(q / S), s = (uint32_t)(q % S);
-    const uint32_t obj = row_obj[r], dep = row_dep[r];
-    ncd_entry e;
-    e.obj = obj;
-    e.dep = dep == NCD_NOTFOUND ? 0u : dep - ctrl.dep_start[obj] + 1u;
+  if (mine == 0) return;
+  uint32_t pos = blk_off[blockIdx.x] + incl - mine;
+  for (uint32_t w = 0; w < warp; ++w) pos += warp_cnt[w];
+  const uint32_t obj = row_obj[r], dep = row_dep[r];
+  ncd_entry e;
+  e.obj = obj;
+  e.dep = dep == NCD_NOTFOUND ? 0u : dep - ctrl.dep_start[obj] + 1u;
+  for (uint32_t s = 0; s < S; ++s) {
+    const uint32_t code = codes[r * S + s];
+    if (code == 0) continue;
     e.shard = s;
     e.code = code;
     if (pos < cap) out[pos] = e;  // a caller-sized buffer may be too small: the header says so
+    ++pos;
   }
 }
 
@@ -650,7 +707,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   algo += ctrl->len_sum;
 
   // scratch: sh_off u64[npairs] | sh_idx u32[npairs] | tag u32[npairs] | blk_cnt u32[nblk+1] | blk_off u32[nblk+1] | dv u8[npairs]
-  const uint64_t nblk = (nq + 255) / 256;
+  const uint64_t nblk = (nrows + 255) / 256;  // k_classify / k_emit: a thread per row
   size_t o_off = 0;
   size_t o_idx = o_off + ncd_align_up(npairs * 8, 256);
   size_t o_tag = o_idx + ncd_align_up(npairs * 4, 256);
@@ -687,12 +744,19 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   }
   NCD_CUDA(cudaEventRecord(evs[2], st));
   if (fused_small) {
-    const uint64_t want = (nc * 8 + 255) / 256, cap = (uint64_t)ctx->sm_count * 16;
+    // four lanes per object for records of about a hundred bytes or less, eight otherwise
+    const bool narrow = nc && ctrl->len_sum / nc <= 128;
+    const uint64_t lpo = narrow ? 4 : 8;
+    const uint64_t want = (nc * lpo + 255) / 256, cap = (uint64_t)ctx->sm_count * 16;
+    const unsigned grid = (unsigned)(want < cap ? want : cap);
     const size_t smem = (size_t)S * 32;
-    if (S <= 4)
-      k_scan_small<4><<<(unsigned)(want < cap ? want : cap), 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
-    else
-      k_scan_small<8><<<(unsigned)(want < cap ? want : cap), 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+    if (S <= 4) {
+      if (narrow) k_scan_small<4, 4><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+      else k_scan_small<4, 4><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+    } else {
+      if (narrow) k_scan_small<8, 4><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+      else k_scan_small<8, 8><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+    }
     ++launches;
     variant_used = 32;
   }
