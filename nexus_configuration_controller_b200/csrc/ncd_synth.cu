@@ -144,7 +144,9 @@ __global__ void k_meta(SynthDev s, const uint32_t* __restrict__ gsel, ncd_arena_
   d.key_len[pos] = make_key(s, g, j, dr.missing, slot);
   d.uid_off[pos] = (uint32_t)(pos * SLOT + UID_AT);
   d.uid_len[pos] = make_uid(s, g, j, slot + UID_AT);
-  own_cnt[pos] = (s.role >= 0 && j > 0 && !dr.rogue) ? 1u : 0u;
+  // dependents carry their template's ownerReference: on a shard unless the drift says rogue, on the
+  // controller always (a controller cluster whose references adoptReferences, controller.go:647-695, has adopted)
+  own_cnt[pos] = (j > 0 && (s.role < 0 || !dr.rogue)) ? 1u : 0u;
   logical[pos] = (uint32_t)i;
   if (s.role < 0) {
     // dependents of the template: secrets first, then configmaps (GetSecretNames /
@@ -339,7 +341,7 @@ extern "C" int ncd_synth_sizes(ncd_ctx* ctx, const ncd_synth_cfg* cfg, int role,
   if (payload_bytes) *payload_bytes = h_sum;
   if (nobj) *nobj = s.n;
   if (aux_bytes) *aux_bytes = (s.n + 1) * SLOT;
-  if (nowner) *nowner = role < 0 ? 0 : nsel * s.nd;
+  if (nowner) *nowner = nsel * s.nd;
   if (ndep) *ndep = role < 0 ? nsel * s.nd : 0;
   return NCD_OK;
 }
@@ -358,7 +360,7 @@ extern "C" int ncd_synth_fill(ncd_ctx* ctx, ncd_arena* a, const ncd_synth_cfg* c
   SynthDev s;
   make_dev(cfg, role, nsel, &s);
   const uint64_t n = s.n;
-  if (n > a->nobj_cap || (n + 1) * SLOT > a->aux_cap || (role >= 0 && nsel * s.nd > a->nowner_cap) ||
+  if (n > a->nobj_cap || (n + 1) * SLOT > a->aux_cap || nsel * s.nd > a->nowner_cap ||
       (role < 0 && nsel * s.nd > a->ndep_cap)) {
     cudaFreeAsync(gsel, st);
     ncd_set_error("ncd_synth_fill: arena too small for %llu objects (size it with ncd_synth_sizes)",

@@ -61,3 +61,43 @@ def test_orphans_are_the_set_difference_of_keys(ctx, seed):
     assert len(ctx.find_orphans(ca, [ca])) == 0
     for a in sas + [ca]:
         a.close()
+
+
+@pytest.mark.parametrize("seed", [6, 7])
+def test_unadopted_references_match_the_oracle(ctx, seed):
+    """ncd_find_unadopted (adoptReferences, controller.go:647-695, as a list) against the CPU restatement: a
+    controller cluster whose dependents are owned by their template, by another template, by several, by a
+    non-template owner with the same UID (isOwnedBy compares UIDs only), or by nobody; dangling references."""
+    import ctypes as C
+    import random
+
+    rng = random.Random(seed)
+    objs, names = [], []
+    for t in range(40):
+        deps = []
+        for k, kind in ((0, A.KIND_SECRET), (1, A.KIND_CONFIGMAP), (2, A.KIND_SECRET)):
+            key = f"default/dep-{t}-{k}"
+            deps.append((kind, key))
+            how = rng.randrange(6)
+            if how == 0:
+                continue  # dangling: the controller does not hold it
+            owners = {1: [], 2: [(True, f"uid-{t}")], 3: [(True, "uid-other")], 4: [(True, "uid-x"), (False, f"uid-{t}"), (True, "uid-y")],
+                      5: [(False, f"uid-{t}")]}[how]
+            objs.append(A.CachedObject(kind, key, b"v", owners=owners))
+        deps.sort(key=lambda d: d[0])
+        objs.append(A.CachedObject(A.KIND_TEMPLATE, f"default/algo-{t}", b"spec", uid=f"uid-{t}", deps=deps))
+    rng.shuffle(objs)
+    host = A.pack(objs)
+    want = oracle.unadopted(host)
+    assert len(want) > 10
+    a = ctx.arena_from_host(host)
+    out = np.zeros((len(want) + 8, 2), dtype=np.uint32)
+    n = C.c_uint64()
+    from nexus_configuration_controller_b200 import _ffi
+
+    _ffi.check(ctx.lib.ncd_find_unadopted(ctx.handle, a.handle, out.ctypes.data_as(_ffi.u32p), len(out), C.byref(n)))
+    np.testing.assert_array_equal(out[: n.value], want)
+    # a buffer that is too small: the count is still the whole answer
+    _ffi.check(ctx.lib.ncd_find_unadopted(ctx.handle, a.handle, out.ctypes.data_as(_ffi.u32p), 3, C.byref(n)))
+    assert n.value == len(want)
+    a.close()
