@@ -159,6 +159,48 @@ def api_bound_model(templates: int, shards: int, writes: float) -> dict:
     }
 
 
+def gathered_matches_spec(parts, workload, groups, S, world) -> bool:
+    """N > 1: the gathered diff lists, mapped back from every rank's local object numbering to the object
+    numbering of the UN-partitioned config, against the decisions the generator's drift function implies
+    (tests/synth_spec.py: plain numpy, no arenas, no payload) — content, not only the count."""
+    import numpy as np
+
+    from tests import synth_spec as SS
+
+    cfg, _ = make_cfg(workload, groups=groups)
+    per = 1 + cfg.n_secrets + cfg.n_configmaps
+    want = SS.expected_codes_np(cfg, S)
+    # rank of every group: ncd_keyhash(TEMPLATE, "nexus/t-%010d") % world, vectorised FNV-1a + fmix64
+    g = np.arange(cfg.groups, dtype=np.uint64)
+    digits = [(g // np.uint64(10 ** (9 - k))) % np.uint64(10) + np.uint64(48) for k in range(10)]
+    h = np.full(cfg.groups, 0xCBF29CE484222325, dtype=np.uint64)
+    P = np.uint64(0x100000001B3)
+    with np.errstate(over="ignore"):
+        h = (h ^ np.uint64(0)) * P  # kind byte (template)
+        for b in b"nexus/t-":
+            h = (h ^ np.uint64(b)) * P
+        for d in digits:
+            h = (h ^ d) * P
+        h ^= h >> np.uint64(33)
+        h *= np.uint64(0xFF51AFD7ED558CCD)
+        h ^= h >> np.uint64(33)
+        h *= np.uint64(0xC4CEB9FE1A85EC53)
+        h ^= h >> np.uint64(33)
+    rank_of = (h % np.uint64(world)).astype(np.int64)
+    got = np.zeros_like(want)
+    for r, (ns, rows, ents) in enumerate(parts):
+        if ns != S or len(ents) == 0:
+            if ns != S:
+                return False
+            continue
+        gsel = np.nonzero(rank_of == r)[0]
+        if rows != len(gsel) * per or np.any(ents[:, 0] % per != 0):
+            return False
+        grow = gsel[ents[:, 0] // per] * per + ents[:, 1]
+        got[grow, ents[:, 2]] = ents[:, 3].astype(np.uint8)
+    return bool(np.array_equal(got, want))
+
+
 def ncu_traffic(workload: str, kernel: str, n_gpus: int, default_size: bool):
     """DRAM bytes per launch of the dominant kernel from the committed ncu capture, if one matches."""
     try:
@@ -413,10 +455,14 @@ def run_ours(args):
     if hdr[3]:
         raise RuntimeError(f"diff list of {hdr[0]} entries exceeds --gather-cap {cap_entries}")
     assert int(hdr[0]) == st.ndiff
-    gathered_total = None
+    gathered_total, gathered_ok, rank_scan_ms = None, None, None
     if dist:
         parts = M.unpack_gathered(gathered if xchg is not None else recvbuf.cpu().numpy().view(np.uint32), world, cap_entries)
         gathered_total = sum(len(e) for _, _, e in parts)
+        gathered_ok = gathered_matches_spec(parts, args.workload, args.groups, S, world) if rank == 0 else None
+        per_rank = [torch.zeros(1, device=f"cuda:{local}") for _ in range(world)]
+        dist.all_gather(per_rank, torch.tensor([sum(tot_ms) / len(tot_ms)], device=f"cuda:{local}"))
+        rank_scan_ms = [round(float(x.item()), 4) for x in per_rank]
         t = torch.tensor([elapsed_ms], device=f"cuda:{local}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed_ms = float(t.item())
@@ -446,6 +492,8 @@ def run_ours(args):
                 "shards": S, "partition": f"ncd_keyhash(template key) % {world}" if world > 1 else "none",
                 "algorithmic_bytes": algo_all, "l2": "inputs >> 126 MB L2, no flush needed", "setup_s": round(setup_s, 2),
                 "diff_entries": ndiff_all, "diff_entries_after_allgather": gathered_total,
+                "gathered_identical": gathered_ok if world > 1 else None,
+                "rank_scan_ms": rank_scan_ms if world > 1 else None,
                 "exchange": None if world == 1 else ("peer-memory stores over NVLink (k_exchange)" if xchg is not None else "nccl all_gather_into_tensor" + (f" ({xchg_note})" if xchg_note else "")),
             },
             "gb_per_s": algo_all / (ms_per_step / 1e3) / 1e9,

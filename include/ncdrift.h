@@ -274,7 +274,7 @@ int ncd_scan_host(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* s
 /* ---- exchange of diff lists between GPUs through peer memory (ncd_exchange.cu) ----------------
  * The multi-GPU drift check partitions objects by key hash (ncd_keyhash % world) and ends with
  * every rank holding every rank's diff list.  An ncd_xchg is one rank's end of that exchange:
- * a device buffer of [2 generations][world slots][header + cap_entries entries] that peers write
+ * a device buffer of [3 generations][world slots][header + cap_entries entries] that peers write
  * into directly over NVLink.  No reference counterpart: the reference is a single CPU process
  * (controller.go:790-831 loops over the shards); this replaces a library all-gather.
  *
@@ -284,15 +284,17 @@ int ncd_scan_host(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* s
  *   ranks in one process:         ncd_xchg_buffer -> ncd_xchg_connect(all buffers, rank order;
  *                                 needs peer access between the devices, or the same device)
  * Per step:       ncd_scan_exchange (asynchronous: scan, compaction into this rank's slot, one
- *                 kernel that stores the slot into every peer's buffer, flags it and waits for
- *                 the peers' flags), then ncd_xchg_fetch (host copy: headers and the entries each
- *                 slot really holds; the rest of host_out is left as it was) or ncd_xchg_result + ncd_sync
- *                 (device view): world x (16 + 16 * cap_entries) bytes, slot r = rank r's list in
- *                 ncd_diff_pack layout.
- * Rules: every rank calls ncd_scan_exchange the same number of times; use a gathered list (or
- * enqueue its use on the ctx stream) before the next ncd_scan_exchange on that context; a peer
- * that does not arrive within the timeout (default 10 s) makes ncd_xchg_fetch fail with
- * NCD_E_STATE instead of hanging the GPU. */
+ *                 kernel that stores the slot into every peer's buffer, flags it, and waits for
+ *                 the peers' lists of the PREVIOUS step: ranks run up to one step apart instead of
+ *                 meeting in every step), then, to use the lists of THIS step: ncd_xchg_fetch (waits
+ *                 for the peers' flags of this step, then copies the headers and the entries each
+ *                 slot really holds to the host; the rest of host_out is left as it was), or
+ *                 ncd_xchg_wait + ncd_xchg_result (device view, ordered on the ctx stream): world x
+ *                 (16 + 16 * cap_entries) bytes, slot r = rank r's list in ncd_diff_pack layout.
+ * Rules: every rank calls ncd_scan_exchange the same number of times; a gathered list stays
+ * intact until two more ncd_scan_exchange have been enqueued on that context; a peer that does
+ * not arrive within the timeout (default 10 s) makes ncd_xchg_fetch fail with NCD_E_STATE
+ * instead of hanging the GPU. */
 int ncd_xchg_create(ncd_ctx* ctx, int world, int rank, uint64_t cap_entries, ncd_xchg** out);
 int ncd_xchg_buffer(ncd_xchg* x, void** dev_ptr, uint64_t* bytes);
 int ncd_xchg_handle(ncd_xchg* x, void* handle64);
@@ -300,6 +302,7 @@ int ncd_xchg_open(ncd_xchg* x, const void* handles /* world x 64 bytes; own entr
 int ncd_xchg_connect(ncd_xchg* x, void* const* peer_bufs /* world pointers; own entry ignored */);
 int ncd_scan_exchange(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* const* shards, int nshards,
                       uint32_t mode, ncd_xchg* x);
+int ncd_xchg_wait(ncd_xchg* x);
 int ncd_xchg_result(ncd_xchg* x, const void** dev_ptr, uint64_t* bytes);
 int ncd_xchg_fetch(ncd_xchg* x, void* host_out, uint64_t bytes);
 int ncd_xchg_set_timeout(ncd_xchg* x, double seconds);

@@ -132,6 +132,7 @@ PROTOTYPES = {
     "ncd_xchg_open": (C.c_int, [VP, VP]),
     "ncd_xchg_connect": (C.c_int, [VP, C.POINTER(VP)]),
     "ncd_scan_exchange": (C.c_int, [VP, VP, C.POINTER(VP), C.c_int, C.c_uint32, VP]),
+    "ncd_xchg_wait": (C.c_int, [VP]),
     "ncd_xchg_result": (C.c_int, [VP, C.POINTER(VP), u64p]),
     "ncd_xchg_fetch": (C.c_int, [VP, VP, C.c_uint64]),
     "ncd_xchg_set_timeout": (C.c_int, [VP, C.c_double]),

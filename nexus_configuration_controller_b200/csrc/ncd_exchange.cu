@@ -7,14 +7,17 @@
 // into the same slot of every peer's buffer over NVLink, raises a flag there, and waits for the
 // peer's flag in the local buffer.  No host round trip, no extra stream, nothing allocated per step.
 //
-//   buffer of one rank:  [2 generations][world slots][16-byte header + cap entries]
-//                        flags  u32 [2][world]   (sequence number of the list the slot holds)
+//   buffer of one rank:  [3 generations][world slots][16-byte header + cap entries]
+//                        flags  u32 [3][world]   (sequence number of the list the slot holds)
 //                        error  u32              (1 = a wait timed out)
 //
-// Two generations alternate by step.  A peer overwrites generation g of step t only at its step
-// t+2, which it starts after it has seen this rank's step t+1 list, which this rank pushes after
-// everything it enqueued before its scan t+1 — so a reader that enqueues its use of a gathered list
-// on the ctx stream before the next ncd_scan_exchange never sees a torn list.
+// Step t pushes this rank's list into generation t % 3 of every peer and then waits for the peers'
+// lists of step t - 1, not of step t: the ranks run up to one step apart, so the slowest rank of a
+// step (the key-hash partition balances bytes only statistically) no longer stalls everybody in
+// every step.  The list of step t is complete once ncd_xchg_wait (or ncd_xchg_fetch, which calls
+// it) has seen the peers' flags of step t.  A peer writes generation g again only at its step
+// t + 3, which it cannot start before this rank has pushed step t + 2: a gathered list stays intact
+// until this rank has enqueued two more exchanges.
 //
 // No reference counterpart: the reference is one process on CPU (controller.go:790-831 walks the
 // shards in a loop); this replaces the NCCL all-gather of the first multi-GPU version.
@@ -35,7 +38,7 @@ struct ncd_xchg {
   bool opened[NCD_XCHG_MAX_WORLD];     // mapped with cudaIpcOpenMemHandle (to be closed)
   uint8_t** d_peers;                   // device copy of peers[]
   bool connected;
-  uint32_t seq;  // steps exchanged so far; step t uses generation t & 1 and flag value t
+  uint32_t seq;  // steps exchanged so far; step t uses generation t % 3 and flag value t
   uint64_t timeout_ns;
 };
 
@@ -57,9 +60,30 @@ __device__ __forceinline__ uint64_t now_ns() {
 
 // Block b serves one peer: push this rank's list into the peer's buffer, flag it, then wait until
 // the peer's list for the same step has arrived here.
+__device__ __forceinline__ void wait_flag(uint8_t* mine, uint64_t flags_off, uint64_t err_off, uint32_t slot, uint32_t seq,
+                                          uint64_t timeout_ns) {
+  const uint32_t* flag = reinterpret_cast<const uint32_t*>(mine + flags_off) + slot;
+  const uint64_t t0 = now_ns();
+  while ((int32_t)(ld_acquire_sys(flag) - seq) < 0) {
+    if (now_ns() - t0 > timeout_ns) {  // a peer that never comes must not hang the GPU
+      atomicExch(reinterpret_cast<uint32_t*>(mine + err_off), 1u);
+      break;
+    }
+    __nanosleep(200);
+  }
+}
+
+// Block b waits until peer b's list of step `seq` (generation gen) has arrived here.
+__global__ void k_xchg_wait(uint8_t* const* __restrict__ peers, int world, int rank, uint64_t flags_off, uint64_t err_off,
+                            uint32_t gen, uint32_t seq, uint64_t timeout_ns) {
+  const int p = (int)blockIdx.x < rank ? (int)blockIdx.x : (int)blockIdx.x + 1;
+  if (threadIdx.x == 0) wait_flag(peers[rank], flags_off, err_off, gen * world + p, seq, timeout_ns);
+}
+
 __global__ void __launch_bounds__(256)
 k_exchange(uint8_t* const* __restrict__ peers, int world, int rank, uint64_t slot_bytes, uint64_t cap,
-           uint64_t flags_off, uint64_t err_off, uint32_t gen, uint32_t seq, uint64_t timeout_ns) {
+           uint64_t flags_off, uint64_t err_off, uint32_t gen, uint32_t seq, uint32_t wait_gen, uint32_t wait_seq,
+           uint64_t timeout_ns) {
   const int p = (int)blockIdx.x < rank ? (int)blockIdx.x : (int)blockIdx.x + 1;
   uint8_t* mine = peers[rank];
   uint8_t* theirs = peers[p];
@@ -73,15 +97,8 @@ k_exchange(uint8_t* const* __restrict__ peers, int world, int rank, uint64_t slo
   __syncthreads();
   if (threadIdx.x == 0) {
     st_release_sys(reinterpret_cast<uint32_t*>(theirs + flags_off) + (gen * world + rank), seq);
-    const uint32_t* flag = reinterpret_cast<const uint32_t*>(mine + flags_off) + (gen * world + p);
-    const uint64_t t0 = now_ns();
-    while ((int32_t)(ld_acquire_sys(flag) - seq) < 0) {
-      if (now_ns() - t0 > timeout_ns) {  // a peer that never comes must not hang the GPU
-        atomicExch(reinterpret_cast<uint32_t*>(mine + err_off), 1u);
-        break;
-      }
-      __nanosleep(200);
-    }
+    // the peer's list of the PREVIOUS step: by now it has usually been here for a whole step
+    wait_flag(mine, flags_off, err_off, wait_gen * world + p, wait_seq, timeout_ns);
   }
 }
 
@@ -111,8 +128,8 @@ extern "C" int ncd_xchg_create(ncd_ctx* ctx, int world, int rank, uint64_t cap_e
   x->rank = rank;
   x->cap = cap_entries;
   x->slot_bytes = 16 + cap_entries * sizeof(ncd_entry);
-  x->flags_off = (2 * (uint64_t)world * x->slot_bytes + 127) & ~127ull;
-  x->err_off = x->flags_off + 2 * (uint64_t)world * sizeof(uint32_t);
+  x->flags_off = (3 * (uint64_t)world * x->slot_bytes + 127) & ~127ull;
+  x->err_off = x->flags_off + 3 * (uint64_t)world * sizeof(uint32_t);
   x->buf_bytes = (x->err_off + sizeof(uint32_t) + 127) & ~127ull;
   x->timeout_ns = 10ull * 1000 * 1000 * 1000;
   if (cudaMalloc((void**)&x->buf, x->buf_bytes) != cudaSuccess || cudaMalloc((void**)&x->d_peers, sizeof(uint8_t*) * world) != cudaSuccess) {
@@ -216,12 +233,12 @@ extern "C" int ncd_scan_exchange(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_
     ncd_set_error("ncd_scan_exchange: exchange not connected (ncd_xchg_open / ncd_xchg_connect first)");
     return NCD_E_STATE;
   }
-  const uint32_t seq = x->seq + 1, gen = seq & 1u;
+  const uint32_t seq = x->seq + 1, gen = seq % 3u;
   uint8_t* slot = x->buf + ((uint64_t)gen * x->world + x->rank) * x->slot_bytes;
   NCD_TRY(ncd_scan_into(ctx, ctrl, shards, nshards, mode, slot, x->cap));
   if (x->world > 1) {
     k_exchange<<<x->world - 1, 256, 0, ctx->stream>>>(x->d_peers, x->world, x->rank, x->slot_bytes, x->cap, x->flags_off,
-                                                      x->err_off, gen, seq, x->timeout_ns);
+                                                      x->err_off, gen, seq, (seq - 1) % 3u, seq - 1, x->timeout_ns);
     NCD_CUDA(cudaGetLastError());
   }
   x->seq = seq;
@@ -233,8 +250,22 @@ extern "C" int ncd_xchg_result(ncd_xchg* x, const void** dev_ptr, uint64_t* byte
     ncd_set_error("ncd_xchg_result: no exchange has been enqueued");
     return x ? NCD_E_STATE : NCD_E_INVALID;
   }
-  if (dev_ptr) *dev_ptr = x->buf + (uint64_t)(x->seq & 1u) * x->world * x->slot_bytes;
+  if (dev_ptr) *dev_ptr = x->buf + (uint64_t)(x->seq % 3u) * x->world * x->slot_bytes;
   if (bytes) *bytes = (uint64_t)x->world * x->slot_bytes;
+  return NCD_OK;
+}
+
+extern "C" int ncd_xchg_wait(ncd_xchg* x) {
+  if (!x || x->seq == 0) {
+    ncd_set_error("ncd_xchg_wait: no exchange has been enqueued");
+    return x ? NCD_E_STATE : NCD_E_INVALID;
+  }
+  if (x->world > 1) {
+    NCD_CUDA(cudaSetDevice(x->ctx->device));
+    k_xchg_wait<<<x->world - 1, 32, 0, x->ctx->stream>>>(x->d_peers, x->world, x->rank, x->flags_off, x->err_off, x->seq % 3u, x->seq,
+                                                         x->timeout_ns);
+    NCD_CUDA(cudaGetLastError());
+  }
   return NCD_OK;
 }
 
@@ -242,6 +273,7 @@ extern "C" int ncd_xchg_fetch(ncd_xchg* x, void* host_out, uint64_t bytes) {
   const void* src = nullptr;
   uint64_t have = 0;
   NCD_TRY(ncd_xchg_result(x, &src, &have));
+  NCD_TRY(ncd_xchg_wait(x));
   if (!host_out || bytes < have) {
     ncd_set_error("ncd_xchg_fetch: output buffer too small (%llu bytes, need %llu)", (unsigned long long)bytes,
                   (unsigned long long)have);

@@ -65,7 +65,7 @@ def test_three_ranks_every_rank_holds_every_list(ctx):
     ctxs, ranks = make_ranks(ctx, world, cap)
     try:
         assert all(len(r.want_ents) > 0 for r in ranks)
-        # seven steps: both generations several times, modes alternating; ranks enqueue in a
+        # seven steps: every generation several times, modes alternating; ranks enqueue in a
         # different order each step, so every rank is at times the one that waits
         for step in range(7):
             mode = (A.MODE_DIRECT, A.MODE_HASH64, A.MODE_XXH64)[step % 3]
@@ -77,6 +77,36 @@ def test_three_ranks_every_rank_holds_every_list(ctx):
                 for src, (ns, rows, ents) in enumerate(parts):
                     assert (ns, rows) == (len(ranks[src].sas), ranks[src].want_codes.shape[0]), (step, src)
                     np.testing.assert_array_equal(ents, ranks[src].want_ents)
+    finally:
+        close_all(ctxs, ranks)
+
+
+def test_ranks_may_run_one_step_apart(ctx):
+    """An exchange waits for the peers' lists of the PREVIOUS step only: a rank finishes its step without the
+    slower peer having started the same step, and stalls only when it would get two steps ahead.  The lists of
+    a step are complete for whoever fetches them (the fetch waits for that step's flags)."""
+    world, cap = 2, 4096
+    ctxs, ranks = make_ranks(ctx, world, cap)
+    try:
+        fast, slow = ranks
+        fast.x.scan(fast.ca, fast.sas, A.MODE_DIRECT)  # step 1: nothing to wait for
+        fast.ctx.sync()  # returns although the peer has not scanned at all
+        slow.x.scan(slow.ca, slow.sas, A.MODE_DIRECT)  # the peer's step 1
+        fast.x.scan(fast.ca, fast.sas, A.MODE_DIRECT)  # step 2 waits for the peer's step 1: there already
+        fast.ctx.sync()
+        slow.x.scan(slow.ca, slow.sas, A.MODE_DIRECT)
+        for r in ranks:
+            parts = M.unpack_gathered(r.x.fetch(), world, cap)
+            for src, (ns, rows, ents) in enumerate(parts):
+                np.testing.assert_array_equal(ents, ranks[src].want_ents)
+        # ten more steps in lockstep order: every generation is reused several times
+        for step in range(10):
+            for r in (ranks if step % 2 else ranks[::-1]):
+                r.x.scan(r.ca, r.sas, A.MODE_DIRECT)
+        for r in ranks:
+            parts = M.unpack_gathered(r.x.fetch(), world, cap)
+            for src, (ns, rows, ents) in enumerate(parts):
+                np.testing.assert_array_equal(ents, ranks[src].want_ents)
     finally:
         close_all(ctxs, ranks)
 
