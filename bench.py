@@ -550,11 +550,10 @@ def run_ours(args):
             import bench_steady as BS
 
             cpu_by = result["cpu_baseline"]["by_churn"]
-            rows = list(result["e2e_by_churn"].values())
             # level by level against the CPU arm at the same churn (the CPU arm's own cost grows with churn too)
             ratios = {k: r["decisions_per_s"] / cpu_by[k]["decisions_per_s"] for k, r in result["e2e_by_churn"].items() if k in cpu_by}
             result["e2e_vs_cpu_by_churn"] = {k: round(v, 3) for k, v in ratios.items()}
-            result["break_even_churn"] = BS.break_even(rows, result["cpu_baseline"]["value"])
+            result["break_even_churn"] = BS.break_even(ratios)
     if rank == 0:
         print(json.dumps(result), flush=True)
     if dist:

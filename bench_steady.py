@@ -237,19 +237,20 @@ def default_steps(churn):
     return 7, 2
 
 
-def break_even(rows_gpu, cpu_decisions_per_s):
-    """The churn at which the GPU arm's decisions/s falls to the CPU arm's (log-linear interpolation between
-    measured levels), or a statement that it does not within the measured range."""
-    pts = sorted((r["churn"], r["decisions_per_s"]) for r in rows_gpu)
-    if all(v > cpu_decisions_per_s for _, v in pts):
-        return {"churn": None, "note": f"GPU arm faster at every measured churn up to {pts[-1][0]:.0%}"}
-    if all(v <= cpu_decisions_per_s for _, v in pts):
-        return {"churn": 0.0, "note": "CPU arm faster at every measured churn"}
+def break_even(ratios):
+    """The churn at which the GPU arm's decisions/s falls to the CPU arm's AT THE SAME CHURN (both arms slow down
+    as more events arrive).  ratios: {churn: gpu / cpu}.  Log-linear interpolation between measured levels, or a
+    statement that the arms do not cross within the measured range."""
     import math
 
+    pts = sorted((float(c), float(v)) for c, v in ratios.items())
+    if all(v > 1 for _, v in pts):
+        return {"churn": None, "note": f"GPU arm faster at every measured churn up to {pts[-1][0]:.0%} (ratio there {pts[-1][1]:.2f})"}
+    if all(v <= 1 for _, v in pts):
+        return {"churn": 0.0, "note": "CPU arm faster at every measured churn"}
     for (c0, v0), (c1, v1) in zip(pts, pts[1:]):
-        if v0 > cpu_decisions_per_s >= v1:
-            t = (math.log(v0) - math.log(cpu_decisions_per_s)) / (math.log(v0) - math.log(v1))
+        if v0 > 1 >= v1:
+            t = math.log(v0) / (math.log(v0) - math.log(v1))
             c = math.exp(math.log(c0) + t * (math.log(c1) - math.log(c0)))
             return {"churn": c, "note": f"between the measured {c0:.1%} and {c1:.1%}"}
     return {"churn": None, "note": "not monotonic in the measured range"}

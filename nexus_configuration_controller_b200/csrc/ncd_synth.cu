@@ -396,7 +396,7 @@ extern "C" int ncd_synth_fill(ncd_ctx* ctx, ncd_arena* a, const ncd_synth_cfg* c
   }
   if (rc == NCD_OK && n) {
     cudaMemcpyAsync(a->d.rec_off, off_tmp, n * 8, cudaMemcpyDeviceToDevice, st);
-    if (role >= 0) k_owners<<<blocks, 256, 0, st>>>(s, gsel, a->d, logical);
+    k_owners<<<blocks, 256, 0, st>>>(s, gsel, a->d, logical);
     k_payload<<<(unsigned)n, 128, 0, st>>>(s, gsel, a->d, logical);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {

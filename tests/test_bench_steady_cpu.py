@@ -49,7 +49,8 @@ def test_both_arms_walk_the_same_steps():
         assert 0 < row["h2d_bytes_per_step"] < 2 * row["value_bytes_per_step"] + 64 * k * 4
         assert row["decisions_per_s"] > 0 and row["cpu_decisions_per_s"] > 0
         assert set(row["split_ms"]) >= {"canon_ms", "pack_ms", "upload_ms", "scan_ms", "other_ms"}
-    be = BS.break_even([r for r in rows.values()], cpu_decisions_per_s=1.0)
-    assert be["churn"] is None
+    assert BS.break_even({0.01: 8.0, 0.1: 2.0, 1.0: 1.5})["churn"] is None
+    be = BS.break_even({0.01: 8.0, 0.1: 2.0, 1.0: 0.5})
+    assert 0.1 < be["churn"] < 1.0
     gpu.close()
     cpu.close()
