@@ -341,31 +341,12 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
   const uint32_t gmask = (LPO == 8 ? 0xFFu : 0xFu) << base;  // the lanes of this object
   const uint64_t group0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LPO;
   const uint64_t ngroups = ((uint64_t)gridDim.x * blockDim.x) / LPO;
-  // Cached join, shards in one group (the steady state): a three-stage pipeline over this group's
-  // objects.  While object i is compared, the object lines of i + 1 are in flight (their indices
-  // arrived during i - 1) and the cached indices of i + 2 are requested: every level of the
-  // dependent chain index -> object line -> payload overlaps the other two.
-  const bool piped = S <= (uint32_t)G && S > 0 && s_sh[0].join_cache != nullptr;  // all shards cached or none (ncd_scan)
-  uint32_t idx1[SLOTS], idx2[SLOTS];  // indices of the next object, of the one after
-  uint4 w0n[SLOTS], w1n[SLOTS];       // first sector of the next object's shard lines
-  auto cached_idx = [&](uint64_t c, int j) -> uint32_t {
-    const uint32_t s = l + j * LPO;
-    return (c < ctrl.nobj && s < S) ? s_sh[s].join_cache[c] : NCD_NOTFOUND;
-  };
-  auto load_line = [&](uint32_t idx, int j, uint4& w0, uint4& w1) {
-    if (idx != NCD_NOTFOUND) {
-      const uint4* line = reinterpret_cast<const uint4*>(s_sh[l + j * LPO].meta + idx);
-      w0 = ncd_ldg_stream(line);  // keyhash | rec_off
-      w1 = ncd_ldg_stream(line + 1);  // rec_len key_off key_len/kind tag
-    }
-  };
-  if (piped) {
+  const bool prefetch = S <= (uint32_t)G && S > 0 && s_sh[0].join_cache != nullptr;  // all shards cached or none (ncd_scan)
+  uint32_t idx_next[SLOTS];
 #pragma unroll
-    for (int j = 0; j < SLOTS; ++j) {
-      idx1[j] = cached_idx(group0, j);
-      idx2[j] = cached_idx(group0 + ngroups, j);
-      load_line(idx1[j], j, w0n[j], w1n[j]);
-    }
+  for (int j = 0; j < SLOTS; ++j) {
+    const uint32_t s = l + j * LPO;
+    idx_next[j] = (prefetch && s < S && group0 < ctrl.nobj) ? s_sh[s].join_cache[group0] : NCD_NOTFOUND;
   }
   for (uint64_t c = group0; c < ctrl.nobj; c += ngroups) {
     const ObjMeta& q = ctrl.meta[c];
@@ -373,16 +354,13 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
     const uint32_t nvec = (len + 15) >> 4, tail = len & 15;
     const uint4* cp = reinterpret_cast<const uint4*>(ctrl.payload + q.rec_off);
     uint32_t idx_cur[SLOTS];
-    uint4 w0c[SLOTS], w1c[SLOTS];
-    if (piped) {
+#pragma unroll
+    for (int j = 0; j < SLOTS; ++j) idx_cur[j] = idx_next[j];
+    if (prefetch && c + ngroups < ctrl.nobj) {
 #pragma unroll
       for (int j = 0; j < SLOTS; ++j) {
-        idx_cur[j] = idx1[j];
-        w0c[j] = w0n[j];
-        w1c[j] = w1n[j];
-        idx1[j] = idx2[j];
-        idx2[j] = cached_idx(c + 2 * ngroups, j);   // stage 1 for object i + 2
-        load_line(idx1[j], j, w0n[j], w1n[j]);       // stage 2 for object i + 1
+        const uint32_t s = l + j * LPO;
+        if (s < S) idx_next[j] = s_sh[s].join_cache[c + ngroups];
       }
     }
     for (uint32_t s0 = 0; s0 < S; s0 += G) {
@@ -399,21 +377,17 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
         mine[j] = nullptr;
         if (s < S) {
           const ShardRef sr = s_sh[s];
-          uint4 w0, w1;
-          if (piped) {
+          if (prefetch) {
             idx[j] = idx_cur[j];
-            w0 = w0c[j];
-            w1 = w1c[j];
+          } else if (sr.join_cache) {
+            idx[j] = sr.join_cache[c];
           } else {
-            if (sr.join_cache) {
-              idx[j] = sr.join_cache[c];
-            } else {
-              idx[j] = ncd_probe_meta(shards[s], q, ctrl.aux);
-              if (sr.join_cache_out) sr.join_cache_out[c] = idx[j];
-            }
-            load_line(idx[j], j + (int)(s0 / LPO), w0, w1);
+            idx[j] = ncd_probe_meta(shards[s], q, ctrl.aux);
+            if (sr.join_cache_out) sr.join_cache_out[c] = idx[j];
           }
           if (idx[j] != NCD_NOTFOUND) {
+            const uint4* line = reinterpret_cast<const uint4*>(sr.meta + idx[j]);
+            const uint4 w0 = line[0], w1 = line[1];  // keyhash | rec_off ; rec_len key_off key_len/kind tag
             tg[j] = w1.w;
             if (w1.x != len) {
               v[j] = DV_DIFF;  // the encoding is injective: different lengths cannot be DeepEqual
