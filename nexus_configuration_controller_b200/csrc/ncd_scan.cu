@@ -321,8 +321,11 @@ k_compare_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
 // When the join is cached and the shards fit one group, the cached indices of the NEXT object are
 // requested while the current one is compared, which takes one level out of the dependent chain
 // (index -> object line -> payload) every object otherwise waits through.
+#ifndef NCD_SS_CTAS
+#define NCD_SS_CTAS 3  // resident CTAs per SM asked of the eight-shard variant (80 registers; 4 would force 64 and spills)
+#endif
 template <int G, int LPO>
-__global__ void __launch_bounds__(256, G == 8 ? 3 : 4)
+__global__ void __launch_bounds__(256, G == 8 ? NCD_SS_CTAS : 4)
 k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t* __restrict__ sh_idx,
              uint8_t* __restrict__ dv, uint32_t* __restrict__ tag) {
   constexpr int SLOTS = G / LPO;  // shards a lane joins per group of G
