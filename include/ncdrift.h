@@ -224,6 +224,14 @@ int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint
  * ncd_arena_counts); any pointer in dst may be NULL to skip that array. */
 int ncd_arena_download(ncd_arena* a, ncd_arena_view* dst);
 int ncd_arena_counts(ncd_arena* a, ncd_arena_view* counts_only);
+/* Reads a few records of a committed arena back: record obj_idx[k] lands at out + out_off[k]
+ * (16-byte padded; out_off has n + 1 entries, the last one = bytes written), lengths are the
+ * arena's rec_len.  A device-side gather and one copy, so sampling a 100 GB arena costs the sample.
+ * Fails with NCD_E_CAPACITY (nothing written) when out_cap is too small; out_off is filled in
+ * either way, so a caller can size the buffer from a first call with out_cap = 0.  No reference
+ * counterpart (used by the full-size parity tests and offline tools). */
+int ncd_arena_fetch_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint8_t* out, uint64_t out_cap,
+                            uint64_t* out_off);
 /* Snapshot of a committed arena as a file, and back (offline
  * diffing — compare what a cluster's caches held at some moment against another snapshot or a
  * live arena).  The file carries every array of ncd_arena_view plus a checksum; it streams

@@ -174,3 +174,73 @@ int ncd_arena_sync_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, ui
   }
   return ncd_arenas_sync_records(1, &a, &n, &obj_idx, &new_payload_bytes);
 }
+
+// ------------------------------------------------------------------ reading records back
+// The reverse of the pull: a few named records of a committed arena gathered on the device into one
+// staging buffer and copied to the host.  For checking a resident arena's contents (the full-size
+// parity tests sample records of 50-110 GB arenas this way) and for offline tools; no reference
+// counterpart.
+__global__ void __launch_bounds__(128)
+k_gather_records(const uint32_t* __restrict__ idx, const uint64_t* __restrict__ out_off, const uint8_t* __restrict__ payload,
+                 const uint64_t* __restrict__ rec_off, const uint32_t* __restrict__ rec_len, uint8_t* __restrict__ out) {
+  const uint32_t i = idx[blockIdx.x];
+  const uint4* src = reinterpret_cast<const uint4*>(payload + rec_off[i]);
+  uint4* dst = reinterpret_cast<uint4*>(out + out_off[blockIdx.x]);
+  const uint32_t nvec = (rec_len[i] + 15) >> 4;
+  for (uint32_t v = threadIdx.x; v < nvec; v += blockDim.x) dst[v] = src[v];
+}
+
+int ncd_arena_fetch_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, uint8_t* out, uint64_t out_cap, uint64_t* out_off) {
+  if (!a || (n && (!obj_idx || !out_off)) || (!out && out_cap)) {
+    ncd_set_error("ncd_arena_fetch_records: null argument");
+    return NCD_E_INVALID;
+  }
+  if (!a->committed) {
+    ncd_set_error("ncd_arena_fetch_records: arena not committed");
+    return NCD_E_STATE;
+  }
+  if (n == 0) return NCD_OK;
+  if (n >= 0x7FFFFFFFull) {
+    ncd_set_error("ncd_arena_fetch_records: too many records in one call");
+    return NCD_E_CAPACITY;
+  }
+  for (uint64_t k = 0; k < n; ++k)
+    if (obj_idx[k] >= a->nobj) {
+      ncd_set_error("ncd_arena_fetch_records: object %u of %llu does not exist", obj_idx[k], (unsigned long long)a->nobj);
+      return NCD_E_INVALID;
+    }
+  ncd_ctx* ctx = a->ctx;
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  // lengths first (they size the staging buffer), then the gather
+  uint32_t* d_idx = nullptr;
+  NCD_CUDA(cudaMallocAsync((void**)&d_idx, n * 4, st));
+  NCD_CUDA(cudaMemcpyAsync(d_idx, obj_idx, n * 4, cudaMemcpyHostToDevice, st));
+  std::vector<uint32_t> lens(a->nobj);
+  NCD_CUDA(cudaMemcpyAsync(lens.data(), a->d.rec_len, a->nobj * 4, cudaMemcpyDeviceToHost, st));
+  NCD_CUDA(cudaStreamSynchronize(st));
+  uint64_t total = 0;
+  for (uint64_t k = 0; k < n; ++k) {
+    out_off[k] = total;
+    total += ((uint64_t)lens[obj_idx[k]] + 15) & ~15ull;
+  }
+  out_off[n] = total;
+  if (total > out_cap) {
+    cudaFreeAsync(d_idx, st);
+    ncd_set_error("ncd_arena_fetch_records: %llu bytes needed, buffer holds %llu", (unsigned long long)total, (unsigned long long)out_cap);
+    return NCD_E_CAPACITY;
+  }
+  uint64_t* d_off = nullptr;
+  uint8_t* d_out = nullptr;
+  NCD_CUDA(cudaMallocAsync((void**)&d_off, (n + 1) * 8, st));
+  NCD_CUDA(cudaMallocAsync((void**)&d_out, total ? total : 16, st));
+  NCD_CUDA(cudaMemcpyAsync(d_off, out_off, (n + 1) * 8, cudaMemcpyHostToDevice, st));
+  k_gather_records<<<(unsigned)n, 128, 0, st>>>(d_idx, d_off, a->d.payload, a->d.rec_off, a->d.rec_len, d_out);
+  if (total) NCD_CUDA(cudaMemcpyAsync(out, d_out, total, cudaMemcpyDeviceToHost, st));
+  NCD_CUDA(cudaFreeAsync(d_idx, st));
+  NCD_CUDA(cudaFreeAsync(d_off, st));
+  NCD_CUDA(cudaFreeAsync(d_out, st));
+  NCD_CUDA(cudaStreamSynchronize(st));
+  NCD_CUDA(cudaGetLastError());
+  return NCD_OK;
+}

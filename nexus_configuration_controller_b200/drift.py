@@ -212,16 +212,45 @@ class Arena:
                 C.memmove(getattr(v, name), src.ctypes.data, nbytes)
 
     def commit(self, nobj, payload_bytes, aux_bytes, nowner, ndep) -> None:
+        self._meta = None
         check(self.ctx.lib.ncd_arena_commit(self.handle, nobj, payload_bytes, aux_bytes, nowner, ndep))
 
     def recommit(self, nobj, payload_bytes, aux_bytes, nowner, ndep, payload_dirty_from) -> None:
         """Structural change: re-upload the per-object arrays and only the appended payload."""
+        self._meta = None
         check(self.ctx.lib.ncd_arena_recommit(self.handle, nobj, payload_bytes, aux_bytes, nowner, ndep, payload_dirty_from))
 
     def sync_records(self, obj_idx: np.ndarray, new_payload_bytes: int) -> None:
         """Pushes the records of `obj_idx` (rewritten in the pinned host arrays) to the device copy."""
+        self._meta = None
         idx = np.ascontiguousarray(obj_idx, dtype=np.uint32)
         check(self.ctx.lib.ncd_arena_sync_records(self.handle, len(idx), idx.ctypes.data_as(_ffi.u32p), new_payload_bytes))
+
+    def fetch_records(self, obj_idx) -> List[bytes]:
+        """The canonical bytes of the named records, read back from the device (ncd_arena_fetch_records)."""
+        idx = np.ascontiguousarray(obj_idx, dtype=np.uint32)
+        n = len(idx)
+        off = np.zeros(n + 1, dtype=np.uint64)
+        lib = self.ctx.lib
+        rc = lib.ncd_arena_fetch_records(self.handle, n, idx.ctypes.data_as(_ffi.u32p), None, 0, off.ctypes.data_as(_ffi.u64p))
+        if rc not in (0, -4):
+            check(rc)
+        buf = np.zeros(max(int(off[n]), 16), dtype=np.uint8)
+        check(lib.ncd_arena_fetch_records(self.handle, n, idx.ctypes.data_as(_ffi.u32p), buf.ctypes.data, buf.nbytes, off.ctypes.data_as(_ffi.u64p)))
+        lens = self.download_meta().rec_len
+        return [buf[int(off[k]) : int(off[k]) + int(lens[idx[k]])].tobytes() for k in range(n)]
+
+    def download_meta(self) -> HostArena:
+        """Every array of the arena except the payload (about 100 bytes per object)."""
+        if getattr(self, "_meta", None) is None:
+            c = self.counts()
+            host = HostArena(c.nobj, 16, c.aux_bytes, c.nowner, c.ndep)
+            host.payload_bytes = c.payload_bytes
+            v = host.view()
+            v.payload = None
+            check(self.ctx.lib.ncd_arena_download(self.handle, C.byref(v)))
+            self._meta = host
+        return self._meta
 
     def counts(self) -> ArenaView:
         v = ArenaView()
