@@ -9,6 +9,30 @@
 
 #include "../../include/ncdrift.h"
 
+// Phase ranges for profilers (nsys, ncu --nvtx): hash / join / compare / classify / exchange / sync.
+// Compiled out unless the library is built with -DNCD_NVTX (NCD_NVCC_EXTRA=-DNCD_NVTX python -m
+// nexus_configuration_controller_b200.build); nvtx3 is header only.
+#ifdef NCD_NVTX
+#include <nvtx3/nvToolsExt.h>
+struct NcdRange {
+  explicit NcdRange(const char* name) { nvtxRangePushA(name); }
+  ~NcdRange() { nvtxRangePop(); }
+};
+#define NCD_RANGE(var, name) NcdRange var(name)
+#define NCD_RANGE_PUSH(name) nvtxRangePushA(name)
+#define NCD_RANGE_POP() nvtxRangePop()
+#else
+#define NCD_RANGE(var, name) \
+  do {                       \
+  } while (0)
+#define NCD_RANGE_PUSH(name) \
+  do {                       \
+  } while (0)
+#define NCD_RANGE_POP() \
+  do {                  \
+  } while (0)
+#endif
+
 #define NCD_NOTFOUND 0xFFFFFFFFu
 #define NCD_NO_OFF 0xFFFFFFFFFFFFFFFFull
 

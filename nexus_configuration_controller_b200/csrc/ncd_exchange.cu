@@ -236,6 +236,7 @@ extern "C" int ncd_scan_exchange(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_
   const uint32_t seq = x->seq + 1, gen = seq % 3u;
   uint8_t* slot = x->buf + ((uint64_t)gen * x->world + x->rank) * x->slot_bytes;
   NCD_TRY(ncd_scan_into(ctx, ctrl, shards, nshards, mode, slot, x->cap));
+  NCD_RANGE(xchg_range, "ncd:exchange");
   if (x->world > 1) {
     k_exchange<<<x->world - 1, 256, 0, ctx->stream>>>(x->d_peers, x->world, x->rank, x->slot_bytes, x->cap, x->flags_off,
                                                       x->err_off, gen, seq, (seq - 1) % 3u, seq - 1, x->timeout_ns);

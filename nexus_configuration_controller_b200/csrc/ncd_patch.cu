@@ -103,6 +103,7 @@ int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t*
     return NCD_OK;
   }
   NCD_CUDA(cudaSetDevice(ctx->device));
+  NCD_RANGE(sync_range, "ncd:sync_records");
   cudaStream_t st = ctx->stream;
   // device: [indices of arena 0 | arena 1 | ...][2 flag words per arena]
   uint32_t* d_idx = nullptr;

@@ -651,6 +651,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
 
   // digests first (hash modes): every copy is hashed once, digests are kept with the arena
   NCD_CUDA(cudaEventRecord(evs[0], st));
+  NCD_RANGE_PUSH("ncd:hash");
   if (hm != NCD_MODE_DIRECT) {
     std::vector<ncd_arena*> all;
     all.push_back(const_cast<ncd_arena*>(ctrl));
@@ -659,7 +660,9 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
       for (ncd_arena* a : all) a->h64_valid = a->sha_valid = a->xxh_valid = false;
     NCD_TRY(ncd_hash_launch_many(ctx, all.data(), (int)all.size(), hm, &launches));
   }
+  NCD_RANGE_POP();
   NCD_CUDA(cudaEventRecord(evs[1], st));
+  NCD_RANGE_PUSH("ncd:join");
 
   // shard descriptors
   if ((int)S > ctx->d_shards_cap) {
@@ -746,6 +749,8 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     ++launches;
   }
   NCD_CUDA(cudaEventRecord(evs[2], st));
+  NCD_RANGE_POP();
+  NCD_RANGE_PUSH("ncd:compare");
   if (fused_small) {
     // four lanes per object for records of about a hundred bytes or less, eight otherwise
     const bool narrow = nc && ctrl->len_sum / nc <= 128;
@@ -821,6 +826,8 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     ++launches;
   }
   NCD_CUDA(cudaEventRecord(evs[3], st));
+  NCD_RANGE_POP();
+  NCD_RANGE(classify_range, "ncd:classify");
   if (nq) {
     const bool fuse = nblk <= 4096;
     k_classify<<<(unsigned)nblk, 256, 0, st>>>(dctrl, ctx->d_shards, S, nrows, ctrl->row_obj,
