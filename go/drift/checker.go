@@ -7,6 +7,7 @@ import (
 	"fmt"
 	"reflect"
 	"strings"
+	"sync"
 	"sync/atomic"
 
 	v1 "github.com/SneaksAndData/nexus-core/pkg/apis/science/v1"
@@ -20,6 +21,7 @@ import (
 type object struct {
 	kind      uint32
 	key, uid  string // key = "namespace/name" (cache.ObjectName.String())
+	version   string // metadata.resourceVersion of the object that was packed
 	value     reflect.Value // .Spec or .Data — the operand of reflect.DeepEqual in the reference
 	owners    []owner
 	secrets   []string // templates: GetSecretNames(), then GetConfigMapNames() (controller.go:505,567)
@@ -30,13 +32,30 @@ type owner struct {
 	uid        string
 }
 
-// snapshot is what Lookup reads; swapped in atomically after every Scan.
+// snapshot is what Lookup reads; swapped in atomically after every Scan, never modified afterwards:
+// handlers on other goroutines (controller.go:875-877) read it without waiting for a Scan in flight.
 type snapshot struct {
-	res      *Result
-	firstRow map[string]int // kind + key -> first row of a template / workgroup
-	ndeps    map[string]int
-	order    []object // controller objects in arena order (Dirty indexes into it)
+	res       *Result
+	firstRow  map[string]int // kind + key -> first row of a template / workgroup
+	ndeps     map[string]int
+	order     []object            // controller objects in arena order (Dirty indexes into it)
+	versions  []map[string]string // [0] controller, [1+s] shard s: kind + key -> resourceVersion that was packed
+	unadopted []Adoption          // references adoptReferences (controller.go:647-695) would still adopt
 }
+
+// Freshness of an answer.  The reference's handlers read LIVE caches (controller.go:766, 792, 507, 516);
+// a snapshot is only as fresh as its Scan, so Lookup compares the resourceVersions that were packed with
+// what the listers hold NOW for everything the decision rests on, and says Stale instead of answering
+// from a past the caches have left.  A caller that gets Stale takes the reference's own path for that
+// object (lister.Get + reflect.DeepEqual + isMissingOwnership) or runs Scan and asks again; it never
+// treats a missing answer as Skip.
+type Freshness int
+
+const (
+	Fresh    Freshness = iota // code is valid for the caches as they are now
+	NotFound                  // the object is not in the controller cache (controller.go:769-772)
+	Stale                     // something the decision rests on changed after the Scan
+)
 
 type Checker struct {
 	ctx       *Ctx
@@ -46,6 +65,7 @@ type Checker struct {
 	secrets   corelisters.SecretLister
 	configs   corelisters.ConfigMapLister
 	shards    []*shards.Shard
+	scanMu    sync.Mutex // one Scan at a time; the ncd_ctx is used under it
 	snap      atomic.Pointer[snapshot]
 }
 
@@ -67,7 +87,7 @@ func list(t nexuslisters.NexusAlgorithmTemplateLister, w nexuslisters.NexusAlgor
 		return nil, err
 	}
 	for _, x := range ts {
-		out = append(out, object{kind: KindTemplate, key: x.Namespace + "/" + x.Name, uid: string(x.UID),
+		out = append(out, object{kind: KindTemplate, key: x.Namespace + "/" + x.Name, uid: string(x.UID), version: x.ResourceVersion,
 			value: reflect.ValueOf(x.Spec), secrets: x.GetSecretNames(), configMap: x.GetConfigMapNames()})
 	}
 	ws, err := w.List(labels.Everything())
@@ -75,14 +95,14 @@ func list(t nexuslisters.NexusAlgorithmTemplateLister, w nexuslisters.NexusAlgor
 		return nil, err
 	}
 	for _, x := range ws {
-		out = append(out, object{kind: KindWorkgroup, key: x.Namespace + "/" + x.Name, uid: string(x.UID), value: reflect.ValueOf(x.Spec)})
+		out = append(out, object{kind: KindWorkgroup, key: x.Namespace + "/" + x.Name, uid: string(x.UID), version: x.ResourceVersion, value: reflect.ValueOf(x.Spec)})
 	}
 	ss, err := s.List(labels.Everything())
 	if err != nil {
 		return nil, err
 	}
 	for _, x := range ss {
-		o := object{kind: KindSecret, key: x.Namespace + "/" + x.Name, uid: string(x.UID), value: reflect.ValueOf(x.Data)}
+		o := object{kind: KindSecret, key: x.Namespace + "/" + x.Name, uid: string(x.UID), version: x.ResourceVersion, value: reflect.ValueOf(x.Data)}
 		for _, r := range x.OwnerReferences {
 			o.owners = append(o.owners, owner{r.Kind == "NexusAlgorithmTemplate", string(r.UID)})
 		}
@@ -93,7 +113,7 @@ func list(t nexuslisters.NexusAlgorithmTemplateLister, w nexuslisters.NexusAlgor
 		return nil, err
 	}
 	for _, x := range cs {
-		o := object{kind: KindConfigMap, key: x.Namespace + "/" + x.Name, uid: string(x.UID), value: reflect.ValueOf(x.Data)}
+		o := object{kind: KindConfigMap, key: x.Namespace + "/" + x.Name, uid: string(x.UID), version: x.ResourceVersion, value: reflect.ValueOf(x.Data)}
 		for _, r := range x.OwnerReferences {
 			o.owners = append(o.owners, owner{r.Kind == "NexusAlgorithmTemplate", string(r.UID)})
 		}
@@ -181,6 +201,8 @@ func (k *Checker) pack(objs []object) (*Arena, error) {
 // Scan: one drift check over the controller cluster and every shard.  Called once per resync
 // sweep (main.go:70-71) or on demand; handlers then consult Lookup.
 func (k *Checker) Scan() error {
+	k.scanMu.Lock()
+	defer k.scanMu.Unlock()
 	ctrlObjs, err := list(k.templates, k.workgroup, k.secrets, k.configs)
 	if err != nil {
 		return err
@@ -190,6 +212,7 @@ func (k *Checker) Scan() error {
 		return err
 	}
 	defer ctrl.Close()
+	versions := []map[string]string{versionsOf(ctrlObjs)}
 	arenas := make([]*Arena, 0, len(k.shards))
 	defer func() {
 		for _, a := range arenas {
@@ -206,12 +229,17 @@ func (k *Checker) Scan() error {
 			return err
 		}
 		arenas = append(arenas, a)
+		versions = append(versions, versionsOf(objs))
+	}
+	unadopted, err := k.ctx.Unadopted(ctrl)
+	if err != nil {
+		return err
 	}
 	res, err := k.ctx.Scan(ctrl, arenas, k.mode)
 	if err != nil {
 		return err
 	}
-	s := &snapshot{res: res, firstRow: map[string]int{}, ndeps: map[string]int{}, order: ctrlObjs}
+	s := &snapshot{res: res, firstRow: map[string]int{}, ndeps: map[string]int{}, order: ctrlObjs, versions: versions, unadopted: unadopted}
 	row := 0
 	for _, o := range ctrlObjs {
 		id := string(rune('0'+o.kind)) + o.key
@@ -228,34 +256,126 @@ func (k *Checker) Scan() error {
 	return nil
 }
 
-// Lookup: the decision of the last Scan.  dep = 0 the object itself, j+1 its j-th dependent
-// (secrets first, then configmaps).  ok is false when the object was not in the controller cache.
-func (k *Checker) Lookup(kind uint32, namespace, name string, dep, shard int) (code uint32, ok bool) {
+func versionsOf(objs []object) map[string]string {
+	m := make(map[string]string, len(objs))
+	for _, o := range objs {
+		m[string(rune('0'+o.kind))+o.key] = o.version
+	}
+	return m
+}
+
+// liveVersion is the resourceVersion a cluster's lister holds NOW for (kind, namespace, name); "" = absent.
+func liveVersion(t nexuslisters.NexusAlgorithmTemplateLister, w nexuslisters.NexusAlgorithmWorkgroupLister,
+	s corelisters.SecretLister, c corelisters.ConfigMapLister, kind uint32, namespace, name string) string {
+	switch kind {
+	case KindTemplate:
+		if x, err := t.NexusAlgorithmTemplates(namespace).Get(name); err == nil {
+			return x.ResourceVersion
+		}
+	case KindWorkgroup:
+		if x, err := w.NexusAlgorithmWorkgroups(namespace).Get(name); err == nil {
+			return x.ResourceVersion
+		}
+	case KindSecret:
+		if x, err := s.Secrets(namespace).Get(name); err == nil {
+			return x.ResourceVersion
+		}
+	case KindConfigMap:
+		if x, err := c.ConfigMaps(namespace).Get(name); err == nil {
+			return x.ResourceVersion
+		}
+	}
+	return ""
+}
+
+// unchanged: does cluster (0 = controller, 1+s = shard s) still hold the version of (kind, key) that was packed?
+func (k *Checker) unchanged(s *snapshot, cluster int, kind uint32, namespace, name string) bool {
+	var live string
+	if cluster == 0 {
+		live = liveVersion(k.templates, k.workgroup, k.secrets, k.configs, kind, namespace, name)
+	} else {
+		sh := k.shards[cluster-1]
+		live = liveVersion(sh.TemplateLister, sh.WorkgroupLister, sh.SecretLister, sh.ConfigMapLister, kind, namespace, name)
+	}
+	return s.versions[cluster][string(rune('0'+kind))+namespace+"/"+name] == live // "" == "": absent then and now
+}
+
+// Lookup: the decision of the last Scan, with its freshness.  dep = 0 the object itself, j+1 its j-th
+// dependent (secrets first, then configmaps).  The decision for (template, dependent, shard) rests on the
+// controller's template and dependent and on the shard's copies of both (the shard template's UID decides
+// ownership, controller.go:529); if any of the four changed since the Scan the answer is Stale.
+func (k *Checker) Lookup(kind uint32, namespace, name string, dep, shard int) (code uint32, f Freshness) {
 	s := k.snap.Load()
 	if s == nil {
-		return 0, false
+		return 0, Stale
 	}
 	id := string(rune('0'+kind)) + namespace + "/" + name
 	row, found := s.firstRow[id]
-	if !found || dep < 0 || dep > s.ndeps[id] || shard < 0 || shard >= s.res.Shards {
-		return 0, false
+	if !found {
+		if liveVersion(k.templates, k.workgroup, k.secrets, k.configs, kind, namespace, name) != "" {
+			return 0, Stale // created after the Scan: not in the snapshot yet, which is not the same as absent
+		}
+		return 0, NotFound
 	}
-	return uint32(s.res.Codes[(row+dep)*s.res.Shards+shard]), true
+	if dep < 0 || dep > s.ndeps[id] || shard < 0 || shard >= s.res.Shards {
+		return 0, Stale
+	}
+	if !k.unchanged(s, 0, kind, namespace, name) || !k.unchanged(s, 1+shard, kind, namespace, name) {
+		return 0, Stale
+	}
+	if dep > 0 {
+		o := s.order[s.objOf(id)]
+		dk, dn := uint32(KindSecret), ""
+		if dep <= len(o.secrets) {
+			dn = o.secrets[dep-1]
+		} else {
+			dk, dn = KindConfigMap, o.configMap[dep-1-len(o.secrets)]
+		}
+		if !k.unchanged(s, 0, dk, namespace, dn) || !k.unchanged(s, 1+shard, dk, namespace, dn) {
+			return 0, Stale
+		}
+	}
+	return uint32(s.res.Codes[(row+dep)*s.res.Shards+shard]), Fresh
 }
 
-// Dirty: the templates / workgroups a resync still has to enqueue (everything else is converged).
+// objOf: index in order of the template / workgroup with this id.
+func (s *snapshot) objOf(id string) int {
+	for i, o := range s.order { // (a map in production; kept short here)
+		if string(rune('0'+o.kind))+o.key == id {
+			return i
+		}
+	}
+	return -1
+}
+
+// Dirty: the templates / workgroups a resync still has to enqueue — those with a shard decision other
+// than Skip, and the templates whose controller-side dependents adoptReferences (controller.go:647-695)
+// would still adopt.  Everything else is converged as far as the shards and the ownerReferences go; the
+// caller additionally enqueues objects whose status lacks the ready condition (reportTemplateInitCondition
+// / reportTemplateSyncedCondition, controller.go:428-480, read nothing this package packs).
 func (k *Checker) Dirty() (templates, workgroups []string) {
 	s := k.snap.Load()
 	if s == nil {
 		return nil, nil
 	}
-	for _, i := range s.res.Dirty {
+	seen := map[uint32]bool{}
+	add := func(i uint32) {
+		if seen[i] {
+			return
+		}
+		seen[i] = true
 		o := s.order[i]
 		if o.kind == KindTemplate {
 			templates = append(templates, o.key)
 		} else {
 			workgroups = append(workgroups, o.key)
 		}
+	}
+	for _, i := range s.res.Dirty {
+		add(i)
+	}
+	for _, a := range s.unadopted {
+		add(a.Obj)
 	}
 	return templates, workgroups
 }

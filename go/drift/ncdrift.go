@@ -207,6 +207,27 @@ func (c *Ctx) Scan(ctrl *Arena, shards []*Arena, mode uint32) (*Result, error) {
 	return r, nil
 }
 
+// Adoption == ncd_adoption: a (template, dependent) reference whose controller-side object does not
+// carry the template's ownerReference yet (adoptReferences, controller.go:647-695).
+type Adoption struct{ Obj, Dep uint32 }
+
+// Unadopted lists the references adoptReferences would still adopt (ncd_find_unadopted).
+func (c *Ctx) Unadopted(ctrl *Arena) ([]Adoption, error) {
+	c.mu.Lock()
+	defer c.mu.Unlock()
+	var n C.uint64_t
+	out := make([]Adoption, 1024)
+	for {
+		if C.ncd_find_unadopted(c.h, ctrl.h, (*C.ncd_adoption)(unsafe.Pointer(&out[0])), C.uint64_t(len(out)), &n) != 0 {
+			return nil, lastErr("ncd_find_unadopted")
+		}
+		if int(n) <= len(out) {
+			return out[:n], nil
+		}
+		out = make([]Adoption, int(n))
+	}
+}
+
 // KeyHash is the multi-GPU partition function: gpu = KeyHash(kind, "ns/name") % nGPUs.
 func KeyHash(kind uint32, key string) uint64 {
 	return uint64(C.ncd_keyhash(C.uint32_t(kind), unsafe.Pointer(unsafe.StringData(key)), C.uint32_t(len(key))))
