@@ -315,6 +315,18 @@ extern "C" int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_
   NCD_TRY(check_counts(a, nobj, payload_bytes, aux_bytes, nowner, ndep));
   NCD_CUDA(cudaSetDevice(a->ctx->device));
   cudaStream_t st = a->ctx->stream;
+  // Digests the arena holds are carried over to the records that survive (ncd_digests_carry): keep
+  // the old offsets and lengths, the only thing that identifies a record once objects are renumbered.
+  const bool had_h64 = a->h64_valid, had_sha = a->sha_valid, had_xxh = a->xxh_valid;
+  const uint64_t old_n = a->nobj;
+  uint64_t* old_off = nullptr;
+  uint32_t* old_len = nullptr;
+  if ((had_h64 || had_sha || had_xxh) && old_n) {
+    NCD_CUDA(cudaMallocAsync((void**)&old_off, old_n * 8, st));
+    NCD_CUDA(cudaMallocAsync((void**)&old_len, old_n * 4, st));
+    NCD_CUDA(cudaMemcpyAsync(old_off, a->d.rec_off, old_n * 8, cudaMemcpyDeviceToDevice, st));
+    NCD_CUDA(cudaMemcpyAsync(old_len, a->d.rec_len, old_n * 4, cudaMemcpyDeviceToDevice, st));
+  }
   for (int i = 0; i < kNumFields; ++i) {
     const Field& f = kFields[i];
     uint64_t bytes = field_count(f, payload_bytes, nobj, aux_bytes, nowner, ndep) * f.elem;
@@ -327,7 +339,14 @@ extern "C" int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_
       NCD_CUDA(cudaMemcpyAsync((char*)*field_ptr(&a->d, f) + from, (const char*)*field_ptr(&a->h, f) + from, bytes,
                                cudaMemcpyHostToDevice, st));
   }
-  return ncd_arena_commit_device(a, nobj, payload_bytes, aux_bytes, nowner, ndep);
+  int rc = ncd_arena_commit_device(a, nobj, payload_bytes, aux_bytes, nowner, ndep);
+  if (rc == NCD_OK && old_off)
+    rc = ncd_digests_carry(a, old_off, old_len, old_n, payload_dirty_from, had_h64, had_sha, had_xxh, &a->last_rehashed);
+  if (old_off) {
+    cudaFreeAsync(old_off, st);
+    cudaFreeAsync(old_len, st);
+  }
+  return rc;
 }
 
 extern "C" int ncd_arena_counts(ncd_arena* a, ncd_arena_view* c) {

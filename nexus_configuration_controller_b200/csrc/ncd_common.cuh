@@ -158,6 +158,7 @@ struct ncd_arena {
   // committed counts
   uint64_t nobj, payload_bytes, aux_bytes, nowner, ndep;
   uint64_t len_sum;  // sum of rec_len: the arena's share of the algorithmic bytes
+  uint64_t last_rehashed;  // records the last re-commit had to hash again (the others kept their digests)
   bool committed;
   ncd_arena_view h;  // pinned host arrays (HOST_PINNED only)
   ncd_arena_view d;  // device arrays
@@ -268,6 +269,8 @@ int ncd_hash_launch(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, uint32_t* launche
 int ncd_hash_records_many(ncd_ctx* ctx, int count, ncd_arena* const* arenas, const uint32_t* const* d_idx,
                           const uint64_t* n);  // ncd_hash.cu: named records only
 int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint32_t mode, uint32_t* launches);
+int ncd_digests_carry(ncd_arena* a, const uint64_t* old_off, const uint32_t* old_len, uint64_t old_n, uint64_t dirty_from,
+                      bool had_h64, bool had_sha, bool had_xxh, uint64_t* rehashed);
 
 // ------------------------------------------------------------------ device helpers
 #ifdef __CUDACC__

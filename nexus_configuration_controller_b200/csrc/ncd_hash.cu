@@ -701,3 +701,123 @@ extern "C" int ncd_hash_arena(ncd_ctx* ctx, ncd_arena* a, uint32_t mode, void* o
   if (kernel_ms) cudaEventElapsedTime(kernel_ms, ctx->ev[5], ctx->ev[6]);
   return NCD_OK;
 }
+
+// ------------------------------------------------------------------ digests across a re-commit
+// ncd_arena_recommit keeps surviving records where they are on the device (same rec_off, same
+// bytes below payload_dirty_from) but may renumber the objects.  The digests the arena held are
+// carried over by RECORD, not by index: a table of the old (rec_off, rec_len) -> old index, one
+// probe per new object, and only the records that are new (appended behind payload_dirty_from, or
+// never hashed) go through the hash kernels again.  A hash-mode sweep after an informer AddFunc /
+// DeleteFunc then costs the added records, not the cluster.
+namespace {
+
+__device__ __forceinline__ uint32_t carry_slot(uint64_t off, uint32_t mask) {
+  return (uint32_t)ncd_fmix64(off >> 4) & mask;
+}
+
+__global__ void k_carry_insert(const uint64_t* __restrict__ old_off, uint32_t old_n, uint32_t* __restrict__ table, uint32_t mask) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= old_n) return;
+  uint32_t slot = carry_slot(old_off[j], mask);
+  while (atomicCAS(&table[slot], 0xFFFFFFFFu, j) != 0xFFFFFFFFu) slot = (slot + 1) & mask;
+}
+
+__global__ void k_carry_lookup(const uint64_t* __restrict__ new_off, const uint32_t* __restrict__ new_len, uint32_t new_n,
+                               const uint64_t* __restrict__ old_off, const uint32_t* __restrict__ old_len,
+                               const uint32_t* __restrict__ table, uint32_t mask, uint64_t dirty_from,
+                               const uint64_t* __restrict__ h64_old, uint64_t* __restrict__ h64_new,
+                               const uint32_t* __restrict__ sha_old, uint32_t* __restrict__ sha_new,
+                               const uint64_t* __restrict__ xxh_old, uint64_t* __restrict__ xxh_new,
+                               uint32_t* __restrict__ rehash, uint32_t* __restrict__ nrehash) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= new_n) return;
+  const uint64_t off = new_off[i];
+  const uint32_t len = new_len[i];
+  uint32_t found = 0xFFFFFFFFu;
+  if (off < dirty_from) {  // appended records are new bytes whatever their offset says
+    for (uint32_t slot = carry_slot(off, mask);; slot = (slot + 1) & mask) {
+      const uint32_t j = table[slot];
+      if (j == 0xFFFFFFFFu) break;
+      if (old_off[j] == off && old_len[j] == len) {
+        found = j;
+        break;
+      }
+    }
+  }
+  if (found == 0xFFFFFFFFu) {
+    rehash[atomicAdd(nrehash, 1u)] = i;
+    return;
+  }
+  if (h64_new) h64_new[i] = h64_old[found];
+  if (xxh_new) xxh_new[i] = xxh_old[found];
+  if (sha_new) {
+    const uint4* s = reinterpret_cast<const uint4*>(sha_old + (size_t)found * 8);
+    uint4* d = reinterpret_cast<uint4*>(sha_new + (size_t)i * 8);
+    d[0] = s[0];
+    d[1] = s[1];
+  }
+}
+
+}  // namespace
+
+// old_off / old_len: device copies of the arena's rec_off / rec_len as they were before the
+// re-commit (old_n entries); had_*: which digests were valid then.  On return the arena holds valid
+// digests of those kinds for its NEW contents.  *rehashed = records that went through the kernels.
+int ncd_digests_carry(ncd_arena* a, const uint64_t* old_off, const uint32_t* old_len, uint64_t old_n, uint64_t dirty_from,
+                      bool had_h64, bool had_sha, bool had_xxh, uint64_t* rehashed) {
+  ncd_ctx* ctx = a->ctx;
+  cudaStream_t st = ctx->stream;
+  const uint64_t n = a->nobj;
+  if (rehashed) *rehashed = 0;
+  if (!(had_h64 || had_sha || had_xxh) || n == 0) return NCD_OK;
+  const size_t dcap = (size_t)(a->nobj_cap > n ? a->nobj_cap : n);
+  uint64_t *h64_new = nullptr, *xxh_new = nullptr;
+  uint32_t* sha_new = nullptr;
+  if (had_h64) NCD_CUDA(cudaMalloc((void**)&h64_new, dcap * 8));
+  if (had_sha) NCD_CUDA(cudaMalloc((void**)&sha_new, dcap * 32));
+  if (had_xxh) NCD_CUDA(cudaMalloc((void**)&xxh_new, dcap * 8));
+  uint32_t tsize = 16;
+  while ((uint64_t)tsize < 2 * old_n) tsize <<= 1;
+  uint32_t *table = nullptr, *list = nullptr, *count = nullptr;
+  NCD_CUDA(cudaMallocAsync((void**)&table, (size_t)tsize * 4, st));
+  NCD_CUDA(cudaMallocAsync((void**)&list, (n + 1) * 4, st));
+  NCD_CUDA(cudaMallocAsync((void**)&count, 4, st));
+  NCD_CUDA(cudaMemsetAsync(table, 0xFF, (size_t)tsize * 4, st));
+  NCD_CUDA(cudaMemsetAsync(count, 0, 4, st));
+  if (old_n) k_carry_insert<<<(unsigned)((old_n + 255) / 256), 256, 0, st>>>(old_off, (uint32_t)old_n, table, tsize - 1);
+  k_carry_lookup<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a->d.rec_off, a->d.rec_len, (uint32_t)n, old_off, old_len, table, tsize - 1,
+                                                             dirty_from, a->h64, h64_new, a->sha, sha_new, a->xxh, xxh_new, list, count);
+  uint32_t nre = 0;
+  NCD_CUDA(cudaMemcpyAsync(&nre, count, 4, cudaMemcpyDeviceToHost, st));
+  NCD_CUDA(cudaStreamSynchronize(st));
+  // the carried digests become the arena's; the old buffers go
+  if (had_h64) {
+    cudaFree(a->h64);
+    a->h64 = h64_new;
+  }
+  if (had_sha) {
+    cudaFree(a->sha);
+    a->sha = sha_new;
+  }
+  if (had_xxh) {
+    cudaFree(a->xxh);
+    a->xxh = xxh_new;
+  }
+  a->h64_valid = had_h64;
+  a->sha_valid = had_sha;
+  a->xxh_valid = had_xxh;
+  int rc = NCD_OK;
+  if (nre) {
+    const uint32_t* lists[1] = {list};
+    const uint64_t counts[1] = {nre};
+    ncd_arena* as[1] = {a};
+    rc = ncd_hash_records_many(ctx, 1, as, lists, counts);
+  }
+  NCD_CUDA(cudaFreeAsync(table, st));
+  NCD_CUDA(cudaFreeAsync(list, st));
+  NCD_CUDA(cudaFreeAsync(count, st));
+  NCD_CUDA(cudaStreamSynchronize(st));
+  if (rc != NCD_OK) a->h64_valid = a->sha_valid = a->xxh_valid = false;
+  if (rehashed) *rehashed = nre;
+  return rc;
+}

@@ -276,3 +276,79 @@ def test_digests_follow_an_arena_that_grows_between_commits(ctx):
         nb.close()
     finally:
         a.close()
+
+
+def test_digests_survive_a_recommit(ctx):
+    """Objects deleted, renumbered and added by ncd_arena_recommit: the digests of the records that stay where
+    they are move with them, only appended records are hashed again, and a hash-mode scan right after the
+    re-commit launches no hash kernel (same launch count as the steady state before it)."""
+    rng = random.Random(99)
+    objs = [A.CachedObject(A.KIND_WORKGROUP, f"default/wg-{i}", rand_bytes(rng, rng.choice([0, 1, 16, 100, 4097, 9000])), uid="u")
+            for i in range(300)]
+    host = A.pack(objs)
+    ctrl = ctx.arena_from_host(host)
+    a = Arena(ctx, host.payload_bytes + (1 << 18), host.nobj + 64, host.aux_bytes + 4096, host.nowner + 1, host.ndep + 1, device_only=False)
+    try:
+        a.fill_from(host)
+        a.commit(host.nobj, host.payload_bytes, host.aux_bytes, host.nowner, host.ndep)
+        modes = (A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64)
+        steady = {}
+        for m in modes:
+            for _ in range(2):
+                d = ctx.scan(ctrl, [a], m)
+                assert len(d.entries()) == 0
+                d.close()
+            steady[m] = ctx.last_stats().launches
+        # new image: drop some objects, reverse the order of the survivors, append new ones behind the old payload
+        keep = [i for i in range(host.nobj) if i % 7 != 3][::-1]
+        added = [A.CachedObject(A.KIND_WORKGROUP, f"default/new-{k}", rand_bytes(rng, 50 + 1000 * k), uid="u") for k in range(5)]
+        arr = a.host_arrays()
+        used, aux = host.payload_bytes, bytearray()
+
+        def put(b):
+            off = len(aux)
+            aux.extend(b)
+            return off, len(b)
+
+        final = []
+        for n, i in enumerate(keep):
+            arr["rec_off"][n], arr["rec_len"][n], arr["kind"][n] = host.rec_off[i], host.rec_len[i], host.kind[i]
+            arr["key_off"][n], arr["key_len"][n] = put(host.key(i).encode())
+            arr["uid_off"][n], arr["uid_len"][n] = put(b"u")
+            final.append(host.record(i))
+        for o in added:
+            n = len(final)
+            pad = (len(o.canon) + 15) // 16 * 16
+            arr["payload"][used : used + len(o.canon)] = np.frombuffer(o.canon, dtype=np.uint8)
+            arr["payload"][used + len(o.canon) : used + pad] = 0
+            arr["rec_off"][n], arr["rec_len"][n], arr["kind"][n] = used, len(o.canon), o.kind
+            arr["key_off"][n], arr["key_len"][n] = put(o.key.encode())
+            arr["uid_off"][n], arr["uid_len"][n] = put(b"u")
+            used += pad
+            final.append(o.canon)
+        n = len(final)
+        arr["own_start"][: n + 1] = 0
+        arr["dep_start"][: n + 1] = 0
+        arr["aux"][: len(aux)] = np.frombuffer(bytes(aux), dtype=np.uint8)
+        a.recommit(n, used, len(aux), 0, 0, host.payload_bytes)
+        dev = a.download()
+        assert [dev.record(i) for i in range(n)] == final
+        # the digests the arena holds are those of the new contents, without anybody asking for a re-hash
+        h64, ms = ctx.hash_arena(a, A.MODE_HASH64 | A.MODE_CACHED)
+        np.testing.assert_array_equal(h64, oracle.h64_arena(dev))
+        assert ms < 0.05
+        sha, _ = ctx.hash_arena(a, A.MODE_SHA256 | A.MODE_CACHED)
+        np.testing.assert_array_equal(sha, oracle.sha256_arena(dev))
+        xxh, _ = ctx.hash_arena(a, A.MODE_XXH64 | A.MODE_CACHED)
+        assert [int(v) for v in xxh] == [oracle.xxh64(r) for r in final]
+        # and a hash-mode scan hashes nothing: the controller still holds its digests, the shard's were carried
+        want_codes, want_ents = oracle.scan(host, [dev])
+        for m in modes:
+            d = ctx.scan(ctrl, [a], m)
+            np.testing.assert_array_equal(d.codes(), want_codes)
+            np.testing.assert_array_equal(d.entries(), want_ents)
+            d.close()
+            assert ctx.last_stats().launches == steady[m], (m, ctx.last_stats().launches, steady[m])
+    finally:
+        a.close()
+        ctrl.close()
