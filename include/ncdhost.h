@@ -134,6 +134,7 @@ typedef struct ncdh_scan_timing {
   uint64_t d2h_bytes; /* bytes it read back                                                                    */
   uint64_t records_synced, full_uploads, structural_uploads;
   uint64_t events;    /* puts / removes that changed something since the previous Scan                         */
+  uint64_t compactions; /* arenas compacted in place so far (ncd_arena_compact: dead payload reclaimed without PCIe) */
 } ncdh_scan_timing;
 int ncdh_last_timing(ncdh_checker* c, ncdh_scan_timing* out);
 

@@ -220,6 +220,14 @@ int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t*
  * is ~40 bytes, so a 1M-object arena re-commits in tens of MB instead of its 8.7 GB. */
 int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
                        uint64_t nowner, uint64_t ndep, uint64_t payload_dirty_from);
+/* Reclaims payload no record references any more (objects that were deleted, the old places of
+ * records that grew and were appended) WITHOUT a re-upload: the live records move to the front of
+ * the payload, on the device (a gather through scratch memory) and in the pinned host arrays (in
+ * place), and rec_off changes identically on both sides; keys, digests and the index stay as they
+ * are.  A long-lived controller's arena (informer events for days: controller.go:286-359) no longer
+ * needs a full ncd_arena_commit over PCIe to stop growing.  *new_payload_bytes = used payload
+ * afterwards; the caller re-reads rec_off from the host view.  No reference counterpart. */
+int ncd_arena_compact(ncd_arena* a, uint64_t* new_payload_bytes);
 /* Copies the committed device arrays into caller buffers (sized from
  * ncd_arena_counts); any pointer in dst may be NULL to skip that array. */
 int ncd_arena_download(ncd_arena* a, ncd_arena_view* dst);

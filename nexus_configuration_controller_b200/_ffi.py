@@ -113,6 +113,7 @@ PROTOTYPES = {
     "ncd_arena_recommit": (C.c_int, [VP, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64]),
     "ncd_arena_sync_records": (C.c_int, [VP, C.c_uint64, u32p, C.c_uint64]),
     "ncd_arena_fetch_records": (C.c_int, [VP, C.c_uint64, u32p, VP, C.c_uint64, u64p]),
+    "ncd_arena_compact": (C.c_int, [VP, u64p]),
     "ncd_arena_download": (C.c_int, [VP, C.POINTER(ArenaView)]),
     "ncd_arena_counts": (C.c_int, [VP, C.POINTER(ArenaView)]),
     "ncd_arena_rows": (C.c_int, [VP, u64p]),

@@ -40,7 +40,7 @@ Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uin
   uint64_t append = 0;
   for (uint32_t i : dirty)
     if (pad16(objs[i].len) > objs[i].rec_cap) append += pad16(objs[i].len);
-  if (payload_used + append > payload_cap) {  // no room to append: move to a larger arena
+  if (payload_used + append > payload_cap && !reclaim(append)) {  // no room to append: move to a larger arena
     dirty.clear();
     return prepare_structural(ctx, threads, h2d, /*regrow=*/true);
   }
@@ -64,6 +64,30 @@ Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uin
   dirty.clear();
   ++uploads_values;
   return Upload::Values;
+}
+
+// Out of payload room: if at least a quarter of what is used is dead (old places of records that
+// grew, records of deleted objects), ncd_arena_compact moves the live records together on both
+// sides without any PCIe traffic, and the arena lives on.  True when `append` more bytes fit afterwards.
+bool ClusterImage::reclaim(uint64_t append) {
+  if (!arena.a || force_full) return false;
+  uint64_t live = 0;
+  for (const CachedObject& o : objs)
+    if (o.live && o.rec_off >= 0) live += o.rec_cap;
+  if (live + append > payload_cap || live * 4 > payload_used * 3) return false;
+  uint64_t used = 0;
+  if (ncd_arena_compact(arena.a, &used) != NCD_OK) return false;  // the arena is untouched on failure: regrow instead
+  ncd_arena_view v = host_view();
+  // positions follow the arena's object numbering of the last commit, which is objs order
+  for (size_t i = 0; i < objs.size() && i < objs_committed; ++i) {
+    CachedObject& o = objs[i];
+    if (o.rec_off < 0) continue;
+    o.rec_off = (int64_t)v.rec_off[i];
+    o.rec_cap = pad16(v.rec_len[i]);  // the spare room a shrunken record kept is given back too
+  }
+  payload_used = used;
+  ++compactions;
+  return payload_used + append <= payload_cap;
 }
 
 // No cache lock held; one scan at a time.  Values uploads are batched by the caller.

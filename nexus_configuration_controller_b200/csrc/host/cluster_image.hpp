@@ -212,7 +212,7 @@ struct ClusterImage {
   uint64_t payload_used = 0, payload_cap = 0, nobj_cap = 0, aux_cap = 0, nowner_cap = 0, ndep_cap = 0;
   bool structural = true;   // keys / owners / dependents changed since the last commit
   bool force_full = false;  // the resident device copy is not trusted: upload everything again
-  uint64_t uploads_full = 0, uploads_structural = 0, uploads_values = 0;
+  uint64_t uploads_full = 0, uploads_structural = 0, uploads_values = 0, compactions = 0;
   std::vector<uint32_t> pending_changed;  // records a prepared Values upload still has to push
 
   const uint8_t* bytes_of(const CachedObject& o) const { return o.pending ? o.pending : host_payload + o.rec_off; }
@@ -324,6 +324,7 @@ struct ClusterImage {
   void assign(CachedObject& o, bool force_append);
   static void copy_record(ncd_arena_view& v, CachedObject& o, const uint8_t* src);
   void bind_arena();
+  bool reclaim(uint64_t append);
   void write_all(ncd_arena_view& v, int threads, const uint8_t* old_payload, bool replace_all);
 };
 

@@ -442,6 +442,7 @@ int ncdh_scan(ncdh_checker* c) {
         c->dir = std::move(dir);
         c->unadopted_valid = false;
       }
+      for (ClusterImage* img : imgs) tm.compactions += img->compactions;
       tm.pack_ms = ms_since(t0);
     }
     // ---- GPU: uploads, then the scan (the cache lock is free: events and lookups go on)

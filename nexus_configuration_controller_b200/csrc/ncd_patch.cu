@@ -8,6 +8,7 @@
 // cross PCIe.  The packer rewrites a changed object's record in the pinned host arrays (in place
 // when it fits, else appended behind the payload end) and names the object here; one kernel
 // pulls exactly those records over PCIe from the pinned (device-mapped) host memory.
+#include <algorithm>
 #include <vector>
 
 #include "ncd_common.cuh"
@@ -243,5 +244,97 @@ int ncd_arena_fetch_records(ncd_arena* a, uint64_t n, const uint32_t* obj_idx, u
   NCD_CUDA(cudaFreeAsync(d_out, st));
   NCD_CUDA(cudaStreamSynchronize(st));
   NCD_CUDA(cudaGetLastError());
+  return NCD_OK;
+}
+
+// ------------------------------------------------------------------ compaction
+// Dead payload — records of deleted objects, old places of records that grew and were appended —
+// used to be reclaimed only by a full ncd_arena_commit, i.e. by sending the whole cluster over
+// PCIe again.  Here the live records are moved to the front of the payload where they are: on the
+// device by a gather through a scratch buffer, in the pinned host arrays by memmove, in ascending
+// order of their offsets so that nothing is overwritten before it is moved.  Offsets change on
+// both sides identically; the index, the join caches and the digests do not depend on them.
+__global__ void __launch_bounds__(128)
+k_compact_gather(const uint8_t* __restrict__ payload, const uint64_t* __restrict__ old_off, const uint64_t* __restrict__ new_off,
+                 const uint32_t* __restrict__ rec_len, uint8_t* __restrict__ tmp) {
+  const uint32_t i = blockIdx.x;
+  const uint4* src = reinterpret_cast<const uint4*>(payload + old_off[i]);
+  uint4* dst = reinterpret_cast<uint4*>(tmp + new_off[i]);
+  const uint32_t nvec = (rec_len[i] + 15) >> 4;
+  for (uint32_t v = threadIdx.x; v < nvec; v += blockDim.x) dst[v] = src[v];
+}
+__global__ void k_compact_offsets(uint64_t* __restrict__ rec_off, ObjMeta* __restrict__ meta, const uint64_t* __restrict__ new_off, uint32_t n) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  rec_off[i] = new_off[i];
+  meta[i].rec_off = new_off[i];
+}
+
+int ncd_arena_compact(ncd_arena* a, uint64_t* new_payload_bytes) {
+  if (!a) {
+    ncd_set_error("ncd_arena_compact: null arena");
+    return NCD_E_INVALID;
+  }
+  if (a->flags != NCD_ARENA_HOST_PINNED || !a->committed) {
+    ncd_set_error("ncd_arena_compact: needs a committed arena with pinned host arrays");
+    return NCD_E_STATE;
+  }
+  const uint64_t n = a->nobj;
+  ncd_ctx* ctx = a->ctx;
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  NCD_CUDA(cudaStreamSynchronize(st));
+  // new offsets: the live records in ascending order of their current offsets, packed
+  std::vector<uint32_t> order(n);
+  for (uint64_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
+  const uint64_t* off = a->h.rec_off;
+  const uint32_t* len = a->h.rec_len;
+  std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) { return off[x] != off[y] ? off[x] < off[y] : len[x] < len[y]; });
+  std::vector<uint64_t> new_off(n);
+  uint64_t cur = 0, prev_end = 0;
+  for (uint64_t k = 0; k < n; ++k) {
+    const uint32_t i = order[k];
+    const uint64_t padded = ((uint64_t)len[i] + 15) & ~15ull;
+    if (off[i] < prev_end && padded) {
+      ncd_set_error("ncd_arena_compact: records %u overlaps the one before it", i);
+      return NCD_E_INVALID;
+    }
+    new_off[i] = cur;
+    cur += padded;
+    if (padded) prev_end = off[i] + padded;
+  }
+  if (cur == a->payload_bytes) {  // nothing to reclaim
+    if (new_payload_bytes) *new_payload_bytes = cur;
+    return NCD_OK;
+  }
+  // device first (it still needs the old offsets, which the device arrays hold)
+  uint64_t* d_new = nullptr;
+  uint8_t* tmp = nullptr;
+  NCD_CUDA(cudaMallocAsync((void**)&d_new, (n ? n : 1) * 8, st));
+  cudaError_t e = cudaMallocAsync((void**)&tmp, cur ? cur : 16, st);
+  if (e != cudaSuccess) {
+    cudaFreeAsync(d_new, st);
+    ncd_set_error("ncd_arena_compact: %llu bytes of device scratch: %s", (unsigned long long)cur, cudaGetErrorString(e));
+    return NCD_E_NOMEM;
+  }
+  if (n) {
+    NCD_CUDA(cudaMemcpyAsync(d_new, new_off.data(), n * 8, cudaMemcpyHostToDevice, st));
+    k_compact_gather<<<(unsigned)n, 128, 0, st>>>(a->d.payload, a->d.rec_off, d_new, a->d.rec_len, tmp);
+    if (cur) NCD_CUDA(cudaMemcpyAsync(a->d.payload, tmp, cur, cudaMemcpyDeviceToDevice, st));
+    k_compact_offsets<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a->d.rec_off, a->meta, d_new, (uint32_t)n);
+  }
+  NCD_CUDA(cudaFreeAsync(tmp, st));
+  NCD_CUDA(cudaFreeAsync(d_new, st));
+  // host: the same moves, front to back, in place (new offset <= old offset for every record)
+  for (uint64_t k = 0; k < n; ++k) {
+    const uint32_t i = order[k];
+    const uint64_t padded = ((uint64_t)len[i] + 15) & ~15ull;
+    if (padded && new_off[i] != off[i]) memmove(a->h.payload + new_off[i], a->h.payload + off[i], padded);
+  }
+  for (uint64_t i = 0; i < n; ++i) a->h.rec_off[i] = new_off[i];
+  NCD_CUDA(cudaStreamSynchronize(st));
+  NCD_CUDA(cudaGetLastError());
+  a->payload_bytes = cur;
+  if (new_payload_bytes) *new_payload_bytes = cur;
   return NCD_OK;
 }

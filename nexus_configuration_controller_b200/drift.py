@@ -252,6 +252,13 @@ class Arena:
             self._meta = host
         return self._meta
 
+    def compact(self) -> int:
+        """Moves the live records to the front of the payload on both sides (ncd_arena_compact); returns the used bytes."""
+        self._meta = None
+        out = C.c_uint64()
+        check(self.ctx.lib.ncd_arena_compact(self.handle, C.byref(out)))
+        return out.value
+
     def counts(self) -> ArenaView:
         v = ArenaView()
         check(self.ctx.lib.ncd_arena_counts(self.handle, C.byref(v)))

@@ -11,6 +11,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <chrono>
 #include <thread>
 #include <vector>
@@ -169,6 +170,35 @@ int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t*
     }
     a->d.payload_bytes = new_payload_bytes[k];
   }
+  return NCD_OK;
+}
+
+int ncd_arena_compact(ncd_arena* a, uint64_t* new_payload_bytes) {
+  if (!a || !a->committed) return fail(NCD_E_STATE, "fake: compact of an uncommitted arena");
+  const uint64_t n = a->d.nobj;
+  std::vector<uint32_t> order(n);
+  for (uint64_t i = 0; i < n; ++i) order[i] = (uint32_t)i;
+  std::sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
+    return a->h.rec_off[x] != a->h.rec_off[y] ? a->h.rec_off[x] < a->h.rec_off[y] : a->h.rec_len[x] < a->h.rec_len[y];
+  });
+  uint64_t cur = 0;
+  std::vector<uint8_t> tmp(a->payload_cap + 16);
+  std::vector<uint64_t> noff(n);
+  for (uint32_t i : order) {  // the "device" copy is gathered from ITS offsets, as the real library does
+    const uint64_t padded = ((uint64_t)a->d.rec_len[i] + 15) / 16 * 16;
+    if (a->d.rec_off[i] != a->h.rec_off[i] || a->d.rec_len[i] != a->h.rec_len[i]) return fail(NCD_E_STATE, "fake: compact of an arena with unsynced records");
+    memcpy(tmp.data() + cur, a->d.payload + a->d.rec_off[i], padded);
+    noff[i] = cur;
+    cur += padded;
+  }
+  memcpy(a->d.payload, tmp.data(), cur);
+  for (uint32_t i : order) {
+    const uint64_t padded = ((uint64_t)a->h.rec_len[i] + 15) / 16 * 16;
+    memmove(a->h.payload + noff[i], a->h.payload + a->h.rec_off[i], padded);
+  }
+  for (uint64_t i = 0; i < n; ++i) a->h.rec_off[i] = a->d.rec_off[i] = noff[i];
+  a->d.payload_bytes = cur;
+  if (new_payload_bytes) *new_payload_bytes = cur;
   return NCD_OK;
 }
 

@@ -352,3 +352,57 @@ def test_digests_survive_a_recommit(ctx):
     finally:
         a.close()
         ctrl.close()
+
+
+def test_compaction_reclaims_dead_payload_in_place(ctx):
+    """ncd_arena_compact after records were rewritten elsewhere: the live records sit packed at the front on the
+    device and in the pinned arrays alike, contents and digests are what they were, scans decide as before, and
+    the arena takes value syncs at the new offsets."""
+    rng = random.Random(123)
+    ctrl_h, shard_hs = random_clusters(55, n_templates=14, n_shards=2)
+    arenas = [resident(ctx, h, 1 << 20) for h in [ctrl_h] + shard_hs]
+    used = [h.payload_bytes for h in [ctrl_h] + shard_hs]
+    try:
+        a, arr = arenas[1], arenas[1].host_arrays()
+        n = a.counts().nobj
+        for rnd in range(3):  # every record of shard 0 grows three times: three dead copies each
+            picks = list(range(n))
+            for i in picks:
+                old = int(arr["rec_len"][i])
+                used[1] = rewrite(rng, arr, used[1], i, rand_bytes(rng, old + rng.randint(1, 40)))
+            a.sync_records(np.array(picks, dtype=np.uint32), used[1])
+        for m in (A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64):
+            ctx.hash_arena(a, m)
+        before = a.download()
+        want_codes, want_ents = oracle.scan(arenas[0].download(), [before, arenas[2].download()])
+        live = sum((int(before.rec_len[i]) + 15) // 16 * 16 for i in range(n))
+        assert used[1] > 2 * live
+        assert a.compact() == live
+        used[1] = live
+        after = a.download()
+        assert after.payload_bytes == live
+        assert [after.record(i) for i in range(n)] == [before.record(i) for i in range(n)]
+        for i in range(n):  # the pinned arrays moved the same way
+            off, ln = int(arr["rec_off"][i]), int(arr["rec_len"][i])
+            assert off == int(after.rec_off[i]) and arr["payload"][off : off + ln].tobytes() == after.record(i)
+        h64, _ = ctx.hash_arena(a, A.MODE_HASH64 | A.MODE_CACHED)
+        np.testing.assert_array_equal(h64, oracle.h64_arena(after))
+        for mode in (A.MODE_DIRECT, A.MODE_HASH64, A.MODE_SHA256, A.MODE_XXH64):
+            d = ctx.scan(arenas[0], arenas[1:], mode)
+            np.testing.assert_array_equal(d.codes(), want_codes)
+            np.testing.assert_array_equal(d.entries(), want_ents)
+            d.close()
+        assert a.compact() == live  # nothing left to reclaim
+        # value syncs keep working at the new offsets
+        i = next(k for k in range(n) if after.rec_len[k] > 0)
+        used[1] = rewrite(rng, arr, used[1], i, rand_bytes(rng, int(after.rec_len[i])))
+        a.sync_records(np.array([i], dtype=np.uint32), used[1])
+        dev = a.download()
+        off = int(arr["rec_off"][i])
+        assert dev.record(i) == arr["payload"][off : off + int(arr["rec_len"][i])].tobytes()
+        d = ctx.scan(arenas[0], arenas[1:], A.MODE_DIRECT)
+        np.testing.assert_array_equal(d.codes(), oracle.scan(arenas[0].download(), [dev, arenas[2].download()])[0])
+        d.close()
+    finally:
+        for x in arenas:
+            x.close()

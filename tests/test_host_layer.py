@@ -450,3 +450,37 @@ def test_a_failed_scan_costs_a_full_upload_not_the_cached_values():
         f.scan()
         assert f.upload_counts(-1)[0] == 2 and f.upload_counts(-1)[2] >= 1
         assert f.plan_template(NS, "test")[1][0] == [["update-data", "configmaps", "test-config"]]
+
+
+def test_an_arena_full_of_dead_payload_is_compacted_not_replaced(make_checker):
+    """Values that keep growing are appended behind the used payload and leave their old places dead.  When the
+    arena runs out of room and most of it is dead, the host layer has it compacted in place (no upload of the
+    cluster) instead of building a larger one; decisions stay right before and after."""
+    with make_checker(1) as f:
+        fleet = Fleet(1, f)
+        cfgs = [new_configmap(f"cfg-{i}", None, {"k": "a" * 3000}) for i in range(8)]
+        tmpl = [new_template(f"algo-{i}", None, cfgs[i]) for i in range(8)]
+        for i in range(8):
+            fleet.put(-1, tmpl[i])
+            fleet.put(-1, with_owners(cfgs[i], [tmpl[i]]))
+            fleet.put(0, tmpl[i])
+            fleet.put(0, with_owners(cfgs[i], [tmpl[i]]))
+        fleet.check()
+        assert f.upload_counts(-1) == (1, 0, 0)
+        # one ConfigMap of the controller grows a little, again and again: every version is appended
+        grown = 0
+        for step in range(60):
+            fleet.put(-1, with_owners(new_configmap("cfg-3", None, {"k": "b" * (3001 + 16 * step)}), [tmpl[3]]))
+            fleet.check()
+            grown += 1
+            if f.timing()["compactions"] > 0:
+                break
+        assert f.timing()["compactions"] >= 1, "the arena was never compacted"
+        assert f.upload_counts(-1)[0] == 1, "a compaction must not cost a full upload"
+        # life goes on in the compacted arena: in-place rewrites, appends, structural changes
+        fleet.put(-1, with_owners(new_configmap("cfg-5", None, {"k": "short"}), [tmpl[5]]))
+        fleet.put(-1, with_owners(new_configmap("cfg-6", None, {"k": "c" * 5000}), [tmpl[6]]))
+        fleet.check()
+        fleet.remove(0, with_owners(cfgs[2], [tmpl[2]]))
+        fleet.check()
+        assert grown > 3
