@@ -593,8 +593,7 @@ def run_e2e_cold(ctx, args, mode, world, rank, dist, ext, gather):
         return float(t.item())
 
     def cold_step():
-        for h, c in hosts:
-            h.commit(c.nobj, c.payload_bytes, c.aux_bytes, c.nowner, c.ndep)
+        ctx.commit_many(arenas, [(c.nobj, c.payload_bytes, c.aux_bytes, c.nowner, c.ndep) for _, c in hosts])
         d = ctx.scan(arenas[0], arenas[1:], mode)
         gather(d)
         ents = d.entries()

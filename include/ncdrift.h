@@ -191,6 +191,13 @@ int ncd_arena_host_view(ncd_arena* a, ncd_arena_view* out);
  * is immutable afterwards until the next commit. */
 int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,
                      uint64_t nowner, uint64_t ndep);
+/* The same for several arenas of one context in one call (the controller cluster and every shard
+ * before a sweep): all uploads are enqueued up front on a copy stream and the index of arena k is
+ * built while arena k+1 is still crossing PCIe, instead of copy and index build taking turns.
+ * Arrays of `count` entries; an arena may appear once.  On an error the arenas before it are
+ * committed, it and the ones after it are not. */
+int ncd_arenas_commit(int count, ncd_arena* const* arenas, const uint64_t* nobj, const uint64_t* payload_bytes,
+                      const uint64_t* aux_bytes, const uint64_t* nowner, const uint64_t* ndep);
 /* Incremental update of a committed NCD_ARENA_HOST_PINNED arena: the records of the listed
  * objects were rewritten in the pinned host arrays (payload bytes at a new or the same rec_off,
  * rec_len; a record that grew is appended behind the old payload end) and the device copy must

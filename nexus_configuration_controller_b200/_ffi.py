@@ -110,6 +110,7 @@ PROTOTYPES = {
     "ncd_arena_destroy": (None, [VP]),
     "ncd_arena_host_view": (C.c_int, [VP, C.POINTER(ArenaView)]),
     "ncd_arena_commit": (C.c_int, [VP, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64]),
+    "ncd_arenas_commit": (C.c_int, [C.c_int, C.POINTER(VP), u64p, u64p, u64p, u64p, u64p]),
     "ncd_arena_recommit": (C.c_int, [VP, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64]),
     "ncd_arena_sync_records": (C.c_int, [VP, C.c_uint64, u32p, C.c_uint64]),
     "ncd_arena_fetch_records": (C.c_int, [VP, C.c_uint64, u32p, VP, C.c_uint64, u64p]),

@@ -316,6 +316,15 @@ struct ClusterImage {
 
   Upload prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uint64_t* h2d);
   void upload(Upload what);
+  // A prepared Full upload, for the caller that commits several clusters in one ncd_arenas_commit.
+  void full_counts(uint64_t out[5]) const {
+    out[0] = objs_committed;
+    out[1] = payload_used;
+    out[2] = aux_used;
+    out[3] = own_used;
+    out[4] = dep_used;
+  }
+  void full_done() { force_full = false; }
 
  private:
   uint64_t aux_used = 0, own_used = 0, dep_used = 0, objs_committed = 0, dirty_from = 0;

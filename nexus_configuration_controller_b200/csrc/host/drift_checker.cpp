@@ -447,14 +447,19 @@ int ncdh_scan(ncdh_checker* c) {
     }
     // ---- GPU: uploads, then the scan (the cache lock is free: events and lookups go on)
     const auto t_up = std::chrono::steady_clock::now();
-    std::vector<ncd_arena*> as;
-    std::vector<uint64_t> ns, pbs;
+    std::vector<ncd_arena*> as, full;
+    std::vector<uint64_t> ns, pbs, fc[5];
     std::vector<const uint32_t*> idx;
     for (size_t k = 0; k < imgs.size(); ++k) {
       ClusterImage* img = imgs[k];
       if (ups[k] == Upload::Full) ++tm.full_uploads;
       if (ups[k] == Upload::Structural) ++tm.structural_uploads;
-      if (ups[k] == Upload::Values) {  // the value rewrites of every cluster: one round trip
+      if (ups[k] == Upload::Full) {  // whole clusters (first scan, a larger arena): their uploads overlap each other's index build
+        uint64_t c5[5];
+        img->full_counts(c5);
+        full.push_back(img->arena.a);
+        for (int q = 0; q < 5; ++q) fc[q].push_back(c5[q]);
+      } else if (ups[k] == Upload::Values) {  // the value rewrites of every cluster: one round trip
         as.push_back(img->arena.a);
         ns.push_back(img->pending_changed.size());
         idx.push_back(img->pending_changed.data());
@@ -463,6 +468,12 @@ int ncdh_scan(ncdh_checker* c) {
       } else {
         img->upload(ups[k]);
       }
+    }
+    if (!full.empty()) {
+      if (ncd_arenas_commit((int)full.size(), full.data(), fc[0].data(), fc[1].data(), fc[2].data(), fc[3].data(), fc[4].data()) != NCD_OK)
+        throw std::runtime_error(ncd_err("ncd_arenas_commit"));
+      for (size_t k = 0; k < imgs.size(); ++k)
+        if (ups[k] == Upload::Full) imgs[k]->full_done();
     }
     if (!as.empty()) {
       const int rc = ncd_arenas_sync_records((int)as.size(), as.data(), ns.data(), idx.data(), pbs.data());

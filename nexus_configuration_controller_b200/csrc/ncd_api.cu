@@ -4,6 +4,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <vector>
+
 #include "ncd_common.cuh"
 
 // ------------------------------------------------------------------ errors
@@ -93,6 +95,7 @@ extern "C" void ncd_destroy(ncd_ctx* ctx) {
   if (ctx->d_shards) cudaFree(ctx->d_shards);
   if (ctx->d_jobs) cudaFree(ctx->d_jobs);
   if (ctx->d_counters) cudaFree(ctx->d_counters);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   if (ctx->list_dev) cudaFree(ctx->list_dev);
   if (ctx->list_host) cudaFreeHost(ctx->list_host);
   for (int i = 0; i < 4; ++i)
@@ -292,6 +295,66 @@ extern "C" int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_by
       NCD_CUDA(cudaMemcpyAsync(*field_ptr(&a->d, f), *field_ptr(&a->h, f), bytes, cudaMemcpyHostToDevice, st));
   }
   return ncd_arena_commit_device(a, nobj, payload_bytes, aux_bytes, nowner, ndep);
+}
+
+// Several arenas of one context committed in one call (a controller without resident state uploads
+// the controller cluster and every shard before each sweep; the host layer does it on its first
+// scan).  Every upload is enqueued up front on a copy stream, so the PCIe link never idles while
+// the index of an earlier arena is being built on the main stream (ncd_arena_commit alone
+// alternates copy -> index build -> copy ...).
+extern "C" int ncd_arenas_commit(int count, ncd_arena* const* arenas, const uint64_t* nobj, const uint64_t* payload_bytes,
+                                 const uint64_t* aux_bytes, const uint64_t* nowner, const uint64_t* ndep) {
+  if (count < 0 || (count > 0 && (!arenas || !nobj || !payload_bytes || !aux_bytes || !nowner || !ndep))) {
+    ncd_set_error("ncd_arenas_commit: null argument");
+    return NCD_E_INVALID;
+  }
+  if (count == 0) return NCD_OK;
+  ncd_ctx* ctx = nullptr;
+  for (int k = 0; k < count; ++k) {
+    ncd_arena* a = arenas[k];
+    if (!a || a->flags != NCD_ARENA_HOST_PINNED) {
+      ncd_set_error("ncd_arenas_commit: arena %d has no pinned host arrays", k);
+      return NCD_E_STATE;
+    }
+    if (ctx && a->ctx != ctx) {
+      ncd_set_error("ncd_arenas_commit: arenas of different contexts");
+      return NCD_E_INVALID;
+    }
+    for (int q = 0; q < k; ++q)
+      if (arenas[q] == a) {
+        ncd_set_error("ncd_arenas_commit: arena %d is listed twice", k);
+        return NCD_E_INVALID;
+      }
+    ctx = a->ctx;
+    NCD_TRY(check_counts(a, nobj[k], payload_bytes[k], aux_bytes[k], nowner[k], ndep[k]));
+  }
+  NCD_CUDA(cudaSetDevice(ctx->device));
+  if (!ctx->copy_stream) NCD_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  NCD_CUDA(cudaStreamSynchronize(ctx->stream));  // nothing on the main stream still reads what is about to be overwritten
+  std::vector<cudaEvent_t> done((size_t)count);
+  for (int k = 0; k < count; ++k) {
+    ncd_arena* a = arenas[k];
+    a->committed = false;
+    for (int i = 0; i < kNumFields; ++i) {
+      const Field& f = kFields[i];
+      uint64_t bytes = field_count(f, payload_bytes[k], nobj[k], aux_bytes[k], nowner[k], ndep[k]) * f.elem;
+      if (f.cap_kind == 0) bytes = payload_bytes[k];
+      if (bytes)
+        NCD_CUDA(cudaMemcpyAsync(*field_ptr(&a->d, f), *field_ptr(&a->h, f), bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    }
+    NCD_CUDA(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
+    NCD_CUDA(cudaEventRecord(done[k], ctx->copy_stream));
+  }
+  int rc = NCD_OK;
+  for (int k = 0; k < count; ++k) {
+    if (rc == NCD_OK) {
+      cudaStreamWaitEvent(ctx->stream, done[k], 0);
+      rc = ncd_arena_commit_device(arenas[k], nobj[k], payload_bytes[k], aux_bytes[k], nowner[k], ndep[k]);
+      if (rc != NCD_OK) cudaStreamSynchronize(ctx->copy_stream);  // the later uploads finish before anybody reuses the host arrays
+    }
+    cudaEventDestroy(done[k]);
+  }
+  return rc;
 }
 
 extern "C" int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes,

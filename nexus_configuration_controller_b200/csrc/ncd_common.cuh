@@ -145,6 +145,7 @@ struct ncd_ctx {
   size_t hpool_cap[4];
   // ncd_scan_host: the diff list buffer (device, header + entries) and its pinned host mirror,
   // kept between scans and grown only when a scan finds more than they hold
+  cudaStream_t copy_stream;  // ncd_arenas_commit: uploads run here while the index of an earlier arena is built
   void* list_dev;
   void* list_host;
   uint64_t list_cap;  // entries

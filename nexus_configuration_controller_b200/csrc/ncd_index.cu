@@ -362,16 +362,21 @@ void ncd_fill_dev_arena(const ncd_arena* a, DevArena* o) {
   o->xxh = a->xxh;
 }
 
+// Index arrays are (re)allocated in stream order from the device's pool (kept cached, ncd_init): a
+// commit of an arena that was committed before neither returns memory to the driver nor stalls the
+// device the way cudaFree / cudaMalloc do — other streams (the uploads of the next arena,
+// ncd_arenas_commit) keep running.
+static thread_local cudaStream_t g_realloc_stream = nullptr;  // the committing context's stream (contexts of different GPUs commit from different threads)
 template <typename T>
 static int dev_realloc(T** p, uint64_t n) {
   if (*p) {
-    cudaFree(*p);
+    cudaFreeAsync(*p, g_realloc_stream);
     *p = nullptr;
   }
   if (n == 0) n = 1;
-  cudaError_t e = cudaMalloc((void**)p, n * sizeof(T));
+  cudaError_t e = cudaMallocAsync((void**)p, n * sizeof(T), g_realloc_stream);
   if (e != cudaSuccess) {
-    ncd_set_error("cudaMalloc of %llu bytes failed: %s", (unsigned long long)(n * sizeof(T)),
+    ncd_set_error("cudaMallocAsync of %llu bytes failed: %s", (unsigned long long)(n * sizeof(T)),
                   cudaGetErrorString(e));
     return NCD_E_NOMEM;
   }
@@ -383,6 +388,7 @@ static int dev_realloc(T** p, uint64_t n) {
 int ncd_rebuild_tiles(ncd_arena* a) {
   ncd_ctx* ctx = a->ctx;
   cudaStream_t st = ctx->stream;
+  g_realloc_stream = st;
   const uint32_t n = (uint32_t)a->nobj;
   const unsigned blocks = (n + 255) / 256;
   DevArena da;
@@ -431,6 +437,7 @@ int ncd_build_index(ncd_arena* a) {
   ncd_ctx* ctx = a->ctx;
   a->generation = g_generation.fetch_add(1) + 1;  // keys may have changed: join caches built on the old index are stale
   cudaStream_t st = ctx->stream;
+  g_realloc_stream = st;
   const uint32_t n = (uint32_t)a->nobj;
   const unsigned blocks = (n + 255) / 256;
 

@@ -100,6 +100,14 @@ class Context:
             )
         )
 
+    def commit_many(self, arenas: Sequence["Arena"], counts: Sequence[Tuple[int, int, int, int, int]]) -> None:
+        """ncd_arenas_commit: counts[k] = (nobj, payload_bytes, aux_bytes, nowner, ndep) of arenas[k]."""
+        k = len(arenas)
+        for a in arenas:
+            a._meta = None
+        cols = [(C.c_uint64 * max(k, 1))(*[int(c[j]) for c in counts]) for j in range(5)]
+        check(self.lib.ncd_arenas_commit(k, (C.c_void_p * max(k, 1))(*[a.handle for a in arenas]), *cols))
+
     def stats_back(self, back: int) -> ScanStats:
         st = ScanStats()
         check(self.lib.ncd_scan_stats_back(self.handle, back, C.byref(st)))

@@ -147,6 +147,14 @@ int ncd_arena_commit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64
   if (!a) return fail(NCD_E_INVALID, "fake: null");
   return upload(a, nobj, payload_bytes, aux_bytes, nowner, ndep, 0);
 }
+int ncd_arenas_commit(int count, ncd_arena* const* arenas, const uint64_t* nobj, const uint64_t* payload_bytes,
+                      const uint64_t* aux_bytes, const uint64_t* nowner, const uint64_t* ndep) {
+  for (int k = 0; k < count; ++k) {
+    const int rc = ncd_arena_commit(arenas[k], nobj[k], payload_bytes[k], aux_bytes[k], nowner[k], ndep[k]);
+    if (rc != NCD_OK) return rc;
+  }
+  return NCD_OK;
+}
 int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint64_t aux_bytes, uint64_t nowner, uint64_t ndep,
                        uint64_t payload_dirty_from) {
   if (!a || !a->committed) return fail(NCD_E_STATE, "fake: recommit before commit");

@@ -406,3 +406,35 @@ def test_compaction_reclaims_dead_payload_in_place(ctx):
     finally:
         for x in arenas:
             x.close()
+
+
+def test_committing_several_arenas_at_once_equals_one_by_one(ctx):
+    """ncd_arenas_commit (uploads of all arenas enqueued up front, index builds behind them) leaves every arena
+    exactly as ncd_arena_commit does, also when the same arenas are committed again and again."""
+    from nexus_configuration_controller_b200._ffi import NcdError
+
+    ctrl_h, shard_hs = random_clusters(66, n_templates=20, n_shards=4)
+    hosts = [ctrl_h] + shard_hs
+    arenas = [Arena(ctx, h.payload_bytes, h.nobj, h.aux_bytes, h.nowner, h.ndep, device_only=False) for h in hosts]
+    want_codes, want_ents = oracle.scan(ctrl_h, shard_hs)
+    try:
+        for a, h in zip(arenas, hosts):
+            a.fill_from(h)
+        for rep in range(3):
+            ctx.commit_many(arenas, [(h.nobj, h.payload_bytes, h.aux_bytes, h.nowner, h.ndep) for h in hosts])
+            for mode in (A.MODE_DIRECT, A.MODE_HASH64):
+                d = ctx.scan(arenas[0], arenas[1:], mode)
+                np.testing.assert_array_equal(d.codes(), want_codes)
+                np.testing.assert_array_equal(d.entries(), want_ents)
+                d.close()
+        for a, h in zip(arenas, hosts):
+            dev = a.download()
+            assert [dev.record(i) for i in range(h.nobj)] == [h.record(i) for i in range(h.nobj)]
+        with pytest.raises(NcdError):  # the same arena twice
+            ctx.commit_many([arenas[1], arenas[1]], [(hosts[1].nobj, hosts[1].payload_bytes, hosts[1].aux_bytes, hosts[1].nowner, hosts[1].ndep)] * 2)
+        with pytest.raises(NcdError):  # beyond capacity
+            ctx.commit_many([arenas[1]], [(hosts[1].nobj + 1, hosts[1].payload_bytes, hosts[1].aux_bytes, hosts[1].nowner, hosts[1].ndep)])
+        ctx.commit_many([], [])
+    finally:
+        for a in arenas:
+            a.close()
