@@ -48,8 +48,11 @@ int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char*
 /* The same as a batch: informer events that arrived since the last call (AddFunc / UpdateFunc /
  * DeleteFunc of the four informers, controller.go:286-359), applied in order.  The values are
  * canonicalised on `threads` threads (<= 0: one per host core), then the cache images are updated
- * under the checker's lock.  An event that fails (malformed value) stops the batch: the events
- * before it are applied, the call returns -1. */
+ * under the checker's lock.  An event that fails (malformed value, unknown cluster) is skipped:
+ * every other event of the batch is applied, the call returns -1 and ncdh_last_error names the
+ * first skipped event.  A new value that fits the place its record already has in the arena's
+ * pinned payload is written there directly (unchanged values — a resync — write nothing); others
+ * wait in pooled memory until the next ncdh_scan lays them out. */
 enum { NCDH_EV_PUT = 0, NCDH_EV_DELETE = 1 };
 typedef struct ncdh_event {
   int32_t cluster;  /* -1 controller, s >= 0 shard s                         */
@@ -135,6 +138,7 @@ typedef struct ncdh_scan_timing {
   uint64_t records_synced, full_uploads, structural_uploads;
   uint64_t events;    /* puts / removes that changed something since the previous Scan                         */
   uint64_t compactions; /* arenas compacted in place so far (ncd_arena_compact: dead payload reclaimed without PCIe) */
+  uint64_t records_in_place; /* of records_synced: written into the pinned payload by their batch, not copied by the packer */
 } ncdh_scan_timing;
 int ncdh_last_timing(ncdh_checker* c, ncdh_scan_timing* out);
 

@@ -38,13 +38,15 @@ Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uin
 
   // same objects, some values changed: rewrite those records, to be pushed alone
   uint64_t append = 0;
-  for (uint32_t i : dirty)
+  ncd_arena_view v = host_view();
+  for (uint32_t i : dirty) {
     if (pad16(objs[i].len) > objs[i].rec_cap) append += pad16(objs[i].len);
+    if (!objs[i].pending) v.rec_len[i] = objs[i].len;  // rewritten in place: a compaction below must move its new length
+  }
   if (payload_used + append > payload_cap && !reclaim(append)) {  // no room to append: move to a larger arena
     dirty.clear();
     return prepare_structural(ctx, threads, h2d, /*regrow=*/true);
   }
-  ncd_arena_view v = host_view();
   for (uint32_t i : dirty) {  // offsets first (serial), bytes after (parallel)
     CachedObject& o = objs[i];
     assign(o, /*force_append=*/false);
@@ -54,11 +56,14 @@ Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uin
   }
   parallel_for(dirty.size(), threads, 64, [&](size_t k) {
     CachedObject& o = objs[dirty[k]];
-    copy_record(v, o, o.pending);
+    if (o.pending) copy_record(v, o, o.pending);  // else the batch wrote the record in place already
   });
+  in_place_last = 0;
   for (uint32_t i : dirty) {  // the arena holds the bytes now: the events' memory is released
+    in_place_last += objs[i].pending ? 0 : 1;
     objs[i].pending = nullptr;
     objs[i].hold.reset();
+    objs[i].direct = false;
   }
   pending_changed.swap(dirty);
   dirty.clear();
@@ -113,7 +118,7 @@ Upload ClusterImage::prepare_structural(ncd_ctx* ctx, int threads, uint64_t* h2d
     for (const auto& s : f.configmaps) aux += f.key.size() + s.size();
     ndep += f.secrets.size() + f.configmaps.size();
     compact += pad16(o.len);
-    if (o.pending) append += pad16(o.len);
+    if (o.pending || o.direct) append += pad16(o.len);
   }
   const bool fits = arena.a && !regrow && objs.size() <= nobj_cap && aux <= aux_cap && nowner <= nowner_cap && ndep <= ndep_cap &&
                     payload_used + append <= payload_cap;
@@ -168,7 +173,8 @@ void ClusterImage::copy_record(ncd_arena_view& v, CachedObject& o, const uint8_t
 
 // Every per-object array from scratch (arena layout: ncdrift.h "arenas").  Same arena: records
 // already in it keep their place and only pending ones are appended (only appended payload is
-// re-uploaded).  New arena (replace_all): every record is placed again, pending ones from their
+// re-uploaded); a record a batch rewrote in place is behind on the device, so it moves to the
+// appended part as well.  New arena (replace_all): every record is placed again, pending ones from their
 // events' memory, the others from the arena being left (old_payload).
 void ClusterImage::write_all(ncd_arena_view& v, int threads, const uint8_t* old_payload, bool replace_all) {
   uint64_t ax = 0, oi = 0, di = 0, i = 0;
@@ -185,11 +191,12 @@ void ClusterImage::write_all(ncd_arena_view& v, int threads, const uint8_t* old_
   std::vector<Copy> to_copy;
   for (CachedObject& o : objs) {
     const ObjInfo& f = *o.info;
-    if (o.pending || replace_all) {
+    if (o.pending || replace_all || o.direct) {
       const uint8_t* src = o.pending;
       if (!src) {
-        if (!old_payload || o.rec_off < 0) throw std::runtime_error("packer: a record has no bytes anywhere");
-        src = old_payload + o.rec_off;
+        const uint8_t* from = replace_all ? old_payload : v.payload;
+        if (!from || o.rec_off < 0) throw std::runtime_error("packer: a record has no bytes anywhere");
+        src = from + o.rec_off;
       }
       assign(o, /*force_append=*/true);
       to_copy.push_back({(uint32_t)i, src});
@@ -224,6 +231,7 @@ void ClusterImage::write_all(ncd_arena_view& v, int threads, const uint8_t* old_
   for (const Copy& c : to_copy) {
     objs[c.obj].pending = nullptr;
     objs[c.obj].hold.reset();
+    objs[c.obj].direct = false;
   }
 }
 

@@ -49,7 +49,10 @@ struct ObjInfo {
 // The compared value's canonical bytes live in exactly one place: in memory the event brought
 // (`pending`, kept alive by `hold`: a batch's slab or a single buffer) until the next Scan lays the
 // record out in the arena's pinned payload, and only there afterwards.  The pinned arena IS the
-// cache of values: no second host copy is kept.
+// cache of values: no second host copy is kept.  A batch may also write a new value that fits the
+// record's place straight into the pinned payload (`direct`: no pending bytes, nothing for the
+// packer to copy); `claimed` is the right to read or write the record's pinned bytes outside the
+// exclusive cache lock, taken and released with the helpers below.
 struct CachedObject {
   std::shared_ptr<const ObjInfo> info;
   uint32_t len = 0;                  // canonical length of the current value
@@ -60,7 +63,13 @@ struct CachedObject {
   // where the record lives in the resident arena's payload (-1: not placed yet)
   int64_t rec_off = -1;
   uint64_t rec_cap = 0;  // padded bytes reserved at rec_off
+  bool direct = false;   // the pinned record was rewritten in place since the last Scan: the device copy is behind
+  uint8_t claimed = 0;   // accessed with __atomic builtins only
 };
+inline bool try_claim(const CachedObject& o) {
+  return __atomic_exchange_n(const_cast<uint8_t*>(&o.claimed), (uint8_t)1, __ATOMIC_ACQUIRE) == 0;
+}
+inline void release_claim(const CachedObject& o) { __atomic_store_n(const_cast<uint8_t*>(&o.claimed), (uint8_t)0, __ATOMIC_RELEASE); }
 
 inline std::string store_key(uint32_t kind, const std::string& key) { return std::string(1, (char)('0' + kind)) + key; }
 inline uint64_t pad16(uint64_t n) { return (n + 15) & ~15ull; }
@@ -213,6 +222,7 @@ struct ClusterImage {
   bool structural = true;   // keys / owners / dependents changed since the last commit
   bool force_full = false;  // the resident device copy is not trusted: upload everything again
   uint64_t uploads_full = 0, uploads_structural = 0, uploads_values = 0, compactions = 0;
+  uint64_t in_place_last = 0;  // records of the last prepared Values upload that needed no copy
   std::vector<uint32_t> pending_changed;  // records a prepared Values upload still has to push
 
   const uint8_t* bytes_of(const CachedObject& o) const { return o.pending ? o.pending : host_payload + o.rec_off; }
@@ -225,28 +235,39 @@ struct ClusterImage {
     uint64_t seen_gen = 0, layout = 0;
     size_t pos = 0;
   };
-  PutHint precheck(const std::string& skey, const ObjInfo& info, const uint8_t* bytes, uint32_t len) const {
+  // Caller holds the claim on the object at `pos` (its bytes may be in the pinned payload, which
+  // another batch could otherwise be rewriting).
+  PutHint precheck(size_t pos, bool same_structure, const uint8_t* bytes, uint32_t len) const {
     PutHint h;
-    auto it = index.find(skey);
-    if (it == index.end()) return h;
-    const CachedObject& o = objs[it->second];
+    const CachedObject& o = objs[pos];
     h.found = true;
-    h.pos = it->second;
+    h.pos = pos;
     h.layout = layout;
     h.seen_gen = o.gen;
     h.same_value = o.len == len && memcmp(bytes_of(o), bytes, len) == 0;
-    h.same_structure = o.info->same_structure(info);
+    h.same_structure = same_structure;
     return h;
+  }
+  // True when a value of up to `len` bytes can be written over the object's record in the pinned
+  // payload: it has a place there and the place is large enough.
+  bool fits_in_place(const CachedObject& o, uint64_t len) const {
+    return arena.a && host_payload && o.rec_off >= 0 && pad16(len) <= o.rec_cap;
+  }
+  // Caller holds the claim and the pinned-memory lock (no Scan is reading the payload).
+  void write_in_place(const CachedObject& o, const uint8_t* bytes, uint32_t len) const {
+    uint8_t* dst = const_cast<uint8_t*>(host_payload) + o.rec_off;
+    memcpy(dst, bytes, len);
+    memset(dst + len, 0, pad16(len) - len);
   }
 
   // ---- events (caller holds the cache lock exclusively)
   // Returns true when the put changed anything.  k = store_key(kind, key); bytes / len = the canonical
   // value, owned by `hold`.
+  // force: the value counts as changed whatever the cache holds (its pinned bytes were overwritten).
   bool put(const std::string& k, std::shared_ptr<const ObjInfo> info, const uint8_t* bytes, uint32_t len,
-           const std::shared_ptr<const void>& hold, uint64_t stamp, const PutHint* hint = nullptr) {
+           const std::shared_ptr<const void>& hold, uint64_t stamp, const PutHint* hint = nullptr, bool force = false) {
     size_t pos = 0;
-    bool hinted = hint && hint->found && hint->layout == layout && hint->pos < objs.size() && objs[hint->pos].live &&
-                  objs[hint->pos].gen == hint->seen_gen;
+    bool hinted = hint && hint_valid(*hint);
     if (hinted) {
       pos = hint->pos;
     } else {
@@ -274,8 +295,8 @@ struct ClusterImage {
       changed = true;
       old.info = std::move(info);
     }
-    if (!(hinted ? hint->same_value : (old.len == len && memcmp(bytes_of(old), bytes, len) == 0))) {
-      if (!old.pending) dirty.push_back((uint32_t)pos);
+    if (force || !(hinted ? hint->same_value : (old.len == len && memcmp(bytes_of(old), bytes, len) == 0))) {
+      if (!old.pending && !old.direct) dirty.push_back((uint32_t)pos);
       old.pending = bytes;
       old.hold = hold;
       old.len = len;
@@ -284,8 +305,29 @@ struct ClusterImage {
     if (changed) old.gen = last_change = stamp;
     return changed;
   }
-  bool drop(uint32_t kind, const std::string& key, uint64_t stamp) {
-    const std::string k = store_key(kind, key);
+  // The put of a value that phase one of a batch already wrote over the record's pinned bytes
+  // (write_in_place).  False when the hint no longer describes the object — something else was
+  // applied to it in between — and the caller has to put the value the ordinary way, with force.
+  bool hint_valid(const PutHint& hint) const {
+    return hint.found && hint.layout == layout && hint.pos < objs.size() && objs[hint.pos].live && objs[hint.pos].gen == hint.seen_gen;
+  }
+  bool put_direct(std::shared_ptr<const ObjInfo>& info, uint32_t len, uint64_t stamp, const PutHint& hint) {
+    if (!hint_valid(hint)) return false;
+    CachedObject& o = objs[hint.pos];
+    if (!hint.same_structure) {
+      structural = true;
+      o.info = std::move(info);
+    }
+    if (!o.pending && !o.direct) dirty.push_back((uint32_t)hint.pos);
+    o.pending = nullptr;  // an older value still waiting for the packer is superseded
+    o.hold.reset();
+    o.len = len;
+    o.direct = true;
+    o.gen = last_change = stamp;
+    return true;
+  }
+  bool drop(uint32_t kind, const std::string& key, uint64_t stamp) { return drop(store_key(kind, key), stamp); }
+  bool drop(const std::string& k, uint64_t stamp) {
     auto it = index.find(k);
     if (it == index.end()) return false;
     objs[it->second].live = false;

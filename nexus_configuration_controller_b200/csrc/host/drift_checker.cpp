@@ -94,6 +94,12 @@ struct ncdh_checker {
   int threads = 1;
   std::shared_mutex cache_mu;
   std::mutex scan_mu;
+  // Who may touch record bytes in the pinned payloads outside the exclusive cache lock: batches
+  // that write values in place hold it shared from their first write until their update is applied;
+  // a Scan holds it exclusively from laying records out until the GPU has pulled them.  Taken
+  // before cache_mu.  Batches only ever TRY it (they have the slab path when a Scan is at work).
+  std::shared_mutex pinned_mu;
+  std::atomic<int> scan_wants_pinned{0};
   std::atomic<uint64_t> clock{0};
   std::atomic<uint64_t> events_since_scan{0};
   std::atomic<uint64_t> canon_ns_since_scan{0};
@@ -144,6 +150,7 @@ struct Prepared {
   uint32_t len = 0;
   ClusterImage::PutHint hint;
   bool hinted = false;
+  bool direct = false;  // the value is already in the record's place in the pinned payload (claim still held)
 };
 
 // Memory the canonical values of a batch of events are written into, one buffer per batch.  The
@@ -198,31 +205,68 @@ struct SlabPool {
 };
 SlabPool g_pool;
 
-// out / cap: where the canonical value goes (cap >= e.value_len always suffices).
-void prepare_event(const ncdh_event& e, Prepared* p, uint8_t* out, uint64_t cap) {
+// An event checked and keyed; the object's description (make_info) is only built when the cache
+// does not already hold an equal one — per event it is a dozen small allocations, freed on another
+// thread, which cost more than canonicalising a small value.
+void prepare_meta(const ncdh_event& e, Prepared* p) {
   if (!e.ns || !e.name) throw std::runtime_error("null namespace / name");
   if (e.kind > NCD_KIND_CONFIGMAP) throw std::runtime_error("unknown kind");
-  auto info = std::make_shared<ObjInfo>();
-  info->kind = e.kind;
-  info->key = std::string(e.ns) + "/" + e.name;  // cache.ObjectName.String()
-  info->name = e.name;
   p->cluster = e.cluster;
   p->op = e.op;
   if (e.op == NCDH_EV_PUT) {
     if (!e.uid || (!e.value && e.value_len)) throw std::runtime_error("null uid / value");
     if (e.nowners < 0 || e.nsecrets < 0 || e.nconfigmaps < 0) throw std::runtime_error("negative count");
+    if (e.value_len >= 0xFFFFFFFFull) throw std::runtime_error("value longer than 4 GiB");
+  } else if (e.op != NCDH_EV_DELETE) {
+    throw std::runtime_error("unknown event op");
+  }
+  const size_t ln = strlen(e.ns), lm = strlen(e.name);
+  p->skey.reserve(ln + lm + 2);
+  p->skey.push_back((char)('0' + e.kind));  // store_key(kind, "namespace/name")
+  p->skey.append(e.ns, ln);
+  p->skey.push_back('/');
+  p->skey.append(e.name, lm);
+}
+
+std::shared_ptr<const ObjInfo> make_info(const ncdh_event& e) {
+  auto info = std::make_shared<ObjInfo>();
+  info->kind = e.kind;
+  info->key = std::string(e.ns) + "/" + e.name;  // cache.ObjectName.String()
+  info->name = e.name;
+  if (e.op == NCDH_EV_PUT) {
     info->uid = e.uid;
     for (int i = 0; i < e.nowners; ++i) info->owners.push_back({e.owner_kinds[i], e.owner_uids[i]});
     for (int i = 0; i < e.nsecrets; ++i) info->secrets.push_back(e.secret_names[i]);
     for (int i = 0; i < e.nconfigmaps; ++i) info->configmaps.push_back(e.configmap_names[i]);
-    if (e.value_len >= 0xFFFFFFFFull) throw std::runtime_error("value longer than 4 GiB");
-    p->len = (uint32_t)canonicalise_into(e.value, e.value_len, out, cap);
-    p->bytes = out;
-  } else if (e.op != NCDH_EV_DELETE) {
-    throw std::runtime_error("unknown event op");
   }
-  p->skey = store_key(info->kind, info->key);
-  p->info = std::move(info);
+  return info;
+}
+
+// ObjInfo::same_structure against an event, without building the event's ObjInfo.
+bool same_structure(const ObjInfo& o, const ncdh_event& e) {
+  if (o.uid != e.uid || o.owners.size() != (size_t)e.nowners || o.secrets.size() != (size_t)e.nsecrets ||
+      o.configmaps.size() != (size_t)e.nconfigmaps)
+    return false;
+  for (int i = 0; i < e.nowners; ++i)
+    if (o.owners[i].kind != e.owner_kinds[i] || o.owners[i].uid != e.owner_uids[i]) return false;
+  for (int i = 0; i < e.nsecrets; ++i)
+    if (o.secrets[i] != e.secret_names[i]) return false;
+  for (int i = 0; i < e.nconfigmaps; ++i)
+    if (o.configmaps[i] != e.configmap_names[i]) return false;
+  return true;
+}
+
+// out / cap: where the canonical value goes (cap >= e.value_len always suffices).
+void prepare_value(const ncdh_event& e, Prepared* p, uint8_t* out, uint64_t cap) {
+  if (e.op != NCDH_EV_PUT) return;
+  p->len = (uint32_t)canonicalise_into(e.value, e.value_len, out, cap);
+  p->bytes = out;
+}
+
+void prepare_event(const ncdh_event& e, Prepared* p, uint8_t* out, uint64_t cap) {
+  prepare_meta(e, p);
+  p->info = make_info(e);
+  prepare_value(e, p, out, cap);
 }
 
 // Applies prepared events in order.  Caller holds cache_mu exclusively.
@@ -237,7 +281,7 @@ int apply_locked(ncdh_checker* c, std::vector<Prepared>& evs, size_t count, cons
     if (p.op == NCDH_EV_PUT) {
       changed = img->put(p.skey, std::move(p.info), p.bytes, p.len, hold, stamp, p.hinted ? &p.hint : nullptr);
     } else {
-      changed = img->drop(p.info->kind, p.info->key, stamp);
+      changed = img->drop(p.skey, stamp);
       if (!changed && removed_missing) ++*removed_missing;
     }
     if (changed) c->events_since_scan.fetch_add(1, std::memory_order_relaxed);
@@ -286,65 +330,142 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
   if (n == 0) return 0;
   if (threads <= 0) threads = c->threads;
   const auto t0 = std::chrono::steady_clock::now();
-  // one slab for the canonical values of the whole batch (a canonical form is as long as its transport form)
-  std::vector<uint64_t> off(n + 1, 0);
-  for (uint64_t i = 0; i < n; ++i) off[i + 1] = off[i] + (events[i].op == NCDH_EV_PUT ? events[i].value_len : 0);
-  const Slab slab = g_pool.take(off[n] ? off[n] : 1);
-  const std::shared_ptr<const void> hold(slab.p, [slab](const void*) { g_pool.give(slab); });  // back to the pool when the
-                                                                                               // last cached object lets go
-  // canonicalise in parallel, outside the exclusive lock, and look every object up and compare its
-  // value with what the cache holds under the SHARED lock: readers and other batches go on, only the
-  // short update below is exclusive.  The first event that cannot be canonicalised ends the batch.
+  constexpr uint32_t kSkipped = 0xFFFFFFFFu;  // Prepared::op of an event that could not be prepared
   std::vector<Prepared> evs(n);
   std::vector<std::string> errs(n);
-  std::atomic<uint64_t> first_bad{n};
-  {
-    std::shared_lock<std::shared_mutex> rd(c->cache_mu);
-    parallel_for(n, threads, 8, [&](size_t i) {
-      try {
+  // claims a failed call would otherwise leave behind
+  struct ClaimGuard {
+    ncdh_checker* c;
+    std::vector<Prepared>& evs;
+    ~ClaimGuard() {
+      for (Prepared& p : evs)
+        if (p.direct) release_claim(c->image(p.cluster)->objs[p.hint.pos]);
+    }
+  };
+  try {
+    // one slab for the canonical values that are not written in place (a canonical form is as long as its transport form)
+    std::vector<uint64_t> off(n + 1, 0);
+    for (uint64_t i = 0; i < n; ++i) off[i + 1] = off[i] + (events[i].op == NCDH_EV_PUT ? events[i].value_len : 0);
+    const Slab slab = g_pool.take(off[n] ? off[n] : 1);
+    const std::shared_ptr<const void> hold(slab.p, [slab](const void*) { g_pool.give(slab); });  // back to the pool when the
+                                                                                                 // last cached object lets go
+    // In place when no Scan is laying out or pulling records; held until the update below is done,
+    // so no Scan can see a record whose bytes are ahead of its cached length.
+    std::shared_lock<std::shared_mutex> pinned(c->pinned_mu, std::defer_lock);
+    const bool in_place = c->scan_wants_pinned.load(std::memory_order_acquire) == 0 && pinned.try_lock();
+    ClaimGuard guard{c, evs};
+    // Canonicalise in parallel, outside the exclusive lock, and look every object up and compare its
+    // value with what the cache holds under the SHARED lock: readers and other batches go on, only the
+    // short update below is exclusive.  A new value that fits its record's place goes straight into
+    // the pinned payload (through a cache-resident scratch buffer, so that an unchanged value — a
+    // resync — writes nothing); any other goes to the slab and waits for the packer.
+    {
+      std::shared_lock<std::shared_mutex> rd(c->cache_mu);
+      parallel_for(n, threads, 8, [&](size_t i) {
         Prepared& p = evs[i];
-        prepare_event(events[i], &p, slab.p + off[i], off[i + 1] - off[i]);
-        ClusterImage* img = c->image(p.cluster);
-        if (img && p.op == NCDH_EV_PUT) {
-          p.hint = img->precheck(p.skey, *p.info, p.bytes, p.len);
-          p.hinted = true;
+        try {
+          const ncdh_event& e = events[i];
+          prepare_meta(e, &p);
+          ClusterImage* img = c->image(p.cluster);
+          if (!img) throw std::runtime_error("no such cluster");
+          if (p.op != NCDH_EV_PUT) return;
+          auto it = img->index.find(p.skey);
+          const CachedObject* o = it == img->index.end() ? nullptr : &img->objs[it->second];
+          if (!o || !try_claim(*o)) {  // new object, or another batch is at its bytes: compared under the exclusive lock
+            p.info = make_info(e);
+            prepare_value(e, &p, slab.p + off[i], off[i + 1] - off[i]);
+            return;
+          }
+          try {
+            const bool same = same_structure(*o->info, e);
+            if (!same) p.info = make_info(e);
+            if (in_place && img->fits_in_place(*o, e.value_len)) {
+              thread_local std::vector<uint8_t> scratch;
+              if (scratch.size() < e.value_len) scratch.resize(e.value_len + e.value_len / 2 + 64);
+              p.len = (uint32_t)canonicalise_into(e.value, e.value_len, scratch.data(), e.value_len);
+              p.hint = img->precheck(it->second, same, scratch.data(), p.len);
+              p.hinted = true;
+              if (!p.hint.same_value) {
+                img->write_in_place(*o, scratch.data(), p.len);
+                p.direct = true;  // the claim stays until the update is applied
+                return;
+              }
+            } else {
+              prepare_value(e, &p, slab.p + off[i], off[i + 1] - off[i]);
+              p.hint = img->precheck(it->second, same, p.bytes, p.len);
+              p.hinted = true;
+            }
+          } catch (...) {
+            release_claim(*o);
+            throw;
+          }
+          release_claim(*o);
+        } catch (const std::exception& e) {
+          errs[i] = e.what();
+          p.op = kSkipped;
         }
-      } catch (const std::exception& e) {
-        errs[i] = e.what();
-        uint64_t cur = first_bad.load();
-        while (i < cur && !first_bad.compare_exchange_weak(cur, i)) {
+      });
+    }
+    c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t0) * 1e6), std::memory_order_relaxed);
+    const double t_phase1 = ms_since(t0);
+    // The update itself: the events of different clusters touch different images, so each cluster's
+    // events are applied, in order, by their own worker.
+    std::vector<std::vector<uint32_t>> by_cluster(c->shards.size() + 1);
+    for (uint64_t i = 0; i < n; ++i)
+      if (evs[i].op != kSkipped) by_cluster[(size_t)(evs[i].cluster + 1)].push_back((uint32_t)i);
+    {
+      std::unique_lock<std::shared_mutex> lk(c->cache_mu);
+      Workers::get().run(by_cluster.size(), threads, [&](size_t k) {
+        ClusterImage* img = c->image((int)k - 1);
+        uint64_t changed_events = 0;
+        for (uint32_t i : by_cluster[k]) {
+          Prepared& p = evs[i];
+          const uint64_t stamp = c->clock.fetch_add(1) + 1;
+          bool changed;
+          if (p.op == NCDH_EV_PUT && !p.info && !(p.hinted && img->hint_valid(p.hint) && p.hint.same_structure))
+            p.info = make_info(events[i]);  // the object phase one compared against is not there any more
+          if (p.op != NCDH_EV_PUT) {
+            changed = img->drop(p.skey, stamp);
+          } else if (p.direct || (!p.bytes && !img->hint_valid(p.hint))) {
+            // written in place, or found equal in phase one without keeping the bytes
+            const bool was_direct = p.direct;
+            if (was_direct && img->put_direct(p.info, p.len, stamp, p.hint)) {
+              changed = true;
+            } else {
+              // something else was applied to the object since phase one looked at it: the value is
+              // canonicalised again and put the ordinary way (after an in-place write the pinned
+              // bytes already are the new value, so it counts as changed without comparing)
+              auto buf = std::make_shared<std::vector<uint8_t>>(events[i].value_len ? events[i].value_len : 1);
+              const uint32_t len = (uint32_t)canonicalise_into(events[i].value, events[i].value_len, buf->data(), events[i].value_len);
+              changed = img->put(p.skey, std::move(p.info), buf->data(), len, std::shared_ptr<const void>(buf, buf->data()), stamp,
+                                 nullptr, /*force=*/was_direct);
+            }
+            if (was_direct) {
+              release_claim(img->objs[p.hint.pos]);
+              p.direct = false;
+            }
+          } else {
+            changed = img->put(p.skey, std::move(p.info), p.bytes, p.len, hold, stamp, p.hinted ? &p.hint : nullptr);
+          }
+          changed_events += changed ? 1 : 0;
         }
-      }
+        c->events_since_scan.fetch_add(changed_events, std::memory_order_relaxed);
+      });
+    }
+    const double t_phase2 = ms_since(t0);
+    parallel_for(n, threads, 256, [&](size_t i) {  // what the events still own is released in parallel too
+      evs[i].info.reset();
+      std::string().swap(evs[i].skey);
     });
+    static const bool profile = getenv("NCDH_PROFILE") != nullptr;
+    if (profile)
+      fprintf(stderr, "ncdh_apply_events: %llu events, lookup + canonicalise %.3f ms, update %.3f ms, release %.3f ms%s\n",
+              (unsigned long long)n, t_phase1, t_phase2 - t_phase1, ms_since(t0) - t_phase2, in_place ? "" : " (slab path: a Scan held the pinned payloads)");
+  } catch (const std::exception& e) {
+    return fail(std::string("ncdh_apply_events: ") + e.what());
   }
-  c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t0) * 1e6), std::memory_order_relaxed);
-  const uint64_t good = first_bad.load();
-  for (uint64_t i = 0; i < good; ++i)
-    if (!c->image(evs[i].cluster)) return fail("ncdh_apply_events: event " + std::to_string(i) + ": no such cluster");
-  // The update itself: the events of different clusters touch different images, so each cluster's
-  // events are applied, in order, by their own worker.
-  std::vector<std::vector<uint32_t>> by_cluster(c->shards.size() + 1);
-  for (uint64_t i = 0; i < good; ++i) by_cluster[(size_t)(evs[i].cluster + 1)].push_back((uint32_t)i);
-  {
-    std::unique_lock<std::shared_mutex> lk(c->cache_mu);
-    Workers::get().run(by_cluster.size(), threads, [&](size_t k) {
-      ClusterImage* img = c->image((int)k - 1);
-      uint64_t changed_events = 0;
-      for (uint32_t i : by_cluster[k]) {
-        Prepared& p = evs[i];
-        const uint64_t stamp = c->clock.fetch_add(1) + 1;
-        const bool changed = p.op == NCDH_EV_PUT ? img->put(p.skey, std::move(p.info), p.bytes, p.len, hold, stamp, p.hinted ? &p.hint : nullptr)
-                                                 : img->drop(p.info->kind, p.info->key, stamp);
-        changed_events += changed ? 1 : 0;
-      }
-      c->events_since_scan.fetch_add(changed_events, std::memory_order_relaxed);
-    });
-  }
-  parallel_for(n, threads, 256, [&](size_t i) {  // what the events still own is released in parallel too
-    evs[i].info.reset();
-    std::string().swap(evs[i].skey);
-  });
-  if (good < n) return fail("ncdh_apply_events: event " + std::to_string(good) + ": " + errs[good]);
+  for (uint64_t i = 0; i < n; ++i)
+    if (evs[i].op == kSkipped) return fail("ncdh_apply_events: event " + std::to_string(i) + ": " + errs[i] + " (skipped; every other event of the batch was applied)");
   return 0;
 }
 
@@ -388,12 +509,9 @@ int ncdh_cluster_add(ncdh_checker* c, int cluster, uint32_t kind, const char* ns
 int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char* ns, const char* name) {
   if (!c || !c->image(cluster) || !ns || !name || kind > NCD_KIND_CONFIGMAP) return fail("ncdh_cluster_remove: bad argument");
   std::vector<Prepared> one(1);
-  auto info = std::make_shared<ObjInfo>();
-  info->kind = kind;
-  info->key = std::string(ns) + "/" + name;
   one[0].cluster = cluster;
   one[0].op = NCDH_EV_DELETE;
-  one[0].info = std::move(info);
+  one[0].skey = store_key(kind, std::string(ns) + "/" + name);
   int missing = 0;
   std::unique_lock<std::shared_mutex> lk(c->cache_mu);
   if (apply_locked(c, one, 1, nullptr, &missing) != 0) return -1;
@@ -406,6 +524,11 @@ int ncdh_scan(ncdh_checker* c) {
   const auto t_all = std::chrono::steady_clock::now();
   ncdh_scan_timing tm;
   memset(&tm, 0, sizeof(tm));
+  // record bytes in pinned memory are this Scan's until the GPU has pulled them: batches in flight
+  // finish first, later ones use the slab path meanwhile
+  c->scan_wants_pinned.fetch_add(1, std::memory_order_release);
+  std::unique_lock<std::shared_mutex> pinned(c->pinned_mu);
+  c->scan_wants_pinned.fetch_sub(1, std::memory_order_release);
   try {
     const size_t S = c->shards.size();
     std::vector<ClusterImage*> imgs;
@@ -465,6 +588,7 @@ int ncdh_scan(ncdh_checker* c) {
         idx.push_back(img->pending_changed.data());
         pbs.push_back(img->payload_used);
         tm.records_synced += img->pending_changed.size();
+        tm.records_in_place += img->in_place_last;
       } else {
         img->upload(ups[k]);
       }
@@ -496,6 +620,7 @@ int ncdh_scan(ncdh_checker* c) {
       tm.d2h_bytes += 8 + n * sizeof(ncd_adoption);
     }
     tm.upload_ms = ms_since(t_up);
+    pinned.unlock();
     const auto t_scan = std::chrono::steady_clock::now();
     std::vector<const ncd_arena*> ptrs;
     for (ClusterImage& sh : c->shards) ptrs.push_back(sh.arena.a);

@@ -35,7 +35,7 @@ class ScanTiming(C.Structure):
     """struct ncdh_scan_timing."""
 
     _fields_ = [(n, C.c_double) for n in ("canon_ms", "pack_ms", "upload_ms", "scan_ms", "publish_ms", "total_ms", "gpu_scan_ms")] + [
-        (n, C.c_uint64) for n in ("h2d_bytes", "d2h_bytes", "records_synced", "full_uploads", "structural_uploads", "events", "compactions")]
+        (n, C.c_uint64) for n in ("h2d_bytes", "d2h_bytes", "records_synced", "full_uploads", "structural_uploads", "events", "compactions", "records_in_place")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

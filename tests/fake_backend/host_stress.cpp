@@ -132,6 +132,38 @@ int main(int argc, char** argv) {
       if (k % 3 == 0) CHECK(ncdh_scan(c) == 0, "scan (writer2): %s", ncdh_last_error());
     }
   });
+  // a third writer at the SAME ConfigMaps as the second, in larger batches: both write values in place
+  // (same length most of the time), so they meet at the same records' pinned bytes
+  std::thread writer3([&] {
+    for (int k = 0; !stop.load(); ++k) {
+      std::vector<std::string> names, vals, uids;
+      for (int q = 0; q < 6; ++q) {
+        const std::string n = std::to_string(T / 2 + (k + q) % (T / 2));
+        names.push_back("cm-" + n);
+        vals.push_back(wire_bytes_map("file", "d" + std::to_string(k % 10) + "-" + n));
+        uids.push_back("c-" + n);
+      }
+      const char* ok[] = {"NexusAlgorithmTemplate"};
+      std::vector<const char*> ou(6);
+      ncdh_event ev[6];
+      memset(ev, 0, sizeof(ev));
+      for (int q = 0; q < 6; ++q) {
+        ou[q] = uids[q].c_str();
+        ev[q].cluster = q % 2 == 0 ? -1 : (k + q) % S;
+        ev[q].kind = NCD_KIND_CONFIGMAP;
+        ev[q].op = NCDH_EV_PUT;
+        ev[q].ns = "default";
+        ev[q].name = names[q].c_str();
+        ev[q].uid = "";
+        ev[q].value = (const uint8_t*)vals[q].data();
+        ev[q].value_len = vals[q].size();
+        ev[q].owner_kinds = ok;
+        ev[q].owner_uids = &ou[q];
+        ev[q].nowners = 1;
+      }
+      CHECK(ncdh_apply_events(c, ev, 6, 3) == 0, "apply_events (writer3): %s", ncdh_last_error());
+    }
+  });
   // the checked writer: rotates secrets of the lower half
   for (int k = 0; k < rounds; ++k) {
     const int t = k % (T / 2);
@@ -140,9 +172,13 @@ int main(int argc, char** argv) {
     add(c, -1, NCD_KIND_SECRET, "sec-" + n, "", wire_bytes_map("token", "v" + std::to_string(k + 1) + "-" + n), ("c-" + n).c_str(), nullptr,
         nullptr);
     int rc = ncdh_lookup(c, NCD_KIND_TEMPLATE, "default", algo.c_str(), 1, 0, &code);
-    CHECK(rc == NCDH_STALE, "round %d: a Secret rotated after the scan was answered rc=%d code=%u instead of STALE", k, rc, code);
+    // STALE — or already UPDATE_DATA when the other writer's scan got in between; never SKIP
+    CHECK(rc == NCDH_STALE || (rc == 0 && code == NCD_UPDATE_DATA),
+          "round %d: a Secret rotated after the scan was answered rc=%d code=%u instead of STALE", k, rc, code);
     char buf[2048];
-    CHECK(ncdh_plan_template(c, "default", algo.c_str(), buf, sizeof(buf)) == -NCDH_STALE, "round %d: plan not stale", k);
+    const int64_t pl = ncdh_plan_template(c, "default", algo.c_str(), buf, sizeof(buf));
+    CHECK(pl == -NCDH_STALE || (pl > 0 && (size_t)pl < sizeof(buf) && std::string(buf, (size_t)pl).find("update-data") != std::string::npos),
+          "round %d: plan neither stale nor an update (%lld)", k, (long long)pl);
     // an untouched template of the lower half is still answered from the snapshot
     const std::string other = "algo-" + std::to_string((t + 1) % (T / 2));
     rc = ncdh_lookup(c, NCD_KIND_TEMPLATE, "default", other.c_str(), 0, 1, &code);
@@ -157,8 +193,49 @@ int main(int argc, char** argv) {
   }
   stop.store(true);
   writer2.join();
+  writer3.join();
   for (auto& r : readers) r.join();
   CHECK(ncdh_scan(c) == 0, "last scan: %s", ncdh_last_error());
+  // whatever the writers left behind, one more batch of equal values everywhere converges the upper half:
+  // nothing written in place may have been lost on the way to the arenas
+  {
+    std::vector<std::string> names, vals, uids;
+    std::vector<ncdh_event> ev;
+    const char* ok[] = {"NexusAlgorithmTemplate"};
+    for (int t = T / 2; t < T; ++t)
+      for (int cluster = -1; cluster < S; ++cluster) {
+        const std::string n = std::to_string(t);
+        names.push_back("cm-" + n);
+        vals.push_back(wire_bytes_map("file", "z9-" + n));
+        uids.push_back((cluster < 0 ? "c-" : "s" + std::to_string(cluster) + "-") + n);
+      }
+    std::vector<const char*> ou(names.size());
+    for (size_t q = 0; q < names.size(); ++q) {
+      ncdh_event e;
+      memset(&e, 0, sizeof(e));
+      ou[q] = uids[q].c_str();
+      e.cluster = (int)(q % (S + 1)) - 1;
+      e.kind = NCD_KIND_CONFIGMAP;
+      e.op = NCDH_EV_PUT;
+      e.ns = "default";
+      e.name = names[q].c_str();
+      e.uid = "";
+      e.value = (const uint8_t*)vals[q].data();
+      e.value_len = vals[q].size();
+      e.owner_kinds = ok;
+      e.owner_uids = &ou[q];
+      e.nowners = 1;
+      ev.push_back(e);
+    }
+    CHECK(ncdh_apply_events(c, ev.data(), ev.size(), 4) == 0, "final batch: %s", ncdh_last_error());
+    CHECK(ncdh_scan(c) == 0, "scan after the final batch: %s", ncdh_last_error());
+    for (int t = T / 2; t < T; ++t)
+      for (int s = 0; s < S; ++s) {
+        uint32_t code = 99;
+        const int rc = ncdh_lookup(c, NCD_KIND_TEMPLATE, "default", ("algo-" + std::to_string(t)).c_str(), 2, s, &code);
+        CHECK(rc == 0 && code == NCD_SKIP, "converged ConfigMap of algo-%d on shard %d answered rc=%d code=%u", t, s, rc, code);
+      }
+  }
   ncdh_checker_destroy(c);
   printf("host_stress: %d rounds, %llu reader iterations, %llu stale answers seen by readers, %d failures\n", rounds,
          (unsigned long long)lookups.load(), (unsigned long long)stale_seen.load(), failures.load());

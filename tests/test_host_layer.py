@@ -82,6 +82,19 @@ class Fleet:
         del self.clusters[cluster][(o.kind, o.namespace, o.name)]
         assert self.f.remove(cluster, o.kind, o.namespace, o.name)
 
+    def apply(self, ops, threads=3):
+        """ops: [("put" | "remove", cluster, Obj)] delivered as ONE batch of informer events."""
+        keep, evs = [], []
+        for op, cluster, o in ops:
+            if op == "put":
+                self.clusters[cluster][(o.kind, o.namespace, o.name)] = o
+                evs.append(Hst.make_event(cluster, o.kind, o.namespace, o.name, o.uid, o.value, o.owner_refs, o.secret_names,
+                                          o.configmap_names, keep=keep))
+            else:
+                self.clusters[cluster].pop((o.kind, o.namespace, o.name), None)
+                evs.append(Hst.make_event(cluster, o.kind, o.namespace, o.name, op=Hst.EV_DELETE, keep=keep))
+        self.f.apply_events(evs, threads=threads)
+
     def check(self):
         self.f.scan()
         ctrl = self.clusters[-1]
@@ -252,7 +265,7 @@ def test_batched_events_equal_single_puts(make_checker):
         batch.scan()
         assert batch.plan_template(NS, "test") == one.plan_template(NS, "test")
         assert batch.counts() == one.counts()
-        # a malformed value stops the batch at that event: the ones before it are in, the rest is not
+        # a malformed value is skipped and reported: every other event of the batch is in
         good = new_workgroup("wg-a", "shard0")
         bad = [Hst.make_event(-1, A.KIND_WORKGROUP, NS, "wg-a", "u", good.value, keep=keep),
                Hst.make_event(-1, A.KIND_WORKGROUP, NS, "wg-b", "u", b"\xff\x00garbage", keep=keep),
@@ -261,7 +274,8 @@ def test_batched_events_equal_single_puts(make_checker):
             batch.apply_events(bad, threads=2)
         batch.scan()
         assert batch.lookup(A.KIND_WORKGROUP, NS, "wg-a", 0, 0) == A.CREATE
-        assert batch.lookup(A.KIND_WORKGROUP, NS, "wg-c", 0, 0) is None
+        assert batch.lookup(A.KIND_WORKGROUP, NS, "wg-b", 0, 0) is None
+        assert batch.lookup(A.KIND_WORKGROUP, NS, "wg-c", 0, 0) == A.CREATE
 
 
 def test_lookups_from_threads_while_another_thread_scans(make_checker):
@@ -355,6 +369,7 @@ def test_synthetic_event_batches_decide_like_the_oracle_on_the_raw_arenas(make_c
         assert t["full_uploads"] == 0 and t["structural_uploads"] == 0
         changed = [i for i in idx if ctrl.rec_len[i] > 0]
         assert t["records_synced"] == len(changed) and t["events"] == len(changed)
+        assert t["records_in_place"] == len(changed)  # same length: written where the record already is, no packer copy
         # the oracle sees the same change when the raw records are patched the same way
         # (ncdh_batch_from_arrays: byte h % len of the record ^= 1 + (h >> 32) % 255, h = mix(salt * P ^ fnv(kind, key)))
         M = (1 << 64) - 1
@@ -484,3 +499,64 @@ def test_an_arena_full_of_dead_payload_is_compacted_not_replaced(make_checker):
         fleet.remove(0, with_owners(cfgs[2], [tmpl[2]]))
         fleet.check()
         assert grown > 3
+
+
+@pytest.mark.parametrize("seed", [31, 32, 33, 34])
+def test_batches_that_rewrite_records_in_place(make_checker, seed):
+    """A batch writes a new value that fits its record's place straight into the pinned payload.  Mixed with
+    everything else a batch may carry — values that grow (appended by the packer), shrink, stay the same
+    (a resync: nothing to upload), several events for one object, deletions and re-additions, owner changes
+    (structural uploads, which must also carry the records rewritten in place) — every plan must still equal
+    the handlers' on the same objects after every batch."""
+    rng = random.Random(seed)
+    n = 6
+    with make_checker(2) as f:
+        fleet = Fleet(2, f)
+        size = {}
+
+        def cfg(i, cluster, owners):
+            ln, fill = size[(cluster, i)]
+            return with_owners(new_configmap(f"cfg-{i}", None, {"k": fill * ln}), owners)
+
+        tmpl = [new_template(f"algo-{i}", None, new_configmap(f"cfg-{i}", None, {})) for i in range(n)]
+        first = []
+        for i in range(n):
+            for cluster in (-1, 0, 1):
+                size[(cluster, i)] = (400, "a")
+                first += [("put", cluster, tmpl[i]), ("put", cluster, cfg(i, cluster, [tmpl[i]]))]
+        fleet.apply(first)
+        fleet.check()
+        in_place = appended = resyncs = 0
+        for _ in range(14):
+            ops = []
+            for _ in range(rng.randint(2, 10)):
+                cluster, i = rng.choice([-1, 0, 1]), rng.randrange(n)
+                present = (A.KIND_CONFIGMAP, NS, f"cfg-{i}") in fleet.clusters[cluster]
+                what = rng.random()
+                if what < 0.5 or not present:  # a new value: same length, shorter or longer
+                    ln = size[(cluster, i)][0]
+                    ln = rng.choice([ln, ln, max(1, ln - rng.randint(1, 300)), ln + rng.randint(1, 900)])
+                    size[(cluster, i)] = (ln, rng.choice("bcdefgh"))
+                    ops.append(("put", cluster, cfg(i, cluster, [tmpl[i]])))
+                elif what < 0.65:  # the informer's resync: the same object again
+                    ops.append(("put", cluster, cfg(i, cluster, [tmpl[i]])))
+                    resyncs += 1
+                elif what < 0.75:  # two events for one object in the same batch
+                    size[(cluster, i)] = (size[(cluster, i)][0], "x")
+                    ops.append(("put", cluster, cfg(i, cluster, [tmpl[i]])))
+                    size[(cluster, i)] = (size[(cluster, i)][0], "y")
+                    ops.append(("put", cluster, cfg(i, cluster, [tmpl[i]])))
+                elif what < 0.85 and cluster >= 0:  # gone from a shard, possibly back in the same batch
+                    ops.append(("remove", cluster, cfg(i, cluster, [])))
+                    if rng.random() < 0.5:
+                        ops.append(("put", cluster, cfg(i, cluster, [tmpl[i]])))
+                else:  # re-owned: a structural change, with a new value of the same length on top
+                    size[(cluster, i)] = (size[(cluster, i)][0], "z")
+                    ops.append(("put", cluster, cfg(i, cluster, [] if rng.random() < 0.5 else [tmpl[(i + 1) % n]])))
+            before = [f.upload_counts(c) for c in (-1, 0, 1)]
+            fleet.apply(ops, threads=rng.choice([1, 3]))
+            fleet.check()
+            after = [f.upload_counts(c) for c in (-1, 0, 1)]
+            in_place += f.timing()["records_in_place"]
+            appended += sum(a[1] - b[1] for a, b in zip(after, before))
+        assert in_place > 0 and appended > 0 and resyncs > 0
