@@ -352,7 +352,8 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     // In place when no Scan is laying out or pulling records; held until the update below is done,
     // so no Scan can see a record whose bytes are ahead of its cached length.
     std::shared_lock<std::shared_mutex> pinned(c->pinned_mu, std::defer_lock);
-    const bool in_place = c->scan_wants_pinned.load(std::memory_order_acquire) == 0 && pinned.try_lock();
+    static const bool no_in_place = getenv("NCDH_NO_IN_PLACE") != nullptr;  // measurement knob: every value through the slab
+    const bool in_place = !no_in_place && c->scan_wants_pinned.load(std::memory_order_acquire) == 0 && pinned.try_lock();
     ClaimGuard guard{c, evs};
     // Canonicalise in parallel, outside the exclusive lock, and look every object up and compare its
     // value with what the cache holds under the SHARED lock: readers and other batches go on, only the
@@ -621,6 +622,16 @@ int ncdh_scan(ncdh_checker* c) {
     }
     tm.upload_ms = ms_since(t_up);
     pinned.unlock();
+    static const bool profile = getenv("NCDH_PROFILE") != nullptr;
+    if (profile) {
+      std::string line = "ncdh_scan: uploads";
+      for (size_t k = 0; k < imgs.size(); ++k) {
+        const char* names[] = {"none", "values", "structural", "full"};
+        line += std::string(" ") + names[(int)ups[k]];
+        if (ups[k] == Upload::Values) line += "(" + std::to_string(imgs[k]->in_place_last) + " in place)";
+      }
+      fprintf(stderr, "%s; pack %.3f ms, upload %.3f ms\n", line.c_str(), tm.pack_ms, tm.upload_ms);
+    }
     const auto t_scan = std::chrono::steady_clock::now();
     std::vector<const ncd_arena*> ptrs;
     for (ClusterImage& sh : c->shards) ptrs.push_back(sh.arena.a);

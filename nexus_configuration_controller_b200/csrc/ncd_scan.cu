@@ -344,7 +344,10 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
   const uint32_t gmask = (LPO == 8 ? 0xFFu : 0xFu) << base;  // the lanes of this object
   const uint64_t group0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LPO;
   const uint64_t ngroups = ((uint64_t)gridDim.x * blockDim.x) / LPO;
-  const bool prefetch = S <= (uint32_t)G && S > 0 && s_sh[0].join_cache != nullptr;  // all shards cached or none (ncd_scan)
+  // look-ahead only when EVERY shard's answer is cached (a shard re-committed since the last scan has
+  // no valid cache while the others still do)
+  bool prefetch = S <= (uint32_t)G && S > 0;
+  for (uint32_t s = 0; s < S && prefetch; ++s) prefetch = s_sh[s].join_cache != nullptr;
   uint32_t idx_next[SLOTS];
 #pragma unroll
   for (int j = 0; j < SLOTS; ++j) {

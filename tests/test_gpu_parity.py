@@ -252,6 +252,46 @@ def test_every_compare_variant_matches_oracle(variant, monkeypatch):
             a.close()
 
 
+@pytest.mark.parametrize("variant", [0, 2, 8, 16, "16-unfused"])
+def test_one_shard_committed_again_between_scans(variant, monkeypatch):
+    """The answers of the join are cached per (controller, shard) pair.  When ONE shard is committed again
+    (other objects, other numbering) its cache is void while the other shards' caches still hold: the next
+    scan must probe that shard and read the caches of the rest — in every kernel that reads them."""
+    from nexus_configuration_controller_b200.drift import Arena, Context
+
+    if variant == "16-unfused":
+        variant = 16
+        monkeypatch.setenv("NCD_FUSE_SMALL", "0")
+    monkeypatch.setenv("NCD_COMPARE_VARIANT", str(variant))
+    with Context(0) as c2:
+        for nshards in (2, 3, 11):
+            ctrl, shards = random_clusters(41, n_templates=14, n_shards=nshards, max_len=3000)
+            _, others = random_clusters(42, n_templates=14, n_shards=nshards, max_len=3000)
+            arenas = [c2.arena_from_host(ctrl)]
+            for s in range(nshards):
+                h, o = shards[s], others[s]
+                a = Arena(c2, max(h.payload_bytes, o.payload_bytes) + 64, max(h.nobj, o.nobj), max(h.aux_bytes, o.aux_bytes) + 64,
+                          max(h.nowner, o.nowner) + 1, max(h.ndep, o.ndep) + 1, device_only=False)
+                a.fill_from(h)
+                a.commit(h.nobj, h.payload_bytes, h.aux_bytes, h.nowner, h.ndep)
+                arenas.append(a)
+            now = list(shards)
+            for step in range(4):
+                for _ in range(2):  # the second scan of each state reads what the first one cached
+                    d = c2.scan(arenas[0], arenas[1:], A.MODE_DIRECT)
+                    want_codes, want_ents = oracle.scan(ctrl, now)
+                    np.testing.assert_array_equal(d.codes(), want_codes)
+                    np.testing.assert_array_equal(d.entries(), want_ents)
+                    d.close()
+                s = (step * 2 + 1) % nshards  # one shard gets the other fleet's objects, or its own back
+                h = others[s] if now[s] is shards[s] else shards[s]
+                arenas[1 + s].fill_from(h)
+                arenas[1 + s].commit(h.nobj, h.payload_bytes, h.aux_bytes, h.nowner, h.ndep)
+                now[s] = h
+            for a in arenas:
+                a.close()
+
+
 def test_scan_into_a_caller_buffer_matches_the_diff_object(ctx):
     """ncd_scan_into: same diff list, written on the device into a caller-owned buffer (the
     all-gather send buffer), no host round trip; too small a buffer is reported, not overrun."""
