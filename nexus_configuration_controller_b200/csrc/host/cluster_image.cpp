@@ -54,10 +54,13 @@ Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uin
     v.rec_len[i] = o.len;
     *h2d += pad16(o.len) + 4;
   }
-  parallel_for(dirty.size(), threads, 64, [&](size_t k) {
-    CachedObject& o = objs[dirty[k]];
-    if (o.pending) copy_record(v, o, o.pending);  // else the batch wrote the record in place already
-  });
+  size_t to_copy = 0;
+  for (uint32_t i : dirty) to_copy += objs[i].pending ? 1 : 0;
+  if (to_copy)  // none when every value was written in place by its batch: not worth waking the workers
+    parallel_for(dirty.size(), threads, 64, [&](size_t k) {
+      CachedObject& o = objs[dirty[k]];
+      if (o.pending) copy_record(v, o, o.pending);
+    });
   in_place_last = 0;
   for (uint32_t i : dirty) {  // the arena holds the bytes now: the events' memory is released
     in_place_last += objs[i].pending ? 0 : 1;
