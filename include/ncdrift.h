@@ -233,7 +233,9 @@ int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint
  * place), and rec_off changes identically on both sides; keys, digests and the index stay as they
  * are.  A long-lived controller's arena (informer events for days: controller.go:286-359) no longer
  * needs a full ncd_arena_commit over PCIe to stop growing.  *new_payload_bytes = used payload
- * afterwards; the caller re-reads rec_off from the host view.  No reference counterpart. */
+ * afterwards; the caller re-reads rec_off from the host view.  A record rewritten in the host arrays
+ * and not synced yet may have a new LENGTH there (the slots are laid out for the host's rec_len);
+ * its rec_off must still be the one the device holds.  No reference counterpart. */
 int ncd_arena_compact(ncd_arena* a, uint64_t* new_payload_bytes);
 /* Copies the committed device arrays into caller buffers (sized from
  * ncd_arena_counts); any pointer in dst may be NULL to skip that array. */

@@ -59,6 +59,13 @@ extern "C" int ncd_init(int device, ncd_ctx** out) {
   ctx->compare_ctas_per_sm = 8;
   ctx->fuse_small = 1;
   if (const char* v = getenv("NCD_FUSE_SMALL")) ctx->fuse_small = atoi(v) != 0;  // experiment knob: 0 = k_join + k_compare_small
+  ctx->line_cache = 1;
+  if (const char* v = getenv("NCD_LINE_CACHE")) ctx->line_cache = atoi(v) != 0;  // experiment knob
+  ctx->ss_lpo = 0;
+  if (const char* v = getenv("NCD_SS_LPO")) {  // experiment knob: lanes per object in k_scan_small
+    const int l = atoi(v);
+    if (l == 4 || l == 8 || l == 16 || l == 32) ctx->ss_lpo = l;
+  }
   if (const char* v = getenv("NCD_COMPARE_VARIANT")) {
     // experiment knob: only the kernels that exist may be named (ncd_scan_stats.compare_variant)
     const int k = atoi(v);
@@ -221,7 +228,7 @@ extern "C" void ncd_arena_destroy(ncd_arena* a) {
     if (h) cudaFreeHost(h);
   }
   void* idx[] = {a->meta,    a->table,     a->row_start,  a->row_obj, a->row_dep, a->row_cidx,
-                 a->tile_obj, a->tile_chunk, a->tile_start, a->h64,     a->sha,     a->xxh,     a->jc_idx,  a->uid_id,  a->own_packed,
+                 a->tile_obj, a->tile_chunk, a->tile_start, a->h64,     a->sha,     a->xxh,     a->jc_idx,  a->uid_id,  a->own_packed, a->jc_line, a->jc_rev,
                  a->ctile_obj, a->ctile_chunk, a->ctile_start};
   for (void* p : idx)
     if (p) cudaFree(p);

@@ -107,6 +107,13 @@ struct DevArena {
   // valid while neither arena's keys changed; exactly one of the two is set by ncd_scan
   const uint32_t* join_cache;  // [controller nobj] read instead of probing
   uint32_t* join_cache_out;    // [controller nobj] filled by this scan's probes
+  // and what the join reads from the found object's line — {rec_off lo, rec_off hi, rec_len, tag} —
+  // cached the same way, so that a steady-state scan streams 20 bytes per pair instead of touching
+  // one random 32-byte sector of the shard's object lines per pair.  Kept current by
+  // k_pull_records through the reverse map (shard object -> controller object).
+  const uint4* join_line;    // [controller nobj] read instead of the object line (only with join_cache)
+  uint4* join_line_out;      // [controller nobj] filled by this scan
+  uint32_t* join_rev_out;    // [shard nobj] filled by this scan
   // digests, filled by the hash kernels
   const uint64_t* h64;      // [nobj]
   const uint32_t* sha;      // [nobj][8]
@@ -121,6 +128,8 @@ struct ncd_ctx {
   int compare_variant;      // -1 = pick per scan, 0 = per-shard loop, 1/2/4 = grouped with CH vectors per lane
   int compare_ctas_per_sm;  // grid = sm_count * this
   int fuse_small;           // 1: small records in direct mode take k_scan_small (join + compare in one kernel)
+  int ss_lpo;               // lanes per object in k_scan_small (0: from the mean record length)
+  int line_cache;           // 1: the join caches the found objects' record offset / length / tag per pair
   cudaStream_t stream;
   cudaEvent_t ev[8];                        // ev[5], ev[6]: ncd_hash_arena
   cudaEvent_t evr[NCD_EV_RING][5];          // per-scan phase events, ring indexed by scan_seq
@@ -195,6 +204,10 @@ struct ncd_arena {
   uint32_t* jc_idx;
   const ncd_arena* jc_ctrl;
   uint64_t jc_ctrl_gen, jc_gen, jc_n;
+  uint4* jc_line;     // [jc_n] see DevArena::join_line
+  uint32_t* jc_rev;   // [jc_rev_n] controller object of each object of this arena, NCD_NOTFOUND if none
+  uint64_t jc_rev_n, jc_line_n;
+  bool jc_line_ok;    // jc_line / jc_rev describe the records as they are now (for the pairs jc_idx describes)
 };
 
 struct ncd_diff {

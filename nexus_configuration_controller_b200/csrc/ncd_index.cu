@@ -357,6 +357,9 @@ void ncd_fill_dev_arena(const ncd_arena* a, DevArena* o) {
   o->own_packed = a->own_packed;
   o->join_cache = nullptr;
   o->join_cache_out = nullptr;
+  o->join_line = nullptr;
+  o->join_line_out = nullptr;
+  o->join_rev_out = nullptr;
   o->h64 = a->h64;
   o->sha = a->sha;
   o->xxh = a->xxh;
@@ -436,6 +439,7 @@ static std::atomic<uint64_t> g_generation{0};  // contexts of different GPUs may
 int ncd_build_index(ncd_arena* a) {
   ncd_ctx* ctx = a->ctx;
   a->generation = g_generation.fetch_add(1) + 1;  // keys may have changed: join caches built on the old index are stale
+  a->jc_line_ok = false;
   cudaStream_t st = ctx->stream;
   g_realloc_stream = st;
   const uint32_t n = (uint32_t)a->nobj;

@@ -19,7 +19,8 @@ __global__ void __launch_bounds__(128)
 k_pull_records(uint32_t* __restrict__ idx, const uint8_t* h_payload, const uint64_t* h_rec_off,
                const uint32_t* h_rec_len, uint8_t* __restrict__ d_payload, uint64_t* __restrict__ d_rec_off,
                uint32_t* __restrict__ d_rec_len, ObjMeta* __restrict__ meta, uint32_t nobj,
-               uint64_t payload_limit, uint32_t* __restrict__ bad /*[0] refused, [1] lengths changed*/) {
+               uint64_t payload_limit, uint32_t* __restrict__ bad /*[0] refused, [1] lengths changed*/,
+               const uint32_t* __restrict__ jc_rev, uint4* __restrict__ jc_line /* the arena's pair cache, or null */) {
   const uint32_t i = idx[blockIdx.x];
   if (i >= nobj) {
     if (threadIdx.x == 0) {
@@ -41,6 +42,10 @@ k_pull_records(uint32_t* __restrict__ idx, const uint8_t* h_payload, const uint6
     d_rec_len[i] = len;
     meta[i].rec_off = off;
     meta[i].rec_len = len;
+    if (jc_rev) {  // the join's cached copy of this object's line follows (DevArena::join_line)
+      const uint32_t c = jc_rev[i];
+      if (c != NCD_NOTFOUND) jc_line[c] = make_uint4((uint32_t)off, (uint32_t)(off >> 32), len, meta[i].tag);
+    }
   }
   const uint4* src = reinterpret_cast<const uint4*>(h_payload + off);
   uint4* dst = reinterpret_cast<uint4*>(d_payload + off);
@@ -120,7 +125,8 @@ int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t*
     NCD_CUDA(cudaMemcpyAsync(d_idx + at, obj_idx[k], n[k] * 4, cudaMemcpyHostToDevice, st));
     k_pull_records<<<(unsigned)n[k], 128, 0, st>>>(d_idx + at, a->h.payload, a->h.rec_off, a->h.rec_len, a->d.payload,
                                                   a->d.rec_off, a->d.rec_len, a->meta, (uint32_t)a->nobj,
-                                                  new_payload_bytes[k], d_flags + 2 * k);
+                                                  new_payload_bytes[k], d_flags + 2 * k,
+                                                  a->jc_line_ok ? a->jc_rev : nullptr, a->jc_line_ok ? a->jc_line : nullptr);
     d_lists[k] = d_idx + at;
     at += n[k];
   }
@@ -307,10 +313,13 @@ int ncd_arena_compact(ncd_arena* a, uint64_t* new_payload_bytes) {
     if (new_payload_bytes) *new_payload_bytes = cur;
     return NCD_OK;
   }
-  // device first (it still needs the old offsets, which the device arrays hold)
+  // device first (it still needs the old offsets, which the device arrays hold).  Lengths come from
+  // the HOST arrays: a record rewritten in place on the host and not synced yet may be longer or
+  // shorter there than the device still believes, and the slots are laid out for the host's lengths.
   uint64_t* d_new = nullptr;
   uint8_t* tmp = nullptr;
-  NCD_CUDA(cudaMallocAsync((void**)&d_new, (n ? n : 1) * 8, st));
+  NCD_CUDA(cudaMallocAsync((void**)&d_new, (n ? n : 1) * 12, st));
+  uint32_t* d_len = reinterpret_cast<uint32_t*>(d_new + (n ? n : 1));
   cudaError_t e = cudaMallocAsync((void**)&tmp, cur ? cur : 16, st);
   if (e != cudaSuccess) {
     cudaFreeAsync(d_new, st);
@@ -319,7 +328,8 @@ int ncd_arena_compact(ncd_arena* a, uint64_t* new_payload_bytes) {
   }
   if (n) {
     NCD_CUDA(cudaMemcpyAsync(d_new, new_off.data(), n * 8, cudaMemcpyHostToDevice, st));
-    k_compact_gather<<<(unsigned)n, 128, 0, st>>>(a->d.payload, a->d.rec_off, d_new, a->d.rec_len, tmp);
+    NCD_CUDA(cudaMemcpyAsync(d_len, len, n * 4, cudaMemcpyHostToDevice, st));
+    k_compact_gather<<<(unsigned)n, 128, 0, st>>>(a->d.payload, a->d.rec_off, d_new, d_len, tmp);
     if (cur) NCD_CUDA(cudaMemcpyAsync(a->d.payload, tmp, cur, cudaMemcpyDeviceToDevice, st));
     k_compact_offsets<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a->d.rec_off, a->meta, d_new, (uint32_t)n);
   }
@@ -335,6 +345,7 @@ int ncd_arena_compact(ncd_arena* a, uint64_t* new_payload_bytes) {
   NCD_CUDA(cudaStreamSynchronize(st));
   NCD_CUDA(cudaGetLastError());
   a->payload_bytes = cur;
+  a->jc_line_ok = false;  // the offsets the join cached per pair are gone: the next scan reads the object lines again
   if (new_payload_bytes) *new_payload_bytes = cur;
   return NCD_OK;
 }

@@ -38,10 +38,30 @@ k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t 
   uint8_t v;
   uint64_t off = NCD_NO_OFF;
   uint32_t tg = NCD_TAG_ROGUE;
-  if (idx != NCD_NOTFOUND) tg = sh.meta[idx].tag;
+  // the found object's record offset, length and tag: from the pair's cached copy, or from its line
+  uint64_t s_off = 0;
+  uint32_t s_len = 0;
+  if (idx != NCD_NOTFOUND) {
+    if (sh.join_line) {
+      const uint4 w = sh.join_line[c];
+      s_off = (uint64_t)w.x | ((uint64_t)w.y << 32);
+      s_len = w.z;
+      tg = w.w;
+    } else {
+      const uint4* line = reinterpret_cast<const uint4*>(sh.meta + idx);
+      const uint4 w0 = line[0], w1 = line[1];  // keyhash | rec_off ; rec_len key_off key_len/kind tag
+      s_off = (uint64_t)w0.z | ((uint64_t)w0.w << 32);
+      s_len = w1.x;
+      tg = w1.w;
+      if (sh.join_line_out) {
+        sh.join_line_out[c] = make_uint4(w0.z, w0.w, s_len, tg);
+        sh.join_rev_out[idx] = c;
+      }
+    }
+  }
   if (idx == NCD_NOTFOUND) {
     v = DV_NOTFOUND;
-  } else if (sh.meta[idx].rec_len != q.rec_len) {
+  } else if (s_len != q.rec_len) {
     v = DV_DIFF;  // the encoding is injective: different lengths cannot be DeepEqual
   } else {
     const uint32_t hm = mode & 0xff;
@@ -58,7 +78,7 @@ k_join(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t 
                      (x1.y ^ y1.y) | (x1.z ^ y1.z) | (x1.w ^ y1.w)) == 0;
     }
     v = maybe_equal ? DV_EQUAL : DV_DIFF;
-    if (maybe_equal && (hm == NCD_MODE_DIRECT || (mode & NCD_MODE_CONFIRM))) off = sh.meta[idx].rec_off;
+    if (maybe_equal && (hm == NCD_MODE_DIRECT || (mode & NCD_MODE_CONFIRM))) off = s_off;
   }
   sh_idx[p] = idx;
   sh_off[p] = off;
@@ -316,8 +336,10 @@ k_compare_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S,
 // against vector v of every shard copy, all loads of a step issued before any is used.  Verdict,
 // shard index and tag go out for k_classify; no tile list, no offsets round trip.
 // Correct for any record length (the lanes loop over the whole record); chosen when records are small.
-// LPO lanes own one object (4 for records up to about a hundred bytes, where eight lanes would
-// leave half of them without a vector; 8 otherwise); a lane answers the join for G / LPO shards.
+// LPO lanes own one object — as many as the record has 16-byte vectors (4, 8, 16 or 32), so that
+// every copy of a typical record is ONE load per lane and an object costs two memory latencies
+// (object lines, then payload) however long it is; lane l answers the join for shards l, l + LPO, ...
+// of the group (the lanes beyond G have no shard to look up and only compare).
 // When the join is cached and the shards fit one group, the cached indices of the NEXT object are
 // requested while the current one is compared, which takes one level out of the dependent chain
 // (index -> object line -> payload) every object otherwise waits through.
@@ -328,31 +350,42 @@ template <int G, int LPO>
 __global__ void __launch_bounds__(256, G == 8 ? NCD_SS_CTAS : 4)
 k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint32_t* __restrict__ sh_idx,
              uint8_t* __restrict__ dv, uint32_t* __restrict__ tag) {
-  constexpr int SLOTS = G / LPO;  // shards a lane joins per group of G
+  constexpr int SLOTS = G > LPO ? G / LPO : 1;  // shards a lane joins per group of G
   struct ShardRef {
     const uint8_t* payload;
     const ObjMeta* meta;
     const uint32_t* join_cache;
     uint32_t* join_cache_out;
+    const uint4* join_line;
+    uint4* join_line_out;
+    uint32_t* join_rev_out;
   };
   extern __shared__ __align__(16) uint8_t s_raw[];
   ShardRef* s_sh = reinterpret_cast<ShardRef*>(s_raw);
   for (uint32_t s = threadIdx.x; s < S; s += blockDim.x)
-    s_sh[s] = ShardRef{shards[s].payload, shards[s].meta, shards[s].join_cache, shards[s].join_cache_out};
+    s_sh[s] = ShardRef{shards[s].payload,   shards[s].meta,          shards[s].join_cache, shards[s].join_cache_out,
+                       shards[s].join_line, shards[s].join_line_out, shards[s].join_rev_out};
   __syncthreads();
   const uint32_t lane = threadIdx.x & 31, l = lane & (LPO - 1), base = lane & ~(uint32_t)(LPO - 1);
-  const uint32_t gmask = (LPO == 8 ? 0xFFu : 0xFu) << base;  // the lanes of this object
+  const uint32_t gmask = LPO == 32 ? 0xFFFFFFFFu : ((1u << (LPO & 31)) - 1u) << base;  // the lanes of this object
   const uint64_t group0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LPO;
   const uint64_t ngroups = ((uint64_t)gridDim.x * blockDim.x) / LPO;
   // look-ahead only when EVERY shard's answer is cached (a shard re-committed since the last scan has
   // no valid cache while the others still do)
   bool prefetch = S <= (uint32_t)G && S > 0;
   for (uint32_t s = 0; s < S && prefetch; ++s) prefetch = s_sh[s].join_cache != nullptr;
+  // ... and of the cached copies of the found objects' lines, when every shard has those too: the
+  // steady state, in which an object then waits for ONE memory latency, its payload's
+  bool prefetch_line = prefetch;
+  for (uint32_t s = 0; s < S && prefetch_line; ++s) prefetch_line = s_sh[s].join_line != nullptr;
   uint32_t idx_next[SLOTS];
+  uint4 line_next[SLOTS];
 #pragma unroll
   for (int j = 0; j < SLOTS; ++j) {
     const uint32_t s = l + j * LPO;
-    idx_next[j] = (prefetch && s < S && group0 < ctrl.nobj) ? s_sh[s].join_cache[group0] : NCD_NOTFOUND;
+    const bool mine_here = s < G && s < S && group0 < ctrl.nobj;
+    idx_next[j] = (prefetch && mine_here) ? s_sh[s].join_cache[group0] : NCD_NOTFOUND;
+    line_next[j] = (prefetch_line && mine_here) ? s_sh[s].join_line[group0] : make_uint4(0, 0, 0, 0);
   }
   for (uint64_t c = group0; c < ctrl.nobj; c += ngroups) {
     const ObjMeta& q = ctrl.meta[c];
@@ -360,13 +393,20 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
     const uint32_t nvec = (len + 15) >> 4, tail = len & 15;
     const uint4* cp = reinterpret_cast<const uint4*>(ctrl.payload + q.rec_off);
     uint32_t idx_cur[SLOTS];
+    uint4 line_cur[SLOTS];
 #pragma unroll
-    for (int j = 0; j < SLOTS; ++j) idx_cur[j] = idx_next[j];
+    for (int j = 0; j < SLOTS; ++j) {
+      idx_cur[j] = idx_next[j];
+      line_cur[j] = line_next[j];
+    }
     if (prefetch && c + ngroups < ctrl.nobj) {
 #pragma unroll
       for (int j = 0; j < SLOTS; ++j) {
         const uint32_t s = l + j * LPO;
-        if (s < S) idx_next[j] = s_sh[s].join_cache[c + ngroups];
+        if (s < G && s < S) {
+          idx_next[j] = s_sh[s].join_cache[c + ngroups];
+          if (prefetch_line) line_next[j] = s_sh[s].join_line[c + ngroups];
+        }
       }
     }
     for (uint32_t s0 = 0; s0 < S; s0 += G) {
@@ -381,7 +421,7 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
         tg[j] = NCD_TAG_ROGUE;
         v[j] = DV_NOTFOUND;
         mine[j] = nullptr;
-        if (s < S) {
+        if (l + j * LPO < G && s < S) {
           const ShardRef sr = s_sh[s];
           if (prefetch) {
             idx[j] = idx_cur[j];
@@ -392,14 +432,26 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
             if (sr.join_cache_out) sr.join_cache_out[c] = idx[j];
           }
           if (idx[j] != NCD_NOTFOUND) {
-            const uint4* line = reinterpret_cast<const uint4*>(sr.meta + idx[j]);
-            const uint4 w0 = line[0], w1 = line[1];  // keyhash | rec_off ; rec_len key_off key_len/kind tag
-            tg[j] = w1.w;
-            if (w1.x != len) {
+            uint4 w;  // rec_off lo, hi, rec_len, tag: the pair's cached copy, or from the object's line
+            if (prefetch_line) {
+              w = line_cur[j];
+            } else if (sr.join_line) {
+              w = sr.join_line[c];
+            } else {
+              const uint4* line = reinterpret_cast<const uint4*>(sr.meta + idx[j]);
+              const uint4 w0 = line[0], w1 = line[1];  // keyhash | rec_off ; rec_len key_off key_len/kind tag
+              w = make_uint4(w0.z, w0.w, w1.x, w1.w);
+              if (sr.join_line_out) {
+                sr.join_line_out[c] = w;
+                sr.join_rev_out[idx[j]] = (uint32_t)c;
+              }
+            }
+            tg[j] = w.w;
+            if (w.z != len) {
               v[j] = DV_DIFF;  // the encoding is injective: different lengths cannot be DeepEqual
             } else {
               v[j] = DV_EQUAL;
-              mine[j] = reinterpret_cast<const uint4*>(sr.payload + ((uint64_t)w0.z | ((uint64_t)w0.w << 32)));
+              mine[j] = reinterpret_cast<const uint4*>(sr.payload + ((uint64_t)w.x | ((uint64_t)w.y << 32)));
             }
           }
         }
@@ -434,7 +486,7 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
 #pragma unroll
       for (int j = 0; j < SLOTS; ++j) {
         const uint32_t s = s0 + l + j * LPO;
-        if (s < S) {
+        if (l + j * LPO < G && s < S) {
           const uint64_t p = c * S + s;
           sh_idx[p] = idx[j];
           dv[p] = v[j];
@@ -679,6 +731,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   ncd_fill_dev_arena(ctrl, &dctrl);
   uint64_t algo = 0;
   std::vector<ncd_arena*> jc_filled;  // shard arenas whose join cache this scan fills
+  std::vector<ncd_arena*> jl_filled;  // ... and whose line cache
   {
     DevArena* tmp = (DevArena*)malloc(sizeof(DevArena) * (S ? S : 1));
     if (!tmp) return NCD_E_NOMEM;
@@ -691,6 +744,37 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
       for (uint32_t q = 0; q < s; ++q) listed_before = listed_before || shards[q] == shards[s];
       const bool valid = sa->jc_idx && sa->jc_ctrl == ctrl && sa->jc_ctrl_gen == ctrl->generation &&
                          sa->jc_gen == sa->generation && sa->jc_n == nc;
+      // the found objects' record offsets / lengths / tags, cached per pair as well (not when the
+      // controller holds a key twice: two pairs would share one shard object and only one could be
+      // kept current by k_pull_records)
+      const bool lines = ctx->line_cache && ctrl->dup_keys == 0 && !listed_before && nc;
+      if (valid && lines && sa->jc_line && sa->jc_line_ok) tmp[s].join_line = sa->jc_line;
+      else if (lines) {
+        if (!sa->jc_line || sa->jc_line_n < nc || sa->jc_rev_n < sa->nobj) {  // first use, or either side grew
+          if (sa->jc_line) cudaFree(sa->jc_line);
+          if (sa->jc_rev) cudaFree(sa->jc_rev);
+          sa->jc_line = nullptr;
+          sa->jc_rev = nullptr;
+          sa->jc_rev_n = sa->jc_line_n = 0;
+          const uint64_t rev_n = sa->nobj + sa->nobj / 8 + 1;
+          if (cudaMalloc((void**)&sa->jc_line, nc * sizeof(uint4)) != cudaSuccess ||
+              cudaMalloc((void**)&sa->jc_rev, rev_n * sizeof(uint32_t)) != cudaSuccess) {
+            cudaGetLastError();
+            if (sa->jc_line) cudaFree(sa->jc_line);
+            sa->jc_line = nullptr;  // no cache: the scan reads the object lines
+          } else {
+            sa->jc_line_n = nc;
+            sa->jc_rev_n = rev_n;
+          }
+        }
+        sa->jc_line_ok = false;
+        if (sa->jc_line) {
+          NCD_CUDA(cudaMemsetAsync(sa->jc_rev, 0xFF, sa->jc_rev_n * sizeof(uint32_t), st));
+          tmp[s].join_line_out = sa->jc_line;
+          tmp[s].join_rev_out = sa->jc_rev;
+          jl_filled.push_back(sa);
+        }
+      }
       if (valid) {
         tmp[s].join_cache = sa->jc_idx;
       } else if (!listed_before && nc) {
@@ -755,28 +839,37 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   NCD_RANGE_POP();
   NCD_RANGE_PUSH("ncd:compare");
   if (fused_small) {
-    // four lanes per object for records of about a hundred bytes or less, eight otherwise
-    const bool narrow = nc && ctrl->len_sum / nc <= 128;
-    const uint64_t lpo = narrow ? 4 : 8;
-    const uint64_t want = (nc * lpo + 255) / 256, cap = (uint64_t)ctx->sm_count * 16;
+    // as many lanes per object as the mean record has 16-byte vectors: 4 (up to ~100 bytes) to 32 (512 and more)
+    const uint64_t mean = nc ? ctrl->len_sum / nc : 0;
+    int lpo = mean <= 96 ? 4 : (mean <= 320 ? 8 : 16);  // 32 measured no better than 16 at 512 and 1024 bytes
+    if (ctx->ss_lpo) lpo = ctx->ss_lpo;
+    const uint64_t want = (nc * (uint64_t)lpo + 255) / 256, cap = (uint64_t)ctx->sm_count * 16;
     const unsigned grid = (unsigned)(want < cap ? want : cap);
-    const size_t smem = (size_t)S * 32;
+    const size_t smem = (size_t)S * 64;
+#define NCD_SS_LAUNCH(G_, L_) k_scan_small<G_, L_><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag)
     if (S <= 4) {
-      if (narrow) k_scan_small<4, 4><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
-      else k_scan_small<4, 4><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+      if (lpo == 4) NCD_SS_LAUNCH(4, 4);
+      else if (lpo == 8) NCD_SS_LAUNCH(4, 8);
+      else if (lpo == 16) NCD_SS_LAUNCH(4, 16);
+      else NCD_SS_LAUNCH(4, 32);
     } else {
-      if (narrow) k_scan_small<8, 4><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
-      else k_scan_small<8, 8><<<grid, 256, smem, st>>>(dctrl, ctx->d_shards, S, sh_idx, dv, tag);
+      if (lpo == 4) NCD_SS_LAUNCH(8, 4);
+      else if (lpo == 8) NCD_SS_LAUNCH(8, 8);
+      else if (lpo == 16) NCD_SS_LAUNCH(8, 16);
+      else NCD_SS_LAUNCH(8, 32);
     }
+#undef NCD_SS_LAUNCH
     ++launches;
     variant_used = 32;
   }
-  if (npairs)
+  if (npairs) {
     for (ncd_arena* sa : jc_filled) {
       sa->jc_ctrl = ctrl;
       sa->jc_ctrl_gen = ctrl->generation;
       sa->jc_gen = sa->generation;
     }
+    for (ncd_arena* sa : jl_filled) sa->jc_line_ok = true;
+  }
   const bool do_compare = !fused_small && ((hm == NCD_MODE_DIRECT) || (mode & NCD_MODE_CONFIRM));
   if (do_compare && npairs && ctrl->ntiles) {
     // Three data-movement shapes for the same compare, picked from the mean tile fill

@@ -192,9 +192,10 @@ int ncd_arena_compact(ncd_arena* a, uint64_t* new_payload_bytes) {
   uint64_t cur = 0;
   std::vector<uint8_t> tmp(a->payload_cap + 16);
   std::vector<uint64_t> noff(n);
-  for (uint32_t i : order) {  // the "device" copy is gathered from ITS offsets, as the real library does
-    const uint64_t padded = ((uint64_t)a->d.rec_len[i] + 15) / 16 * 16;
-    if (a->d.rec_off[i] != a->h.rec_off[i] || a->d.rec_len[i] != a->h.rec_len[i]) return fail(NCD_E_STATE, "fake: compact of an arena with unsynced records");
+  for (uint32_t i : order) {  // the "device" copy is gathered from ITS offsets, as the real library does, the slots
+                              // sized by the HOST's lengths (a record rewritten in place may not be synced yet)
+    const uint64_t padded = ((uint64_t)a->h.rec_len[i] + 15) / 16 * 16;
+    if (a->d.rec_off[i] != a->h.rec_off[i]) return fail(NCD_E_STATE, "fake: compact of an arena with a record moved and not synced");
     memcpy(tmp.data() + cur, a->d.payload + a->d.rec_off[i], padded);
     noff[i] = cur;
     cur += padded;

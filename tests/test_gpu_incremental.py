@@ -408,6 +408,57 @@ def test_compaction_reclaims_dead_payload_in_place(ctx):
             x.close()
 
 
+def test_compaction_with_records_rewritten_in_place_and_not_synced_yet(ctx):
+    """The host layer writes a new value that fits over its record in the pinned arrays as soon as the event
+    arrives; a compaction may come before the sync that pulls it.  The host's lengths then differ from the
+    device's (shorter, or longer within the record's old room): the slots are laid out for the host's
+    lengths, no neighbour is damaged on either side, and after the sync the scan decides like the oracle."""
+    rng = random.Random(321)
+    ctrl_h, shard_hs = random_clusters(56, n_templates=14, n_shards=2)
+    arenas = [resident(ctx, h, 1 << 20) for h in [ctrl_h] + shard_hs]
+    used = [h.payload_bytes for h in [ctrl_h] + shard_hs]
+    try:
+        a, arr = arenas[1], arenas[1].host_arrays()
+        n = a.counts().nobj
+        for i in range(n):  # dead payload to reclaim: every record grows once
+            used[1] = rewrite(rng, arr, used[1], i, rand_bytes(rng, int(arr["rec_len"][i]) + 40))
+        a.sync_records(np.arange(n, dtype=np.uint32), used[1])
+        # in place, not synced: every third record shrinks, every third grows back into room it has
+        touched, expect = [], {}
+        for i in range(n):
+            ln = int(arr["rec_len"][i])
+            if i % 3 == 0 and ln > 20:
+                new = rand_bytes(rng, ln - rng.randint(17, min(ln - 1, 200)))
+            elif i % 3 == 1:
+                new = rand_bytes(rng, ln - ln % 16 + rng.randint(1, 15) if ln % 16 else ln)  # same padded size, other length
+            else:
+                continue
+            off = int(arr["rec_off"][i])
+            assert rewrite(rng, arr, used[1], i, new) == used[1] and int(arr["rec_off"][i]) == off  # stayed in place
+            touched.append(i)
+            expect[i] = new
+        untouched = {i: a.download().record(i) for i in range(n) if i not in expect}
+        live = sum((int(arr["rec_len"][i]) + 15) // 16 * 16 for i in range(n))
+        assert a.compact() == live
+        used[1] = live
+        for i in range(n):  # pinned arrays: every record whole at its new place
+            off, ln = int(arr["rec_off"][i]), int(arr["rec_len"][i])
+            assert arr["payload"][off : off + ln].tobytes() == (expect[i] if i in expect else untouched[i]), i
+        a.sync_records(np.array(touched, dtype=np.uint32), used[1])
+        dev = a.download()
+        for i in range(n):
+            assert dev.record(i) == (expect[i] if i in expect else untouched[i]), i
+        for _ in range(2):
+            d = ctx.scan(arenas[0], arenas[1:], A.MODE_DIRECT)
+            want_codes, want_ents = oracle.scan(arenas[0].download(), [dev, arenas[2].download()])
+            np.testing.assert_array_equal(d.codes(), want_codes)
+            np.testing.assert_array_equal(d.entries(), want_ents)
+            d.close()
+    finally:
+        for x in arenas:
+            x.close()
+
+
 def test_committing_several_arenas_at_once_equals_one_by_one(ctx):
     """ncd_arenas_commit (uploads of all arenas enqueued up front, index builds behind them) leaves every arena
     exactly as ncd_arena_commit does, also when the same arenas are committed again and again."""

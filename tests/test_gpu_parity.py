@@ -463,3 +463,49 @@ def test_small_records_take_the_sub_warp_compare(ctx):
     codes, _, st = gpu_scan(ctx, ctrl, shards, A.MODE_HASH64 | A.MODE_CONFIRM)
     assert st.compare_variant == 16
     np.testing.assert_array_equal(codes, want_codes)
+
+
+@pytest.mark.parametrize("lpo", [4, 8, 16, 32])
+@pytest.mark.parametrize("nshards", [3, 8, 9])
+def test_fused_small_scan_with_every_lane_grouping(lpo, nshards, monkeypatch):
+    """k_scan_small gives an object as many lanes as its records have 16-byte vectors (4 to 32, picked from the
+    mean record length); every grouping must decide every record length alike — shorter than one vector per
+    lane, exactly one, several rounds — for fewer shards than a group, exactly one group, and more."""
+    import random
+
+    from nexus_configuration_controller_b200.drift import Context
+
+    monkeypatch.setenv("NCD_SS_LPO", str(lpo))
+    monkeypatch.setenv("NCD_COMPARE_VARIANT", "16")
+    rng = random.Random(100 + lpo + nshards)
+    n = 1500
+    datas = [rand_bytes(rng, rng.choice([0, 1, 16, 63, 64, 65, 127, 128, 255, 256, 257, 511, 512, 513, 1500, 5000])) for _ in range(n)]
+    ctrl = A.pack([A.CachedObject(A.KIND_WORKGROUP, f"default/wg-{i}", d, uid="u") for i, d in enumerate(datas)])
+    shards = []
+    for s in range(nshards):
+        objs = []
+        for i, d in enumerate(datas):
+            roll = rng.random()
+            if roll < 0.1:
+                continue
+            if roll < 0.3 and d:
+                b = bytearray(d)
+                b[rng.choice([0, len(b) - 1, len(b) // 2])] ^= 1 << rng.randrange(8)
+                d = bytes(b)
+            elif roll < 0.35:
+                d = d + b"x"
+            objs.append(A.CachedObject(A.KIND_WORKGROUP, f"default/wg-{i}", d, uid="v"))
+        rng.shuffle(objs)
+        shards.append(A.pack(objs))
+    want_codes, want_ents = oracle.scan(ctrl, shards)
+    with Context(0) as c2:
+        ca = c2.arena_from_host(ctrl)
+        sas = [c2.arena_from_host(h) for h in shards]
+        for _ in range(2):  # probing, then from the join cache
+            d = c2.scan(ca, sas, A.MODE_DIRECT)
+            assert c2.last_stats().compare_variant == 32
+            np.testing.assert_array_equal(d.codes(), want_codes)
+            np.testing.assert_array_equal(d.entries(), want_ents)
+            d.close()
+        for a in sas + [ca]:
+            a.close()
