@@ -331,20 +331,48 @@ __device__ __forceinline__ uint64_t xxh_merge(uint64_t h, uint64_t v) {
 // into its own shared-memory row with one bulk copy (cp.async.bulk, completion counted in bytes on
 // the warp's mbarrier), and then runs the stripes out of that row.  Rows are padded by one vector
 // so that LDS.128 at a row stride is conflict-free.
+// What held this kernel at 0.81 of the HBM peak was not the staging but DIVERGENCE: with 32 records
+// of different lengths per warp, almost every round had some lane in its record's last window (a
+// second, generic stripe loop ran beside the unrolled one) and some lane finishing (a hundred-odd
+// instructions for one active lane): 3.8 executed instructions per byte for 1.25 of hashing.  Now
+// the stripe loop is one predicated stream for all lanes and finishing is batched (see `flush`):
+// 0.89-0.90.  Staging variants measured on top of that (profiles/r02_xxh64_variants.txt): windows
+// of 512 bytes copied by the warp together, 16 bytes per lane (cp.async: every request one contiguous
+// window) 0.90; one bulk copy per lane 0.89; two row sets of 256 bytes with the next window in flight
+// while one is hashed 0.87 / 0.79 — larger windows beat overlap at the same shared memory.  The FETCH
+// side runs ahead of the HASH side by NBUF - 1 windows; what a window holds (record length,
+// position, where the digest goes) travels with it in registers.
 #ifndef NCD_XXH_WIN
 #define NCD_XXH_WIN 512
 #endif
-constexpr int XXH_WIN = NCD_XXH_WIN;       // bytes of one record staged per round (multiple of 32)
+#ifndef NCD_XXH_NBUF
+#define NCD_XXH_NBUF 1  // row sets per warp: 1 = stage, wait, hash; 2 = the next window in flight while one is hashed
+#endif
+#ifndef NCD_XXH_STAGE
+#define NCD_XXH_STAGE 1  // 0: one bulk copy per lane (its own record's window); 1: the warp copies window after window
+                         //    together, 16 bytes per lane (cp.async), so every request is one contiguous window
+#endif
+constexpr int XXH_WIN = NCD_XXH_WIN;       // bytes of one record staged per window (multiple of 32)
 constexpr int XXH_ROW = XXH_WIN / 16 + 1;  // uint4 per shared-memory row
-constexpr int XXH_Q = 64;                  // records a warp takes from the global counter at a time
+constexpr int XXH_NBUF = NCD_XXH_NBUF;
+static_assert(XXH_NBUF == 1 || XXH_NBUF == 2, "one or two row sets");
+static_assert(NCD_XXH_STAGE == 0 || XXH_WIN == 256 || XXH_WIN == 512, "cooperative staging covers 1 or 2 windows per instruction");
+constexpr int XXH_Q = 16;                  // records a warp takes from the global counter at a time
 constexpr int XXH_WARPS = 4;
 
 struct XxhSmem {
-  uint4 win[XXH_WARPS][32][XXH_ROW];
+  uint4 win[XXH_WARPS][XXH_NBUF][32][XXH_ROW];
   const unsigned char* qbase[XXH_WARPS][XXH_Q];
   uint64_t* qout[XXH_WARPS][XXH_Q];
   uint32_t qlen[XXH_WARPS][XXH_Q];
-  uint64_t bar[XXH_WARPS];
+  uint4 tail[XXH_WARPS][32][2];  // the last < 32 bytes of a record parked for finishing, per lane
+  uint64_t bar[XXH_WARPS][2];    // bulk-copy staging only
+};
+
+struct XxhWindow {  // what one staged window holds, per lane
+  uint64_t* out;
+  uint32_t len, pos;  // the record's length; the window starts at byte `pos` of it
+  bool valid;
 };
 
 __global__ void __launch_bounds__(128)
@@ -355,41 +383,41 @@ k_xxh64(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned in
   XxhSmem* sm = reinterpret_cast<XxhSmem*>(xxh_raw);
   uint64_t* s_base = reinterpret_cast<uint64_t*>(sm + 1);  // [njobs] first global record of each job
   for (int j = threadIdx.x; j < njobs; j += blockDim.x) s_base[j] = jobs[j].rec_base;
-  if (threadIdx.x < XXH_WARPS) mbar_init(&sm->bar[threadIdx.x], 1);
+  if (threadIdx.x < 2 * XXH_WARPS) mbar_init(&sm->bar[threadIdx.x >> 1][threadIdx.x & 1], 1);
   if (threadIdx.x == 0) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  uint4(*win)[XXH_ROW] = sm->win[wid];
-  uint64_t* bar = &sm->bar[wid];
   const uint64_t pol = l2_evict_first_policy();
-  uint32_t phase = 0;
   // Records are handed out to the warp XXH_Q at a time (one global atomic and one round of index
-  // loads per XXH_Q records, not per record); inside the warp, lanes that finished take the next
-  // entries in ballot order.  head / qn / drained are warp-uniform.
+  // loads per XXH_Q records, not per record); inside the warp, lanes whose fetch side ran out take
+  // the next entries in ballot order.  head / qn / drained are warp-uniform.
   const unsigned char** qb = sm->qbase[wid];
   uint32_t* ql = sm->qlen[wid];
   uint64_t** qo = sm->qout[wid];
   uint32_t head = 0, qn = 0;
-  const unsigned char* base = nullptr;  // first byte of the record
-  uint64_t* out = nullptr;
+  bool drained = false;
+  // fetch side: the record whose windows are being staged
+  const unsigned char* f_base = nullptr;
+  uint64_t* f_out = nullptr;
+  uint32_t f_len = 0, f_pos = 0;
+  bool f_have = false;
+  // hash side
   uint64_t v1 = 0, v2 = 0, v3 = 0, v4 = 0;
-  uint32_t len = 0, pos = 0;
-  bool have = false, drained = false;
-  for (;;) {
+  uint32_t phase[2] = {0, 0};
+
+  // Stages the next window of every lane into row set b.  Returns the bytes the warp asked for
+  // (warp-uniform; 0: nothing was armed, nobody waits).
+  auto fetch = [&](int b, XxhWindow& w) -> uint32_t {
     for (int pass = 0; pass < 2; ++pass) {
-      const unsigned m = __ballot_sync(0xffffffffu, !have);
+      const unsigned m = __ballot_sync(0xffffffffu, !f_have);
       if (!m) break;
       const uint32_t rank = __popc(m & ((1u << lane) - 1u)), avail = qn - head;
-      if (!have && rank < avail) {
-        base = qb[head + rank];
-        len = ql[head + rank];
-        out = qo[head + rank];
-        pos = 0;
-        have = true;
-        v1 = P1 + P2;
-        v2 = P2;
-        v3 = 0;
-        v4 = 0ull - P1;
+      if (!f_have && rank < avail) {
+        f_base = qb[head + rank];
+        f_len = ql[head + rank];
+        f_out = qo[head + rank];
+        f_pos = 0;
+        f_have = true;
       }
       head += min((uint32_t)__popc(m), avail);
       if ((uint32_t)__popc(m) <= avail || drained || pass) break;
@@ -411,79 +439,176 @@ k_xxh64(const HashJob* __restrict__ jobs, int njobs, uint32_t nrecs, unsigned in
       }
       __syncwarp();
     }
-    if (!__any_sync(0xffffffffu, have)) break;
-    // stage: the next window of every lane's record (16-byte granular; the arena pads records to 16)
-    const uint32_t want = have ? min((uint32_t)XXH_WIN, (len - pos + 15u) & ~15u) : 0u;
+    // 16-byte granular (the arena pads records to 16)
+    const uint32_t want = f_have ? min((uint32_t)XXH_WIN, (f_len - f_pos + 15u) & ~15u) : 0u;
     const uint32_t total = __reduce_add_sync(0xffffffffu, want);
+    w.valid = f_have;
+    w.out = f_out;
+    w.len = f_len;
+    w.pos = f_pos;
+#if NCD_XXH_STAGE == 0
     if (total) {
+      uint64_t* bar = &sm->bar[wid][b];
       if (lane == 0) mbar_arrive_expect_tx(bar, total);
       __syncwarp();
-      if (want) bulk_g2s(win[lane], base + pos, want, bar, pol);
-      mbar_wait(bar, phase);
-      phase ^= 1u;
+      if (want) bulk_g2s(sm->win[wid][b][lane], f_base + f_pos, want, bar, pol);
     }
-    if (have) {
-      const uint4* row = win[lane];
-      uint32_t w = 0;  // bytes of the window consumed
-      const uint32_t nfull = min((len - pos) >> 5, (uint32_t)(XXH_WIN / 32));  // whole stripes in this window
-      if (nfull == XXH_WIN / 32) {  // the common case, branch-free
+#else
+    {
+      // lane l copies chunk (l % C) of the window of record (l / C) of each group of 32 / C records
+      constexpr int C = XXH_WIN / 16, PER = 32 / C;  // chunks per window, windows per instruction
+      const unsigned long long src = (unsigned long long)(f_base + f_pos);
+      const uint32_t chunk = lane % C;
 #pragma unroll
-        for (int k = 0; k < XXH_WIN / 32; ++k) {
-          const uint4 x = row[2 * k], y = row[2 * k + 1];
-          v1 = xxh_round2(v1, x.x, x.y);
-          v2 = xxh_round2(v2, x.z, x.w);
-          v3 = xxh_round2(v3, y.x, y.y);
-          v4 = xxh_round2(v4, y.z, y.w);
+      for (int g = 0; g < 32 / PER; ++g) {
+        const int r = g * PER + lane / C;
+        const unsigned long long a = __shfl_sync(0xffffffffu, src, r);
+        const uint32_t wr = __shfl_sync(0xffffffffu, want, r);
+        if (chunk * 16u < wr) {
+          const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&sm->win[wid][b][r][chunk]);
+          asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(dst), "l"(a + chunk * 16ull), "l"(pol)
+                       : "memory");
         }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+#endif
+    if (f_have) {
+      if (f_len - f_pos <= (uint32_t)XXH_WIN) f_have = false;  // that was the record's last window (its tail included)
+      else f_pos += XXH_WIN;
+    }
+    return total;
+  };
+
+  // Hashes the window staged in row set b.
+  // A record's last steps (merging the accumulators, its tail of < 32 bytes, the avalanche) are a
+  // hundred-odd instructions that only the finishing lane needs; run when each lane gets there, the
+  // whole warp pays for them 32 times per generation of records.  So a finishing lane only parks
+  // what they need (accumulators and length in registers, the tail in shared memory) and goes on
+  // with its next record; the parked records are finished TOGETHER, when a lane that still has
+  // one parked finishes another (and at the end).
+  uint64_t s_v1 = 0, s_v2 = 0, s_v3 = 0, s_v4 = 0;
+  uint64_t* s_out = nullptr;
+  uint32_t s_len = 0;
+  bool s_full = false;
+  auto flush = [&]() {
+    if (s_full) {
+      uint64_t h;
+      if (s_len >= 32) {
+        h = rotl64(s_v1, 1) + rotl64(s_v2, 7) + rotl64(s_v3, 12) + rotl64(s_v4, 18);
+        h = xxh_merge(h, s_v1);
+        h = xxh_merge(h, s_v2);
+        h = xxh_merge(h, s_v3);
+        h = xxh_merge(h, s_v4);
       } else {
-        for (uint32_t k = 0; k < nfull; ++k) {
-          const uint4 x = row[2 * k], y = row[2 * k + 1];
-          v1 = xxh_round2(v1, x.x, x.y);
-          v2 = xxh_round2(v2, x.z, x.w);
-          v3 = xxh_round2(v3, y.x, y.y);
-          v4 = xxh_round2(v4, y.z, y.w);
-        }
+        h = P5;
       }
-      pos += 32 * nfull;
-      w = 32 * nfull;
-      const uint32_t rem = len - pos;
-      if (rem < 32 && w + rem <= XXH_WIN) {  // the tail is inside this window: finish the record
-        uint64_t h;
-        if (len >= 32) {
-          h = rotl64(v1, 1) + rotl64(v2, 7) + rotl64(v3, 12) + rotl64(v4, 18);
-          h = xxh_merge(h, v1);
-          h = xxh_merge(h, v2);
-          h = xxh_merge(h, v3);
-          h = xxh_merge(h, v4);
-        } else {
-          h = P5;
-        }
-        h += (uint64_t)len;
-        const uint32_t* t = reinterpret_cast<const uint32_t*>(row) + (w >> 2);  // the tail, as words
-        uint32_t o = 0;  // byte offset inside the tail; bytes past rem (padding) are never used
-        for (; o + 8 <= rem; o += 8) {
-          h ^= xxh_round(0, (uint64_t)t[o >> 2] | ((uint64_t)t[(o >> 2) + 1] << 32));
-          h = rotl64(h, 27) * P1 + P4;
-        }
-        if (o + 4 <= rem) {
-          h ^= (uint64_t)t[o >> 2] * P1;
-          h = rotl64(h, 23) * P2 + P3;
-          o += 4;
-        }
-        for (; o < rem; ++o) {
-          h ^= (uint64_t)((t[o >> 2] >> (8 * (o & 3))) & 0xffu) * P5;
-          h = rotl64(h, 11) * P1;
-        }
-        h ^= h >> 33;
-        h *= P2;
-        h ^= h >> 29;
-        h *= P3;
-        h ^= h >> 32;
-        *out = h;
-        have = false;
+      h += (uint64_t)s_len;
+      const uint32_t rem = s_len & 31u;
+      const uint32_t* t = reinterpret_cast<const uint32_t*>(sm->tail[wid][lane]);  // the tail, as words
+      uint32_t o = 0;  // byte offset inside the tail; bytes past rem (padding) are never used
+      for (; o + 8 <= rem; o += 8) {
+        h ^= xxh_round(0, (uint64_t)t[o >> 2] | ((uint64_t)t[(o >> 2) + 1] << 32));
+        h = rotl64(h, 27) * P1 + P4;
       }
+      if (o + 4 <= rem) {
+        h ^= (uint64_t)t[o >> 2] * P1;
+        h = rotl64(h, 23) * P2 + P3;
+        o += 4;
+      }
+      for (; o < rem; ++o) {
+        h ^= (uint64_t)((t[o >> 2] >> (8 * (o & 3))) & 0xffu) * P5;
+        h = rotl64(h, 11) * P1;
+      }
+      h ^= h >> 33;
+      h *= P2;
+      h ^= h >> 29;
+      h *= P3;
+      h ^= h >> 32;
+      *s_out = h;
+      s_full = false;
+    }
+  };
+
+  // Hashes the window staged in row set b.  One instruction stream for every lane: the stripes a
+  // lane's window does not have (a record's last window, a lane without a record) are computed on
+  // whatever the row holds and discarded.
+  auto hash = [&](int b, const XxhWindow& w, uint32_t armed) {
+#if NCD_XXH_STAGE == 0
+    if (armed) {
+      mbar_wait(&sm->bar[wid][b], phase[b]);
+      phase[b] ^= 1u;
+    }
+#else
+    // this row set's group is the oldest but (NBUF - 1): every lane's part of it has landed, then the warp's
+    if (XXH_NBUF == 2) asm volatile("cp.async.wait_group 1;" ::: "memory");
+    else asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
+    (void)armed;
+#endif
+    const uint4* row = sm->win[wid][b][lane];
+    const uint32_t len = w.len;
+    if (w.valid && w.pos == 0) {
+      v1 = P1 + P2;
+      v2 = P2;
+      v3 = 0;
+      v4 = 0ull - P1;
+    }
+    const uint32_t nfull = w.valid ? min((len - w.pos) >> 5, (uint32_t)(XXH_WIN / 32)) : 0u;  // whole stripes in this window
+#pragma unroll
+    for (int k = 0; k < XXH_WIN / 32; ++k) {
+      const uint4 x = row[2 * k], y = row[2 * k + 1];
+      const bool on = (uint32_t)k < nfull;
+      const uint64_t n1 = xxh_round2(v1, x.x, x.y), n2 = xxh_round2(v2, x.z, x.w);
+      const uint64_t n3 = xxh_round2(v3, y.x, y.y), n4 = xxh_round2(v4, y.z, y.w);
+      v1 = on ? n1 : v1;
+      v2 = on ? n2 : v2;
+      v3 = on ? n3 : v3;
+      v4 = on ? n4 : v4;
+    }
+    const uint32_t w_used = 32 * nfull;  // bytes of the window consumed
+    const uint32_t rem = len - (w.pos + w_used);
+    const bool fin = w.valid && rem < 32 && w_used + rem <= XXH_WIN;  // the tail is inside this window: the record ends here
+    if (__any_sync(0xffffffffu, fin && s_full)) flush();
+    if (fin) {
+      const uint32_t ti = min(w_used >> 4, (uint32_t)(XXH_WIN / 16 - 1));  // rem == 0 when the window was used up
+      sm->tail[wid][lane][0] = row[ti];
+      sm->tail[wid][lane][1] = row[ti + 1];
+      s_v1 = v1;
+      s_v2 = v2;
+      s_v3 = v3;
+      s_v4 = v4;
+      s_len = len;
+      s_out = w.out;
+      s_full = true;
+    }
+  };
+
+  XxhWindow w0, w1;
+  if (XXH_NBUF == 1) {
+    for (;;) {
+      const uint32_t armed = fetch(0, w0);
+      if (!__any_sync(0xffffffffu, w0.valid)) break;
+      hash(0, w0, armed);
+      __syncwarp();  // every lane is done reading the rows before they are staged again
+    }
+  } else {
+    uint32_t armed0 = fetch(0, w0), armed1;
+    for (;;) {
+      armed1 = fetch(XXH_NBUF - 1, w1);
+      if (!__any_sync(0xffffffffu, w0.valid)) break;  // the fetch side ran dry one window ago: w1 is empty too
+      hash(0, w0, armed0);
+      __syncwarp();  // every lane is done reading row set 0 before it is staged again
+      armed0 = fetch(0, w0);
+      if (!__any_sync(0xffffffffu, w1.valid)) break;
+      hash(XXH_NBUF - 1, w1, armed1);
+      __syncwarp();
     }
   }
+#if NCD_XXH_STAGE == 1
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+#endif
+  flush();
 }
 
 // ------------------------------------------------------------------ host side
@@ -575,7 +700,7 @@ int ncd_hash_launch_many(ncd_ctx* ctx, ncd_arena* const* arenas, int count, uint
     } else {
       const size_t xs = sizeof(XxhSmem) + smem;
       NCD_CUDA(cudaFuncSetAttribute(k_xxh64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xs));
-      const uint64_t per_sm = (216u * 1024u) / xs ? (216u * 1024u) / xs : 1;
+      const uint64_t per_sm = (227u * 1024u) / (xs + 1024) ? (227u * 1024u) / (xs + 1024) : 1;  // 1 KB per CTA is the system's
       const uint64_t want = (recs + 32 * XXH_WARPS - 1) / (32 * XXH_WARPS), cap = (uint64_t)ctx->sm_count * per_sm;
       k_xxh64<<<(unsigned)(want < cap ? want : cap), 32 * XXH_WARPS, xs, st>>>(dj, njobs, (uint32_t)recs, next);
     }
@@ -649,7 +774,7 @@ int ncd_hash_records_many(ncd_ctx* ctx, int count, ncd_arena* const* arenas, con
       NCD_CUDA(cudaMemcpyAsync(djx, xxh_jobs.data(), sizeof(HashJob) * m, cudaMemcpyHostToDevice, st));
       const size_t xs = sizeof(XxhSmem) + sizeof(uint64_t) * m;
       NCD_CUDA(cudaFuncSetAttribute(k_xxh64, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)xs));
-      const uint64_t per_sm = (216u * 1024u) / xs ? (216u * 1024u) / xs : 1;
+      const uint64_t per_sm = (227u * 1024u) / (xs + 1024) ? (227u * 1024u) / (xs + 1024) : 1;  // 1 KB per CTA is the system's
       const uint64_t want = (xxh_recs + 32 * XXH_WARPS - 1) / (32 * XXH_WARPS), cap = (uint64_t)ctx->sm_count * per_sm;
       k_xxh64<<<(unsigned)(want < cap ? want : cap), 32 * XXH_WARPS, xs, st>>>(djx, m, (uint32_t)xxh_recs, next + 1);
     }
