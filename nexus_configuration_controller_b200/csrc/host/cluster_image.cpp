@@ -15,9 +15,13 @@ void ClusterImage::bind_arena() { host_payload = arena.a ? host_view().payload :
 // Caller holds the cache lock exclusively; no GPU work here except creating a larger arena.
 // h2d: bytes that upload will move.  tomb_floor: removals at or before this stamp are part of the
 // published snapshot and can be forgotten.
-Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uint64_t* h2d) {
+Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uint64_t* h2d, bool* deferred) {
   for (auto it = tomb.begin(); it != tomb.end();)
     it = it->second <= tomb_floor ? tomb.erase(it) : std::next(it);
+  if (deferred && (!arena.a || structural || force_full)) {
+    *deferred = true;
+    return Upload::None;
+  }
   if (structural) {  // forget dead objects (their payload becomes unreferenced until the arena is re-made)
     bool any_dead = false;
     for (const CachedObject& o : objs) any_dead = any_dead || !o.live;
@@ -42,6 +46,10 @@ Upload ClusterImage::prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uin
   for (uint32_t i : dirty) {
     if (pad16(objs[i].len) > objs[i].rec_cap) append += pad16(objs[i].len);
     if (!objs[i].pending) v.rec_len[i] = objs[i].len;  // rewritten in place: a compaction below must move its new length
+  }
+  if (deferred && payload_used + append > payload_cap) {
+    *deferred = true;
+    return Upload::None;
   }
   if (payload_used + append > payload_cap && !reclaim(append)) {  // no room to append: move to a larger arena
     dirty.clear();

@@ -356,7 +356,10 @@ struct ClusterImage {
     pending_changed.clear();
   }
 
-  Upload prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uint64_t* h2d);
+  // deferred != null: only the cheap case is handled (values rewritten inside a resident arena that has
+  // room for them) — anything that makes or compacts an arena or rebuilds the per-object arrays sets
+  // *deferred and returns without having changed anything, for the caller to run alone later.
+  Upload prepare(ncd_ctx* ctx, int threads, uint64_t tomb_floor, uint64_t* h2d, bool* deferred = nullptr);
   void upload(Upload what);
   // A prepared Full upload, for the caller that commits several clusters in one ncd_arenas_commit.
   void full_counts(uint64_t out[5]) const {

@@ -545,7 +545,20 @@ int ncdh_scan(ncdh_checker* c) {
       snap->clock = c->clock.load();
       tm.events = c->events_since_scan.exchange(0);
       tm.canon_ms = (double)c->canon_ns_since_scan.exchange(0) / 1e6;
-      for (size_t k = 0; k < imgs.size(); ++k) ups[k] = imgs[k]->prepare(c->ctx, c->threads, prev ? prev->clock : 0, &tm.h2d_bytes);
+      // the common case — values rewritten inside resident arenas — for all clusters at once, one worker
+      // each; whatever needs a new arena, a compaction or new per-object arrays runs alone afterwards
+      const uint64_t floor = prev ? prev->clock : 0;
+      std::vector<uint64_t> h2d(imgs.size(), 0);
+      std::vector<char> later(imgs.size(), 0);
+      Workers::get().run(imgs.size(), c->threads, [&](size_t k) {
+        bool deferred = false;
+        ups[k] = imgs[k]->prepare(c->ctx, 1, floor, &h2d[k], &deferred);
+        later[k] = deferred;
+      });
+      for (size_t k = 0; k < imgs.size(); ++k) {
+        if (later[k]) ups[k] = imgs[k]->prepare(c->ctx, c->threads, floor, &h2d[k]);
+        tm.h2d_bytes += h2d[k];
+      }
       if (ups[0] == Upload::Full || ups[0] == Upload::Structural || !c->dir) {
         // row numbering: arena order, one row per template + one per dependent, one per workgroup
         auto dir = std::make_shared<RowDirectory>();
