@@ -9,7 +9,15 @@ ncd_arena_view ClusterImage::host_view() {
   return v;
 }
 
-void ClusterImage::bind_arena() { host_payload = arena.a ? host_view().payload : nullptr; }
+void ClusterImage::bind_arena() {
+  host_payload = nullptr;
+  host_rec_len = nullptr;
+  if (arena.a) {
+    const ncd_arena_view v = host_view();
+    host_payload = v.payload;
+    host_rec_len = v.rec_len;
+  }
+}
 
 // Brings the pinned host arrays up to date with the image and says what has to be uploaded.
 // Caller holds the cache lock exclusively; no GPU work here except creating a larger arena.

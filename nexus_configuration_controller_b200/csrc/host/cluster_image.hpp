@@ -218,11 +218,14 @@ struct ClusterImage {
   uint64_t layout = 0;                             // bumped whenever positions in objs are reassigned
   ArenaHandle arena;
   const uint8_t* host_payload = nullptr;           // the arena's pinned payload (where placed records are read back from)
+  uint32_t* host_rec_len = nullptr;                // ... and its pinned rec_len array
   uint64_t payload_used = 0, payload_cap = 0, nobj_cap = 0, aux_cap = 0, nowner_cap = 0, ndep_cap = 0;
   bool structural = true;   // keys / owners / dependents changed since the last commit
   bool force_full = false;  // the resident device copy is not trusted: upload everything again
   uint64_t uploads_full = 0, uploads_structural = 0, uploads_values = 0, compactions = 0;
   uint64_t in_place_last = 0;  // records of the last prepared Values upload that needed no copy
+  uint64_t pulled_early = 0;   // records handed to the device as their batch was applied, since the last Scan
+  uint64_t payload_in_use() const { return payload_used; }
   std::vector<uint32_t> pending_changed;  // records a prepared Values upload still has to push
 
   const uint8_t* bytes_of(const CachedObject& o) const { return o.pending ? o.pending : host_payload + o.rec_off; }
@@ -311,19 +314,30 @@ struct ClusterImage {
   bool hint_valid(const PutHint& hint) const {
     return hint.found && hint.layout == layout && hint.pos < objs.size() && objs[hint.pos].live && objs[hint.pos].gen == hint.seen_gen;
   }
-  bool put_direct(std::shared_ptr<const ObjInfo>& info, uint32_t len, uint64_t stamp, const PutHint& hint) {
+  // pull_now != null: a record that was clean until now is not left for the next Scan's lay-out — its new
+  // length goes into the pinned rec_len array here and its position onto *pull_now, for the caller to have
+  // it pulled to the device right away (the record stays clean).
+  bool put_direct(std::shared_ptr<const ObjInfo>& info, uint32_t len, uint64_t stamp, const PutHint& hint,
+                  std::vector<uint32_t>* pull_now = nullptr) {
     if (!hint_valid(hint)) return false;
     CachedObject& o = objs[hint.pos];
     if (!hint.same_structure) {
       structural = true;
       o.info = std::move(info);
     }
-    if (!o.pending && !o.direct) dirty.push_back((uint32_t)hint.pos);
+    const bool clean = !o.pending && !o.direct;
     o.pending = nullptr;  // an older value still waiting for the packer is superseded
     o.hold.reset();
     o.len = len;
-    o.direct = true;
     o.gen = last_change = stamp;
+    if (clean && pull_now && !force_full && host_rec_len) {
+      host_rec_len[hint.pos] = len;
+      pull_now->push_back((uint32_t)hint.pos);
+      ++pulled_early;
+      return true;
+    }
+    if (clean) dirty.push_back((uint32_t)hint.pos);
+    o.direct = true;
     return true;
   }
   bool drop(uint32_t kind, const std::string& key, uint64_t stamp) { return drop(store_key(kind, key), stamp); }

@@ -23,11 +23,14 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <deque>
 #include <memory>
 #include <mutex>
 #include <shared_mutex>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -88,6 +91,100 @@ struct Snapshot {
 
 }  // namespace
 
+// Pulls records to the device while the batch that rewrote them is still being applied: a batch is
+// worked off in chunks, and while the host canonicalises chunk k + 1 this thread has the GPU fetch
+// the records chunk k wrote in place (ncd_arenas_sync_records, synchronous in here only).  One job at
+// a time, in order.  A Scan drains it before it touches the arenas.
+struct Puller {
+  // The batch hands over its claims on the records with them: nobody writes a record's pinned bytes
+  // while the GPU reads them; the claims are released when the pull is done.
+  struct Job {
+    std::vector<ClusterImage*> images;
+    std::vector<ncd_arena*> arenas;
+    std::vector<std::vector<uint32_t>> lists;  // positions in images[q]->objs == object numbers in arenas[q]
+    std::vector<uint64_t> payload_bytes;
+  };
+  std::mutex mu;
+  std::condition_variable cv, idle;
+  std::deque<Job> jobs;
+  bool busy = false, stop = false, started = false;
+  std::string error;           // first failure since the last drain
+  uint64_t records = 0, bytes = 0, calls = 0;
+  double busy_ms = 0;
+  std::thread th;
+  std::mutex* gpu_mu = nullptr;  // library calls on the checker's context are made one at a time
+  std::shared_mutex* cache_mu = nullptr;
+
+  void submit(Job&& j) {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!started) {
+      started = true;
+      th = std::thread([this] { loop(); });
+    }
+    jobs.push_back(std::move(j));
+    cv.notify_one();
+  }
+  // Waits until everything submitted has been pulled; returns the first error since the last drain.
+  std::string drain() {
+    std::unique_lock<std::mutex> lk(mu);
+    idle.wait(lk, [&] { return jobs.empty() && !busy; });
+    std::string e;
+    e.swap(error);
+    return e;
+  }
+  void shutdown() {
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      stop = true;
+      cv.notify_all();
+    }
+    if (th.joinable()) th.join();
+  }
+  void loop() {
+    for (;;) {
+      Job j;
+      {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return stop || !jobs.empty(); });
+        if (jobs.empty()) return;  // stop, and nothing left
+        j = std::move(jobs.front());
+        jobs.pop_front();
+        busy = true;
+      }
+      const auto t0 = std::chrono::steady_clock::now();
+      std::vector<uint64_t> ns;
+      std::vector<const uint32_t*> idx;
+      uint64_t recs = 0;
+      for (const auto& l : j.lists) {
+        ns.push_back(l.size());
+        idx.push_back(l.data());
+        recs += l.size();
+      }
+      int rc;
+      {
+        std::lock_guard<std::mutex> g(*gpu_mu);
+        rc = ncd_arenas_sync_records((int)j.arenas.size(), j.arenas.data(), ns.data(), idx.data(), j.payload_bytes.data());
+      }
+      const std::string err = rc == NCD_OK ? std::string() : ncd_err("ncd_arenas_sync_records (early pull)");
+      // objs does not move while the cache lock is held shared; in slices, so that a batch waiting to
+      // update (exclusive) is not held up by a long list
+      for (size_t q = 0; q < j.images.size(); ++q)
+        for (size_t at = 0; at < j.lists[q].size(); at += 256) {
+          std::shared_lock<std::shared_mutex> rd(*cache_mu);
+          const size_t end = std::min(j.lists[q].size(), at + 256);
+          for (size_t x = at; x < end; ++x) release_claim(j.images[q]->objs[j.lists[q][x]]);
+        }
+      std::lock_guard<std::mutex> lk(mu);
+      if (!err.empty() && error.empty()) error = err;
+      records += recs;
+      ++calls;
+      busy_ms += ms_since(t0);
+      busy = false;
+      if (jobs.empty()) idle.notify_all();
+    }
+  }
+};
+
 struct ncdh_checker {
   ncd_ctx* ctx = nullptr;
   uint32_t mode = 0;
@@ -100,6 +197,9 @@ struct ncdh_checker {
   // before cache_mu.  Batches only ever TRY it (they have the slab path when a Scan is at work).
   std::shared_mutex pinned_mu;
   std::atomic<int> scan_wants_pinned{0};
+  std::mutex gpu_mu;  // one library call at a time on ctx (a Scan's uploads and scan; the early pulls)
+  Puller puller;
+  std::atomic<uint64_t> early_h2d{0};  // bytes of the records handed to the puller since the last Scan
   std::atomic<uint64_t> clock{0};
   std::atomic<uint64_t> events_since_scan{0};
   std::atomic<uint64_t> canon_ns_since_scan{0};
@@ -310,6 +410,8 @@ int ncdh_checker_create(int device, uint32_t mode, int nshards, ncdh_checker** o
   std::unique_ptr<ncdh_checker> c(new ncdh_checker);
   if (ncd_init(device, &c->ctx) != NCD_OK) return fail(ncd_err("ncd_init"));  // no GPU: an error, not a fallback
   c->mode = mode;
+  c->puller.gpu_mu = &c->gpu_mu;
+  c->puller.cache_mu = &c->cache_mu;
   c->shards.resize(nshards);
   const unsigned hc = std::thread::hardware_concurrency();
   c->threads = hc ? (int)(hc > 32 ? 32 : hc) : 4;
@@ -319,6 +421,7 @@ int ncdh_checker_create(int device, uint32_t mode, int nshards, ncdh_checker** o
 
 void ncdh_checker_destroy(ncdh_checker* c) {
   if (!c) return;
+  c->puller.shutdown();         // pulls what was still queued, then ends the thread
   c->controller.arena.reset();  // arenas before the context they live in
   for (ClusterImage& sh : c->shards) sh.arena.reset();
   if (c->ctx) ncd_destroy(c->ctx);
@@ -355,6 +458,15 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     static const bool no_in_place = getenv("NCDH_NO_IN_PLACE") != nullptr;  // measurement knob: every value through the slab
     const bool in_place = !no_in_place && c->scan_wants_pinned.load(std::memory_order_acquire) == 0 && pinned.try_lock();
     ClaimGuard guard{c, evs};
+    // A large batch is worked off in chunks: the records one chunk wrote in place are pulled to the
+    // device (Puller) while the next chunk is canonicalised.
+    static const bool no_early = getenv("NCDH_NO_EARLY_PULL") != nullptr;  // measurement knob
+    const bool early = in_place && !no_early;
+    const uint64_t chunk = early ? std::max<uint64_t>(2048, std::min<uint64_t>(8192, (n + 3) / 4)) : n;
+    double t_phase1 = 0, t_phase2 = 0;
+    for (uint64_t c0 = 0; c0 < n; c0 += chunk) {
+    const uint64_t c1 = std::min(n, c0 + chunk);
+    const auto t_chunk = std::chrono::steady_clock::now();
     // Canonicalise in parallel, outside the exclusive lock, and look every object up and compare its
     // value with what the cache holds under the SHARED lock: readers and other batches go on, only the
     // short update below is exclusive.  A new value that fits its record's place goes straight into
@@ -362,7 +474,8 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     // resync — writes nothing); any other goes to the slab and waits for the packer.
     {
       std::shared_lock<std::shared_mutex> rd(c->cache_mu);
-      parallel_for(n, threads, 8, [&](size_t i) {
+      parallel_for(c1 - c0, threads, 8, [&](size_t ii) {
+        const size_t i = c0 + ii;
         Prepared& p = evs[i];
         try {
           const ncdh_event& e = events[i];
@@ -407,13 +520,17 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
         }
       });
     }
-    c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t0) * 1e6), std::memory_order_relaxed);
-    const double t_phase1 = ms_since(t0);
+    c->canon_ns_since_scan.fetch_add((uint64_t)(ms_since(t_chunk) * 1e6), std::memory_order_relaxed);
+    t_phase1 += ms_since(t_chunk);
+    const auto t_update = std::chrono::steady_clock::now();
     // The update itself: the events of different clusters touch different images, so each cluster's
     // events are applied, in order, by their own worker.
     std::vector<std::vector<uint32_t>> by_cluster(c->shards.size() + 1);
-    for (uint64_t i = 0; i < n; ++i)
+    for (uint64_t i = c0; i < c1; ++i)
       if (evs[i].op != kSkipped) by_cluster[(size_t)(evs[i].cluster + 1)].push_back((uint32_t)i);
+    std::vector<std::vector<uint32_t>> pull_now(by_cluster.size());  // per cluster: records to hand to the device at once
+    std::vector<uint64_t> pull_bytes(by_cluster.size(), 0);
+    Puller::Job job;
     {
       std::unique_lock<std::shared_mutex> lk(c->cache_mu);
       Workers::get().run(by_cluster.size(), threads, [&](size_t k) {
@@ -430,8 +547,10 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
           } else if (p.direct || (!p.bytes && !img->hint_valid(p.hint))) {
             // written in place, or found equal in phase one without keeping the bytes
             const bool was_direct = p.direct;
-            if (was_direct && img->put_direct(p.info, p.len, stamp, p.hint)) {
+            const size_t before = pull_now[k].size();
+            if (was_direct && img->put_direct(p.info, p.len, stamp, p.hint, early ? &pull_now[k] : nullptr)) {
               changed = true;
+              if (pull_now[k].size() != before) pull_bytes[k] += pad16(p.len) + 4;
             } else {
               // something else was applied to the object since phase one looked at it: the value is
               // canonicalised again and put the ordinary way (after an in-place write the pinned
@@ -442,7 +561,7 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
                                  nullptr, /*force=*/was_direct);
             }
             if (was_direct) {
-              release_claim(img->objs[p.hint.pos]);
+              if (pull_now[k].size() == before) release_claim(img->objs[p.hint.pos]);  // else the claim goes with the pull
               p.direct = false;
             }
           } else {
@@ -452,16 +571,29 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
         }
         c->events_since_scan.fetch_add(changed_events, std::memory_order_relaxed);
       });
+      for (size_t k = 0; k < pull_now.size(); ++k)  // arena and payload size as they are under the lock
+        if (!pull_now[k].empty()) {
+          ClusterImage* img = c->image((int)k - 1);
+          job.images.push_back(img);
+          job.arenas.push_back(img->arena.a);
+          job.payload_bytes.push_back(img->payload_in_use());
+          job.lists.push_back(std::move(pull_now[k]));
+          c->early_h2d.fetch_add(pull_bytes[k], std::memory_order_relaxed);
+        }
     }
-    const double t_phase2 = ms_since(t0);
+    if (!job.arenas.empty()) c->puller.submit(std::move(job));
+    t_phase2 += ms_since(t_update);
+    }  // chunks
+    const auto t_release = std::chrono::steady_clock::now();
     parallel_for(n, threads, 256, [&](size_t i) {  // what the events still own is released in parallel too
       evs[i].info.reset();
       std::string().swap(evs[i].skey);
     });
     static const bool profile = getenv("NCDH_PROFILE") != nullptr;
     if (profile)
-      fprintf(stderr, "ncdh_apply_events: %llu events, lookup + canonicalise %.3f ms, update %.3f ms, release %.3f ms%s\n",
-              (unsigned long long)n, t_phase1, t_phase2 - t_phase1, ms_since(t0) - t_phase2, in_place ? "" : " (slab path: a Scan held the pinned payloads)");
+      fprintf(stderr, "ncdh_apply_events: %llu events in chunks of %llu, lookup + canonicalise %.3f ms, update %.3f ms, release %.3f ms, total %.3f ms%s\n",
+              (unsigned long long)n, (unsigned long long)chunk, t_phase1, t_phase2, ms_since(t_release), ms_since(t0),
+              in_place ? "" : " (slab path: a Scan held the pinned payloads)");
   } catch (const std::exception& e) {
     return fail(std::string("ncdh_apply_events: ") + e.what());
   }
@@ -531,6 +663,11 @@ int ncdh_scan(ncdh_checker* c) {
   std::unique_lock<std::shared_mutex> pinned(c->pinned_mu);
   c->scan_wants_pinned.fetch_sub(1, std::memory_order_release);
   try {
+    // records that batches handed to the device as they were applied: all of them are there now
+    const auto t_drain = std::chrono::steady_clock::now();
+    const std::string early_error = c->puller.drain();
+    if (!early_error.empty()) throw std::runtime_error(early_error);
+    const double drain_ms = ms_since(t_drain);
     const size_t S = c->shards.size();
     std::vector<ClusterImage*> imgs;
     imgs.push_back(&c->controller);
@@ -579,10 +716,17 @@ int ncdh_scan(ncdh_checker* c) {
         c->dir = std::move(dir);
         c->unadopted_valid = false;
       }
-      for (ClusterImage* img : imgs) tm.compactions += img->compactions;
+      for (ClusterImage* img : imgs) {
+        tm.compactions += img->compactions;
+        tm.records_synced += img->pulled_early;
+        tm.records_in_place += img->pulled_early;
+        img->pulled_early = 0;
+      }
+      tm.h2d_bytes += c->early_h2d.exchange(0);
       tm.pack_ms = ms_since(t0);
     }
     // ---- GPU: uploads, then the scan (the cache lock is free: events and lookups go on)
+    std::lock_guard<std::mutex> gpu(c->gpu_mu);
     const auto t_up = std::chrono::steady_clock::now();
     std::vector<ncd_arena*> as, full;
     std::vector<uint64_t> ns, pbs, fc[5];
@@ -633,7 +777,7 @@ int ncdh_scan(ncdh_checker* c) {
       c->unadopted_valid = true;
       tm.d2h_bytes += 8 + n * sizeof(ncd_adoption);
     }
-    tm.upload_ms = ms_since(t_up);
+    tm.upload_ms = ms_since(t_up) + drain_ms;  // what this Scan still had to wait for
     pinned.unlock();
     static const bool profile = getenv("NCDH_PROFILE") != nullptr;
     if (profile) {
