@@ -51,7 +51,8 @@ int ncdh_cluster_remove(ncdh_checker* c, int cluster, uint32_t kind, const char*
  * under the checker's lock.  An event that fails (malformed value, unknown cluster) is skipped:
  * every other event of the batch is applied, the call returns -1 and ncdh_last_error names the
  * first skipped event.  A new value that fits the place its record already has in the arena's
- * pinned payload is written there directly (unchanged values — a resync — write nothing); others
+ * pinned payload is written there directly (unchanged values — a resync — write nothing) and, in a
+ * large batch, pulled to the device while the rest of the batch is still canonicalised; others
  * wait in pooled memory until the next ncdh_scan lays them out. */
 enum { NCDH_EV_PUT = 0, NCDH_EV_DELETE = 1 };
 typedef struct ncdh_event {

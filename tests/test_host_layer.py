@@ -563,3 +563,39 @@ def test_batches_that_rewrite_records_in_place(make_checker, seed):
             in_place += f.timing()["records_in_place"]
             appended += sum(a[1] - b[1] for a, b in zip(after, before))
         assert in_place > 0 and appended > 0 and resyncs > 0
+
+
+def test_a_large_batch_is_pulled_while_it_is_applied(make_checker, request):
+    """A batch of thousands of events is applied in chunks; the records one chunk rewrote in place are pulled to
+    the device by the puller thread while the next chunk is canonicalised, and the Scan that follows has nothing
+    left to upload.  The diff list must be the oracle fleet's for the same events, before and after."""
+    import oracle
+    from tests.helpers import random_clusters
+
+    lib = fake_lib() if "fake" in request.node.name else None
+    ctrl, shards = random_clusters(77, n_templates=3000, n_shards=2, max_len=600)
+    assert ctrl.nobj > 3 * 2048  # several chunks
+    fleet = oracle.Fleet(2)
+    with make_checker(2) as f:
+        first = [Hst.EventBatch(ctrl, cluster=-1, lib=lib)] + [Hst.EventBatch(h, cluster=s, lib=lib) for s, h in enumerate(shards)]
+        for b in first:
+            f.apply_events(b, threads=4)
+            fleet.apply(b.events, b.n, threads=2)
+        f.scan()
+        _, decisions, ndiff, dirty, digest = fleet.sweep(threads=2)
+        assert f.counts() == (ndiff, decisions) and f.diff_digest() == (digest, dirty)
+        for salt in (3, 4):  # every controller object gets a new value of the same length, twice
+            upd = Hst.EventBatch(ctrl, cluster=-1, salt=salt, threads=4, lib=lib)
+            f.apply_events(upd, threads=4)
+            fleet.apply(upd.events, upd.n, threads=2)
+            f.scan()
+            t = f.timing()
+            changed = sum(1 for i in range(ctrl.nobj) if ctrl.rec_len[i] > 0)
+            assert (t["full_uploads"], t["structural_uploads"]) == (0, 0)
+            assert t["records_synced"] == changed and t["records_in_place"] == changed and t["events"] == changed
+            _, decisions, ndiff, dirty, digest = fleet.sweep(threads=2)
+            assert f.counts() == (ndiff, decisions) and f.diff_digest() == (digest, dirty)
+            upd.close()
+        for b in first:
+            b.close()
+    fleet.close()
