@@ -536,9 +536,21 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
       Workers::get().run(by_cluster.size(), threads, [&](size_t k) {
         ClusterImage* img = c->image((int)k - 1);
         uint64_t changed_events = 0;
-        for (uint32_t i : by_cluster[k]) {
+        const std::vector<uint32_t>& mine = by_cluster[k];
+        // one block of stamps per cluster and chunk (the clock is shared by every cluster's worker): an
+        // object's history only needs its own stamps to rise, and all of them to lie after earlier Scans
+        uint64_t stamp = mine.empty() ? 0 : c->clock.fetch_add(mine.size());
+        for (size_t at = 0; at < mine.size(); ++at) {
+          const uint32_t i = mine[at];
           Prepared& p = evs[i];
-          const uint64_t stamp = c->clock.fetch_add(1) + 1;
+          ++stamp;
+          if (at + 4 < mine.size()) {  // the next objects' lines: each is a cache miss otherwise
+            const Prepared& nx = evs[mine[at + 4]];
+            if (nx.hinted && nx.hint.pos < img->objs.size()) {
+              __builtin_prefetch(&img->objs[nx.hint.pos], 1);
+              if (img->host_rec_len) __builtin_prefetch(img->host_rec_len + nx.hint.pos, 1);
+            }
+          }
           bool changed;
           if (p.op == NCDH_EV_PUT && !p.info && !(p.hinted && img->hint_valid(p.hint) && p.hint.same_structure))
             p.info = make_info(events[i]);  // the object phase one compared against is not there any more
@@ -995,6 +1007,7 @@ int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap) {
   // objects with a shard decision != SKIP, merged with templates that still have references to
   // adopt on the controller cluster; both lists are ordered by controller index
   std::string text;
+  text.reserve(64 * (s->entries.size() / (s->nshards ? s->nshards : 1) + s->unadopted.size() + 1));
   size_t i = 0, j = 0;
   uint32_t last = 0xFFFFFFFFu;
   while (i < s->entries.size() || j < s->unadopted.size()) {
@@ -1004,7 +1017,9 @@ int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap) {
     if (obj == last) continue;
     last = obj;
     const ObjInfo& f = *s->dir->objs[obj];
-    text += std::string(f.kind == NCD_KIND_TEMPLATE ? "template" : "workgroup") + "\t" + f.key + "\n";
+    text.append(f.kind == NCD_KIND_TEMPLATE ? "template\t" : "workgroup\t");
+    text.append(f.key);
+    text.push_back('\n');
   }
   if (out && text.size() <= cap) memcpy(out, text.data(), text.size());
   return (int64_t)text.size();
