@@ -237,6 +237,7 @@ struct ClusterImage {
     bool found = false, same_value = false, same_structure = false;
     uint64_t seen_gen = 0, layout = 0;
     size_t pos = 0;
+    uint32_t first_diff = 0;  // the record's pinned bytes equal the new value up to here (a multiple of 256)
   };
   // Caller holds the claim on the object at `pos` (its bytes may be in the pinned payload, which
   // another batch could otherwise be rewriting).
@@ -247,7 +248,18 @@ struct ClusterImage {
     h.pos = pos;
     h.layout = layout;
     h.seen_gen = o.gen;
-    h.same_value = o.len == len && memcmp(bytes_of(o), bytes, len) == 0;
+    h.same_value = false;
+    if (o.len == len) {  // block by block: where the first difference is tells write_in_place what it can skip
+      const uint8_t* have = bytes_of(o);
+      uint32_t at = 0;
+      while (at < len) {
+        const uint32_t n = len - at < 256u ? len - at : 256u;
+        if (memcmp(have + at, bytes + at, n) != 0) break;
+        at += n;
+      }
+      h.same_value = at == len;
+      if (!o.pending) h.first_diff = at & ~255u;  // only the pinned record itself can be kept in part
+    }
     h.same_structure = same_structure;
     return h;
   }
@@ -257,9 +269,10 @@ struct ClusterImage {
     return arena.a && host_payload && o.rec_off >= 0 && pad16(len) <= o.rec_cap;
   }
   // Caller holds the claim and the pinned-memory lock (no Scan is reading the payload).
-  void write_in_place(const CachedObject& o, const uint8_t* bytes, uint32_t len) const {
+  // from: the pinned bytes before it already equal the new value (PutHint::first_diff).
+  void write_in_place(const CachedObject& o, const uint8_t* bytes, uint32_t len, uint32_t from = 0) const {
     uint8_t* dst = const_cast<uint8_t*>(host_payload) + o.rec_off;
-    memcpy(dst, bytes, len);
+    memcpy(dst + from, bytes + from, len - from);
     memset(dst + len, 0, pad16(len) - len);
   }
 

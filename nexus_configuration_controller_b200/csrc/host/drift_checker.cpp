@@ -500,7 +500,7 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
               p.hint = img->precheck(it->second, same, scratch.data(), p.len);
               p.hinted = true;
               if (!p.hint.same_value) {
-                img->write_in_place(*o, scratch.data(), p.len);
+                img->write_in_place(*o, scratch.data(), p.len, p.hint.first_diff);
                 p.direct = true;  // the claim stays until the update is applied
                 return;
               }
