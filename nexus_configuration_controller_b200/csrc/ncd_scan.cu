@@ -502,6 +502,30 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
 // owning template are read once, the verdicts and tags of its S pairs are contiguous, and the grid
 // is rows / 256 blocks instead of rows x shards / 256 (the compaction's block scan stays in one
 // block for up to a million rows).
+// The decision from values already in registers: v / mine = verdict and tag of the compared object's
+// pair, tv / ttag = of the owning template's pair (dependent rows only), p = the pair's index.
+__device__ __forceinline__ uint32_t decide_vals(const DevArena* __restrict__ shards, uint32_t s, uint32_t dep, uint32_t cidx,
+                                                uint8_t v, uint32_t mine, uint8_t tv, uint32_t ttag,
+                                                const uint32_t* __restrict__ sh_idx, uint64_t p) {
+  if (dep == NCD_NOTFOUND) return v == DV_NOTFOUND ? NCD_CREATE : (v == DV_DIFF ? NCD_UPDATE_DATA : NCD_SKIP);
+  if (cidx == NCD_NOTFOUND) return NCD_ERR_MISSING_REF;
+  if (v == DV_NOTFOUND) return NCD_CREATE;
+  if (mine == NCD_TAG_ROGUE) return NCD_ERR_ROGUE;
+  bool missing = true;
+  if (tv != DV_NOTFOUND) {
+    const uint32_t want = ttag | 0x80000000u;
+    if (mine != NCD_TAG_MANY) {
+      missing = mine != want;
+    } else {
+      const DevArena& sh = shards[s];
+      const uint32_t j = sh_idx[p];
+      for (uint32_t o = sh.own_start[j]; o < sh.own_start[j + 1] && missing; ++o)
+        if (sh.own_packed[o] == want) missing = false;
+    }
+  }
+  return (v == DV_DIFF ? NCD_UPDATE_DATA : 0u) | (missing ? NCD_UPDATE_OWNER : 0u);
+}
+
 __device__ __forceinline__ uint32_t decide_pair(const DevArena* __restrict__ shards, uint32_t S, uint32_t s, uint32_t obj,
                                                 uint32_t dep, uint32_t cidx, const uint32_t* __restrict__ sh_idx,
                                                 const uint8_t* __restrict__ dv, const uint32_t* __restrict__ tag) {
@@ -550,10 +574,46 @@ k_classify(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uint6
   uint32_t mine = 0;
   if (r < nrows) {
     const uint32_t obj = row_obj[r], dep = row_dep[r], cidx = row_cidx[r];
-    for (uint32_t s = 0; s < S; ++s) {
-      const uint32_t code = decide_pair(shards, S, s, obj, dep, cidx, sh_idx, dv, tag);
-      codes[r * S + s] = (uint8_t)code;
-      mine += code != NCD_SKIP;
+    if (S == 8) {
+      // eight shards: a row's verdicts are 8 bytes and its tags 32, both contiguous and aligned (the
+      // scratch arrays start on 256-byte boundaries) — six vector loads and one vector store per row
+      // instead of 32 loads and 8 byte stores
+      const bool is_dep = dep != NCD_NOTFOUND, has_c = cidx != NCD_NOTFOUND;
+      uint2 vw = make_uint2(0, 0), tvw = make_uint2(0, 0);
+      uint4 t0 = make_uint4(0, 0, 0, 0), t1 = t0, u0 = t0, u1 = t0;
+      if (has_c) {
+        vw = *reinterpret_cast<const uint2*>(dv + (uint64_t)cidx * 8);
+        if (is_dep) {
+          const uint4* tp4 = reinterpret_cast<const uint4*>(tag + (uint64_t)cidx * 8);
+          t0 = tp4[0];
+          t1 = tp4[1];
+        }
+      }
+      if (is_dep) {
+        tvw = *reinterpret_cast<const uint2*>(dv + (uint64_t)obj * 8);
+        const uint4* up4 = reinterpret_cast<const uint4*>(tag + (uint64_t)obj * 8);
+        u0 = up4[0];
+        u1 = up4[1];
+      }
+      const uint32_t tg[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+      const uint32_t ug[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+      uint32_t lo = 0, hi = 0;
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        const uint8_t v = (uint8_t)((s < 4 ? vw.x : vw.y) >> (8 * (s & 3)));
+        const uint8_t tv = (uint8_t)((s < 4 ? tvw.x : tvw.y) >> (8 * (s & 3)));
+        const uint32_t code = decide_vals(shards, (uint32_t)s, dep, cidx, v, tg[s], tv, ug[s], sh_idx, (uint64_t)cidx * 8 + s);
+        if (s < 4) lo |= code << (8 * s);
+        else hi |= code << (8 * (s - 4));
+        mine += code != NCD_SKIP;
+      }
+      *reinterpret_cast<uint2*>(codes + r * 8) = make_uint2(lo, hi);
+    } else {
+      for (uint32_t s = 0; s < S; ++s) {
+        const uint32_t code = decide_pair(shards, S, s, obj, dep, cidx, sh_idx, dv, tag);
+        codes[r * S + s] = (uint8_t)code;
+        mine += code != NCD_SKIP;
+      }
     }
   }
   // entries this block will emit
@@ -627,8 +687,16 @@ k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ r
   const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint32_t mine = 0;
-  if (r < nrows)
-    for (uint32_t s = 0; s < S; ++s) mine += codes[r * S + s] != 0;
+  uint2 cw = make_uint2(0, 0);  // eight shards: the row's codes in one load
+  if (r < nrows) {
+    if (S == 8) {
+      cw = *reinterpret_cast<const uint2*>(codes + r * 8);
+#pragma unroll
+      for (int s = 0; s < 8; ++s) mine += (((s < 4 ? cw.x : cw.y) >> (8 * (s & 3))) & 0xffu) != 0;
+    } else {
+      for (uint32_t s = 0; s < S; ++s) mine += codes[r * S + s] != 0;
+    }
+  }
   // exclusive scan of the per-row counts inside the block
   uint32_t incl = mine;
 #pragma unroll
@@ -646,7 +714,7 @@ k_emit(DevArena ctrl, uint32_t S, uint64_t nrows, const uint32_t* __restrict__ r
   e.obj = obj;
   e.dep = dep == NCD_NOTFOUND ? 0u : dep - ctrl.dep_start[obj] + 1u;
   for (uint32_t s = 0; s < S; ++s) {
-    const uint32_t code = codes[r * S + s];
+    const uint32_t code = S == 8 ? (((s < 4 ? cw.x : cw.y) >> (8 * (s & 3))) & 0xffu) : codes[r * S + s];
     if (code == 0) continue;
     e.shard = s;
     e.code = code;
