@@ -168,6 +168,7 @@ struct ncd_arena {
   // committed counts
   uint64_t nobj, payload_bytes, aux_bytes, nowner, ndep;
   uint64_t len_sum;  // sum of rec_len: the arena's share of the algorithmic bytes
+  uint32_t len_max;  // longest record
   uint64_t last_rehashed;  // records the last re-commit had to hash again (the others kept their digests)
   bool committed;
   ncd_arena_view h;  // pinned host arrays (HOST_PINNED only)

@@ -278,16 +278,20 @@ __global__ void k_rows_fill(DevArena a, const uint32_t* __restrict__ row_start,
 
 // ------------------------------------------------------------------ tiles
 __global__ void k_tile_counts(DevArena a, uint32_t* __restrict__ counts,
-                              unsigned long long* __restrict__ len_sum) {
+                              unsigned long long* __restrict__ len_sum, uint32_t* __restrict__ len_max) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   unsigned long long len = 0;
   if (i < a.nobj) {
     len = a.rec_len[i];
     counts[i] = (uint32_t)((len + NCD_TILE_BYTES - 1) / NCD_TILE_BYTES);
   }
+  const uint32_t longest = __reduce_max_sync(0xffffffffu, (uint32_t)len);
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) len += __shfl_xor_sync(0xffffffffu, len, d);
-  if ((threadIdx.x & 31) == 0 && len) atomicAdd(len_sum, len);
+  if ((threadIdx.x & 31) == 0 && len) {
+    atomicAdd(len_sum, len);
+    atomicMax(len_max, longest);
+  }
 }
 
 __global__ void k_ctile_counts(DevArena a, uint32_t* __restrict__ counts) {
@@ -396,21 +400,22 @@ int ncd_rebuild_tiles(ncd_arena* a) {
   const unsigned blocks = (n + 255) / 256;
   DevArena da;
   ncd_fill_dev_arena(a, &da);
-  uint32_t* d_small = nullptr;  // [0] tiles, [1] compare tiles, [2..3] u64 sum of rec_len
+  uint32_t* d_small = nullptr;  // [0] tiles, [1] compare tiles, [2..3] u64 sum of rec_len, [4] longest record
   uint32_t* counts = nullptr;
-  NCD_CUDA(cudaMallocAsync((void**)&d_small, 4 * sizeof(uint32_t), st));
-  NCD_CUDA(cudaMemsetAsync(d_small, 0, 4 * sizeof(uint32_t), st));
+  NCD_CUDA(cudaMallocAsync((void**)&d_small, 6 * sizeof(uint32_t), st));
+  NCD_CUDA(cudaMemsetAsync(d_small, 0, 6 * sizeof(uint32_t), st));
   NCD_CUDA(cudaMallocAsync((void**)&counts, ((size_t)n + 1) * 4, st));
   if (!a->tile_start) NCD_TRY(dev_realloc(&a->tile_start, (uint64_t)n + 1));
   if (!a->ctile_start) NCD_TRY(dev_realloc(&a->ctile_start, (uint64_t)n + 1));
-  if (n) k_tile_counts<<<blocks, 256, 0, st>>>(da, counts, (unsigned long long*)(d_small + 2));
+  if (n) k_tile_counts<<<blocks, 256, 0, st>>>(da, counts, (unsigned long long*)(d_small + 2), d_small + 4);
   NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->tile_start, n, d_small + 0));
   if (n) k_ctile_counts<<<blocks, 256, 0, st>>>(da, counts);
   NCD_TRY(ncd_exclusive_scan_u32(ctx, counts, a->ctile_start, n, d_small + 1));
-  uint32_t h_small[4];
+  uint32_t h_small[6];
   NCD_CUDA(cudaMemcpyAsync(h_small, d_small, sizeof(h_small), cudaMemcpyDeviceToHost, st));
   NCD_CUDA(cudaStreamSynchronize(st));
   memcpy(&a->len_sum, &h_small[2], 8);
+  a->len_max = h_small[4];
   if (h_small[0] > a->tile_cap || !a->tile_obj) {
     a->tile_cap = h_small[0] + h_small[0] / 16;
     NCD_TRY(dev_realloc(&a->tile_obj, a->tile_cap));

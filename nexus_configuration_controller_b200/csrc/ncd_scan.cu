@@ -896,6 +896,11 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   if (variant < 0 && ctrl->ntiles) {
     const uint64_t fill = ctrl->len_sum / ctrl->ntiles;
     variant = fill >= 3500 ? 0 : (fill >= 2500 ? 8 : (fill >= 700 ? 2 : 16));
+    // The fused join + compare kernel walks a record with a handful of lanes: measured ahead of the tile
+    // kernels up to records of ~1.5 KB (1 KiB: 1.62 vs 1.88 ms per 1M x 8), level at 2 KB — as long as no
+    // record is long enough to keep one group of lanes busy after all others are done.
+    if (hm == NCD_MODE_DIRECT && ctx->fuse_small && fill < 1800 && ctrl->len_max <= 16384) variant = 16;
+    if (variant == 16 && ctrl->len_max > 16384) variant = 2;  // mostly small records and a few large ones: tiles spread those
   }
   const bool fused_small = npairs && variant == 16 && hm == NCD_MODE_DIRECT && ctx->fuse_small;
   if (npairs && !fused_small) {

@@ -509,3 +509,40 @@ def test_fused_small_scan_with_every_lane_grouping(lpo, nshards, monkeypatch):
             d.close()
         for a in sas + [ca]:
             a.close()
+
+
+def test_the_fused_scan_covers_kilobyte_records_but_not_a_skewed_mix(ctx):
+    """Records of about a kilobyte still take the fused join + compare kernel (measured ahead of the tile kernels
+    up to ~1.5 KB); a fleet of small records with one very long one does not — a handful of lanes would walk that
+    record long after everything else is done — and takes the tile kernels, which spread it."""
+    import random
+
+    rng = random.Random(77)
+
+    def fleet(lengths):
+        datas = [rand_bytes(rng, n) for n in lengths]
+        ctrl = A.pack([A.CachedObject(A.KIND_WORKGROUP, f"default/wg-{i}", d, uid="u") for i, d in enumerate(datas)])
+        shards = []
+        for s in range(3):
+            objs = []
+            for i, d in enumerate(datas):
+                roll = rng.random()
+                if roll < 0.1:
+                    continue
+                if roll < 0.3:
+                    b = bytearray(d)
+                    b[rng.randrange(len(b))] ^= 1 << rng.randrange(8)
+                    d = bytes(b)
+                objs.append(A.CachedObject(A.KIND_WORKGROUP, f"default/wg-{i}", d, uid="v"))
+            rng.shuffle(objs)
+            shards.append(A.pack(objs))
+        return ctrl, shards
+
+    for lengths, want_variant in (([rng.randint(900, 1500) for _ in range(1500)], 32),
+                                  ([rng.randint(40, 300) for _ in range(1500)] + [100_000], 2)):
+        ctrl, shards = fleet(lengths)
+        want_codes, want_ents = oracle.scan(ctrl, shards)
+        codes, ents, st = gpu_scan(ctx, ctrl, shards, A.MODE_DIRECT)
+        assert st.compare_variant == want_variant
+        np.testing.assert_array_equal(codes, want_codes)
+        np.testing.assert_array_equal(ents, want_ents)
