@@ -461,15 +461,17 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
       uint32_t x[G];
 #pragma unroll
       for (int k = 0; k < G; ++k) {  // shard s0 + k was joined by lane k % LPO in its slot k / LPO
-        const unsigned long long p = __shfl_sync(gmask, (unsigned long long)mine[k / LPO], base + (k % LPO));
-        sp[k] = reinterpret_cast<const uint4*>(p);
+        // a copy with nothing to compare (absent, or another length) reads the controller's own bytes instead:
+        // no difference can come of it, and the loop below has no per-copy condition
+        const uint4* src = mine[k / LPO] != nullptr ? mine[k / LPO] : cp;
+        sp[k] = reinterpret_cast<const uint4*>(__shfl_sync(gmask, (unsigned long long)src, base + (k % LPO)));
         x[k] = 0;
       }
       for (uint32_t vv = l; vv < nvec; vv += LPO) {
         uint4 a = ncd_ldg_stream(cp + vv);
         uint4 b[G];
 #pragma unroll
-        for (int k = 0; k < G; ++k) b[k] = sp[k] != nullptr ? ncd_ldg_stream(sp[k] + vv) : a;
+        for (int k = 0; k < G; ++k) b[k] = ncd_ldg_stream(sp[k] + vv);
         if (tail && vv == nvec - 1) {
           a = mask_tail(a, tail);
 #pragma unroll
@@ -478,11 +480,13 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
 #pragma unroll
         for (int k = 0; k < G; ++k) x[k] |= (a.x ^ b[k].x) | (a.y ^ b[k].y) | (a.z ^ b[k].z) | (a.w ^ b[k].w);
       }
+      uint32_t xm = 0;  // bit k: this lane saw copy k differ; one OR over the object's lanes instead of a vote per copy
 #pragma unroll
-      for (int k = 0; k < G; ++k) {
-        const uint32_t differs = __ballot_sync(gmask, x[k] != 0) & gmask;
-        if (differs && l == (uint32_t)(k % LPO)) v[k / LPO] = DV_DIFF;  // sp[k] is null unless that lane found bytes to compare
-      }
+      for (int k = 0; k < G; ++k) xm |= x[k] != 0 ? 1u << k : 0u;
+      xm = __reduce_or_sync(gmask, xm);
+#pragma unroll
+      for (int j = 0; j < SLOTS; ++j)
+        if (xm & (1u << ((l + j * LPO) & 31))) v[j] = DV_DIFF;  // only a copy with bytes to compare can differ; lanes past G set nothing that is stored
 #pragma unroll
       for (int j = 0; j < SLOTS; ++j) {
         const uint32_t s = s0 + l + j * LPO;
