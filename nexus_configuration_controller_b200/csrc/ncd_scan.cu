@@ -367,7 +367,6 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
                        shards[s].join_line, shards[s].join_line_out, shards[s].join_rev_out};
   __syncthreads();
   const uint32_t lane = threadIdx.x & 31, l = lane & (LPO - 1), base = lane & ~(uint32_t)(LPO - 1);
-  const uint32_t gmask = LPO == 32 ? 0xFFFFFFFFu : ((1u << (LPO & 31)) - 1u) << base;  // the lanes of this object
   const uint64_t group0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / LPO;
   const uint64_t ngroups = ((uint64_t)gridDim.x * blockDim.x) / LPO;
   // look-ahead only when EVERY shard's answer is cached (a shard re-committed since the last scan has
@@ -387,9 +386,15 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
     idx_next[j] = (prefetch && mine_here) ? s_sh[s].join_cache[group0] : NCD_NOTFOUND;
     line_next[j] = (prefetch_line && mine_here) ? s_sh[s].join_line[group0] : make_uint4(0, 0, 0, 0);
   }
-  for (uint64_t c = group0; c < ctrl.nobj; c += ngroups) {
-    const ObjMeta& q = ctrl.meta[c];
-    const uint32_t len = q.rec_len;
+  // The loop is uniform over the warp (its groups hold consecutive objects; the warp goes on while its first
+  // group has one): shuffles and reductions below can name the whole warp, which spares the collective
+  // prologue and epilogue a partial, run-time member mask costs on every one of them.  A group past the last
+  // object (the last warp's last round) walks a record of no bytes and stores nothing.
+  for (uint64_t cw = group0 - lane / LPO; cw < ctrl.nobj; cw += ngroups) {
+    const uint64_t c = cw + lane / LPO;
+    const bool act = c < ctrl.nobj;
+    const ObjMeta& q = ctrl.meta[act ? c : cw];
+    const uint32_t len = act ? q.rec_len : 0u;
     const uint32_t nvec = (len + 15) >> 4, tail = len & 15;
     const uint4* cp = reinterpret_cast<const uint4*>(ctrl.payload + q.rec_off);
     uint32_t idx_cur[SLOTS];
@@ -421,7 +426,7 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
         tg[j] = NCD_TAG_ROGUE;
         v[j] = DV_NOTFOUND;
         mine[j] = nullptr;
-        if (l + j * LPO < G && s < S) {
+        if (act && l + j * LPO < G && s < S) {
           const ShardRef sr = s_sh[s];
           if (prefetch) {
             idx[j] = idx_cur[j];
@@ -464,7 +469,7 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
         // a copy with nothing to compare (absent, or another length) reads the controller's own bytes instead:
         // no difference can come of it, and the loop below has no per-copy condition
         const uint4* src = mine[k / LPO] != nullptr ? mine[k / LPO] : cp;
-        sp[k] = reinterpret_cast<const uint4*>(__shfl_sync(gmask, (unsigned long long)src, base + (k % LPO)));
+        sp[k] = reinterpret_cast<const uint4*>(__shfl_sync(0xffffffffu, (unsigned long long)src, base + (k % LPO)));
         x[k] = 0;
       }
       for (uint32_t vv = l; vv < nvec; vv += LPO) {
@@ -483,14 +488,15 @@ k_scan_small(DevArena ctrl, const DevArena* __restrict__ shards, uint32_t S, uin
       uint32_t xm = 0;  // bit k: this lane saw copy k differ; one OR over the object's lanes instead of a vote per copy
 #pragma unroll
       for (int k = 0; k < G; ++k) xm |= x[k] != 0 ? 1u << k : 0u;
-      xm = __reduce_or_sync(gmask, xm);
+#pragma unroll
+      for (int d = 1; d < LPO; d <<= 1) xm |= __shfl_xor_sync(0xffffffffu, xm, d);  // stays inside the object's LPO lanes
 #pragma unroll
       for (int j = 0; j < SLOTS; ++j)
         if (xm & (1u << ((l + j * LPO) & 31))) v[j] = DV_DIFF;  // only a copy with bytes to compare can differ; lanes past G set nothing that is stored
 #pragma unroll
       for (int j = 0; j < SLOTS; ++j) {
         const uint32_t s = s0 + l + j * LPO;
-        if (l + j * LPO < G && s < S) {
+        if (act && l + j * LPO < G && s < S) {
           const uint64_t p = c * S + s;
           sh_idx[p] = idx[j];
           dv[p] = v[j];
