@@ -909,7 +909,12 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     // The fused join + compare kernel walks a record with a handful of lanes: measured ahead of the tile
     // kernels up to records of ~1.5 KB (1 KiB: 1.62 vs 1.88 ms per 1M x 8), level at 2 KB — as long as no
     // record is long enough to keep one group of lanes busy after all others are done.
-    if (hm == NCD_MODE_DIRECT && ctx->fuse_small && fill < 1800 && ctrl->len_max <= 16384) variant = 16;
+    // With five to eight shards (one group: nine loads per lane in flight) it is also ahead on larger records up
+    // to 16 KB — it has no join launch and no tile lists to read (cfg 4: 12.12 vs 12.44 ms with k_compare_tma on
+    // one box, cfg 2: 0.162 vs 0.183 ms); with more shards, few shards or long records the tile kernels stay ahead
+    // (cfg 3: 64 KB x 16 shards, cfg 5: 1 MiB x 4).
+    const bool fusable = hm == NCD_MODE_DIRECT && ctx->fuse_small && ctrl->len_max <= 16384;
+    if (fusable && (fill < 1800 || (S >= 5 && S <= 8))) variant = 16;
     if (variant == 16 && ctrl->len_max > 16384) variant = 2;  // mostly small records and a few large ones: tiles spread those
   }
   const bool fused_small = npairs && variant == 16 && hm == NCD_MODE_DIRECT && ctx->fuse_small;
@@ -924,7 +929,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   if (fused_small) {
     // as many lanes per object as the mean record has 16-byte vectors: 4 (up to ~100 bytes) to 32 (512 and more)
     const uint64_t mean = nc ? ctrl->len_sum / nc : 0;
-    int lpo = mean <= 96 ? 4 : (mean <= 320 ? 8 : 16);  // 32 measured no better than 16 at 512 and 1024 bytes
+    int lpo = mean <= 96 ? 4 : (mean <= 320 ? 8 : (mean <= 2048 ? 16 : 32));  // 32 no better than 16 at 512 and 1024 bytes, ahead at 4 KB
     if (ctx->ss_lpo) lpo = ctx->ss_lpo;
     const uint64_t want = (nc * (uint64_t)lpo + 255) / 256, cap = (uint64_t)ctx->sm_count * 16;
     const unsigned grid = (unsigned)(want < cap ? want : cap);
