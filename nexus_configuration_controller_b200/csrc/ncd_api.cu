@@ -100,6 +100,7 @@ extern "C" void ncd_destroy(ncd_ctx* ctx) {
   if (ctx->pending) ncd_diff_destroy(ctx->pending);
   if (ctx->scratch) cudaFree(ctx->scratch);
   if (ctx->d_shards) cudaFree(ctx->d_shards);
+  free(ctx->h_shards_last);
   if (ctx->d_jobs) cudaFree(ctx->d_jobs);
   if (ctx->d_counters) cudaFree(ctx->d_counters);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);

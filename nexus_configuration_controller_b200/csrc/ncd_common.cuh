@@ -139,6 +139,8 @@ struct ncd_ctx {
   void* scratch;
   size_t scratch_bytes;
   DevArena* d_shards;  // device array of shard descriptors
+  DevArena* h_shards_last;  // what it holds (host copy), to skip the upload when nothing changed
+  uint32_t h_shards_last_n;
   void* d_jobs;        // device array of hash jobs (ncd_hash.cu)
   int d_jobs_cap;
   int d_shards_cap;

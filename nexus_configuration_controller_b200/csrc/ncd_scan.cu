@@ -804,6 +804,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
     int cap = S < 16 ? 16 : (int)S;
     NCD_CUDA(cudaMalloc((void**)&ctx->d_shards, sizeof(DevArena) * cap));
     ctx->d_shards_cap = cap;
+    ctx->h_shards_last_n = 0;  // nothing is on the device yet
   }
   DevArena dctrl;
   ncd_fill_dev_arena(ctrl, &dctrl);
@@ -811,7 +812,7 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
   std::vector<ncd_arena*> jc_filled;  // shard arenas whose join cache this scan fills
   std::vector<ncd_arena*> jl_filled;  // ... and whose line cache
   {
-    DevArena* tmp = (DevArena*)malloc(sizeof(DevArena) * (S ? S : 1));
+    DevArena* tmp = (DevArena*)calloc(S ? S : 1, sizeof(DevArena));  // zeroed: the copy is compared bytewise below
     if (!tmp) return NCD_E_NOMEM;
     for (uint32_t s = 0; s < S; ++s) {
       ncd_fill_dev_arena(shards[s], &tmp[s]);
@@ -870,10 +871,19 @@ static int scan_enqueue(ncd_ctx* ctx, const ncd_arena* ctrl, const ncd_arena* co
         if (sa->jc_idx) jc_filled.push_back(sa);
       }
     }
-    // pageable source: the runtime stages it before returning, tmp can be freed right away
-    cudaError_t e = cudaMemcpyAsync(ctx->d_shards, tmp, sizeof(DevArena) * S, cudaMemcpyHostToDevice, st);
-    free(tmp);
-    NCD_CUDA(e);
+    // The descriptors change only with a commit, a new cache or another shard list: a steady-state scan finds
+    // them on the device already and skips the copy (a few microseconds, which a small scan notices).
+    const size_t bytes = sizeof(DevArena) * S;
+    if (ctx->h_shards_last && ctx->h_shards_last_n == S && memcmp(ctx->h_shards_last, tmp, bytes) == 0) {
+      free(tmp);
+    } else {
+      // pageable source: the runtime stages it before returning
+      cudaError_t e = cudaMemcpyAsync(ctx->d_shards, tmp, bytes, cudaMemcpyHostToDevice, st);
+      free(ctx->h_shards_last);
+      ctx->h_shards_last = tmp;
+      ctx->h_shards_last_n = S;
+      NCD_CUDA(e);
+    }
   }
   algo += ctrl->len_sum;
 
