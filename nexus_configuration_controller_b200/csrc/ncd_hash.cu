@@ -52,8 +52,14 @@ __device__ __forceinline__ int find_job(const uint64_t* base, int njobs, uint64_
 
 // Contribution T of one tile (chunk-th 4 KiB of a record, nbytes of it real) to the record's digest;
 // the whole warp calls it, every lane returns T.  keys: (k0, k1) per vector position, in shared memory.
+// mix: splitmix64(i) for i < NCD_H64_MIXTAB in shared memory (the per-tile constants of the first 256 tiles of a record,
+// which a record of up to 1 MiB never leaves).
+constexpr uint32_t NCD_H64_MIXTAB = 512;
+__device__ __forceinline__ uint64_t h64_mix(const uint64_t* mix, uint64_t i) {
+  return i < NCD_H64_MIXTAB ? mix[i] : ncd_splitmix64(i);
+}
 __device__ __forceinline__ uint64_t h64_tile(const uint8_t* tile, uint32_t nbytes, uint32_t chunk, const uint4* keys,
-                                             uint32_t lane) {
+                                             const uint64_t* mix, uint32_t lane) {
   constexpr int U = NCD_TILE_VECS / 32;
   const uint32_t nvec = (nbytes + 15) >> 4;
   const uint32_t tail = nbytes & 15;
@@ -65,21 +71,20 @@ __device__ __forceinline__ uint64_t h64_tile(const uint8_t* tile, uint32_t nbyte
     d[u] = v < nvec ? ncd_ldg_stream(p + v) : make_uint4(0, 0, 0, 0);
   }
   // bytes past rec_len in the record's last vector do not belong to the value: clear them once,
-  // outside the accumulate loop (one lane of one tile of a record ever takes this branch)
-  if (tail && (nvec - 1) % 32 == lane) {
-    const uint32_t ut = (nvec - 1) / 32;
+  // outside the accumulate loop.  `tail` and the vector's place are the same for the whole warp, so
+  // a tile without a ragged end (two of three) skips this as a branch, not as predicated-off instructions.
+  if (tail) {
+    const uint32_t last = nvec - 1, ut = last >> 5, ll = last & 31;
+    uint32_t m[4];
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      if ((uint32_t)u == ut) {
-        uint32_t w[4] = {d[u].x, d[u].y, d[u].z, d[u].w};
+    for (int i = 0; i < 4; ++i) {
+      const int nb = (int)tail - 4 * i;
+      m[i] = nb <= 0 ? 0u : (nb < 4 ? (1u << (8 * nb)) - 1u : 0xffffffffu);
+    }
+    if (lane == ll) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int nb = (int)tail - 4 * i;
-          if (nb <= 0) w[i] = 0;
-          else if (nb < 4) w[i] &= (1u << (8 * nb)) - 1u;
-        }
-        d[u] = make_uint4(w[0], w[1], w[2], w[3]);
-      }
+      for (int u = 0; u < U; ++u)
+        if ((uint32_t)u == ut) d[u] = make_uint4(d[u].x & m[0], d[u].y & m[1], d[u].z & m[2], d[u].w & m[3]);
     }
   }
   uint64_t A = 0, B = 0;
@@ -100,7 +105,10 @@ __device__ __forceinline__ uint64_t h64_tile(const uint8_t* tile, uint32_t nbyte
     A += __shfl_xor_sync(0xffffffffu, A, s);
     B += __shfl_xor_sync(0xffffffffu, B, s);
   }
-  return ncd_fmix64(ncd_fmix64(A + ncd_splitmix64(2ull * chunk)) + rotl64(B, 31) + ncd_splitmix64(2ull * chunk + 1));
+  return ncd_fmix64(ncd_fmix64(A + h64_mix(mix, 2ull * chunk)) + rotl64(B, 31) + h64_mix(mix, 2ull * chunk + 1));
+}
+__device__ __forceinline__ void h64_fill_mix(uint64_t* mix) {
+  for (uint32_t i = threadIdx.x; i < NCD_H64_MIXTAB; i += blockDim.x) mix[i] = ncd_splitmix64(i);
 }
 
 __device__ __forceinline__ void h64_fill_keys(uint4* keys) {
@@ -114,6 +122,7 @@ __device__ __forceinline__ void h64_fill_keys(uint4* keys) {
 __global__ void __launch_bounds__(256)
 k_h64_tiles(const HashJob* __restrict__ jobs, int njobs, uint64_t ntiles) {
   __shared__ uint4 keys[NCD_TILE_VECS];  // (k0, k1) per vector position
+  __shared__ uint64_t mix[NCD_H64_MIXTAB];
   extern __shared__ uint64_t s_dyn[];    // [njobs] first global tile of each job, then the jobs themselves
   uint64_t* s_base = s_dyn;
   HashJob* s_jobs = reinterpret_cast<HashJob*>(s_dyn + njobs);
@@ -122,19 +131,22 @@ k_h64_tiles(const HashJob* __restrict__ jobs, int njobs, uint64_t ntiles) {
     s_jobs[j] = jobs[j];
   }
   h64_fill_keys(keys);
+  h64_fill_mix(mix);
   __syncthreads();
   const uint32_t lane = threadIdx.x & 31;
   const uint64_t warp0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  int cur = 0;  // the job of the warp's last tile: its next tile, nwarps further on, is almost always in the same arena
   for (uint64_t g = warp0; g < ntiles; g += nwarps) {
-    const HashJob& a = s_jobs[find_job(s_base, njobs, g)];
+    if (g < s_base[cur] || (cur + 1 < njobs && g >= s_base[cur + 1])) cur = find_job(s_base, njobs, g);
+    const HashJob& a = s_jobs[cur];
     const uint64_t t = g - a.tile_base;
     unsigned long long* acc = a.acc;
     const uint32_t c = a.tile_obj[t], chunk = a.tile_chunk[t];
     const uint32_t len = a.rec_len[c];
     const uint64_t toff = (uint64_t)chunk * NCD_TILE_BYTES;
     const uint32_t nbytes = min(NCD_TILE_BYTES, len - (uint32_t)toff);
-    const uint64_t T = h64_tile(a.payload + a.rec_off[c] + toff, nbytes, chunk, keys, lane);
+    const uint64_t T = h64_tile(a.payload + a.rec_off[c] + toff, nbytes, chunk, keys, mix, lane);
     if (lane == 0) atomicAdd(&acc[c], (unsigned long long)T);
   }
 }
@@ -156,8 +168,10 @@ __global__ void __launch_bounds__(256)
 k_h64_records(const uint32_t* __restrict__ idx, const uint8_t* __restrict__ payload, const uint64_t* __restrict__ rec_off,
               const uint32_t* __restrict__ rec_len, unsigned long long* __restrict__ out) {
   __shared__ uint4 keys[NCD_TILE_VECS];
+  __shared__ uint64_t mix[NCD_H64_MIXTAB];
   __shared__ uint64_t part[8];
   h64_fill_keys(keys);
+  h64_fill_mix(mix);
   __syncthreads();
   const uint32_t c = idx[blockIdx.x];
   const uint32_t len = rec_len[c];
@@ -167,7 +181,7 @@ k_h64_records(const uint32_t* __restrict__ idx, const uint8_t* __restrict__ payl
   uint64_t sum = 0;
   for (uint32_t chunk = warp; chunk < ntiles; chunk += 8) {
     const uint32_t toff = chunk * NCD_TILE_BYTES;
-    sum += h64_tile(rec + toff, min(NCD_TILE_BYTES, len - toff), chunk, keys, lane);
+    sum += h64_tile(rec + toff, min(NCD_TILE_BYTES, len - toff), chunk, keys, mix, lane);
   }
   if (lane == 0) part[warp] = sum;
   __syncthreads();
