@@ -1006,8 +1006,8 @@ int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap) {
   if (!s) return fail("ncdh_sweep_queue: no scan yet");
   // objects with a shard decision != SKIP, merged with templates that still have references to
   // adopt on the controller cluster; both lists are ordered by controller index
-  std::string text;
-  text.reserve(64 * (s->entries.size() / (s->nshards ? s->nshards : 1) + s->unadopted.size() + 1));
+  std::vector<uint32_t> objs;  // the merged, de-duplicated object numbers (a sequential walk)
+  objs.reserve(s->entries.size() / (s->nshards ? s->nshards : 1) + s->unadopted.size() + 1);
   size_t i = 0, j = 0;
   uint32_t last = 0xFFFFFFFFu;
   while (i < s->entries.size() || j < s->unadopted.size()) {
@@ -1016,10 +1016,30 @@ int64_t ncdh_sweep_queue(ncdh_checker* c, char* out, uint64_t cap) {
     else obj = s->unadopted[j++].obj;
     if (obj == last) continue;
     last = obj;
-    const ObjInfo& f = *s->dir->objs[obj];
-    text.append(f.kind == NCD_KIND_TEMPLATE ? "template\t" : "workgroup\t");
-    text.append(f.key);
-    text.push_back('\n');
+    objs.push_back(obj);
+  }
+  // their names: every one is two or three cache misses away (directory -> object -> key), so long lists are
+  // rendered in slices on the worker pool
+  auto render = [&](size_t from, size_t to, std::string& text) {
+    text.reserve(64 * (to - from));
+    for (size_t k = from; k < to; ++k) {
+      const ObjInfo& f = *s->dir->objs[objs[k]];
+      text.append(f.kind == NCD_KIND_TEMPLATE ? "template\t" : "workgroup\t");
+      text.append(f.key);
+      text.push_back('\n');
+    }
+  };
+  std::string text;
+  if (objs.size() < 2048 || c->threads < 2) {
+    render(0, objs.size(), text);
+  } else {
+    const size_t slices = std::min<size_t>((size_t)c->threads, objs.size() / 512);
+    std::vector<std::string> parts(slices);
+    Workers::get().run(slices, c->threads, [&](size_t k) { render(objs.size() * k / slices, objs.size() * (k + 1) / slices, parts[k]); });
+    size_t total = 0;
+    for (const std::string& p : parts) total += p.size();
+    text.reserve(total);
+    for (const std::string& p : parts) text.append(p);
   }
   if (out && text.size() <= cap) memcpy(out, text.data(), text.size());
   return (int64_t)text.size();

@@ -595,6 +595,8 @@ def test_a_large_batch_is_pulled_while_it_is_applied(make_checker, request):
             assert t["records_synced"] == changed and t["records_in_place"] == changed and t["events"] == changed
             _, decisions, ndiff, dirty, digest = fleet.sweep(threads=2)
             assert f.counts() == (ndiff, decisions) and f.diff_digest() == (digest, dirty)
+            q = f.sweep_queue()  # long enough to be rendered in slices on the worker pool: still every dirty object once, in order
+            assert len(q) == dirty > 2048 and len(set(q)) == dirty
             upd.close()
         for b in first:
             b.close()
