@@ -462,7 +462,7 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     // device (Puller) while the next chunk is canonicalised.
     static const bool no_early = getenv("NCDH_NO_EARLY_PULL") != nullptr;  // measurement knob
     const bool early = in_place && !no_early;
-    const uint64_t chunk = early ? std::max<uint64_t>(2048, std::min<uint64_t>(8192, (n + 3) / 4)) : n;
+    const uint64_t chunk = early ? std::max<uint64_t>(2048, std::min<uint64_t>(65536, (n + 3) / 4)) : n;  // four chunks, within bounds
     double t_phase1 = 0, t_phase2 = 0;
     for (uint64_t c0 = 0; c0 < n; c0 += chunk) {
     const uint64_t c1 = std::min(n, c0 + chunk);
