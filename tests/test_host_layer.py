@@ -504,8 +504,9 @@ def test_an_arena_full_of_dead_payload_is_compacted_not_replaced(make_checker):
         assert grown > 3
 
 
+@pytest.mark.parametrize("mode", [0, A.MODE_HASH64], ids=["direct", "hash64"])
 @pytest.mark.parametrize("seed", [31, 32, 33, 34])
-def test_batches_that_rewrite_records_in_place(make_checker, seed):
+def test_batches_that_rewrite_records_in_place(make_checker, seed, mode):
     """A batch writes a new value that fits its record's place straight into the pinned payload.  Mixed with
     everything else a batch may carry — values that grow (appended by the packer), shrink, stay the same
     (a resync: nothing to upload), several events for one object, deletions and re-additions, owner changes
@@ -513,7 +514,7 @@ def test_batches_that_rewrite_records_in_place(make_checker, seed):
     the handlers' on the same objects after every batch."""
     rng = random.Random(seed)
     n = 6
-    with make_checker(2) as f:
+    with make_checker(2, mode) as f:  # hash64: the digests an arena holds must follow every in-place rewrite and early pull
         fleet = Fleet(2, f)
         size = {}
 
