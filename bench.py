@@ -424,13 +424,15 @@ def run_ours(args):
     # warm-up
     for _ in range(max(args.warmup, 3) if not args.allow_short_warmup else args.warmup):
         step()
-    torch.cuda.synchronize()
-    if dist:
-        dist.barrier()
+    # the clock sampler (a thread, NVML) starts BEFORE the barrier: started after it, rank 0 entered its timed region
+    # milliseconds late and every other rank's clock ran while it waited for rank 0's first lists
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    if dist:
+        dist.barrier()
     torch.cuda.synchronize()
     e0.record(ext)
     for _ in range(args.steps):
