@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <thread>
 #include <vector>
@@ -161,8 +162,16 @@ int ncd_arena_recommit(ncd_arena* a, uint64_t nobj, uint64_t payload_bytes, uint
   if (payload_dirty_from > payload_bytes || (payload_dirty_from & 15)) return fail(NCD_E_INVALID, "fake: bad payload_dirty_from");
   return upload(a, nobj, payload_bytes, aux_bytes, nowner, ndep, payload_dirty_from);
 }
+// Test hook: the next `n` value syncs fail the way a CUDA error would, nothing copied.
+static std::atomic<int> g_fail_syncs{0};
+void ncd_fake_fail_next_syncs(int n) { g_fail_syncs.store(n); }
+
 int ncd_arenas_sync_records(int count, ncd_arena* const* arenas, const uint64_t* n, const uint32_t* const* obj_idx,
                             const uint64_t* new_payload_bytes) {
+  if (g_fail_syncs.load() > 0) {
+    g_fail_syncs.fetch_sub(1);
+    return fail(NCD_E_CUDA, "fake: injected sync failure");
+  }
   for (int k = 0; k < count; ++k) {
     ncd_arena* a = arenas[k];
     if (!a || !a->committed) return fail(NCD_E_STATE, "fake: sync before commit");

@@ -602,3 +602,28 @@ def test_a_large_batch_is_pulled_while_it_is_applied(make_checker, request):
         for b in first:
             b.close()
     fleet.close()
+
+
+def test_a_failed_early_pull_fails_the_scan_and_costs_a_full_upload():
+    """Records a batch wrote in place are pulled to the device by the puller thread while the batch is still being
+    applied.  When such a pull fails (here: injected into the CPU double), the records are ahead of the device
+    copy and nobody else knows: the next Scan must report it, publish nothing, and the one after must upload every
+    cluster in full from the pinned arenas — the only copy of the values — and decide correctly."""
+    lib = fake_lib()
+    lib.ncd_fake_fail_next_syncs.argtypes = [C.c_int]
+    with Hst.DriftChecker(2, lib=lib) as f:
+        fleet = Fleet(2, f)
+        cfgs = [new_configmap(f"cfg-{i}", None, {"k": "a" * 200}) for i in range(4)]
+        tmpl = [new_template(f"algo-{i}", None, cfgs[i]) for i in range(4)]
+        fleet.apply([("put", c, o) for c in (-1, 0, 1) for i in range(4) for o in (tmpl[i], with_owners(cfgs[i], [tmpl[i]]))])
+        fleet.check()
+        before = f.upload_counts(-1)[0]
+        lib.ncd_fake_fail_next_syncs(1)
+        fleet.apply([("put", -1, with_owners(new_configmap("cfg-2", None, {"k": "b" * 200}), [tmpl[2]]))])  # same length: in place, pulled early
+        with pytest.raises(Hst.HostError, match="injected sync failure"):
+            f.scan()
+        with pytest.raises(Hst.Stale):
+            f.plan_template(NS, "algo-2")
+        fleet.check()  # scans again: full uploads, and the plans equal the handlers' on the new value
+        assert f.upload_counts(-1)[0] == before + 1 and f.upload_counts(0)[0] == before + 1
+        assert f.plan_template(NS, "algo-2")[1][0] == [["update-data", "configmaps", "cfg-2"]]
