@@ -474,49 +474,87 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     // resync — writes nothing); any other goes to the slab and waits for the packer.
     {
       std::shared_lock<std::shared_mutex> rd(c->cache_mu);
-      parallel_for(c1 - c0, threads, 8, [&](size_t ii) {
-        const size_t i = c0 + ii;
-        Prepared& p = evs[i];
-        try {
-          const ncdh_event& e = events[i];
-          prepare_meta(e, &p);
-          ClusterImage* img = c->image(p.cluster);
-          if (!img) throw std::runtime_error("no such cluster");
-          if (p.op != NCDH_EV_PUT) return;
-          auto it = img->index.find(p.skey);
-          const CachedObject* o = it == img->index.end() ? nullptr : &img->objs[it->second];
-          if (!o || !try_claim(*o)) {  // new object, or another batch is at its bytes: compared under the exclusive lock
-            p.info = make_info(e);
-            prepare_value(e, &p, slab.p + off[i], off[i + 1] - off[i]);
-            return;
-          }
+      // In blocks of eight events: first the keys and the lookups of all eight (each lookup ends in a few
+      // dependent cache misses: bucket, node, object, its description, its pinned record), with the lines
+      // they lead to requested, then the events themselves — the misses of eight events overlap instead
+      // of queueing behind one another on the thread.
+      constexpr size_t B = 8;
+      constexpr size_t kNone = ~(size_t)0;
+      parallel_for((c1 - c0 + B - 1) / B, threads, 1, [&](size_t bk) {
+        const size_t b0 = c0 + bk * B, b1 = std::min<size_t>(c1, b0 + B);
+        size_t pos[B];
+        ClusterImage* imgs[B];
+        for (size_t i = b0; i < b1; ++i) {
+          const size_t k = i - b0;
+          Prepared& p = evs[i];
+          pos[k] = kNone;
+          imgs[k] = nullptr;
           try {
-            const bool same = same_structure(*o->info, e);
-            if (!same) p.info = make_info(e);
-            if (in_place && img->fits_in_place(*o, e.value_len)) {
-              thread_local std::vector<uint8_t> scratch;
-              if (scratch.size() < e.value_len) scratch.resize(e.value_len + e.value_len / 2 + 64);
-              p.len = (uint32_t)canonicalise_into(e.value, e.value_len, scratch.data(), e.value_len);
-              p.hint = img->precheck(it->second, same, scratch.data(), p.len);
-              p.hinted = true;
-              if (!p.hint.same_value) {
-                img->write_in_place(*o, scratch.data(), p.len, p.hint.first_diff);
-                p.direct = true;  // the claim stays until the update is applied
-                return;
-              }
-            } else {
-              prepare_value(e, &p, slab.p + off[i], off[i + 1] - off[i]);
-              p.hint = img->precheck(it->second, same, p.bytes, p.len);
-              p.hinted = true;
+            const ncdh_event& e = events[i];
+            prepare_meta(e, &p);
+            imgs[k] = c->image(p.cluster);
+            if (!imgs[k]) throw std::runtime_error("no such cluster");
+            if (p.op != NCDH_EV_PUT) continue;
+            auto it = imgs[k]->index.find(p.skey);
+            if (it != imgs[k]->index.end()) {
+              pos[k] = it->second;
+              __builtin_prefetch(&imgs[k]->objs[pos[k]]);
+              __builtin_prefetch(reinterpret_cast<const char*>(&imgs[k]->objs[pos[k]]) + 64);
             }
-          } catch (...) {
-            release_claim(*o);
-            throw;
+            if (e.value) __builtin_prefetch(e.value);
+          } catch (const std::exception& e) {
+            errs[i] = e.what();
+            p.op = kSkipped;
           }
-          release_claim(*o);
-        } catch (const std::exception& e) {
-          errs[i] = e.what();
-          p.op = kSkipped;
+        }
+        for (size_t i = b0; i < b1; ++i) {
+          const size_t k = i - b0;
+          if (pos[k] == kNone) continue;
+          const CachedObject& o = imgs[k]->objs[pos[k]];
+          __builtin_prefetch(o.info.get());
+          if (!o.pending && o.rec_off >= 0 && imgs[k]->host_payload) __builtin_prefetch(imgs[k]->host_payload + o.rec_off);
+        }
+        for (size_t i = b0; i < b1; ++i) {
+          const size_t k = i - b0;
+          Prepared& p = evs[i];
+          if (p.op != NCDH_EV_PUT) continue;  // deletions and skipped events have nothing more to prepare
+          ClusterImage* img = imgs[k];
+          const ncdh_event& e = events[i];
+          try {
+            const CachedObject* o = pos[k] == kNone ? nullptr : &img->objs[pos[k]];
+            if (!o || !try_claim(*o)) {  // new object, or another batch is at its bytes: compared under the exclusive lock
+              p.info = make_info(e);
+              prepare_value(e, &p, slab.p + off[i], off[i + 1] - off[i]);
+              continue;
+            }
+            try {
+              const bool same = same_structure(*o->info, e);
+              if (!same) p.info = make_info(e);
+              if (in_place && img->fits_in_place(*o, e.value_len)) {
+                thread_local std::vector<uint8_t> scratch;
+                if (scratch.size() < e.value_len) scratch.resize(e.value_len + e.value_len / 2 + 64);
+                p.len = (uint32_t)canonicalise_into(e.value, e.value_len, scratch.data(), e.value_len);
+                p.hint = img->precheck(pos[k], same, scratch.data(), p.len);
+                p.hinted = true;
+                if (!p.hint.same_value) {
+                  img->write_in_place(*o, scratch.data(), p.len, p.hint.first_diff);
+                  p.direct = true;  // the claim stays until the update is applied
+                  continue;
+                }
+              } else {
+                prepare_value(e, &p, slab.p + off[i], off[i + 1] - off[i]);
+                p.hint = img->precheck(pos[k], same, p.bytes, p.len);
+                p.hinted = true;
+              }
+            } catch (...) {
+              release_claim(*o);
+              throw;
+            }
+            release_claim(*o);
+          } catch (const std::exception& ex) {
+            errs[i] = ex.what();
+            p.op = kSkipped;
+          }
         }
       });
     }
