@@ -353,6 +353,44 @@ struct ClusterImage {
     o.direct = true;
     return true;
   }
+  // The same for a caller that applies a cluster's in-place events on SEVERAL threads at once (the objects are
+  // distinct and each is claimed by the caller): only the object itself is touched here; what belongs to the
+  // image as a whole is collected in `acc` and added by merge_direct, on one thread.
+  struct DirectAcc {
+    std::vector<uint32_t> pull, dirty;
+    uint64_t last_change = 0, pulled = 0;
+    bool structural = false;
+  };
+  bool put_direct_mt(std::shared_ptr<const ObjInfo>& info, uint32_t len, uint64_t stamp, const PutHint& hint, bool pull_now,
+                     DirectAcc& acc) {
+    if (!hint_valid(hint)) return false;
+    CachedObject& o = objs[hint.pos];
+    if (!hint.same_structure) {
+      acc.structural = true;
+      o.info = std::move(info);
+    }
+    const bool clean = !o.pending && !o.direct;
+    o.pending = nullptr;
+    o.hold.reset();
+    o.len = len;
+    o.gen = stamp;
+    if (stamp > acc.last_change) acc.last_change = stamp;
+    if (clean && pull_now && !force_full && host_rec_len) {
+      host_rec_len[hint.pos] = len;
+      acc.pull.push_back((uint32_t)hint.pos);
+      ++acc.pulled;
+      return true;
+    }
+    if (clean) acc.dirty.push_back((uint32_t)hint.pos);
+    o.direct = true;
+    return true;
+  }
+  void merge_direct(const DirectAcc& acc) {
+    dirty.insert(dirty.end(), acc.dirty.begin(), acc.dirty.end());
+    if (acc.last_change > last_change) last_change = acc.last_change;
+    pulled_early += acc.pulled;
+    structural = structural || acc.structural;
+  }
   bool drop(uint32_t kind, const std::string& key, uint64_t stamp) { return drop(store_key(kind, key), stamp); }
   bool drop(const std::string& k, uint64_t stamp) {
     auto it = index.find(k);

@@ -464,6 +464,7 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     const bool early = in_place && !no_early;
     const uint64_t chunk = early ? std::max<uint64_t>(2048, std::min<uint64_t>(65536, (n + 3) / 4)) : n;  // four chunks, within bounds
     double t_phase1 = 0, t_phase2 = 0;
+    uint64_t sliced = 0;  // events applied in slices on several workers (a cluster's chunk written in place throughout)
     for (uint64_t c0 = 0; c0 < n; c0 += chunk) {
     const uint64_t c1 = std::min(n, c0 + chunk);
     const auto t_chunk = std::chrono::steady_clock::now();
@@ -571,56 +572,112 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     Puller::Job job;
     {
       std::unique_lock<std::shared_mutex> lk(c->cache_mu);
-      Workers::get().run(by_cluster.size(), threads, [&](size_t k) {
+      // One event, the ordinary way (in order, on the cluster's one worker).
+      auto apply_one = [&](size_t k, uint32_t i, uint64_t stamp) -> bool {
         ClusterImage* img = c->image((int)k - 1);
-        uint64_t changed_events = 0;
+        Prepared& p = evs[i];
+        bool changed;
+        if (p.op == NCDH_EV_PUT && !p.info && !(p.hinted && img->hint_valid(p.hint) && p.hint.same_structure))
+          p.info = make_info(events[i]);  // the object phase one compared against is not there any more
+        if (p.op != NCDH_EV_PUT) {
+          changed = img->drop(p.skey, stamp);
+        } else if (p.direct || (!p.bytes && !img->hint_valid(p.hint))) {
+          // written in place, or found equal in phase one without keeping the bytes
+          const bool was_direct = p.direct;
+          const size_t before = pull_now[k].size();
+          if (was_direct && img->put_direct(p.info, p.len, stamp, p.hint, early ? &pull_now[k] : nullptr)) {
+            changed = true;
+            if (pull_now[k].size() != before) pull_bytes[k] += pad16(p.len) + 4;
+          } else {
+            // something else was applied to the object since phase one looked at it: the value is
+            // canonicalised again and put the ordinary way (after an in-place write the pinned
+            // bytes already are the new value, so it counts as changed without comparing)
+            auto buf = std::make_shared<std::vector<uint8_t>>(events[i].value_len ? events[i].value_len : 1);
+            const uint32_t len = (uint32_t)canonicalise_into(events[i].value, events[i].value_len, buf->data(), events[i].value_len);
+            changed = img->put(p.skey, std::move(p.info), buf->data(), len, std::shared_ptr<const void>(buf, buf->data()), stamp,
+                               nullptr, /*force=*/was_direct);
+          }
+          if (was_direct) {
+            if (pull_now[k].size() == before) release_claim(img->objs[p.hint.pos]);  // else the claim goes with the pull
+            p.direct = false;
+          }
+        } else {
+          changed = img->put(p.skey, std::move(p.info), p.bytes, p.len, hold, stamp, p.hinted ? &p.hint : nullptr);
+        }
+        return changed;
+      };
+      // Work items: a cluster's events in order on one worker — or, when every one of them was written in place
+      // (the steady state: distinct objects, each claimed by this batch, nothing to order), the cluster's list
+      // in several slices on several workers, which touch the objects only and leave what belongs to the
+      // image to be merged afterwards.
+      struct Item {
+        size_t k, from, to;
+        bool fast;
+        ClusterImage::DirectAcc acc;
+        uint64_t bytes = 0, changed = 0;
+        std::vector<uint32_t> retry;
+      };
+      std::vector<Item> items;
+      for (size_t k = 0; k < by_cluster.size(); ++k) {
         const std::vector<uint32_t>& mine = by_cluster[k];
-        // one block of stamps per cluster and chunk (the clock is shared by every cluster's worker): an
-        // object's history only needs its own stamps to rise, and all of them to lie after earlier Scans
-        uint64_t stamp = mine.empty() ? 0 : c->clock.fetch_add(mine.size());
-        for (size_t at = 0; at < mine.size(); ++at) {
+        if (mine.empty()) continue;
+        bool all_direct = mine.size() >= 1024;
+        for (size_t at = 0; at < mine.size() && all_direct; ++at) all_direct = evs[mine[at]].op == NCDH_EV_PUT && evs[mine[at]].direct;
+        const size_t parts = all_direct ? std::min<size_t>(4, mine.size() / 512) : 1;
+        for (size_t q = 0; q < parts; ++q) {
+          Item it;
+          it.k = k;
+          it.from = mine.size() * q / parts;
+          it.to = mine.size() * (q + 1) / parts;
+          it.fast = all_direct;
+          items.push_back(std::move(it));
+        }
+      }
+      Workers::get().run(items.size(), threads, [&](size_t q) {
+        Item& it = items[q];
+        ClusterImage* img = c->image((int)it.k - 1);
+        const std::vector<uint32_t>& mine = by_cluster[it.k];
+        // one block of stamps per item (the clock is shared by every worker): an object's history only
+        // needs its own stamps to rise, and all of them to lie after earlier Scans
+        uint64_t stamp = c->clock.fetch_add(it.to - it.from);
+        for (size_t at = it.from; at < it.to; ++at) {
           const uint32_t i = mine[at];
-          Prepared& p = evs[i];
           ++stamp;
-          if (at + 4 < mine.size()) {  // the next objects' lines: each is a cache miss otherwise
+          if (at + 4 < it.to) {  // the next objects' lines: each is a cache miss otherwise
             const Prepared& nx = evs[mine[at + 4]];
             if (nx.hinted && nx.hint.pos < img->objs.size()) {
               __builtin_prefetch(&img->objs[nx.hint.pos], 1);
               if (img->host_rec_len) __builtin_prefetch(img->host_rec_len + nx.hint.pos, 1);
             }
           }
-          bool changed;
-          if (p.op == NCDH_EV_PUT && !p.info && !(p.hinted && img->hint_valid(p.hint) && p.hint.same_structure))
-            p.info = make_info(events[i]);  // the object phase one compared against is not there any more
-          if (p.op != NCDH_EV_PUT) {
-            changed = img->drop(p.skey, stamp);
-          } else if (p.direct || (!p.bytes && !img->hint_valid(p.hint))) {
-            // written in place, or found equal in phase one without keeping the bytes
-            const bool was_direct = p.direct;
-            const size_t before = pull_now[k].size();
-            if (was_direct && img->put_direct(p.info, p.len, stamp, p.hint, early ? &pull_now[k] : nullptr)) {
-              changed = true;
-              if (pull_now[k].size() != before) pull_bytes[k] += pad16(p.len) + 4;
-            } else {
-              // something else was applied to the object since phase one looked at it: the value is
-              // canonicalised again and put the ordinary way (after an in-place write the pinned
-              // bytes already are the new value, so it counts as changed without comparing)
-              auto buf = std::make_shared<std::vector<uint8_t>>(events[i].value_len ? events[i].value_len : 1);
-              const uint32_t len = (uint32_t)canonicalise_into(events[i].value, events[i].value_len, buf->data(), events[i].value_len);
-              changed = img->put(p.skey, std::move(p.info), buf->data(), len, std::shared_ptr<const void>(buf, buf->data()), stamp,
-                                 nullptr, /*force=*/was_direct);
-            }
-            if (was_direct) {
-              if (pull_now[k].size() == before) release_claim(img->objs[p.hint.pos]);  // else the claim goes with the pull
-              p.direct = false;
-            }
-          } else {
-            changed = img->put(p.skey, std::move(p.info), p.bytes, p.len, hold, stamp, p.hinted ? &p.hint : nullptr);
+          if (!it.fast) {
+            it.changed += apply_one(it.k, i, stamp) ? 1 : 0;
+            continue;
           }
-          changed_events += changed ? 1 : 0;
+          Prepared& p = evs[i];
+          if (!p.info && !(img->hint_valid(p.hint) && p.hint.same_structure)) p.info = make_info(events[i]);
+          const size_t before = it.acc.pull.size();
+          if (img->put_direct_mt(p.info, p.len, stamp, p.hint, early, it.acc)) {
+            ++it.changed;
+            if (it.acc.pull.size() != before) it.bytes += pad16(p.len) + 4;  // the claim goes with the pull
+            else release_claim(img->objs[p.hint.pos]);
+            p.direct = false;
+          } else {
+            it.retry.push_back(i);  // something else was applied to the object meanwhile: the ordinary way, below
+          }
         }
-        c->events_since_scan.fetch_add(changed_events, std::memory_order_relaxed);
       });
+      for (Item& it : items) {
+        ClusterImage* img = c->image((int)it.k - 1);
+        if (it.fast) {
+          sliced += it.to - it.from;
+          img->merge_direct(it.acc);
+          pull_now[it.k].insert(pull_now[it.k].end(), it.acc.pull.begin(), it.acc.pull.end());
+          pull_bytes[it.k] += it.bytes;
+          for (uint32_t i : it.retry) it.changed += apply_one(it.k, i, c->clock.fetch_add(1) + 1) ? 1 : 0;
+        }
+        c->events_since_scan.fetch_add(it.changed, std::memory_order_relaxed);
+      }
       for (size_t k = 0; k < pull_now.size(); ++k)  // arena and payload size as they are under the lock
         if (!pull_now[k].empty()) {
           ClusterImage* img = c->image((int)k - 1);
@@ -641,8 +698,8 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
     });
     static const bool profile = getenv("NCDH_PROFILE") != nullptr;
     if (profile)
-      fprintf(stderr, "ncdh_apply_events: %llu events in chunks of %llu, lookup + canonicalise %.3f ms, update %.3f ms, release %.3f ms, total %.3f ms%s\n",
-              (unsigned long long)n, (unsigned long long)chunk, t_phase1, t_phase2, ms_since(t_release), ms_since(t0),
+      fprintf(stderr, "ncdh_apply_events: %llu events in chunks of %llu, lookup + canonicalise %.3f ms, update %.3f ms (%llu events in slices), release %.3f ms, total %.3f ms%s\n",
+              (unsigned long long)n, (unsigned long long)chunk, t_phase1, t_phase2, (unsigned long long)sliced, ms_since(t_release), ms_since(t0),
               in_place ? "" : " (slab path: a Scan held the pinned payloads)");
   } catch (const std::exception& e) {
     return fail(std::string("ncdh_apply_events: ") + e.what());

@@ -585,8 +585,11 @@ def test_a_large_batch_is_pulled_while_it_is_applied(make_checker, request):
         f.scan()
         _, decisions, ndiff, dirty, digest = fleet.sweep(threads=2)
         assert f.counts() == (ndiff, decisions) and f.diff_digest() == (digest, dirty)
-        for salt in (3, 4):  # every controller object gets a new value of the same length, twice
-            upd = Hst.EventBatch(ctrl, cluster=-1, salt=salt, threads=4, lib=lib)
+        for salt in (3, 4, 5):  # every controller object gets a new value of the same length, three times
+            # (the last time only the objects that have bytes to change: a chunk whose every event was written in place
+            # is applied in slices on several workers, the others in order on one)
+            idx = None if salt < 5 else [i for i in range(ctrl.nobj) if ctrl.rec_len[i] > 0]
+            upd = Hst.EventBatch(ctrl, cluster=-1, obj_idx=idx, salt=salt, threads=4, lib=lib)
             f.apply_events(upd, threads=4)
             fleet.apply(upd.events, upd.n, threads=2)
             f.scan()
