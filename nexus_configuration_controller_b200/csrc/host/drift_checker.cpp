@@ -621,9 +621,9 @@ int ncdh_apply_events(ncdh_checker* c, const ncdh_event* events, uint64_t n, int
       for (size_t k = 0; k < by_cluster.size(); ++k) {
         const std::vector<uint32_t>& mine = by_cluster[k];
         if (mine.empty()) continue;
-        bool all_direct = mine.size() >= 1024;
+        bool all_direct = mine.size() >= 512;
         for (size_t at = 0; at < mine.size() && all_direct; ++at) all_direct = evs[mine[at]].op == NCDH_EV_PUT && evs[mine[at]].direct;
-        const size_t parts = all_direct ? std::min<size_t>(4, mine.size() / 512) : 1;
+        const size_t parts = all_direct ? std::min<size_t>(4, mine.size() / 256) : 1;
         for (size_t q = 0; q < parts; ++q) {
           Item it;
           it.k = k;
