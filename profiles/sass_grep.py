@@ -2,7 +2,7 @@
 
     python profiles/sass_grep.py > profiles/sass_grep.txt
 
-UBLKCP = cp.async.bulk (the TMA engine's 1-D bulk copy), SYNCS = mbarrier arrive / try_wait, REDUX = warp
+UBLKCP = cp.async.bulk (the TMA engine's 1-D bulk copy), LDGSTS = cp.async (16-byte global-to-shared copies), SYNCS = mbarrier arrive / try_wait, REDUX = warp
 reductions in hardware, LDG.E.128 = 16-byte global loads, UTMALDG / UTCMMA / tcgen05 would be tensor-map TMA and
 5th-generation tensor cores (none expected: nothing here is a contraction).  Built from the library in the tree.
 """
@@ -16,7 +16,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "nexus_configuration_controller_b200", "lib", "libncdrift.so")
 # label -> regex over one SASS line
 PATTERNS = collections.OrderedDict([
-    ("UBLKCP", r"\bUBLKCP"), ("SYNCS.ARRIVE", r"\bSYNCS\.ARRIVE"), ("SYNCS.TRYWAIT", r"\bSYNCS\.PHASECHK"), ("REDUX", r"\bREDUX"),
+    ("UBLKCP", r"\bUBLKCP"), ("LDGSTS", r"\bLDGSTS"), ("SYNCS.ARRIVE", r"\bSYNCS\.ARRIVE"), ("SYNCS.TRYWAIT", r"\bSYNCS\.PHASECHK"), ("REDUX", r"\bREDUX"),
     ("LDG.128", r"\bLDG\.E[.A-Z0-9]*\.128"), ("STG.128", r"\bSTG\.E[.A-Z0-9]*\.128"), ("LDS.128", r"\bLDS[.A-Z0-9]*\.128"),
     ("ATOMG/RED", r"\b(ATOMG|RED)\b|\b(ATOMG|RED)\."), ("SHFL", r"\bSHFL"), ("VOTE", r"\bVOTE"),
     ("UTMALDG", r"\bUTMALDG"), ("UTCMMA", r"\bUTC[A-Z]*MMA"), ("HMMA", r"\b[HIDQ]MMA"),
